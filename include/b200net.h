@@ -1,0 +1,173 @@
+/* b200net C-ABI: the drop-in boundary for the ResNet-50 data-parallel hot path on B200 (sm_100a).
+ *
+ * The reference (VaibhavKamat/Performance-Comparison-of-TensorFlow-PyTorch-and-their-Distributed-Counterparts)
+ * has no FFI of its own: its scripts program against the PyTorch object protocol and the arithmetic lives in
+ * ATen/cuDNN/oneDNN.  Each entry point below therefore cites the reference statement whose work it carries
+ * (file:line in /root/reference; .ipynb lines are raw JSON lines) and the ATen operator it stands in for.
+ *
+ * Conventions
+ *  - plain pointers and sizes only; every pointer is a DEVICE pointer unless it says "host";
+ *  - activations are NHWC ("[rows = N*H*W][C]"), dtype B200_F32 or B200_BF16; statistics, gradients of
+ *    parameters and optimizer state are always fp32; parameters cross the boundary as OIHW fp32;
+ *  - every call returns a status (0 = OK), never throws, never exits; b200_last_error() gives the message of
+ *    the calling thread's last failure;
+ *  - `stream` is a cudaStream_t passed as void*; work is enqueued, not synchronised;
+ *  - the library never allocates device memory: scratch is caller-provided (`ws`, `ws_bytes`; the matching
+ *    *_workspace_bytes query gives the size) and nothing is retained after the call returns;
+ *  - there is no CPU / cuDNN / cuBLAS fallback: an unsupported shape is a hard error.
+ */
+#ifndef B200NET_H_
+#define B200NET_H_
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum { B200_OK = 0, B200_INVALID_ARG = 1, B200_UNSUPPORTED = 2, B200_CUDA_ERROR = 3, B200_NCCL_ERROR = 4,
+       B200_WORKSPACE_TOO_SMALL = 5 };
+enum { B200_F32 = 0, B200_BF16 = 1 };
+
+int32_t b200_version(void);
+const char* b200_last_error(void);
+
+/* ------------------------------------------------------------------ layout / packing
+ * inputs.to(device) hands the model NCHW fp32 (pytorch_training_inference_on_image.ipynb:667); the first kernel
+ * converts to the internal NHWC layout (and to bf16 in bf16 mode). */
+int32_t b200_nchw_to_nhwc(const float* x_nchw, void* y_nhwc, int32_t N, int32_t C, int32_t H, int32_t W,
+                          int32_t out_dtype, void* stream);
+int32_t b200_nhwc_to_nchw(const void* x_nhwc, float* y_nchw, int32_t N, int32_t C, int32_t H, int32_t W,
+                          int32_t in_dtype, void* stream);
+/* OIHW fp32 parameter -> [K][ld] (dtype) with column (r*S+s)*C+c: the K-major operand of the implicit GEMM.
+ * ld >= R*S*C is the row stride, zero-filled past R*S*C (b200_conv_weight_ld gives the value the conv entry
+ * points expect: R*S*C rounded up to a multiple of 8). */
+int32_t b200_conv_weight_ld(int32_t R, int32_t S, int32_t C);
+int32_t b200_pack_weight(const float* w_oihw, void* w_krsc, int32_t K, int32_t C, int32_t R, int32_t S,
+                         int32_t ld, int32_t out_dtype, void* stream);
+/* dtype cast of a flat buffer (fp32 <-> bf16) */
+int32_t b200_cast(const void* x, void* y, int64_t n, int32_t in_dtype, int32_t out_dtype, void* stream);
+
+/* ------------------------------------------------------------------ convolution  (Conv2d.forward / backward;
+ * 53 instances, repr at pytorch_training_inference_on_image.ipynb:455-626; called through model.forward(inputs)
+ * :669 and loss.backward() :671; replaces aten::cudnn_convolution / convolution_backward)
+ * Implicit GEMM: fprop M=N*Ho*Wo, N=K(out channels), K=R*S*C. */
+typedef struct {
+  int32_t N, H, W, C;   /* input  NHWC */
+  int32_t K, R, S;      /* filter: K output channels, RxS */
+  int32_t stride, pad;
+  int32_t dtype;        /* B200_F32 (exact FFMA path) or B200_BF16 (tcgen05 path, fp32 accumulate) */
+} b200_conv_desc;
+
+enum { B200_CONV_FPROP = 0, B200_CONV_DGRAD = 1, B200_CONV_WGRAD = 2 };
+int64_t b200_conv_workspace_bytes(const b200_conv_desc* d, int32_t which);
+/* y[N,Ho,Wo,K] = conv(x[N,H,W,C], w[K,R,S,C]) */
+int32_t b200_conv_fprop(const b200_conv_desc* d, const void* x, const void* w_krsc, void* y, void* ws,
+                        int64_t ws_bytes, void* stream);
+/* dx[N,H,W,C] (+)= conv_transpose(dy[N,Ho,Wo,K], w[K,R,S,C]);  accumulate!=0 adds into dx */
+int32_t b200_conv_dgrad(const b200_conv_desc* d, const void* dy, const void* w_krsc, void* dx, int32_t accumulate,
+                        void* ws, int64_t ws_bytes, void* stream);
+/* dw_oihw[K,C,R,S] fp32 = sum_{n,p,q} dy * x   (deterministic split-K; written in the parameter's own layout) */
+int32_t b200_conv_wgrad(const b200_conv_desc* d, const void* x, const void* dy, float* dw_oihw, void* ws,
+                        int64_t ws_bytes, void* stream);
+
+/* ------------------------------------------------------------------ GEMM (Linear layers of the head,
+ * pytorch_training_inference_on_image.ipynb:439-443; replaces aten::addmm / mm)
+ * C[M,N] (+)= op(A) * op(B) (+ bias[N]) (ReLU).  a_mn==0: A is [M][lda] (K contiguous); a_mn!=0: A is [K][lda]
+ * (M contiguous).  b_mn==0: B is [N][ldb] (K contiguous); b_mn!=0: B is [K][ldb] (N contiguous). */
+int32_t b200_gemm_f32(const float* A, const float* B, float* C, int32_t M, int32_t N, int32_t K, int64_t lda,
+                      int64_t ldb, int64_t ldc, int32_t a_mn, int32_t b_mn, const float* bias, int32_t relu,
+                      int32_t accumulate, void* stream);
+/* bf16 operands on tcgen05 tensor cores, fp32 accumulate; out_dtype selects C's type.  splits>1 needs
+ * ws >= splits*M*ldc*4 bytes and writes the reduced result to C. */
+int32_t b200_gemm_bf16(const void* A, const void* B, void* C, int32_t M, int32_t N, int32_t K, int64_t lda,
+                       int64_t ldb, int64_t ldc, int32_t a_mn, int32_t b_mn, int32_t out_dtype, int32_t accumulate,
+                       int32_t splits, void* ws, int64_t ws_bytes, void* stream);
+
+/* ------------------------------------------------------------------ BatchNorm2d (+ReLU, +residual)
+ * (53 instances, eps 1e-5, momentum 0.1: pytorch_training_inference_on_image.ipynb:456; train mode in the
+ * training loop :664-673 and in Standalone_Inference_Imagenette_trial.ipynb:180, eval mode :678,853;
+ * replaces aten::cudnn_batch_norm / native_batch_norm(_backward), relu_, add_)
+ * x is [rows][C].  All per-channel vectors are fp32 [C]. */
+int64_t b200_bn_workspace_bytes(int64_t rows, int32_t C);
+/* batch statistics -> mean, invstd; scale = gamma*invstd, shift = beta - mean*scale;
+ * running_mean/var EMA update (unbiased variance) when running_mean != NULL. */
+int32_t b200_bn_train_stats(const void* x, int64_t rows, int32_t C, int32_t dtype, const float* gamma,
+                            const float* beta, float* running_mean, float* running_var, float momentum, float eps,
+                            float* save_mean, float* save_invstd, float* scale, float* shift, void* ws,
+                            int64_t ws_bytes, void* stream);
+/* eval mode: scale/shift from running statistics */
+int32_t b200_bn_eval_coeffs(const float* gamma, const float* beta, const float* running_mean,
+                            const float* running_var, float eps, float* scale, float* shift, int32_t C, void* stream);
+/* y = act(x*scale + shift (+ residual)) ; act = ReLU when relu != 0 */
+int32_t b200_bn_apply(const void* x, const void* residual, void* y, int64_t rows, int32_t C, int32_t dtype,
+                      const float* scale, const float* shift, int32_t relu, void* stream);
+/* Backward of y = act(bn(x) (+res)).  g = dz * [z>0] when relu (z = saved output), else g = dz.
+ *   dgamma = sum g*xhat, dbeta = sum g, dx = gamma*invstd*(g - dbeta/n - xhat*dgamma/n);
+ *   dres (optional, may be NULL) receives g (gradient of the residual branch). */
+int32_t b200_bn_backward(const void* dz, const void* z, const void* x, void* dx, void* dres, int64_t rows, int32_t C,
+                         int32_t dtype, const float* gamma, const float* save_mean, const float* save_invstd,
+                         int32_t relu, float* dgamma, float* dbeta, void* ws, int64_t ws_bytes, void* stream);
+/* standalone ReLU backward / elementwise add used between blocks: y = a + b ; y = dz*[z>0] */
+int32_t b200_add(const void* a, const void* b, void* y, int64_t n, int32_t dtype, void* stream);
+int32_t b200_relu_bwd(const void* dz, const void* z, void* dx, int64_t n, int32_t dtype, void* stream);
+
+/* ------------------------------------------------------------------ pooling
+ * MaxPool2d(3, stride 2, pad 1) (:458) and AdaptiveAvgPool2d((1,1)) (:627). */
+int32_t b200_maxpool3x3s2_fwd(const void* x, void* y, uint8_t* argmax, int32_t N, int32_t H, int32_t W, int32_t C,
+                              int32_t dtype, void* stream);
+int32_t b200_maxpool3x3s2_bwd(const void* dy, const uint8_t* argmax, void* dx, int32_t N, int32_t H, int32_t W,
+                              int32_t C, int32_t dtype, void* stream);
+/* y[N,C] fp32 = mean over HW */
+int32_t b200_avgpool_fwd(const void* x, float* y, int32_t N, int32_t HW, int32_t C, int32_t dtype, void* stream);
+int32_t b200_avgpool_bwd(const float* dy, void* dx, int32_t N, int32_t HW, int32_t C, int32_t dtype, void* stream);
+
+/* ------------------------------------------------------------------ head: ReLU / Dropout / LogSoftmax / NLLLoss
+ * nn.Sequential(Linear, ReLU, Dropout(0.2), Linear, LogSoftmax(dim=1)) + nn.NLLLoss()
+ * (pytorch_training_inference_on_image.ipynb:439-444). fp32 [rows][cols]. */
+int32_t b200_relu_fwd_f32(const float* x, float* y, int64_t n, void* stream);
+/* Philox4x32-10 keyed by (seed, offset); mask[i] in {0,1}; y = x*mask/(1-p) */
+int32_t b200_dropout_fwd(const float* x, float* y, uint8_t* mask, int64_t n, float p, uint64_t seed,
+                         uint64_t offset, void* stream);
+int32_t b200_dropout_bwd(const float* dy, const uint8_t* mask, float* dx, int64_t n, float p, void* stream);
+int32_t b200_log_softmax_fwd(const float* x, float* y, int32_t rows, int32_t cols, void* stream);
+int32_t b200_log_softmax_bwd(const float* dy, const float* y, float* dx, int32_t rows, int32_t cols, void* stream);
+/* loss[0] = -mean_n logp[n, label[n]];  dlogp = -dloss/N at the label */
+int32_t b200_nll_loss_fwd(const float* logp, const int64_t* labels, float* loss, int32_t rows, int32_t cols,
+                          void* stream);
+int32_t b200_nll_loss_bwd(const float* dloss, const int64_t* labels, float* dlogp, int32_t rows, int32_t cols,
+                          void* stream);
+/* bias gradient: db[N] = sum over rows of dy[rows][N] */
+int32_t b200_colsum_f32(const float* dy, float* db, int32_t rows, int32_t cols, void* stream);
+
+/* ------------------------------------------------------------------ optimizers (multi-tensor, fp32)
+ * optim.Adam(model.fc.parameters(), lr=0.003) (:445), SGD(lr=0.001) (resnet.py:24), AdamW(lr=2e-5, eps=1e-8)
+ * + clip_grad_norm_(.., 1.0) (pytorch_on_language_distr.py:167-170,273).  Pointer tables are HOST arrays of
+ * device pointers; they are passed to the kernels by value (no device allocation). */
+int32_t b200_multi_tensor_sgd(int32_t n, float* const* params, const float* const* grads, float* const* momentum_bufs,
+                              const int64_t* sizes, float lr, float momentum, float dampening, float weight_decay,
+                              int32_t nesterov, int32_t first_step, float grad_scale, void* stream);
+/* decoupled_wd!=0 -> AdamW.  step is the 1-based step count used for bias correction. */
+int32_t b200_multi_tensor_adam(int32_t n, float* const* params, const float* const* grads, float* const* exp_avg,
+                               float* const* exp_avg_sq, const int64_t* sizes, float lr, float beta1, float beta2,
+                               float eps, float weight_decay, int32_t decoupled_wd, int64_t step, float grad_scale,
+                               void* stream);
+/* out[0] = sum of squares over all tensors (deterministic two-stage); ws >= b200_l2norm_workspace_bytes() */
+int64_t b200_l2norm_workspace_bytes(void);
+int32_t b200_multi_tensor_l2norm_sq(int32_t n, const float* const* tensors, const int64_t* sizes, float* out,
+                                    void* ws, int64_t ws_bytes, void* stream);
+/* t *= min(1, max_norm / (sqrt(norm_sq[0]) + 1e-6))   (clip_grad_norm_ semantics, scale read on device) */
+int32_t b200_multi_tensor_clip_scale(int32_t n, float* const* tensors, const int64_t* sizes, const float* norm_sq,
+                                     float max_norm, void* stream);
+int32_t b200_multi_tensor_zero(int32_t n, float* const* tensors, const int64_t* sizes, void* stream);
+/* gradient bucket pack/unpack for DistributedDataParallel (commented constructor at
+ * pytorch_on_language_distr.py:220-221): flat[off_i ..] = src_i * scale ; dst_i = flat[off_i ..] * scale */
+int32_t b200_bucket_pack(int32_t n, const float* const* srcs, const int64_t* sizes, float* flat, float scale,
+                         void* stream);
+int32_t b200_bucket_unpack(int32_t n, float* const* dsts, const int64_t* sizes, const float* flat, float scale,
+                           void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200NET_H_ */

@@ -1,0 +1,366 @@
+// BatchNorm2d (+ReLU, +residual) over NHWC activations [rows][C]: bandwidth kernels.
+//   statistics : vectorised column sums (16-byte loads), per-block partials in the workspace, fp64 finalize
+//                (deterministic: no atomics), running-stat EMA in the same finalize launch
+//   apply      : y = act(x*scale + shift (+res)), one pass, 16-byte loads/stores
+//   backward   : partial sums of g and g*(x-mean) -> finalize (dgamma, dbeta, dx coefficients) -> one dx pass that
+//                also emits the residual-branch gradient
+#include "common.cuh"
+
+namespace b200 {
+
+constexpr int BN_THREADS = 256;
+constexpr int BN_MAX_BLOCKS = 592;  // 4 x 148 SMs
+
+static inline int pow2_ceil(int v) {
+  int p = 1;
+  while (p < v) p <<= 1;
+  return p;
+}
+
+// part layout: [nblk][2][C]
+template <typename T, int VEC, bool BWD>
+__global__ void __launch_bounds__(BN_THREADS)
+bn_partial_kernel(const T* __restrict__ x, const T* __restrict__ dz, const T* __restrict__ z,
+                  const float* __restrict__ mean, long long rows, int C, int cx, long long rows_per_block, int relu,
+                  float* __restrict__ part) {
+  __shared__ float red[BN_THREADS][2 * VEC + 1];
+  const int nvec = C / VEC;
+  const int ry = BN_THREADS / cx;
+  const int tx = threadIdx.x % cx, ty = threadIdx.x / cx;
+  const long long r0 = blockIdx.x * rows_per_block;
+  long long r1 = r0 + rows_per_block;
+  if (r1 > rows) r1 = rows;
+  for (int base = 0; base < nvec; base += cx) {
+    const int cv = base + tx;
+    const bool active = cv < nvec;
+    float s0[VEC], s1[VEC], mu[VEC];
+#pragma unroll
+    for (int e = 0; e < VEC; ++e) { s0[e] = 0.f; s1[e] = 0.f; mu[e] = 0.f; }
+    if (active) {
+      if (BWD) {
+#pragma unroll
+        for (int e = 0; e < VEC; ++e) mu[e] = mean[cv * VEC + e];
+      }
+      for (long long r = r0 + ty; r < r1; r += ry) {
+        const long long off = r * C + (long long)cv * VEC;
+        float xv[VEC];
+        if constexpr (VEC == 1) xv[0] = to_f(x[off]);
+        else load_vec(x + off, reinterpret_cast<float(&)[VecTraits<T>::W]>(xv));
+        if (!BWD) {
+#pragma unroll
+          for (int e = 0; e < VEC; ++e) { s0[e] += xv[e]; s1[e] = fmaf(xv[e], xv[e], s1[e]); }
+        } else {
+          float gv[VEC], zv[VEC];
+          if constexpr (VEC == 1) { gv[0] = to_f(dz[off]); zv[0] = relu ? to_f(z[off]) : 1.f; }
+          else {
+            load_vec(dz + off, reinterpret_cast<float(&)[VecTraits<T>::W]>(gv));
+            if (relu) load_vec(z + off, reinterpret_cast<float(&)[VecTraits<T>::W]>(zv));
+          }
+#pragma unroll
+          for (int e = 0; e < VEC; ++e) {
+            const float g = (!relu || zv[e] > 0.f) ? gv[e] : 0.f;
+            s0[e] += g;
+            s1[e] = fmaf(g, xv[e] - mu[e], s1[e]);
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int e = 0; e < VEC; ++e) { red[threadIdx.x][e] = s0[e]; red[threadIdx.x][VEC + e] = s1[e]; }
+    __syncthreads();
+    if (ty == 0 && active) {
+#pragma unroll
+      for (int e = 0; e < VEC; ++e) {
+        float a = 0.f, b = 0.f;
+        for (int yy = 0; yy < ry; ++yy) { a += red[yy * cx + tx][e]; b += red[yy * cx + tx][VEC + e]; }
+        part[((long long)blockIdx.x * 2 + 0) * C + cv * VEC + e] = a;
+        part[((long long)blockIdx.x * 2 + 1) * C + cv * VEC + e] = b;
+      }
+    }
+    __syncthreads();
+  }
+}
+
+__global__ void bn_finalize_fwd_kernel(const float* __restrict__ part, int nblk, int C, double n,
+                                       const float* __restrict__ gamma, const float* __restrict__ beta,
+                                       float* __restrict__ running_mean, float* __restrict__ running_var,
+                                       float momentum, float eps, float* __restrict__ save_mean,
+                                       float* __restrict__ save_invstd, float* __restrict__ scale,
+                                       float* __restrict__ shift) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  double s = 0, q = 0;
+  for (int b = 0; b < nblk; ++b) {
+    s += part[((long long)b * 2 + 0) * C + c];
+    q += part[((long long)b * 2 + 1) * C + c];
+  }
+  const double mean = s / n;
+  double var = q / n - mean * mean;
+  if (var < 0) var = 0;
+  const float invstd = (float)(1.0 / sqrt(var + (double)eps));
+  const float g = gamma ? gamma[c] : 1.f, bt = beta ? beta[c] : 0.f;
+  save_mean[c] = (float)mean;
+  save_invstd[c] = invstd;
+  const float sc = g * invstd;
+  scale[c] = sc;
+  shift[c] = bt - (float)mean * sc;
+  if (running_mean) {
+    const double unbiased = n > 1 ? var * n / (n - 1) : var;
+    running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * (float)mean;
+    running_var[c] = (1.f - momentum) * running_var[c] + momentum * (float)unbiased;
+  }
+}
+
+// coef layout: [3][C] : A = gamma*invstd ; B = gamma*invstd^3*S2/n ; Cc = A*dbeta/n
+__global__ void bn_finalize_bwd_kernel(const float* __restrict__ part, int nblk, int C, double n,
+                                       const float* __restrict__ gamma, const float* __restrict__ invstd,
+                                       float* __restrict__ dgamma, float* __restrict__ dbeta,
+                                       float* __restrict__ coef) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  double s = 0, q = 0;
+  for (int b = 0; b < nblk; ++b) {
+    s += part[((long long)b * 2 + 0) * C + c];
+    q += part[((long long)b * 2 + 1) * C + c];
+  }
+  const double is = invstd[c], g = gamma ? gamma[c] : 1.0;
+  if (dgamma) dgamma[c] = (float)(q * is);
+  if (dbeta) dbeta[c] = (float)s;
+  const double A = g * is;
+  coef[c] = (float)A;
+  coef[C + c] = (float)(g * is * is * is * q / n);
+  coef[2 * C + c] = (float)(A * s / n);
+}
+
+template <typename T, int VEC>
+__global__ void bn_apply_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __restrict__ y,
+                                long long nvec_total, int nvec, const float* __restrict__ scale,
+                                const float* __restrict__ shift, int relu) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < nvec_total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % nvec) * VEC;
+    const long long off = i * VEC;
+    float xv[VEC], rv[VEC];
+    if constexpr (VEC == 1) { xv[0] = to_f(x[off]); if (res) rv[0] = to_f(res[off]); }
+    else {
+      load_vec(x + off, reinterpret_cast<float(&)[VecTraits<T>::W]>(xv));
+      if (res) load_vec(res + off, reinterpret_cast<float(&)[VecTraits<T>::W]>(rv));
+    }
+#pragma unroll
+    for (int e = 0; e < VEC; ++e) {
+      float v = fmaf(xv[e], scale[c + e], shift[c + e]);
+      if (res) v += rv[e];
+      if (relu) v = fmaxf(v, 0.f);
+      xv[e] = v;
+    }
+    if constexpr (VEC == 1) y[off] = from_f<T>(xv[0]);
+    else store_vec(y + off, reinterpret_cast<float(&)[VecTraits<T>::W]>(xv));
+  }
+}
+
+template <typename T, int VEC>
+__global__ void bn_bwd_dx_kernel(const T* __restrict__ dz, const T* __restrict__ z, const T* __restrict__ x,
+                                 T* __restrict__ dx, T* __restrict__ dres, long long nvec_total, int nvec, int C,
+                                 const float* __restrict__ mean, const float* __restrict__ coef, int relu) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < nvec_total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % nvec) * VEC;
+    const long long off = i * VEC;
+    float gv[VEC], zv[VEC], xv[VEC];
+    if constexpr (VEC == 1) { gv[0] = to_f(dz[off]); xv[0] = to_f(x[off]); zv[0] = relu ? to_f(z[off]) : 1.f; }
+    else {
+      load_vec(dz + off, reinterpret_cast<float(&)[VecTraits<T>::W]>(gv));
+      load_vec(x + off, reinterpret_cast<float(&)[VecTraits<T>::W]>(xv));
+      if (relu) load_vec(z + off, reinterpret_cast<float(&)[VecTraits<T>::W]>(zv));
+    }
+#pragma unroll
+    for (int e = 0; e < VEC; ++e) {
+      const float g = (!relu || zv[e] > 0.f) ? gv[e] : 0.f;
+      gv[e] = g;
+      xv[e] = coef[c + e] * g - coef[2 * C + c + e] - coef[C + c + e] * (xv[e] - mean[c + e]);
+    }
+    if constexpr (VEC == 1) { dx[off] = from_f<T>(xv[0]); if (dres) dres[off] = from_f<T>(gv[0]); }
+    else {
+      store_vec(dx + off, reinterpret_cast<float(&)[VecTraits<T>::W]>(xv));
+      if (dres) store_vec(dres + off, reinterpret_cast<float(&)[VecTraits<T>::W]>(gv));
+    }
+  }
+}
+
+template <typename T>
+__global__ void add_kernel(const T* __restrict__ a, const T* __restrict__ b, T* __restrict__ y, long long n) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    y[i] = from_f<T>(to_f(a[i]) + to_f(b[i]));
+}
+template <typename T>
+__global__ void relu_bwd_kernel(const T* __restrict__ dz, const T* __restrict__ z, T* __restrict__ dx, long long n) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    dx[i] = to_f(z[i]) > 0.f ? dz[i] : from_f<T>(0.f);
+}
+
+static inline int ew_grid(long long total) {
+  long long b = (total + BN_THREADS - 1) / BN_THREADS;
+  const long long cap = (long long)num_sms() * 8;
+  if (b > cap) b = cap;
+  return (int)(b < 1 ? 1 : b);
+}
+
+struct BnPlan {
+  int vec, cx, nblk;
+  long long rows_per_block;
+};
+template <typename T>
+static BnPlan bn_plan(long long rows, int C) {
+  BnPlan p;
+  p.vec = (C % VecTraits<T>::W == 0) ? VecTraits<T>::W : 1;
+  const int nvec = C / p.vec;
+  p.cx = pow2_ceil(nvec);
+  if (p.cx > BN_THREADS) p.cx = BN_THREADS;
+  const int ry = BN_THREADS / p.cx;
+  // at least 8 rows per row-lane, at most BN_MAX_BLOCKS blocks
+  long long rpb = (long long)ry * 8;
+  long long nblk = (rows + rpb - 1) / rpb;
+  if (nblk > BN_MAX_BLOCKS) {
+    rpb = (rows + BN_MAX_BLOCKS - 1) / BN_MAX_BLOCKS;
+    rpb = (rpb + ry - 1) / ry * ry;
+    nblk = (rows + rpb - 1) / rpb;
+  }
+  p.nblk = (int)nblk;
+  p.rows_per_block = rpb;
+  return p;
+}
+
+template <typename T>
+static int32_t bn_stats_impl(const T* x, long long rows, int C, const float* gamma, const float* beta, float* rm,
+                             float* rv, float momentum, float eps, float* save_mean, float* save_invstd, float* scale,
+                             float* shift, float* part, cudaStream_t st) {
+  const BnPlan p = bn_plan<T>(rows, C);
+  if (p.vec == 1)
+    bn_partial_kernel<T, 1, false><<<p.nblk, BN_THREADS, 0, st>>>(x, nullptr, nullptr, nullptr, rows, C, p.cx, p.rows_per_block, 0, part);
+  else
+    bn_partial_kernel<T, VecTraits<T>::W, false><<<p.nblk, BN_THREADS, 0, st>>>(x, nullptr, nullptr, nullptr, rows, C, p.cx, p.rows_per_block, 0, part);
+  bn_finalize_fwd_kernel<<<(C + 127) / 128, 128, 0, st>>>(part, p.nblk, C, (double)rows, gamma, beta, rm, rv, momentum, eps, save_mean, save_invstd, scale, shift);
+  return check_launch("bn_train_stats");
+}
+
+template <typename T>
+static int32_t bn_apply_impl(const T* x, const T* res, T* y, long long rows, int C, const float* scale,
+                             const float* shift, int relu, cudaStream_t st) {
+  const bool aligned = ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y) | reinterpret_cast<uintptr_t>(res)) & 15) == 0;
+  if (C % VecTraits<T>::W == 0 && aligned) {
+    constexpr int V = VecTraits<T>::W;
+    bn_apply_kernel<T, V><<<ew_grid(rows * (C / V)), BN_THREADS, 0, st>>>(x, res, y, rows * (C / V), C / V, scale, shift, relu);
+  } else {
+    bn_apply_kernel<T, 1><<<ew_grid(rows * C), BN_THREADS, 0, st>>>(x, res, y, rows * C, C, scale, shift, relu);
+  }
+  return check_launch("bn_apply");
+}
+
+template <typename T>
+static int32_t bn_bwd_impl(const T* dz, const T* z, const T* x, T* dx, T* dres, long long rows, int C,
+                           const float* gamma, const float* mean, const float* invstd, int relu, float* dgamma,
+                           float* dbeta, float* ws, cudaStream_t st) {
+  const BnPlan p = bn_plan<T>(rows, C);
+  float* part = ws;
+  float* coef = ws + (size_t)BN_MAX_BLOCKS * 2 * C;
+  if (p.vec == 1)
+    bn_partial_kernel<T, 1, true><<<p.nblk, BN_THREADS, 0, st>>>(x, dz, z, mean, rows, C, p.cx, p.rows_per_block, relu, part);
+  else
+    bn_partial_kernel<T, VecTraits<T>::W, true><<<p.nblk, BN_THREADS, 0, st>>>(x, dz, z, mean, rows, C, p.cx, p.rows_per_block, relu, part);
+  bn_finalize_bwd_kernel<<<(C + 127) / 128, 128, 0, st>>>(part, p.nblk, C, (double)rows, gamma, invstd, dgamma, dbeta, coef);
+  const bool aligned = ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(dz) | reinterpret_cast<uintptr_t>(z) |
+                         reinterpret_cast<uintptr_t>(dx) | reinterpret_cast<uintptr_t>(dres)) & 15) == 0;
+  if (p.vec != 1 && aligned) {
+    constexpr int V = VecTraits<T>::W;
+    bn_bwd_dx_kernel<T, V><<<ew_grid(rows * (C / V)), BN_THREADS, 0, st>>>(dz, z, x, dx, dres, rows * (C / V), C / V, C, mean, coef, relu);
+  } else {
+    bn_bwd_dx_kernel<T, 1><<<ew_grid(rows * C), BN_THREADS, 0, st>>>(dz, z, x, dx, dres, rows * C, C, C, mean, coef, relu);
+  }
+  return check_launch("bn_backward");
+}
+
+__global__ void bn_eval_coeffs_kernel(const float* gamma, const float* beta, const float* rm, const float* rv, float eps,
+                                      float* scale, float* shift, int C) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  const float invstd = 1.0f / sqrtf(rv[c] + eps);
+  const float sc = (gamma ? gamma[c] : 1.f) * invstd;
+  scale[c] = sc;
+  shift[c] = (beta ? beta[c] : 0.f) - rm[c] * sc;
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int64_t b200_bn_workspace_bytes(int64_t rows, int32_t C) {
+  (void)rows;
+  return (int64_t)((size_t)BN_MAX_BLOCKS * 2 * C + 3 * (size_t)C) * 4;
+}
+
+extern "C" int32_t b200_bn_train_stats(const void* x, int64_t rows, int32_t C, int32_t dtype, const float* gamma,
+                                       const float* beta, float* running_mean, float* running_var, float momentum,
+                                       float eps, float* save_mean, float* save_invstd, float* scale, float* shift,
+                                       void* ws, int64_t ws_bytes, void* stream) {
+  if (!x || rows <= 0 || C <= 0 || !save_mean || !save_invstd || !scale || !shift)
+    return fail(B200_INVALID_ARG, "bn_train_stats: bad arguments");
+  if (!ws || ws_bytes < b200_bn_workspace_bytes(rows, C)) return fail(B200_WORKSPACE_TOO_SMALL, "bn_train_stats: workspace too small");
+  if ((reinterpret_cast<uintptr_t>(x) & 15) != 0) return fail(B200_INVALID_ARG, "bn_train_stats: x must be 16-byte aligned");
+  cudaStream_t st = as_stream(stream);
+  if (dtype == B200_F32)
+    return bn_stats_impl<float>((const float*)x, rows, C, gamma, beta, running_mean, running_var, momentum, eps, save_mean, save_invstd, scale, shift, (float*)ws, st);
+  if (dtype == B200_BF16)
+    return bn_stats_impl<__nv_bfloat16>((const __nv_bfloat16*)x, rows, C, gamma, beta, running_mean, running_var, momentum, eps, save_mean, save_invstd, scale, shift, (float*)ws, st);
+  return fail(B200_INVALID_ARG, "bn_train_stats: bad dtype");
+}
+
+extern "C" int32_t b200_bn_eval_coeffs(const float* gamma, const float* beta, const float* running_mean,
+                                       const float* running_var, float eps, float* scale, float* shift, int32_t C,
+                                       void* stream) {
+  if (!running_mean || !running_var || !scale || !shift || C <= 0) return fail(B200_INVALID_ARG, "bn_eval_coeffs: bad arguments");
+  bn_eval_coeffs_kernel<<<(C + 127) / 128, 128, 0, as_stream(stream)>>>(gamma, beta, running_mean, running_var, eps, scale, shift, C);
+  return check_launch("bn_eval_coeffs");
+}
+
+extern "C" int32_t b200_bn_apply(const void* x, const void* residual, void* y, int64_t rows, int32_t C, int32_t dtype,
+                                 const float* scale, const float* shift, int32_t relu, void* stream) {
+  if (!x || !y || !scale || !shift || rows <= 0 || C <= 0) return fail(B200_INVALID_ARG, "bn_apply: bad arguments");
+  cudaStream_t st = as_stream(stream);
+  if (dtype == B200_F32) return bn_apply_impl<float>((const float*)x, (const float*)residual, (float*)y, rows, C, scale, shift, relu, st);
+  if (dtype == B200_BF16)
+    return bn_apply_impl<__nv_bfloat16>((const __nv_bfloat16*)x, (const __nv_bfloat16*)residual, (__nv_bfloat16*)y, rows, C, scale, shift, relu, st);
+  return fail(B200_INVALID_ARG, "bn_apply: bad dtype");
+}
+
+extern "C" int32_t b200_bn_backward(const void* dz, const void* z, const void* x, void* dx, void* dres, int64_t rows,
+                                    int32_t C, int32_t dtype, const float* gamma, const float* save_mean,
+                                    const float* save_invstd, int32_t relu, float* dgamma, float* dbeta, void* ws,
+                                    int64_t ws_bytes, void* stream) {
+  if (!dz || !x || !dx || !save_mean || !save_invstd || rows <= 0 || C <= 0 || (relu && !z))
+    return fail(B200_INVALID_ARG, "bn_backward: bad arguments");
+  if (!ws || ws_bytes < b200_bn_workspace_bytes(rows, C)) return fail(B200_WORKSPACE_TOO_SMALL, "bn_backward: workspace too small");
+  cudaStream_t st = as_stream(stream);
+  if (dtype == B200_F32)
+    return bn_bwd_impl<float>((const float*)dz, (const float*)z, (const float*)x, (float*)dx, (float*)dres, rows, C, gamma, save_mean, save_invstd, relu, dgamma, dbeta, (float*)ws, st);
+  if (dtype == B200_BF16)
+    return bn_bwd_impl<__nv_bfloat16>((const __nv_bfloat16*)dz, (const __nv_bfloat16*)z, (const __nv_bfloat16*)x, (__nv_bfloat16*)dx, (__nv_bfloat16*)dres, rows, C, gamma, save_mean, save_invstd, relu, dgamma, dbeta, (float*)ws, st);
+  return fail(B200_INVALID_ARG, "bn_backward: bad dtype");
+}
+
+extern "C" int32_t b200_add(const void* a, const void* b, void* y, int64_t n, int32_t dtype, void* stream) {
+  if (!a || !b || !y || n <= 0) return fail(B200_INVALID_ARG, "add: bad arguments");
+  cudaStream_t st = as_stream(stream);
+  if (dtype == B200_F32) add_kernel<float><<<ew_grid(n), BN_THREADS, 0, st>>>((const float*)a, (const float*)b, (float*)y, n);
+  else if (dtype == B200_BF16) add_kernel<__nv_bfloat16><<<ew_grid(n), BN_THREADS, 0, st>>>((const __nv_bfloat16*)a, (const __nv_bfloat16*)b, (__nv_bfloat16*)y, n);
+  else return fail(B200_INVALID_ARG, "add: bad dtype");
+  return check_launch("add");
+}
+
+extern "C" int32_t b200_relu_bwd(const void* dz, const void* z, void* dx, int64_t n, int32_t dtype, void* stream) {
+  if (!dz || !z || !dx || n <= 0) return fail(B200_INVALID_ARG, "relu_bwd: bad arguments");
+  cudaStream_t st = as_stream(stream);
+  if (dtype == B200_F32) relu_bwd_kernel<float><<<ew_grid(n), BN_THREADS, 0, st>>>((const float*)dz, (const float*)z, (float*)dx, n);
+  else if (dtype == B200_BF16) relu_bwd_kernel<__nv_bfloat16><<<ew_grid(n), BN_THREADS, 0, st>>>((const __nv_bfloat16*)dz, (const __nv_bfloat16*)z, (__nv_bfloat16*)dx, n);
+  else return fail(B200_INVALID_ARG, "relu_bwd: bad dtype");
+  return check_launch("relu_bwd");
+}

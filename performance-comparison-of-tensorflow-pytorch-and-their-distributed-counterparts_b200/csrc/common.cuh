@@ -89,9 +89,3 @@ inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 }  // namespace b200
 
-#define B200_DISPATCH_DTYPE(dtype, T, ...)                                         \
-  do {                                                                             \
-    if ((dtype) == B200_F32) { using T = float; __VA_ARGS__; }                     \
-    else if ((dtype) == B200_BF16) { using T = __nv_bfloat16; __VA_ARGS__; }       \
-    else return b200::fail(B200_INVALID_ARG, "unknown dtype %d", (int)(dtype));   \
-  } while (0)

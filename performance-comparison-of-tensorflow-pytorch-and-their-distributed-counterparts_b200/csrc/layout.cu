@@ -1,0 +1,279 @@
+// Layout / packing kernels at the PyTorch boundary: NCHW fp32 <-> NHWC (fp32|bf16), OIHW fp32 -> KRSC, casts,
+// im2col / col2im for the explicit-GEMM convolution paths.
+#include "common.cuh"
+
+namespace b200 {
+
+// ---------------------------------------------------------------- NCHW <-> NHWC
+// small C (images, C<=4): one thread per pixel, coalesced plane reads, contiguous pixel writes
+template <typename T>
+__global__ void nchw_to_nhwc_smallc(const float* __restrict__ x, T* __restrict__ y, int C, long long HW,
+                                    long long total_pix) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total_pix;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long n = i / HW, hw = i - n * HW;
+    const float* src = x + n * C * HW + hw;
+    T* dst = y + i * C;
+    for (int c = 0; c < C; ++c) dst[c] = from_f<T>(src[c * HW]);
+  }
+}
+// general: per image transpose [C][HW] -> [HW][C] through a 32x33 smem tile
+template <typename TI, typename TO>
+__global__ void transpose_batched(const TI* __restrict__ x, TO* __restrict__ y, int rows, int cols) {
+  // x: [batch][rows][cols] -> y: [batch][cols][rows]
+  __shared__ float tile[32][33];
+  const long long b = blockIdx.z;
+  const TI* xb = x + b * (long long)rows * cols;
+  TO* yb = y + b * (long long)rows * cols;
+  const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+  for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+    int r = r0 + j, c = c0 + threadIdx.x;
+    if (r < rows && c < cols) tile[j][threadIdx.x] = to_f(xb[(long long)r * cols + c]);
+  }
+  __syncthreads();
+  for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+    int c = c0 + j, r = r0 + threadIdx.x;
+    if (r < rows && c < cols) yb[(long long)c * rows + r] = from_f<TO>(tile[threadIdx.x][j]);
+  }
+}
+
+// ---------------------------------------------------------------- weights: OIHW fp32 -> [K][ld] with (r,s,c) order
+template <typename T>
+__global__ void pack_weight_kernel(const float* __restrict__ w, T* __restrict__ out, int K, int C, int R, int S,
+                                   int ld) {
+  const long long total = (long long)K * ld;
+  const int RSC = R * S * C;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int k = (int)(i / ld), j = (int)(i - (long long)k * ld);
+    float v = 0.f;
+    if (j < RSC) {
+      const int c = j % C, rs = j / C;
+      v = w[((long long)k * C + c) * (R * S) + rs];
+    }
+    out[i] = from_f<T>(v);
+  }
+}
+
+template <typename TI, typename TO>
+__global__ void cast_kernel(const TI* __restrict__ x, TO* __restrict__ y, long long n) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    y[i] = from_f<TO>(to_f(x[i]));
+}
+
+// ---------------------------------------------------------------- im2col (NHWC -> [M][ld], column = (r*S+s)*C + c)
+template <typename T, int VEC>
+__global__ void im2col_kernel(const T* __restrict__ x, T* __restrict__ col, int N, int H, int W, int C, int R, int S,
+                              int stride, int pad, int Ho, int Wo, int ld) {
+  const int cv = C / VEC;               // channel vectors per tap
+  const int per_row = R * S * cv;
+  const long long M = (long long)N * Ho * Wo;
+  const long long total = M * per_row;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long m = i / per_row;
+    const int j = (int)(i - m * per_row);
+    const int tap = j / cv, c = (j - tap * cv) * VEC;
+    const int r = tap / S, s = tap - r * S;
+    const int q = (int)(m % Wo);
+    const long long t = m / Wo;
+    const int p = (int)(t % Ho);
+    const int n = (int)(t / Ho);
+    const int h = p * stride + r - pad, w = q * stride + s - pad;
+    T* dst = col + m * ld + (long long)tap * C + c;
+    if (h >= 0 && h < H && w >= 0 && w < W) {
+      const T* src = x + (((long long)n * H + h) * W + w) * C + c;
+      if constexpr (VEC == 1) dst[0] = src[0];
+      else *reinterpret_cast<typename VecTraits<T>::V*>(dst) = *reinterpret_cast<const typename VecTraits<T>::V*>(src);
+    } else {
+      if constexpr (VEC == 1) dst[0] = from_f<T>(0.f);
+      else {
+        typename VecTraits<T>::V z;
+        memset(&z, 0, sizeof(z));
+        *reinterpret_cast<typename VecTraits<T>::V*>(dst) = z;
+      }
+    }
+  }
+}
+template <typename T>
+__global__ void im2col_pad_kernel(T* __restrict__ col, long long M, int used, int ld) {
+  const int padw = ld - used;
+  const long long total = M * padw;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long m = i / padw;
+    const int j = (int)(i - m * padw);
+    col[m * ld + used + j] = from_f<T>(0.f);
+  }
+}
+
+// ---------------------------------------------------------------- col2im: dx[n,h,w,c] (+)= sum over taps of dcol
+// dcol is fp32 [M][ld] with column (r*S+s)*C + c.
+template <typename T>
+__global__ void col2im_kernel(const float* __restrict__ dcol, T* __restrict__ dx, int N, int H, int W, int C, int R,
+                              int S, int stride, int pad, int Ho, int Wo, int ld, int accumulate) {
+  const long long total = (long long)N * H * W * C;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C);
+    long long t = i / C;
+    const int w = (int)(t % W);
+    t /= W;
+    const int h = (int)(t % H);
+    const int n = (int)(t / H);
+    float acc = accumulate ? to_f(dx[i]) : 0.f;
+    for (int r = 0; r < R; ++r) {
+      const int hp = h + pad - r;
+      if (hp < 0 || hp % stride) continue;
+      const int p = hp / stride;
+      if (p >= Ho) continue;
+      for (int s = 0; s < S; ++s) {
+        const int wq = w + pad - s;
+        if (wq < 0 || wq % stride) continue;
+        const int q = wq / stride;
+        if (q >= Wo) continue;
+        acc += dcol[(((long long)n * Ho + p) * Wo + q) * ld + (long long)(r * S + s) * C + c];
+      }
+    }
+    dx[i] = from_f<T>(acc);
+  }
+}
+
+// ---------------------------------------------------------------- split-K reduce
+// partial slabs [S][rows][ld] fp32 -> wgrad in OIHW fp32: row k, column (r*S+s)*C+c  ->  dw[((k*C+c)*R+r)*S+s]
+__global__ void reduce_wgrad_kernel(const float* __restrict__ part, int slabs, long long slab_stride, int K, int C,
+                                    int RS, int ld, float* __restrict__ dw) {
+  const int RSC = RS * C;
+  const long long total = (long long)K * RSC;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int k = (int)(i / RSC), j = (int)(i - (long long)k * RSC);
+    const int rs = j / C, c = j - rs * C;
+    float acc = 0.f;
+    for (int s = 0; s < slabs; ++s) acc += part[s * slab_stride + (long long)k * ld + j];
+    dw[((long long)k * C + c) * RS + rs] = acc;
+  }
+}
+// partial slabs -> plain [rows][ldo] (fp32 or bf16), optional accumulate
+template <typename T>
+__global__ void reduce_plain_kernel(const float* __restrict__ part, int slabs, long long slab_stride, int rows,
+                                    int cols, long long ldp, T* __restrict__ out, long long ldo, int accumulate) {
+  const long long total = (long long)rows * cols;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / cols;
+    const int c = (int)(i - r * cols);
+    float acc = accumulate ? to_f(out[r * ldo + c]) : 0.f;
+    for (int s = 0; s < slabs; ++s) acc += part[s * slab_stride + r * ldp + c];
+    out[r * ldo + c] = from_f<T>(acc);
+  }
+}
+
+static inline int grid_for(long long total, int threads = 256, int max_waves = 8) {
+  long long b = (total + threads - 1) / threads;
+  long long cap = (long long)num_sms() * max_waves;
+  if (b > cap) b = cap;
+  if (b < 1) b = 1;
+  return (int)b;
+}
+
+// host-side helpers used by conv.cu
+int32_t launch_im2col(const void* x, void* col, int dtype, int N, int H, int W, int C, int R, int S, int stride,
+                      int pad, int Ho, int Wo, int ld, cudaStream_t st) {
+  const long long M = (long long)N * Ho * Wo;
+  if (dtype == B200_F32) {
+    if (C % 4 == 0 && ld % 4 == 0)
+      im2col_kernel<float, 4><<<grid_for(M * R * S * (C / 4)), 256, 0, st>>>((const float*)x, (float*)col, N, H, W, C, R, S, stride, pad, Ho, Wo, ld);
+    else
+      im2col_kernel<float, 1><<<grid_for(M * R * S * C), 256, 0, st>>>((const float*)x, (float*)col, N, H, W, C, R, S, stride, pad, Ho, Wo, ld);
+    if (ld > R * S * C) im2col_pad_kernel<float><<<grid_for(M * (ld - R * S * C)), 256, 0, st>>>((float*)col, M, R * S * C, ld);
+  } else {
+    if (C % 8 == 0 && ld % 8 == 0)
+      im2col_kernel<__nv_bfloat16, 8><<<grid_for(M * R * S * (C / 8)), 256, 0, st>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)col, N, H, W, C, R, S, stride, pad, Ho, Wo, ld);
+    else
+      im2col_kernel<__nv_bfloat16, 1><<<grid_for(M * R * S * C), 256, 0, st>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)col, N, H, W, C, R, S, stride, pad, Ho, Wo, ld);
+    if (ld > R * S * C) im2col_pad_kernel<__nv_bfloat16><<<grid_for(M * (ld - R * S * C)), 256, 0, st>>>((__nv_bfloat16*)col, M, R * S * C, ld);
+  }
+  return check_launch("im2col");
+}
+int32_t launch_col2im(const float* dcol, void* dx, int dtype, int N, int H, int W, int C, int R, int S, int stride,
+                      int pad, int Ho, int Wo, int ld, int accumulate, cudaStream_t st) {
+  const long long total = (long long)N * H * W * C;
+  if (dtype == B200_F32)
+    col2im_kernel<float><<<grid_for(total), 256, 0, st>>>(dcol, (float*)dx, N, H, W, C, R, S, stride, pad, Ho, Wo, ld, accumulate);
+  else
+    col2im_kernel<__nv_bfloat16><<<grid_for(total), 256, 0, st>>>(dcol, (__nv_bfloat16*)dx, N, H, W, C, R, S, stride, pad, Ho, Wo, ld, accumulate);
+  return check_launch("col2im");
+}
+int32_t launch_reduce_wgrad(const float* part, int slabs, long long slab_stride, int K, int C, int RS, int ld,
+                            float* dw, cudaStream_t st) {
+  reduce_wgrad_kernel<<<grid_for((long long)K * RS * C), 256, 0, st>>>(part, slabs, slab_stride, K, C, RS, ld, dw);
+  return check_launch("reduce_wgrad");
+}
+int32_t launch_reduce_plain(const float* part, int slabs, long long slab_stride, int rows, int cols, long long ldp,
+                            void* out, long long ldo, int out_dtype, int accumulate, cudaStream_t st) {
+  if (out_dtype == B200_F32)
+    reduce_plain_kernel<float><<<grid_for((long long)rows * cols), 256, 0, st>>>(part, slabs, slab_stride, rows, cols, ldp, (float*)out, ldo, accumulate);
+  else
+    reduce_plain_kernel<__nv_bfloat16><<<grid_for((long long)rows * cols), 256, 0, st>>>(part, slabs, slab_stride, rows, cols, ldp, (__nv_bfloat16*)out, ldo, accumulate);
+  return check_launch("reduce_plain");
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int32_t b200_nchw_to_nhwc(const float* x, void* y, int32_t N, int32_t C, int32_t H, int32_t W,
+                                     int32_t out_dtype, void* stream) {
+  if (!x || !y || N <= 0 || C <= 0 || H <= 0 || W <= 0) return fail(B200_INVALID_ARG, "nchw_to_nhwc: bad args");
+  cudaStream_t st = as_stream(stream);
+  const long long HW = (long long)H * W;
+  if (C <= 4) {
+    if (out_dtype == B200_F32) nchw_to_nhwc_smallc<float><<<grid_for(N * HW), 256, 0, st>>>(x, (float*)y, C, HW, N * HW);
+    else if (out_dtype == B200_BF16) nchw_to_nhwc_smallc<__nv_bfloat16><<<grid_for(N * HW), 256, 0, st>>>(x, (__nv_bfloat16*)y, C, HW, N * HW);
+    else return fail(B200_INVALID_ARG, "bad dtype");
+  } else {
+    dim3 grid((unsigned)((HW + 31) / 32), (C + 31) / 32, N), block(32, 8);
+    if (out_dtype == B200_F32) transpose_batched<float, float><<<grid, block, 0, st>>>(x, (float*)y, C, (int)HW);
+    else if (out_dtype == B200_BF16) transpose_batched<float, __nv_bfloat16><<<grid, block, 0, st>>>(x, (__nv_bfloat16*)y, C, (int)HW);
+    else return fail(B200_INVALID_ARG, "bad dtype");
+  }
+  return check_launch("nchw_to_nhwc");
+}
+
+extern "C" int32_t b200_nhwc_to_nchw(const void* x, float* y, int32_t N, int32_t C, int32_t H, int32_t W,
+                                     int32_t in_dtype, void* stream) {
+  if (!x || !y || N <= 0 || C <= 0 || H <= 0 || W <= 0) return fail(B200_INVALID_ARG, "nhwc_to_nchw: bad args");
+  cudaStream_t st = as_stream(stream);
+  const long long HW = (long long)H * W;
+  dim3 grid((C + 31) / 32, (unsigned)((HW + 31) / 32), N), block(32, 8);
+  if (in_dtype == B200_F32) transpose_batched<float, float><<<grid, block, 0, st>>>((const float*)x, y, (int)HW, C);
+  else if (in_dtype == B200_BF16) transpose_batched<__nv_bfloat16, float><<<grid, block, 0, st>>>((const __nv_bfloat16*)x, y, (int)HW, C);
+  else return fail(B200_INVALID_ARG, "bad dtype");
+  return check_launch("nhwc_to_nchw");
+}
+
+extern "C" int32_t b200_pack_weight(const float* w, void* out, int32_t K, int32_t C, int32_t R, int32_t S, int32_t ld,
+                                    int32_t out_dtype, void* stream) {
+  if (!w || !out || ld < R * S * C) return fail(B200_INVALID_ARG, "pack_weight: bad args");
+  cudaStream_t st = as_stream(stream);
+  if (out_dtype == B200_F32) pack_weight_kernel<float><<<grid_for((long long)K * ld), 256, 0, st>>>(w, (float*)out, K, C, R, S, ld);
+  else if (out_dtype == B200_BF16) pack_weight_kernel<__nv_bfloat16><<<grid_for((long long)K * ld), 256, 0, st>>>(w, (__nv_bfloat16*)out, K, C, R, S, ld);
+  else return fail(B200_INVALID_ARG, "bad dtype");
+  return check_launch("pack_weight");
+}
+
+extern "C" int32_t b200_cast(const void* x, void* y, int64_t n, int32_t in_dtype, int32_t out_dtype, void* stream) {
+  cudaStream_t st = as_stream(stream);
+  if (n <= 0) return B200_OK;
+  if (in_dtype == B200_F32 && out_dtype == B200_BF16)
+    cast_kernel<float, __nv_bfloat16><<<grid_for(n), 256, 0, st>>>((const float*)x, (__nv_bfloat16*)y, n);
+  else if (in_dtype == B200_BF16 && out_dtype == B200_F32)
+    cast_kernel<__nv_bfloat16, float><<<grid_for(n), 256, 0, st>>>((const __nv_bfloat16*)x, (float*)y, n);
+  else if (in_dtype == B200_F32 && out_dtype == B200_F32)
+    cast_kernel<float, float><<<grid_for(n), 256, 0, st>>>((const float*)x, (float*)y, n);
+  else if (in_dtype == B200_BF16 && out_dtype == B200_BF16)
+    cast_kernel<__nv_bfloat16, __nv_bfloat16><<<grid_for(n), 256, 0, st>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, n);
+  else return fail(B200_INVALID_ARG, "cast: bad dtypes");
+  return check_launch("cast");
+}

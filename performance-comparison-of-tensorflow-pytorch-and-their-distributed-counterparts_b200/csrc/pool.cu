@@ -1,0 +1,153 @@
+// MaxPool2d(3, stride 2, pad 1) and AdaptiveAvgPool2d((1,1)) over NHWC activations.
+// max-pool keeps a uint8 window index per output element (first maximum in scan order, like ATen) so the backward
+// is a pure gather with no atomics.
+#include "common.cuh"
+#include <math_constants.h>
+
+namespace b200 {
+
+template <typename T>
+__global__ void maxpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, uint8_t* __restrict__ amax, int N,
+                                   int H, int W, int C, int Ho, int Wo) {
+  const long long total = (long long)N * Ho * Wo * C;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C);
+    long long t = i / C;
+    const int q = (int)(t % Wo);
+    t /= Wo;
+    const int p = (int)(t % Ho);
+    const int n = (int)(t / Ho);
+    float best = -CUDART_INF_F;
+    int bi = 0;
+    bool any = false;
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      const int h = 2 * p - 1 + r;
+      if (h < 0 || h >= H) continue;
+#pragma unroll
+      for (int s = 0; s < 3; ++s) {
+        const int w = 2 * q - 1 + s;
+        if (w < 0 || w >= W) continue;
+        const float v = to_f(x[(((long long)n * H + h) * W + w) * C + c]);
+        if (!any || v > best || v != v) {
+          best = v;
+          bi = r * 3 + s;
+          any = true;
+        }
+      }
+    }
+    y[i] = from_f<T>(best);
+    if (amax) amax[i] = (uint8_t)bi;
+  }
+}
+
+template <typename T>
+__global__ void maxpool_bwd_kernel(const T* __restrict__ dy, const uint8_t* __restrict__ amax, T* __restrict__ dx,
+                                   int N, int H, int W, int C, int Ho, int Wo) {
+  const long long total = (long long)N * H * W * C;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C);
+    long long t = i / C;
+    const int w = (int)(t % W);
+    t /= W;
+    const int h = (int)(t % H);
+    const int n = (int)(t / H);
+    float acc = 0.f;
+    // windows p with 2p-1 <= h <= 2p+1
+    const int p_lo = h / 2, p_hi = (h + 1) / 2;
+    const int q_lo = w / 2, q_hi = (w + 1) / 2;
+    for (int p = p_lo; p <= p_hi; ++p) {
+      if (p >= Ho) continue;
+      const int r = h - (2 * p - 1);
+      for (int q = q_lo; q <= q_hi; ++q) {
+        if (q >= Wo) continue;
+        const int s = w - (2 * q - 1);
+        const long long o = (((long long)n * Ho + p) * Wo + q) * C + c;
+        if (amax[o] == r * 3 + s) acc += to_f(dy[o]);
+      }
+    }
+    dx[i] = from_f<T>(acc);
+  }
+}
+
+template <typename T>
+__global__ void avgpool_fwd_kernel(const T* __restrict__ x, float* __restrict__ y, int N, int HW, int C) {
+  const long long total = (long long)N * C;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C);
+    const long long n = i / C;
+    float acc = 0.f;
+    for (int j = 0; j < HW; ++j) acc += to_f(x[(n * HW + j) * C + c]);
+    y[i] = acc / (float)HW;
+  }
+}
+template <typename T>
+__global__ void avgpool_bwd_kernel(const float* __restrict__ dy, T* __restrict__ dx, int N, int HW, int C) {
+  const long long total = (long long)N * HW * C;
+  const float inv = 1.f / (float)HW;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C);
+    const long long n = i / ((long long)HW * C);
+    dx[i] = from_f<T>(dy[n * C + c] * inv);
+  }
+}
+
+static inline int pgrid(long long total) {
+  long long b = (total + 255) / 256;
+  const long long cap = (long long)num_sms() * 8;
+  if (b > cap) b = cap;
+  return (int)(b < 1 ? 1 : b);
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int32_t b200_maxpool3x3s2_fwd(const void* x, void* y, uint8_t* argmax, int32_t N, int32_t H, int32_t W,
+                                         int32_t C, int32_t dtype, void* stream) {
+  if (!x || !y || N <= 0 || H <= 0 || W <= 0 || C <= 0) return fail(B200_INVALID_ARG, "maxpool_fwd: bad arguments");
+  const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;
+  const long long total = (long long)N * Ho * Wo * C;
+  cudaStream_t st = as_stream(stream);
+  if (dtype == B200_F32) maxpool_fwd_kernel<float><<<pgrid(total), 256, 0, st>>>((const float*)x, (float*)y, argmax, N, H, W, C, Ho, Wo);
+  else if (dtype == B200_BF16) maxpool_fwd_kernel<__nv_bfloat16><<<pgrid(total), 256, 0, st>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, argmax, N, H, W, C, Ho, Wo);
+  else return fail(B200_INVALID_ARG, "maxpool_fwd: bad dtype");
+  return check_launch("maxpool_fwd");
+}
+
+extern "C" int32_t b200_maxpool3x3s2_bwd(const void* dy, const uint8_t* argmax, void* dx, int32_t N, int32_t H,
+                                         int32_t W, int32_t C, int32_t dtype, void* stream) {
+  if (!dy || !argmax || !dx || N <= 0 || H <= 0 || W <= 0 || C <= 0) return fail(B200_INVALID_ARG, "maxpool_bwd: bad arguments");
+  const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;
+  const long long total = (long long)N * H * W * C;
+  cudaStream_t st = as_stream(stream);
+  if (dtype == B200_F32) maxpool_bwd_kernel<float><<<pgrid(total), 256, 0, st>>>((const float*)dy, argmax, (float*)dx, N, H, W, C, Ho, Wo);
+  else if (dtype == B200_BF16) maxpool_bwd_kernel<__nv_bfloat16><<<pgrid(total), 256, 0, st>>>((const __nv_bfloat16*)dy, argmax, (__nv_bfloat16*)dx, N, H, W, C, Ho, Wo);
+  else return fail(B200_INVALID_ARG, "maxpool_bwd: bad dtype");
+  return check_launch("maxpool_bwd");
+}
+
+extern "C" int32_t b200_avgpool_fwd(const void* x, float* y, int32_t N, int32_t HW, int32_t C, int32_t dtype,
+                                    void* stream) {
+  if (!x || !y || N <= 0 || HW <= 0 || C <= 0) return fail(B200_INVALID_ARG, "avgpool_fwd: bad arguments");
+  cudaStream_t st = as_stream(stream);
+  if (dtype == B200_F32) avgpool_fwd_kernel<float><<<pgrid((long long)N * C), 256, 0, st>>>((const float*)x, y, N, HW, C);
+  else if (dtype == B200_BF16) avgpool_fwd_kernel<__nv_bfloat16><<<pgrid((long long)N * C), 256, 0, st>>>((const __nv_bfloat16*)x, y, N, HW, C);
+  else return fail(B200_INVALID_ARG, "avgpool_fwd: bad dtype");
+  return check_launch("avgpool_fwd");
+}
+
+extern "C" int32_t b200_avgpool_bwd(const float* dy, void* dx, int32_t N, int32_t HW, int32_t C, int32_t dtype,
+                                    void* stream) {
+  if (!dy || !dx || N <= 0 || HW <= 0 || C <= 0) return fail(B200_INVALID_ARG, "avgpool_bwd: bad arguments");
+  cudaStream_t st = as_stream(stream);
+  const long long total = (long long)N * HW * C;
+  if (dtype == B200_F32) avgpool_bwd_kernel<float><<<pgrid(total), 256, 0, st>>>(dy, (float*)dx, N, HW, C);
+  else if (dtype == B200_BF16) avgpool_bwd_kernel<__nv_bfloat16><<<pgrid(total), 256, 0, st>>>(dy, (__nv_bfloat16*)dx, N, HW, C);
+  else return fail(B200_INVALID_ARG, "avgpool_bwd: bad dtype");
+  return check_launch("avgpool_bwd");
+}
