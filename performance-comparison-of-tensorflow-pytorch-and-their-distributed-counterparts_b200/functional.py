@@ -1,0 +1,447 @@
+"""Autograd glue: torch.autograd.Function wrappers whose forward/backward enqueue b200net kernels.
+
+Two granularities:
+  * `resnet_backbone(model, x)` -- the hot path: ONE autograd node for the whole torchvision-shaped backbone
+    (stem -> layer1..4 -> avgpool).  Forward and backward are hand-scheduled lists of kernel launches over NHWC
+    activations; nothing goes through ATen convolution / batch_norm.
+    Mirrors ResNet._forward_impl as called from `model.forward(inputs)`
+    (pytorch_training_inference_on_image.ipynb:669) and `loss.backward()` (:671).
+  * per-layer functions (conv2d, batch_norm, linear, relu, dropout, log_softmax, nll_loss ...) used by the
+    stand-alone modules in nn.py and by the classifier head.
+"""
+import os
+
+import torch
+from torch.autograd.function import once_differentiable
+
+from . import ops
+
+# ------------------------------------------------------------------ precision switch
+_PRECISION = os.environ.get("B200_PRECISION", "bf16").lower()
+
+
+def set_precision(p):
+    """'bf16' (tcgen05 tensor cores, fp32 accumulate, fp32 statistics/params) or 'fp32' (exact FFMA parity mode)."""
+    global _PRECISION
+    p = p.lower()
+    if p not in ("bf16", "fp32"):
+        raise ValueError("precision must be 'bf16' or 'fp32'")
+    _PRECISION = p
+
+
+def get_precision():
+    return _PRECISION
+
+
+def act_dtype():
+    return torch.bfloat16 if _PRECISION == "bf16" else torch.float32
+
+
+# ------------------------------------------------------------------ gradient sink (set by parallel.DistributedDataParallel)
+# Called as sink(param, grad) the moment a parameter gradient has been enqueued inside the fused backbone backward;
+# returns the tensor to hand to autograd (DDP returns the parameter's bucket slice).
+_GRAD_SINK = None
+
+
+def set_grad_sink(fn):
+    global _GRAD_SINK
+    _GRAD_SINK = fn
+
+
+# ------------------------------------------------------------------ packed-weight cache
+# key: id(param) -> (data_ptr, version, dtype, packed).  Our optimizers bump the parameter version after the raw
+# in-place update (torch.autograd.graph.increment_version), stock optimizers do it through ATen.
+_PACKED = {}
+
+
+def packed_weight(w, dtype):
+    key = id(w)
+    e = _PACKED.get(key)
+    if e is not None and e[0] == w.data_ptr() and e[1] == w._version and e[2] == dtype:
+        return e[3]
+    p = ops.pack_weight(w, dtype)
+    _PACKED[key] = (w.data_ptr(), w._version, dtype, p)
+    return p
+
+
+def _conv_geom(conv):
+    if conv.groups != 1 or conv.dilation not in ((1, 1), 1):
+        raise NotImplementedError("b200net Conv2d: groups=1, dilation=1 only")
+    k = conv.kernel_size
+    s = conv.stride
+    p = conv.padding
+    if s[0] != s[1] or p[0] != p[1]:
+        raise NotImplementedError("b200net Conv2d: square stride / padding only")
+    if conv.bias is not None:
+        raise NotImplementedError("b200net Conv2d: bias=False only (ResNet convolutions carry no bias)")
+    return conv.out_channels, k[0], k[1], s[0], p[0]
+
+
+# ------------------------------------------------------------------ BN helpers shared by both granularities
+def _bn_coeffs(bn, y):
+    """Returns (scale, shift, mean, invstd); mean/invstd are None in eval mode.  Updates running stats in train mode."""
+    use_batch = bn.training or (bn.running_mean is None and bn.running_var is None)
+    if use_batch:
+        momentum = 0.0
+        rm, rv = bn.running_mean, bn.running_var
+        if bn.training and bn.track_running_stats and rm is not None:
+            if bn.num_batches_tracked is not None:
+                bn.num_batches_tracked.add_(1)
+            momentum = bn.momentum if bn.momentum is not None else 1.0 / float(bn.num_batches_tracked)
+        else:
+            rm = rv = None
+        mean, invstd, scale, shift = ops.bn_train_stats(y, bn.weight, bn.bias, rm, rv, momentum, bn.eps)
+        return scale, shift, mean, invstd
+    scale, shift = ops.bn_eval_coeffs(bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.eps)
+    return scale, shift, None, None
+
+
+# ------------------------------------------------------------------ the backbone as one autograd node
+class _Unit(object):
+    """Saved state of one conv -> BN (-> +residual) (-> ReLU) unit."""
+    __slots__ = ("conv", "bn", "x", "y", "z", "mean", "invstd", "relu", "geom")
+
+
+def _unit_forward(conv, bn, x, relu, residual, save):
+    K, R, S, stride, pad = _conv_geom(conv)
+    wp = packed_weight(conv.weight, x.dtype)
+    y = ops.conv_fprop(x, wp, K, R, S, stride, pad)
+    scale, shift, mean, invstd = _bn_coeffs(bn, y)
+    # eval mode: y is dead after the apply -> write in place
+    z = ops.bn_apply(y, scale, shift, relu, residual, out=None if save else y)
+    if not save:
+        return z, None
+    u = _Unit()
+    u.conv, u.bn, u.x, u.y, u.z, u.mean, u.invstd, u.relu = conv, bn, x, y, z, mean, invstd, relu
+    u.geom = (K, R, S, stride, pad)
+    return z, u
+
+
+def _backbone_params(model):
+    ps = [model.conv1.weight, model.bn1.weight, model.bn1.bias]
+    for layer in (model.layer1, model.layer2, model.layer3, model.layer4):
+        for blk in layer:
+            ps += [blk.conv1.weight, blk.bn1.weight, blk.bn1.bias, blk.conv2.weight, blk.bn2.weight, blk.bn2.bias,
+                   blk.conv3.weight, blk.bn3.weight, blk.bn3.bias]
+            if blk.downsample is not None:
+                ps += [blk.downsample[0].weight, blk.downsample[1].weight, blk.downsample[1].bias]
+    return ps
+
+
+class _ResNetBackbone(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, model, x, *params):
+        # forward() runs with grad mode off; needs_input_grad already folds in the caller's grad mode
+        save = any(ctx.needs_input_grad)
+        dtype = act_dtype()
+        xh = ops.to_nhwc(x, dtype)
+        units = []
+        z, u = _unit_forward(model.conv1, model.bn1, xh, True, None, save)
+        units.append(u)
+        stem_shape = z.shape
+        cur, pool_idx = ops.maxpool_fwd(z, save)
+        blocks = []
+        for layer in (model.layer1, model.layer2, model.layer3, model.layer4):
+            for blk in layer:
+                z1, u1 = _unit_forward(blk.conv1, blk.bn1, cur, True, None, save)
+                z2, u2 = _unit_forward(blk.conv2, blk.bn2, z1, True, None, save)
+                ud = None
+                if blk.downsample is not None:
+                    res, ud = _unit_forward(blk.downsample[0], blk.downsample[1], cur, False, None, save)
+                else:
+                    res = cur
+                cur, u3 = _unit_forward(blk.conv3, blk.bn3, z2, True, res, save)
+                blocks.append((u1, u2, u3, ud))
+        feat = ops.avgpool_fwd(cur)
+        if save:
+            ctx.units0 = units[0]
+            ctx.blocks = blocks
+            ctx.pool_idx = pool_idx
+            ctx.stem_shape = stem_shape
+            ctx.final_shape = cur.shape
+            ctx.dtype = dtype
+            ctx.x_needs_grad = ctx.needs_input_grad[1]
+            ctx.params = params
+            ctx.param_needs = list(ctx.needs_input_grad[2:])
+        return feat
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dfeat):
+        dfeat = dfeat.contiguous().float()
+        grads = {}  # id(param) -> grad
+        sink = _GRAD_SINK
+
+        def emit(p, g):
+            grads[id(p)] = sink(p, g) if sink is not None else g
+
+        def unit_backward(u, dz, want_dres, need_dx=True):
+            """dz: grad w.r.t. the unit output. Returns (dx_of_conv_input or None, dres)."""
+            if u.mean is None:
+                raise RuntimeError("b200net: backward through BatchNorm in eval mode is not supported on this path")
+            need_bn = u.bn.weight is not None and (u.bn.weight.requires_grad or u.bn.bias.requires_grad)
+            dy, dres, dgamma, dbeta = ops.bn_backward(dz, u.z if u.relu else None, u.y, u.bn.weight, u.mean, u.invstd,
+                                                      u.relu, want_dres=want_dres, want_param_grads=need_bn)
+            if need_bn:
+                if u.bn.bias.requires_grad:
+                    emit(u.bn.bias, dbeta)
+                if u.bn.weight.requires_grad:
+                    emit(u.bn.weight, dgamma)
+            K, R, S, stride, pad = u.geom
+            if u.conv.weight.requires_grad:
+                emit(u.conv.weight, ops.conv_wgrad(u.x, dy, K, R, S, stride, pad))
+            return dy, dres
+
+        def dgrad(u, dy, out=None, accumulate=False):
+            K, R, S, stride, pad = u.geom
+            wp = packed_weight(u.conv.weight, dy.dtype)
+            return ops.conv_dgrad(dy, wp, u.x.shape, K, R, S, stride, pad, out=out, accumulate=accumulate)
+
+        dcur = ops.avgpool_bwd(dfeat, ctx.final_shape, ctx.dtype)
+        for (u1, u2, u3, ud) in reversed(ctx.blocks):
+            dy3, g = unit_backward(u3, dcur, want_dres=True)
+            dz2 = dgrad(u3, dy3)
+            dy2, _ = unit_backward(u2, dz2, want_dres=False)
+            dz1 = dgrad(u2, dy2)
+            dy1, _ = unit_backward(u1, dz1, want_dres=False)
+            if ud is not None:
+                dyd, _ = unit_backward(ud, g, want_dres=False)
+                dcur = dgrad(ud, dyd)
+                dgrad(u1, dy1, out=dcur, accumulate=True)
+            else:
+                dcur = dgrad(u1, dy1, out=g, accumulate=True)
+        dz0 = ops.maxpool_bwd(dcur, ctx.pool_idx, ctx.stem_shape)
+        u0 = ctx.units0
+        dy0, _ = unit_backward(u0, dz0, want_dres=False)
+        dx = None
+        if ctx.x_needs_grad:
+            dx = ops.to_nchw(dgrad(u0, dy0))
+        out = (None, dx) + tuple(grads.get(id(p)) if need else None for p, need in zip(ctx.params, ctx.param_needs))
+        ctx.blocks = None
+        ctx.units0 = None
+        ctx.params = None
+        return out
+
+
+def resnet_backbone(model, x):
+    """[N,3,H,W] fp32 NCHW -> [N,2048] fp32 features (everything up to and including avgpool + flatten)."""
+    return _ResNetBackbone.apply(model, x, *_backbone_params(model))
+
+
+# ------------------------------------------------------------------ classifier head (fp32, [rows][features])
+def _c2d(t):
+    if not t.is_cuda:
+        raise RuntimeError("b200net kernels run on CUDA tensors only (no CPU fallback)")
+    if t.dtype != torch.float32:
+        t = t.float()
+    return t.contiguous()
+
+
+class _Linear(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, w, b):
+        x, w = _c2d(x), _c2d(w)
+        ctx.save_for_backward(x, w)
+        ctx.has_bias = b is not None
+        return ops.linear_fwd(x, w, _c2d(b) if b is not None else None)
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dy):
+        x, w = ctx.saved_tensors
+        dy = _c2d(dy)
+        dx = ops.linear_bwd_input(dy, w) if ctx.needs_input_grad[0] else None
+        dw = ops.linear_bwd_weight(dy, x) if ctx.needs_input_grad[1] else None
+        db = ops.colsum(dy) if (ctx.has_bias and ctx.needs_input_grad[2]) else None
+        return dx, dw, db
+
+
+def linear(x, w, b=None):
+    lead = x.shape[:-1]
+    y = _Linear.apply(x.reshape(-1, x.shape[-1]), w, b)
+    return y.reshape(*lead, w.shape[0])
+
+
+class _ReLU(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        y = ops.relu_fwd(_c2d(x))
+        ctx.save_for_backward(y)
+        return y
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dy):
+        (y,) = ctx.saved_tensors
+        return ops.relu_bwd(_c2d(dy), y)
+
+
+def relu(x):
+    return _ReLU.apply(x)
+
+
+_DROPOUT_CALLS = [0]
+
+
+class _Dropout(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, p):
+        x = _c2d(x)
+        seed = torch.cuda.initial_seed() & 0xFFFFFFFFFFFFFFFF
+        offset = _DROPOUT_CALLS[0]
+        _DROPOUT_CALLS[0] += (x.numel() + 3) // 4
+        y, mask = ops.dropout_fwd(x, p, seed, offset)
+        ctx.save_for_backward(mask)
+        ctx.p = p
+        return y
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dy):
+        (mask,) = ctx.saved_tensors
+        return ops.dropout_bwd(_c2d(dy), mask, ctx.p), None
+
+
+def dropout(x, p, training):
+    if not training or p == 0.0:
+        return x
+    return _Dropout.apply(x, p)
+
+
+class _LogSoftmax(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        y = ops.log_softmax_fwd(_c2d(x))
+        ctx.save_for_backward(y)
+        return y
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dy):
+        (y,) = ctx.saved_tensors
+        return ops.log_softmax_bwd(_c2d(dy), y)
+
+
+def log_softmax(x, dim=-1):
+    if x.dim() != 2 or dim not in (1, -1):
+        raise NotImplementedError("b200net log_softmax: 2-D input, dim=1")
+    return _LogSoftmax.apply(x)
+
+
+class _NLLLoss(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logp, labels):
+        logp = _c2d(logp)
+        labels = labels.contiguous()
+        if labels.dtype != torch.int64:
+            labels = labels.long()
+        ctx.save_for_backward(labels)
+        ctx.shape = logp.shape
+        return ops.nll_loss_fwd(logp, labels)
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dloss):
+        (labels,) = ctx.saved_tensors
+        return ops.nll_loss_bwd(_c2d(dloss).reshape(1), labels, ctx.shape[0], ctx.shape[1]), None
+
+
+def nll_loss(logp, labels):
+    return _NLLLoss.apply(logp, labels)
+
+
+# ------------------------------------------------------------------ stand-alone NCHW layers (module-level use)
+class _Conv2d(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, w, geom):
+        K, R, S, stride, pad = geom
+        dtype = act_dtype()
+        xh = ops.to_nhwc(x, dtype)
+        y = ops.conv_fprop(xh, packed_weight(w, dtype), K, R, S, stride, pad)
+        ctx.save_for_backward(xh, w)
+        ctx.geom = geom
+        return ops.to_nchw(y)
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dy):
+        xh, w = ctx.saved_tensors
+        K, R, S, stride, pad = ctx.geom
+        dyh = ops.to_nhwc(dy, xh.dtype)
+        dx = dw = None
+        if ctx.needs_input_grad[0]:
+            dx = ops.to_nchw(ops.conv_dgrad(dyh, packed_weight(w, xh.dtype), xh.shape, K, R, S, stride, pad))
+        if ctx.needs_input_grad[1]:
+            dw = ops.conv_wgrad(xh, dyh, K, R, S, stride, pad)
+        return dx, dw, None
+
+
+def conv2d_module(conv, x):
+    return _Conv2d.apply(x, conv.weight, _conv_geom(conv))
+
+
+class _BatchNorm2d(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, gamma, beta, bn):
+        xh = ops.to_nhwc(x, act_dtype())
+        scale, shift, mean, invstd = _bn_coeffs(bn, xh)
+        z = ops.bn_apply(xh, scale, shift, False)
+        ctx.bn = bn
+        ctx.stats = (mean, invstd)
+        ctx.save_for_backward(xh)
+        return ops.to_nchw(z)
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dz):
+        (xh,) = ctx.saved_tensors
+        mean, invstd = ctx.stats
+        if mean is None:
+            raise RuntimeError("b200net: backward through BatchNorm in eval mode is not supported")
+        dzh = ops.to_nhwc(dz, xh.dtype)
+        dx, _, dgamma, dbeta = ops.bn_backward(dzh, None, xh, ctx.bn.weight, mean, invstd, False)
+        return ops.to_nchw(dx), dgamma, dbeta, None
+
+
+def batch_norm_module(bn, x):
+    return _BatchNorm2d.apply(x, bn.weight, bn.bias, bn)
+
+
+class _MaxPool(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        xh = ops.to_nhwc(x, act_dtype())
+        y, idx = ops.maxpool_fwd(xh, True)
+        ctx.save_for_backward(idx)
+        ctx.shape = xh.shape
+        ctx.dtype = xh.dtype
+        return ops.to_nchw(y)
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dy):
+        (idx,) = ctx.saved_tensors
+        return ops.to_nchw(ops.maxpool_bwd(ops.to_nhwc(dy, ctx.dtype), idx, ctx.shape))
+
+
+def maxpool3x3s2(x):
+    return _MaxPool.apply(x)
+
+
+class _AvgPool(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        xh = ops.to_nhwc(x, act_dtype())
+        ctx.shape = xh.shape
+        ctx.dtype = xh.dtype
+        return ops.avgpool_fwd(xh).reshape(x.shape[0], x.shape[1], 1, 1)
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dy):
+        N, H, W, C = ctx.shape
+        return ops.to_nchw(ops.avgpool_bwd(dy.reshape(N, C).contiguous().float(), ctx.shape, ctx.dtype))
+
+
+def global_avgpool(x):
+    return _AvgPool.apply(x)

@@ -1,0 +1,323 @@
+"""Tensor-level wrappers over the C-ABI: torch owns every buffer (caching allocator), the library only sees
+device pointers, sizes and the current stream.  Internal activations are NHWC tensors ([N,H,W,C], fp32 or bf16).
+
+Nothing here falls back to ATen/cuDNN/cuBLAS: a CPU tensor or a missing library is an error.
+"""
+import torch
+
+from . import _C
+from ._C import lib, check, ConvDesc
+import ctypes
+
+_DT = {torch.float32: _C.F32, torch.bfloat16: _C.BF16}
+
+
+def _dt(t):
+    try:
+        return _DT[t.dtype]
+    except KeyError:
+        raise TypeError("b200net: unsupported dtype %s (float32 / bfloat16 only)" % t.dtype)
+
+
+def _need_cuda(t):
+    if not t.is_cuda:
+        raise RuntimeError("b200net kernels run on CUDA tensors only (no CPU fallback); got a %s tensor" % t.device)
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+# ------------------------------------------------------------------ workspace (one growing buffer per device)
+_WS = {}
+
+
+def workspace(nbytes, device):
+    key = device.index if device.index is not None else torch.cuda.current_device()
+    buf = _WS.get(key)
+    if buf is None or buf.numel() < nbytes:
+        # stream-ordered reuse: every consumer runs on the current stream
+        buf = torch.empty(max(int(nbytes), 1 << 20), dtype=torch.uint8, device=device)
+        _WS[key] = buf
+    return buf
+
+
+# ------------------------------------------------------------------ layout
+def to_nhwc(x, dtype):
+    """NCHW fp32 (what the reference's loaders produce, ...on_image.ipynb:667) -> NHWC `dtype`."""
+    _need_cuda(x)
+    if x.dtype != torch.float32:
+        x = x.float()
+    x = x.contiguous()
+    N, C, H, W = x.shape
+    y = torch.empty((N, H, W, C), dtype=dtype, device=x.device)
+    check(lib.b200_nchw_to_nhwc(x.data_ptr(), y.data_ptr(), N, C, H, W, _DT[dtype], _stream()), "nchw_to_nhwc")
+    return y
+
+
+def to_nchw(x):
+    _need_cuda(x)
+    N, H, W, C = x.shape
+    y = torch.empty((N, C, H, W), dtype=torch.float32, device=x.device)
+    check(lib.b200_nhwc_to_nchw(x.data_ptr(), y.data_ptr(), N, C, H, W, _dt(x), _stream()), "nhwc_to_nchw")
+    return y
+
+
+def weight_ld(R, S, C):
+    return (R * S * C + 7) // 8 * 8
+
+
+def pack_weight(w, dtype):
+    """OIHW fp32 parameter -> [K][ld] `dtype`, (r,s,c) column order."""
+    _need_cuda(w)
+    K, C, R, S = w.shape
+    ld = weight_ld(R, S, C)
+    out = torch.empty((K, ld), dtype=dtype, device=w.device)
+    wd = w.detach()
+    if wd.dtype != torch.float32 or not wd.is_contiguous():
+        wd = wd.float().contiguous()
+    check(lib.b200_pack_weight(wd.data_ptr(), out.data_ptr(), K, C, R, S, ld, _DT[dtype], _stream()), "pack_weight")
+    return out
+
+
+# ------------------------------------------------------------------ convolution
+_DESC = {}
+
+
+def _desc(N, H, W, C, K, R, S, stride, pad, dt):
+    key = (N, H, W, C, K, R, S, stride, pad, dt)
+    e = _DESC.get(key)
+    if e is None:
+        d = ConvDesc(N, H, W, C, K, R, S, stride, pad, dt)
+        ws = [int(lib.b200_conv_workspace_bytes(ctypes.byref(d), which)) for which in range(3)]
+        if min(ws) < 0:
+            raise RuntimeError("b200net conv: unsupported descriptor %s: %s" % (key, _C.last_error()))
+        Ho = (H + 2 * pad - R) // stride + 1
+        Wo = (W + 2 * pad - S) // stride + 1
+        e = (d, ctypes.byref(d), ws, Ho, Wo)
+        _DESC[key] = e
+    return e
+
+
+def conv_fprop(x, wp, K, R, S, stride, pad):
+    N, H, W, C = x.shape
+    d, dref, ws, Ho, Wo = _desc(N, H, W, C, K, R, S, stride, pad, _dt(x))
+    y = torch.empty((N, Ho, Wo, K), dtype=x.dtype, device=x.device)
+    w = workspace(ws[0], x.device) if ws[0] else None
+    check(lib.b200_conv_fprop(dref, x.data_ptr(), wp.data_ptr(), y.data_ptr(), w.data_ptr() if w is not None else None,
+                              ws[0], _stream()), "conv_fprop")
+    return y
+
+
+def conv_dgrad(dy, wp, x_shape, K, R, S, stride, pad, out=None, accumulate=False):
+    N, H, W, C = x_shape
+    d, dref, ws, Ho, Wo = _desc(N, H, W, C, K, R, S, stride, pad, _dt(dy))
+    if out is None:
+        out = torch.empty((N, H, W, C), dtype=dy.dtype, device=dy.device)
+        accumulate = False
+    w = workspace(ws[1], dy.device) if ws[1] else None
+    check(lib.b200_conv_dgrad(dref, dy.data_ptr(), wp.data_ptr(), out.data_ptr(), 1 if accumulate else 0,
+                              w.data_ptr() if w is not None else None, ws[1], _stream()), "conv_dgrad")
+    return out
+
+
+def conv_wgrad(x, dy, K, R, S, stride, pad):
+    N, H, W, C = x.shape
+    d, dref, ws, Ho, Wo = _desc(N, H, W, C, K, R, S, stride, pad, _dt(x))
+    dw = torch.empty((K, C, R, S), dtype=torch.float32, device=x.device)
+    w = workspace(ws[2], x.device)
+    check(lib.b200_conv_wgrad(dref, x.data_ptr(), dy.data_ptr(), dw.data_ptr(), w.data_ptr(), ws[2], _stream()),
+          "conv_wgrad")
+    return dw
+
+
+# ------------------------------------------------------------------ batch norm
+def _bn_ws(rows, C, device):
+    n = int(lib.b200_bn_workspace_bytes(rows, C))
+    return workspace(n, device), n
+
+
+def bn_train_stats(x, gamma, beta, running_mean, running_var, momentum, eps):
+    """x: [..., C] NHWC. Returns (mean, invstd, scale, shift), all fp32 [C]; updates running stats in place."""
+    C = x.shape[-1]
+    rows = x.numel() // C
+    st = torch.empty((4, C), dtype=torch.float32, device=x.device)
+    ws, n = _bn_ws(rows, C, x.device)
+    check(lib.b200_bn_train_stats(
+        x.data_ptr(), rows, C, _dt(x), gamma.data_ptr() if gamma is not None else None,
+        beta.data_ptr() if beta is not None else None,
+        running_mean.data_ptr() if running_mean is not None else None,
+        running_var.data_ptr() if running_var is not None else None,
+        float(momentum), float(eps), st[0].data_ptr(), st[1].data_ptr(), st[2].data_ptr(), st[3].data_ptr(),
+        ws.data_ptr(), n, _stream()), "bn_train_stats")
+    return st[0], st[1], st[2], st[3]
+
+
+def bn_eval_coeffs(gamma, beta, running_mean, running_var, eps):
+    C = running_mean.numel()
+    st = torch.empty((2, C), dtype=torch.float32, device=running_mean.device)
+    check(lib.b200_bn_eval_coeffs(gamma.data_ptr() if gamma is not None else None,
+                                  beta.data_ptr() if beta is not None else None, running_mean.data_ptr(),
+                                  running_var.data_ptr(), float(eps), st[0].data_ptr(), st[1].data_ptr(), C, _stream()),
+          "bn_eval_coeffs")
+    return st[0], st[1]
+
+
+def bn_apply(x, scale, shift, relu, residual=None, out=None):
+    C = x.shape[-1]
+    rows = x.numel() // C
+    y = torch.empty_like(x) if out is None else out
+    check(lib.b200_bn_apply(x.data_ptr(), residual.data_ptr() if residual is not None else None, y.data_ptr(), rows, C,
+                            _dt(x), scale.data_ptr(), shift.data_ptr(), 1 if relu else 0, _stream()), "bn_apply")
+    return y
+
+
+def bn_backward(dz, z, x, gamma, mean, invstd, relu, want_dres=False, want_param_grads=True):
+    C = x.shape[-1]
+    rows = x.numel() // C
+    dx = torch.empty_like(x)
+    dres = torch.empty_like(x) if want_dres else None
+    pg = torch.empty((2, C), dtype=torch.float32, device=x.device) if want_param_grads else None
+    ws, n = _bn_ws(rows, C, x.device)
+    check(lib.b200_bn_backward(
+        dz.data_ptr(), z.data_ptr() if z is not None else None, x.data_ptr(), dx.data_ptr(),
+        dres.data_ptr() if dres is not None else None, rows, C, _dt(x),
+        gamma.data_ptr() if gamma is not None else None, mean.data_ptr(), invstd.data_ptr(), 1 if relu else 0,
+        pg[0].data_ptr() if pg is not None else None, pg[1].data_ptr() if pg is not None else None,
+        ws.data_ptr(), n, _stream()), "bn_backward")
+    if pg is None:
+        return dx, dres, None, None
+    return dx, dres, pg[0], pg[1]
+
+
+def add(a, b):
+    y = torch.empty_like(a)
+    check(lib.b200_add(a.data_ptr(), b.data_ptr(), y.data_ptr(), a.numel(), _dt(a), _stream()), "add")
+    return y
+
+
+def relu_bwd(dz, z):
+    dx = torch.empty_like(dz)
+    check(lib.b200_relu_bwd(dz.data_ptr(), z.data_ptr(), dx.data_ptr(), dz.numel(), _dt(dz), _stream()), "relu_bwd")
+    return dx
+
+
+# ------------------------------------------------------------------ pooling
+def maxpool_fwd(x, want_index):
+    N, H, W, C = x.shape
+    Ho, Wo = (H - 1) // 2 + 1, (W - 1) // 2 + 1
+    y = torch.empty((N, Ho, Wo, C), dtype=x.dtype, device=x.device)
+    idx = torch.empty((N, Ho, Wo, C), dtype=torch.uint8, device=x.device) if want_index else None
+    check(lib.b200_maxpool3x3s2_fwd(x.data_ptr(), y.data_ptr(), idx.data_ptr() if idx is not None else None, N, H, W, C,
+                                    _dt(x), _stream()), "maxpool_fwd")
+    return y, idx
+
+
+def maxpool_bwd(dy, idx, x_shape):
+    N, H, W, C = x_shape
+    dx = torch.empty((N, H, W, C), dtype=dy.dtype, device=dy.device)
+    check(lib.b200_maxpool3x3s2_bwd(dy.data_ptr(), idx.data_ptr(), dx.data_ptr(), N, H, W, C, _dt(dy), _stream()),
+          "maxpool_bwd")
+    return dx
+
+
+def avgpool_fwd(x):
+    N, H, W, C = x.shape
+    y = torch.empty((N, C), dtype=torch.float32, device=x.device)
+    check(lib.b200_avgpool_fwd(x.data_ptr(), y.data_ptr(), N, H * W, C, _dt(x), _stream()), "avgpool_fwd")
+    return y
+
+
+def avgpool_bwd(dy, x_shape, dtype):
+    N, H, W, C = x_shape
+    dx = torch.empty((N, H, W, C), dtype=dtype, device=dy.device)
+    check(lib.b200_avgpool_bwd(dy.data_ptr(), dx.data_ptr(), N, H * W, C, _DT[dtype], _stream()), "avgpool_bwd")
+    return dx
+
+
+# ------------------------------------------------------------------ head (fp32 matrices)
+def gemm_f32(A, B, M, N, K, lda, ldb, a_mn, b_mn, bias=None, relu=False, out=None, accumulate=False):
+    C = torch.empty((M, N), dtype=torch.float32, device=A.device) if out is None else out
+    check(lib.b200_gemm_f32(A.data_ptr(), B.data_ptr(), C.data_ptr(), M, N, K, lda, ldb, N, 1 if a_mn else 0,
+                            1 if b_mn else 0, bias.data_ptr() if bias is not None else None, 1 if relu else 0,
+                            1 if accumulate else 0, _stream()), "gemm_f32")
+    return C
+
+
+def linear_fwd(x, w, b, relu=False):
+    """y[M,N] = x[M,K] @ w[N,K]^T + b   (nn.Linear; head at ...on_image.ipynb:439-442)"""
+    M, K = x.shape
+    N = w.shape[0]
+    return gemm_f32(x, w, M, N, K, K, K, False, False, bias=b, relu=relu)
+
+
+def linear_bwd_input(dy, w):
+    """dx[M,K] = dy[M,N] @ w[N,K]"""
+    M, N = dy.shape
+    K = w.shape[1]
+    return gemm_f32(dy, w, M, K, N, N, K, False, True)
+
+
+def linear_bwd_weight(dy, x):
+    """dw[N,K] = dy[M,N]^T @ x[M,K]"""
+    M, N = dy.shape
+    K = x.shape[1]
+    return gemm_f32(dy, x, N, K, M, N, K, True, True)
+
+
+def colsum(dy):
+    M, N = dy.shape
+    db = torch.empty((N,), dtype=torch.float32, device=dy.device)
+    check(lib.b200_colsum_f32(dy.data_ptr(), db.data_ptr(), M, N, _stream()), "colsum")
+    return db
+
+
+def relu_fwd(x):
+    y = torch.empty_like(x)
+    check(lib.b200_relu_fwd_f32(x.data_ptr(), y.data_ptr(), x.numel(), _stream()), "relu_fwd")
+    return y
+
+
+def dropout_fwd(x, p, seed, offset):
+    y = torch.empty_like(x)
+    mask = torch.empty(x.shape, dtype=torch.uint8, device=x.device)
+    check(lib.b200_dropout_fwd(x.data_ptr(), y.data_ptr(), mask.data_ptr(), x.numel(), float(p), seed, offset,
+                               _stream()), "dropout_fwd")
+    return y, mask
+
+
+def dropout_bwd(dy, mask, p):
+    dx = torch.empty_like(dy)
+    check(lib.b200_dropout_bwd(dy.data_ptr(), mask.data_ptr(), dx.data_ptr(), dy.numel(), float(p), _stream()),
+          "dropout_bwd")
+    return dx
+
+
+def log_softmax_fwd(x):
+    rows, cols = x.shape
+    y = torch.empty_like(x)
+    check(lib.b200_log_softmax_fwd(x.data_ptr(), y.data_ptr(), rows, cols, _stream()), "log_softmax_fwd")
+    return y
+
+
+def log_softmax_bwd(dy, y):
+    rows, cols = y.shape
+    dx = torch.empty_like(y)
+    check(lib.b200_log_softmax_bwd(dy.data_ptr(), y.data_ptr(), dx.data_ptr(), rows, cols, _stream()),
+          "log_softmax_bwd")
+    return dx
+
+
+def nll_loss_fwd(logp, labels):
+    rows, cols = logp.shape
+    loss = torch.empty((), dtype=torch.float32, device=logp.device)
+    check(lib.b200_nll_loss_fwd(logp.data_ptr(), labels.data_ptr(), loss.data_ptr(), rows, cols, _stream()),
+          "nll_loss_fwd")
+    return loss
+
+
+def nll_loss_bwd(dloss, labels, rows, cols):
+    d = torch.empty((rows, cols), dtype=torch.float32, device=labels.device)
+    check(lib.b200_nll_loss_bwd(dloss.data_ptr(), labels.data_ptr(), d.data_ptr(), rows, cols, _stream()),
+          "nll_loss_bwd")
+    return d

@@ -1,0 +1,32 @@
+"""Gradient utilities with torch.nn.utils signatures."""
+import torch
+
+from ._C import lib, check, ptr_array, i64_array
+
+
+def clip_grad_norm_(parameters, max_norm, norm_type=2.0):
+    """`torch.nn.utils.clip_grad_norm_(model.parameters(), 1.0)` (pytorch_on_language_distr.py:273): global L2 norm
+    over all gradients (deterministic two-stage reduction), then an in-place scale by min(1, max_norm/(norm+1e-6)).
+    The scale is read on the device: no host synchronisation.  Returns the total norm as a 0-d tensor."""
+    if isinstance(parameters, torch.Tensor):
+        parameters = [parameters]
+    if float(norm_type) != 2.0:
+        raise NotImplementedError("b200net clip_grad_norm_: L2 norm only")
+    grads = [p.grad for p in parameters if p.grad is not None]
+    if not grads:
+        return torch.tensor(0.0)
+    for g in grads:
+        if not g.is_cuda or g.dtype != torch.float32 or not g.is_contiguous():
+            raise RuntimeError("b200net clip_grad_norm_: gradients must be contiguous float32 CUDA tensors")
+    dev = grads[0].device
+    st = torch.cuda.current_stream().cuda_stream
+    nbytes = int(lib.b200_l2norm_workspace_bytes())
+    ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    norm_sq = torch.empty(1, dtype=torch.float32, device=dev)
+    ptrs = ptr_array([g.data_ptr() for g in grads])
+    sizes = i64_array([g.numel() for g in grads])
+    check(lib.b200_multi_tensor_l2norm_sq(len(grads), ptrs, sizes, norm_sq.data_ptr(), ws.data_ptr(), nbytes, st),
+          "l2norm")
+    check(lib.b200_multi_tensor_clip_scale(len(grads), ptrs, sizes, norm_sq.data_ptr(), float(max_norm), st),
+          "clip_scale")
+    return norm_sq.sqrt().reshape(())
