@@ -1,0 +1,278 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the hot path (BASELINE.json):
+
+    ResNet-50 training step (all layers trainable, SGD lr 0.001, NLL loss -- resnet.py:17-25 recipe on the torchvision
+    graph the reference uses at pytorch_training_inference_on_image.ipynb:389), bf16 tensor-core mode,
+    batch 256 per GPU, synthetic Imagenette-shaped input 3x160x160 (configs[1]); weak scaling under
+    b200net.parallel.DistributedDataParallel for --gpus > 1 (configs[2]).
+
+    python bench.py --gpus N --steps K --warmup W            # our arm (one JSON line from rank 0)
+    python bench.py --impl reference --gpus N ...            # the reference's CPU path on the host cores
+
+value  : images/s, whole job, inputs resident in HBM when the timed region starts (CUDA events, max over ranks)
+e2e    : the reference's loop verbatim -- inputs.to(device) from pinned host memory and loss.item() every step
+roofline: the tcgen05 conv/GEMM kernel family, algorithmic FLOPs (12.398 GFLOP/img) over the
+         summed per-launch CUDA-event durations of that kernel, against the measured sustained bf16 peak
+cpu_baseline: the oracle (stock torch CPU fp32, the reference's statements) on a bounded sample, rank 0, N=1 only
+"""
+import argparse
+import json
+import os
+import statistics
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "resnet50_train_images_per_sec"
+UNIT = "img/s"
+PER_GPU_BATCH = 256
+HW = 160
+GFLOP_PER_IMG_TRAIN = 12.398     # BASELINE.md section 3 / SURVEY 8(d): fwd + dgrad + wgrad, no stem dgrad
+CPU_SAMPLE_BATCH = 32            # configs[0] batch: the reference's own CPU-runnable case
+WORKLOAD = ("resnet50 train step (Mode A: all layers trainable, SGD 0.001, NLL), batch %d/GPU, 3x%dx%d "
+            "(BASELINE.json configs[1]; DDP = configs[2] when n_gpus > 1)")
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return {"tflops": d.get("bf16_tflops_sustained", d.get("bf16_tflops")), "hbm": d.get("hbm_gbs"), "src": "measured"}
+    return {"tflops": 1400.0, "hbm": 6650.0, "src": "fallback"}
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons of one GPU through NVML while the timed region runs."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index = index
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop_evt = threading.Event()
+
+    def run(self):
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            names = {
+                getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8): "hw_slowdown",
+                getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+                getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+                getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
+                getattr(nv, "nvmlClocksEventReasonHwPowerBrakeSlowdown", 0x80): "hw_power_brake",
+            }
+            while not self._stop_evt.is_set():
+                self.samples.append(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+                except Exception:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+                time.sleep(0.05)
+        except Exception as e:  # NVML unavailable: report that instead of inventing numbers
+            self.reasons.add("nvml_unavailable:%s" % type(e).__name__)
+
+    def stop(self):
+        self._stop_evt.set()
+        self.join(timeout=2)
+        return {"sm_mhz": statistics.median(self.samples) if self.samples else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons)}
+
+
+def cpu_reference_run(steps, warmup, batch=CPU_SAMPLE_BATCH):
+    """The reference's training-step statements on stock torch CPU fp32, all host threads."""
+    import torch
+    from oracle import torch_oracle as O
+    cores = O.cpu_threads()
+    torch.set_num_threads(cores)
+    model = O.build_reference_model(dropout=True)
+    opt, crit = O.mode_a(model)
+    model.train()
+    x, y = O.make_batch(batch, HW, 0)
+    for _ in range(warmup):
+        O.train_step(model, opt, crit, x, y)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        O.train_step(model, opt, crit, x, y)
+    dt = time.perf_counter() - t0
+    return batch * steps / dt, dt / steps * 1e3, cores
+
+
+def run_reference(args, rank):
+    if rank != 0:
+        return
+    ips, ms, cores = cpu_reference_run(args.steps, args.warmup)
+    sample = ("stock torch %s CPU fp32 executing the reference train-step statements "
+              "(pytorch_training_inference_on_image.ipynb:667-673, all layers trainable, SGD 0.001); each step = "
+              "%d images of the %dx3x%dx%d workload" % (__import__("torch").__version__, CPU_SAMPLE_BATCH,
+                                                         PER_GPU_BATCH, HW, HW))
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": ips, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD % (PER_GPU_BATCH, HW, HW), "cpu_sample_batch": CPU_SAMPLE_BATCH},
+        "cpu_baseline": {"value": ips, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": ips, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200net", choices=["b200net", "reference"])
+    ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--batch", type=int, default=PER_GPU_BATCH)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--local_rank", type=int, default=0)     # torch.distributed.launch compatibility
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", str(args.local_rank)))
+
+    if args.impl == "reference":
+        return run_reference(args, rank)
+
+    import torch
+    import torch.distributed as dist
+    import b200net
+    from oracle import torch_oracle as O   # data generator + head definition only (checker infrastructure)
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (b200net has no CPU fallback)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    distributed = world > 1
+    if distributed:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    b200net.set_precision(args.precision)
+    torch.manual_seed(O.SEED_WEIGHTS)
+    model = b200net.models.resnet50(pretrained=False)
+    model.fc = b200net.nn.Sequential(b200net.nn.Linear(2048, 512), b200net.nn.ReLU(), b200net.nn.Dropout(0.2),
+                                     b200net.nn.Linear(512, 10), b200net.nn.LogSoftmax(dim=1))
+    model.to(dev).train()
+    criterion = b200net.nn.NLLLoss()
+    optimizer = b200net.optim.SGD(model.parameters(), lr=0.001)
+    if distributed:
+        model = b200net.parallel.DistributedDataParallel(model, device_ids=[local_rank], output_device=local_rank)
+
+    B = args.batch
+    x_host, y_host = O.make_batch(B, HW, 1000 + rank)
+    x_host, y_host = x_host.pin_memory(), y_host.pin_memory()
+    x_dev, y_dev = x_host.to(dev), y_host.to(dev)
+
+    def step_resident():
+        optimizer.zero_grad()
+        logps = model.forward(x_dev)
+        loss = criterion(logps, y_dev)
+        loss.backward()
+        optimizer.step()
+        return loss
+
+    def step_e2e():
+        # the reference loop body verbatim (...on_image.ipynb:667-673): H2D copy, step, loss.item()
+        inputs, labels = x_host.to(dev, non_blocking=True), y_host.to(dev, non_blocking=True)
+        optimizer.zero_grad()
+        logps = model.forward(inputs)
+        loss = criterion(logps, labels)
+        loss.backward()
+        optimizer.step()
+        return loss.item()
+
+    def barrier():
+        if distributed:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if distributed:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return ms.item()
+
+    lib = b200net._C.lib
+    for _ in range(max(args.warmup, 3)):
+        step_resident()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    l0 = lib.b200_launch_count()
+    total_ms = timed(step_resident, args.steps)
+    launches = (lib.b200_launch_count() - l0) // max(args.steps, 1)
+    clocks = sampler.stop()
+    for _ in range(2):
+        step_e2e()
+    e2e_ms = timed(step_e2e, args.steps)
+
+    # roofline leg: per-launch CUDA-event timing of the tcgen05 GEMM kernel over 3 extra steps (outside the timed region)
+    import ctypes
+    roof = None
+    if args.precision == "bf16":
+        prof_steps = 3
+        torch.cuda.synchronize()
+        lib.b200_gemm_timing_enable(1)
+        for _ in range(prof_steps):
+            step_resident()
+        torch.cuda.synchronize()
+        ms, n, fl = ctypes.c_double(), ctypes.c_int64(), ctypes.c_double()
+        lib.b200_gemm_timing_read(ctypes.byref(ms), ctypes.byref(n), ctypes.byref(fl))
+        lib.b200_gemm_timing_enable(0)
+        pk = peaks()
+        algo_flops = GFLOP_PER_IMG_TRAIN * 1e9 * B * prof_steps
+        achieved = algo_flops / (ms.value * 1e-3) / 1e12
+        roof = {"bound": "tensor", "kernel": "gemm_sm100_kernel (tcgen05 conv fprop/dgrad/wgrad family)",
+                "achieved": achieved, "peak": pk["tflops"], "unit": "TFLOP/s", "frac": achieved / pk["tflops"],
+                "peak_source": pk["src"] + " sustained bf16", "traffic": None,
+                "launches_per_step": n.value // prof_steps, "kernel_ms_per_step": ms.value / prof_steps,
+                "executed_gemm_tflop_per_step": fl.value / prof_steps / 1e12}
+
+    if rank == 0:
+        ips = world * B * args.steps / (total_ms * 1e-3)
+        e2e_ips = world * B * args.steps / (e2e_ms * 1e-3)
+        out = {
+            "metric": METRIC, "value": ips, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "bf16" if args.precision == "bf16" else "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD % (B, HW, HW),
+                       "global_batch": world * B, "parallelism": "dp%d" % world,
+                       "l2": "per-step working set (saved activations ~6 GB) far exceeds the 126 MB L2; no explicit flush",
+                       "step_tflop": GFLOP_PER_IMG_TRAIN * B / 1e3,
+                       "tensor_util_step": GFLOP_PER_IMG_TRAIN * 1e9 * ips / world / 1e12 / peaks()["tflops"]},
+            "clocks": clocks,
+            "e2e": {"value": e2e_ips, "unit": UNIT, "h2d_bytes_per_step": x_host.numel() * 4 + y_host.numel() * 8,
+                    "d2h_bytes_per_step": 4, "ms_per_step": e2e_ms / args.steps},
+            "gpu_launches": int(launches) * args.steps,
+            "gpu_launches_per_step": int(launches),
+        }
+        if roof:
+            out["roofline"] = roof
+        if world == 1 and not args.no_cpu_baseline:
+            cips, cms, cores = cpu_reference_run(steps=5, warmup=2)
+            out["cpu_baseline"] = {"value": cips, "unit": UNIT, "cores": cores, "kind": "port",
+                                   "sample": "oracle (stock torch CPU fp32, the reference's train-step statements) on "
+                                             "%d images per step of the same workload, 2 warm-up + 5 timed steps"
+                                             % CPU_SAMPLE_BATCH}
+        print(json.dumps(out), flush=True)
+    if distributed:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

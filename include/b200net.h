@@ -31,6 +31,11 @@ enum { B200_F32 = 0, B200_BF16 = 1 };
 
 int32_t b200_version(void);
 const char* b200_last_error(void);
+/* measurement aids (bench.py): kernels launched by this library so far; per-launch CUDA-event timing of the
+ * tcgen05 GEMM kernel (enable -> run -> read sums the launches recorded since enable). */
+int64_t b200_launch_count(void);
+int32_t b200_gemm_timing_enable(int32_t on);
+int32_t b200_gemm_timing_read(double* total_ms, int64_t* launches, double* flops);
 
 /* ------------------------------------------------------------------ layout / packing
  * inputs.to(device) hands the model NCHW fp32 (pytorch_training_inference_on_image.ipynb:667); the first kernel

@@ -35,6 +35,9 @@ _PI64 = POINTER(c_int64)
 SIGNATURES = {
     "b200_version": (I32, []),
     "b200_last_error": (c_char_p, []),
+    "b200_launch_count": (I64, []),
+    "b200_gemm_timing_enable": (I32, [I32]),
+    "b200_gemm_timing_read": (I32, [POINTER(ctypes.c_double), POINTER(c_int64), POINTER(ctypes.c_double)]),
     "b200_nchw_to_nhwc": (I32, [P, P, I32, I32, I32, I32, I32, P]),
     "b200_nhwc_to_nchw": (I32, [P, P, I32, I32, I32, I32, I32, P]),
     "b200_conv_weight_ld": (I32, [I32, I32, I32]),

@@ -240,7 +240,7 @@ static int32_t bn_stats_impl(const T* x, long long rows, int C, const float* gam
   else
     bn_partial_kernel<T, VecTraits<T>::W, false><<<p.nblk, BN_THREADS, 0, st>>>(x, nullptr, nullptr, nullptr, rows, C, p.cx, p.rows_per_block, 0, part);
   bn_finalize_fwd_kernel<<<(C + 127) / 128, 128, 0, st>>>(part, p.nblk, C, (double)rows, gamma, beta, rm, rv, momentum, eps, save_mean, save_invstd, scale, shift);
-  return check_launch("bn_train_stats");
+  return check_launch("bn_train_stats", 2);
 }
 
 template <typename T>
@@ -276,7 +276,7 @@ static int32_t bn_bwd_impl(const T* dz, const T* z, const T* x, T* dx, T* dres, 
   } else {
     bn_bwd_dx_kernel<T, 1><<<ew_grid(rows * C), BN_THREADS, 0, st>>>(dz, z, x, dx, dres, rows * C, C, C, mean, coef, relu);
   }
-  return check_launch("bn_backward");
+  return check_launch("bn_backward", 3);
 }
 
 __global__ void bn_eval_coeffs_kernel(const float* gamma, const float* beta, const float* rm, const float* rv, float eps,

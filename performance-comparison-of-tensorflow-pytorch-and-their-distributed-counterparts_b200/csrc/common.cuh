@@ -21,7 +21,10 @@ inline int32_t fail(int32_t code, const char* fmt, ...) {
   va_end(ap);
   return code;
 }
-inline int32_t check_launch(const char* what) {
+// number of kernels this library has launched (bench.py reports the delta over the timed region)
+long long& launch_counter();
+inline int32_t check_launch(const char* what, int kernels = 1) {
+  launch_counter() += kernels;
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail(B200_CUDA_ERROR, "%s: %s", what, cudaGetErrorString(e));
   return B200_OK;

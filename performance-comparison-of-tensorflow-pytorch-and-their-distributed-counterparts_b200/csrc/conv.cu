@@ -6,6 +6,8 @@
 // path validated by tools/umma_probe.cu replaces the staging for the bf16 3x3 convolutions).
 #include "common.cuh"
 #include "gemm_sm100.cuh"
+#include <vector>
+#include <utility>
 
 namespace b200 {
 int32_t launch_sgemm(const float*, const float*, float*, int, int, int, long long, long long, long long, bool, bool,
@@ -60,6 +62,17 @@ static inline int wgrad_splits(const b200_conv_desc* d, const ConvGeom& g) {
   return (int)s;
 }
 
+// optional per-launch timing of the tcgen05 GEMM (bench.py roofline leg): CUDA events on the launching stream
+struct GemmTiming {
+  bool on = false;
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev;
+  double flops = 0;
+};
+static GemmTiming& gemm_timing() {
+  static GemmTiming t;
+  return t;
+}
+
 static int32_t gemm_bf16_run(const void* A, const void* B, void* C, int M, int N, int K, long long lda, long long ldb,
                              long long ldc, bool a_mn, bool b_mn, int out_dtype, int accumulate, int splits,
                              long long split_stride, cudaStream_t st) {
@@ -71,7 +84,20 @@ static int32_t gemm_bf16_run(const void* A, const void* B, void* C, int M, int N
   p.out.vec_ok = ((reinterpret_cast<uintptr_t>(C) & 15) == 0) && (ldc % (out_dtype == B200_F32 ? 4 : 8) == 0);
   if ((reinterpret_cast<uintptr_t>(A) & 15) || (reinterpret_cast<uintptr_t>(B) & 15) || (lda % 8) || (ldb % 8))
     return fail(B200_UNSUPPORTED, "gemm_bf16: operands must be 16-byte aligned with leading dimensions multiple of 8");
+  GemmTiming& gt = gemm_timing();
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  if (gt.on) {
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    cudaEventRecord(e0, st);
+  }
   int rc = launch_gemm_sm100(p, st);
+  if (gt.on) {
+    cudaEventRecord(e1, st);
+    gt.ev.emplace_back(e0, e1);
+    gt.flops += 2.0 * M * N * K;
+  }
+  launch_counter() += 1;
   if (rc) return fail(B200_CUDA_ERROR, "gemm_bf16: launch failed (code %d: %s)", rc, cudaGetErrorString(cudaGetLastError()));
   return B200_OK;
 }
@@ -199,4 +225,27 @@ extern "C" int32_t b200_gemm_bf16(const void* A, const void* B, void* C, int32_t
   if (int32_t rc = gemm_bf16_run(A, B, ws, M, N, K, lda, ldb, ldc, a_mn != 0, b_mn != 0, B200_F32, 0, splits, slab, st))
     return rc;
   return launch_reduce_plain((const float*)ws, eff, slab, M, N, ldc, C, ldc, out_dtype, accumulate, st);
+}
+
+extern "C" int32_t b200_gemm_timing_enable(int32_t on) {
+  GemmTiming& gt = gemm_timing();
+  for (auto& pr : gt.ev) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
+  gt.ev.clear();
+  gt.flops = 0;
+  gt.on = on != 0;
+  return B200_OK;
+}
+extern "C" int32_t b200_gemm_timing_read(double* total_ms, int64_t* launches, double* flops) {
+  GemmTiming& gt = gemm_timing();
+  double ms = 0;
+  for (auto& pr : gt.ev) {
+    if (cudaEventSynchronize(pr.second) != cudaSuccess) return fail(B200_CUDA_ERROR, "gemm_timing_read: event sync failed");
+    float t = 0;
+    cudaEventElapsedTime(&t, pr.first, pr.second);
+    ms += t;
+  }
+  if (total_ms) *total_ms = ms;
+  if (launches) *launches = (int64_t)gt.ev.size();
+  if (flops) *flops = gt.flops;
+  return B200_OK;
 }

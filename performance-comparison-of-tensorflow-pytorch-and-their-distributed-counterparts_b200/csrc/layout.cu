@@ -194,7 +194,7 @@ int32_t launch_im2col(const void* x, void* col, int dtype, int N, int H, int W, 
       im2col_kernel<__nv_bfloat16, 1><<<grid_for(M * R * S * C), 256, 0, st>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)col, N, H, W, C, R, S, stride, pad, Ho, Wo, ld);
     if (ld > R * S * C) im2col_pad_kernel<__nv_bfloat16><<<grid_for(M * (ld - R * S * C)), 256, 0, st>>>((__nv_bfloat16*)col, M, R * S * C, ld);
   }
-  return check_launch("im2col");
+  return check_launch("im2col", ld > R * S * C ? 2 : 1);
 }
 int32_t launch_col2im(const float* dcol, void* dx, int dtype, int N, int H, int W, int C, int R, int S, int stride,
                       int pad, int Ho, int Wo, int ld, int accumulate, cudaStream_t st) {

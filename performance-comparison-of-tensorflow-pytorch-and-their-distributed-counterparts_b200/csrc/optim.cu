@@ -136,6 +136,7 @@ using namespace b200;
   for (int lo = 0; lo < (n_); lo += MT_MAX) {              \
     const int hi = lo + MT_MAX < (n_) ? lo + MT_MAX : (n_); \
     const int cnt = hi - lo;                               \
+    ++nlaunch;                                             \
     MtArgs t;                                              \
     __VA_ARGS__                                            \
   }
@@ -148,6 +149,7 @@ extern "C" int32_t b200_multi_tensor_sgd(int32_t n, float* const* params, const 
   if (momentum != 0.f && !momentum_bufs) return fail(B200_INVALID_ARG, "sgd: momentum needs buffers");
   cudaStream_t st = as_stream(stream);
   SgdHyper h{lr, momentum, dampening, weight_decay, grad_scale, nesterov, first_step, momentum != 0.f};
+  int nlaunch = 0;
   MT_FOREACH_CHUNK(n, {
     for (int i = 0; i < cnt; ++i) {
       t.a[i] = params[lo + i]; t.b[i] = (void*)grads[lo + i]; t.c[i] = h.has_mom ? momentum_bufs[lo + i] : nullptr;
@@ -155,7 +157,7 @@ extern "C" int32_t b200_multi_tensor_sgd(int32_t n, float* const* params, const 
     }
     mt_sgd_kernel<<<dim3(mt_blocks(sizes, lo, hi, 2 * num_sms()), cnt), MT_THREADS, 0, st>>>(t, h);
   })
-  return check_launch("multi_tensor_sgd");
+  return check_launch("multi_tensor_sgd", nlaunch);
 }
 
 extern "C" int32_t b200_multi_tensor_adam(int32_t n, float* const* params, const float* const* grads,
@@ -168,6 +170,7 @@ extern "C" int32_t b200_multi_tensor_adam(int32_t n, float* const* params, const
   const double bc1 = 1.0 - pow((double)beta1, (double)step);
   const double bc2 = 1.0 - pow((double)beta2, (double)step);
   AdamHyper h{lr, beta1, beta2, eps, weight_decay, (float)((double)lr / bc1), (float)sqrt(bc2), grad_scale, decoupled_wd};
+  int nlaunch = 0;
   MT_FOREACH_CHUNK(n, {
     for (int i = 0; i < cnt; ++i) {
       t.a[i] = params[lo + i]; t.b[i] = (void*)grads[lo + i]; t.c[i] = exp_avg[lo + i]; t.d[i] = exp_avg_sq[lo + i];
@@ -175,7 +178,7 @@ extern "C" int32_t b200_multi_tensor_adam(int32_t n, float* const* params, const
     }
     mt_adam_kernel<<<dim3(mt_blocks(sizes, lo, hi, 2 * num_sms()), cnt), MT_THREADS, 0, st>>>(t, h);
   })
-  return check_launch("multi_tensor_adam");
+  return check_launch("multi_tensor_adam", nlaunch);
 }
 
 constexpr int L2_BLOCKS = 32;
@@ -189,34 +192,37 @@ extern "C" int32_t b200_multi_tensor_l2norm_sq(int32_t n, const float* const* te
   if ((long long)n * L2_BLOCKS > L2_MAX_PARTIALS) return fail(B200_UNSUPPORTED, "l2norm: more than %d tensors", L2_MAX_PARTIALS / L2_BLOCKS);
   cudaStream_t st = as_stream(stream);
   int base = 0;
+  int nlaunch = 0;
   MT_FOREACH_CHUNK(n, {
     for (int i = 0; i < cnt; ++i) { t.a[i] = (void*)tensors[lo + i]; t.b[i] = t.c[i] = t.d[i] = nullptr; t.n[i] = sizes[lo + i]; }
     mt_sumsq_kernel<<<dim3(L2_BLOCKS, cnt), MT_THREADS, 0, st>>>(t, (float*)ws, base);
     base += cnt * L2_BLOCKS;
   })
   sum_partials_kernel<<<1, 1024, 0, st>>>((const float*)ws, base, out);
-  return check_launch("multi_tensor_l2norm_sq");
+  return check_launch("multi_tensor_l2norm_sq", nlaunch + 1);
 }
 
 extern "C" int32_t b200_multi_tensor_clip_scale(int32_t n, float* const* tensors, const int64_t* sizes,
                                                 const float* norm_sq, float max_norm, void* stream) {
   if (n <= 0 || !tensors || !sizes || !norm_sq) return fail(B200_INVALID_ARG, "clip_scale: bad arguments");
   cudaStream_t st = as_stream(stream);
+  int nlaunch = 0;
   MT_FOREACH_CHUNK(n, {
     for (int i = 0; i < cnt; ++i) { t.a[i] = tensors[lo + i]; t.b[i] = t.c[i] = t.d[i] = nullptr; t.n[i] = sizes[lo + i]; }
     mt_clip_kernel<<<dim3(mt_blocks(sizes, lo, hi, 2 * num_sms()), cnt), MT_THREADS, 0, st>>>(t, norm_sq, max_norm);
   })
-  return check_launch("multi_tensor_clip_scale");
+  return check_launch("multi_tensor_clip_scale", nlaunch);
 }
 
 extern "C" int32_t b200_multi_tensor_zero(int32_t n, float* const* tensors, const int64_t* sizes, void* stream) {
   if (n <= 0 || !tensors || !sizes) return fail(B200_INVALID_ARG, "zero: bad arguments");
   cudaStream_t st = as_stream(stream);
+  int nlaunch = 0;
   MT_FOREACH_CHUNK(n, {
     for (int i = 0; i < cnt; ++i) { t.a[i] = tensors[lo + i]; t.b[i] = t.c[i] = t.d[i] = nullptr; t.n[i] = sizes[lo + i]; }
     mt_zero_kernel<<<dim3(mt_blocks(sizes, lo, hi, 2 * num_sms()), cnt), MT_THREADS, 0, st>>>(t);
   })
-  return check_launch("multi_tensor_zero");
+  return check_launch("multi_tensor_zero", nlaunch);
 }
 
 extern "C" int32_t b200_bucket_pack(int32_t n, const float* const* srcs, const int64_t* sizes, float* flat, float scale,
@@ -224,6 +230,7 @@ extern "C" int32_t b200_bucket_pack(int32_t n, const float* const* srcs, const i
   if (n <= 0 || !srcs || !sizes || !flat) return fail(B200_INVALID_ARG, "bucket_pack: bad arguments");
   cudaStream_t st = as_stream(stream);
   long long off = 0;
+  int nlaunch = 0;
   MT_FOREACH_CHUNK(n, {
     for (int i = 0; i < cnt; ++i) {
       t.a[i] = flat + off; t.b[i] = (void*)srcs[lo + i]; t.c[i] = t.d[i] = nullptr; t.n[i] = sizes[lo + i];
@@ -231,7 +238,7 @@ extern "C" int32_t b200_bucket_pack(int32_t n, const float* const* srcs, const i
     }
     mt_copy_scale_kernel<<<dim3(mt_blocks(sizes, lo, hi, 2 * num_sms()), cnt), MT_THREADS, 0, st>>>(t, scale);
   })
-  return check_launch("bucket_pack");
+  return check_launch("bucket_pack", nlaunch);
 }
 
 extern "C" int32_t b200_bucket_unpack(int32_t n, float* const* dsts, const int64_t* sizes, const float* flat,
@@ -239,6 +246,7 @@ extern "C" int32_t b200_bucket_unpack(int32_t n, float* const* dsts, const int64
   if (n <= 0 || !dsts || !sizes || !flat) return fail(B200_INVALID_ARG, "bucket_unpack: bad arguments");
   cudaStream_t st = as_stream(stream);
   long long off = 0;
+  int nlaunch = 0;
   MT_FOREACH_CHUNK(n, {
     for (int i = 0; i < cnt; ++i) {
       t.a[i] = dsts[lo + i]; t.b[i] = (void*)(flat + off); t.c[i] = t.d[i] = nullptr; t.n[i] = sizes[lo + i];
@@ -246,8 +254,15 @@ extern "C" int32_t b200_bucket_unpack(int32_t n, float* const* dsts, const int64
     }
     mt_copy_scale_kernel<<<dim3(mt_blocks(sizes, lo, hi, 2 * num_sms()), cnt), MT_THREADS, 0, st>>>(t, scale);
   })
-  return check_launch("bucket_unpack");
+  return check_launch("bucket_unpack", nlaunch);
 }
 
+namespace b200 {
+long long& launch_counter() {
+  static long long n = 0;
+  return n;
+}
+}  // namespace b200
+extern "C" int64_t b200_launch_count(void) { return b200::launch_counter(); }
 extern "C" int32_t b200_version(void) { return 100; }
 extern "C" const char* b200_last_error(void) { return last_error_buf(); }

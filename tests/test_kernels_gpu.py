@@ -1,0 +1,316 @@
+"""Per-kernel parity on the GPU, through the C-ABI (b200net.ops -> ctypes -> libb200net.so), against stock torch
+in float64 on the same seeded inputs.  Shapes follow SURVEY.md 8(a') (conv classes S,a,b,c,f,h,l,...) at small N,
+plus odd sizes.  Tolerances: fp32 path 2e-5 of the output scale (FFMA, different summation order only);
+bf16 path 2e-2 of the output scale (bf16 storage of the result, fp32 accumulation)."""
+import math
+
+import pytest
+import torch
+import torch.nn.functional as TF
+
+pytestmark = pytest.mark.gpu
+
+DT = {"fp32": torch.float32, "bf16": torch.bfloat16}
+TOL = {"fp32": 2e-5, "bf16": 2e-2}
+
+
+def _dev():
+    return torch.device("cuda:0")
+
+
+def _rel(a, b):
+    a, b = a.double(), b.double()
+    return ((a - b).abs().max() / b.abs().max().clamp_min(1e-30)).item()
+
+
+def _nhwc(t, dtype):
+    return t.permute(0, 2, 3, 1).contiguous().to(dtype)
+
+
+def _rand(shape, dtype, seed, scale=1.0):
+    g = torch.Generator().manual_seed(seed)
+    return (torch.randn(shape, generator=g) * scale).to(dtype).to(_dev())
+
+
+# ---------------------------------------------------------------------------------------------- layout
+def test_layout_roundtrip():
+    from b200net import ops
+    for C, H, W in ((3, 17, 23), (64, 9, 10), (130, 5, 7)):
+        x = torch.rand(2, C, H, W, device=_dev())
+        for dt in DT.values():
+            y = ops.to_nhwc(x, dt)
+            assert y.shape == (2, H, W, C)
+            assert torch.equal(y, x.permute(0, 2, 3, 1).to(dt))
+            assert torch.equal(ops.to_nchw(y), x.to(dt).float())
+
+
+# ---------------------------------------------------------------------------------------------- GEMM
+@pytest.mark.parametrize("a_mn,b_mn", [(0, 0), (0, 1), (1, 0), (1, 1)])
+@pytest.mark.parametrize("M,N,K", [(128, 128, 64), (300, 200, 136), (33, 10, 520), (1000, 72, 4100)])
+def test_gemm_f32(a_mn, b_mn, M, N, K):
+    from b200net import ops
+    A = _rand((M, K), torch.float32, 1)
+    B = _rand((N, K), torch.float32, 2)
+    bias = _rand((N,), torch.float32, 3)
+    As = A.t().contiguous() if a_mn else A
+    Bs = B.t().contiguous() if b_mn else B
+    ref = A.double() @ B.double().t()
+    C = ops.gemm_f32(As, Bs, M, N, K, As.shape[1], Bs.shape[1], a_mn, b_mn)
+    assert _rel(C, ref) < 2e-6 * math.sqrt(K)
+    C2 = ops.gemm_f32(As, Bs, M, N, K, As.shape[1], Bs.shape[1], a_mn, b_mn, bias=bias, relu=True)
+    assert _rel(C2, torch.relu(ref + bias.double())) < 2e-6 * math.sqrt(K)
+    C3 = C.clone()
+    ops.gemm_f32(As, Bs, M, N, K, As.shape[1], Bs.shape[1], a_mn, b_mn, out=C3, accumulate=True)
+    assert _rel(C3, 2 * ref) < 2e-6 * math.sqrt(K)
+
+
+@pytest.mark.parametrize("a_mn,b_mn", [(0, 0), (0, 1), (1, 0), (1, 1)])
+@pytest.mark.parametrize("M,N,K,splits", [(256, 256, 512, 1), (300, 200, 136, 1), (64, 576, 6000, 9), (1000, 72, 264, 2)])
+def test_gemm_bf16_tcgen05(a_mn, b_mn, M, N, K, splits):
+    """tcgen05.mma + TMA + TMEM GEMM through the C-ABI, every operand major-ness, M/N/K tails, split-K."""
+    import b200net
+    from b200net._C import lib, check
+    pad8 = lambda v: (v + 7) // 8 * 8
+    A = _rand((M, K), torch.bfloat16, 1)
+    B = _rand((N, K), torch.bfloat16, 2)
+    ref = A.double() @ B.double().t()
+
+    def store(X, mn):  # leading dimensions padded to multiples of 8 elements (16-byte TMA strides)
+        rows, cols = (X.shape[1], X.shape[0]) if mn else X.shape
+        buf = torch.zeros((rows, pad8(cols)), dtype=torch.bfloat16, device=_dev())
+        buf[:, :cols] = X.t() if mn else X
+        return buf
+
+    As, Bs = store(A, a_mn), store(B, b_mn)
+    ldc = pad8(N)
+    st = torch.cuda.current_stream().cuda_stream
+    for out_dtype, tdt, tol in ((0, torch.float32, 1e-5 * math.sqrt(K)), (1, torch.bfloat16, 1e-2)):
+        C = torch.full((M, ldc), float("nan"), dtype=tdt, device=_dev())
+        ws = torch.empty(max(1, splits) * M * ldc * 4 + 16, dtype=torch.uint8, device=_dev())
+        check(lib.b200_gemm_bf16(As.data_ptr(), Bs.data_ptr(), C.data_ptr(), M, N, K, As.shape[1], Bs.shape[1], ldc,
+                                 a_mn, b_mn, out_dtype, 0, splits, ws.data_ptr(), ws.numel(), st), "gemm_bf16")
+        assert _rel(C[:, :N], ref) < tol
+        check(lib.b200_gemm_bf16(As.data_ptr(), Bs.data_ptr(), C.data_ptr(), M, N, K, As.shape[1], Bs.shape[1], ldc,
+                                 a_mn, b_mn, out_dtype, 1, splits, ws.data_ptr(), ws.numel(), st), "gemm_bf16 acc")
+        assert _rel(C[:, :N], 2 * ref) < 2 * tol
+
+
+# ---------------------------------------------------------------------------------------------- convolution
+CONV_CASES = [
+    # N, H, C, K, R, stride, pad        (SURVEY 8(a') class)
+    (2, 40, 3, 64, 7, 2, 3),     # S  stem (C=3, K-dim 147 -> padded 152)
+    (2, 20, 64, 64, 1, 1, 0),    # a  1x1
+    (2, 20, 64, 64, 3, 1, 1),    # b  3x3
+    (2, 20, 64, 256, 1, 1, 0),   # c
+    (3, 20, 128, 128, 3, 2, 1),  # f  3x3 stride 2
+    (2, 20, 256, 512, 1, 2, 0),  # h  1x1 stride 2 downsample
+    (2, 10, 256, 256, 3, 1, 1),  # p
+    (4, 5, 512, 2048, 1, 1, 0),  # s  tiny M
+    (1, 21, 64, 72, 3, 2, 1),    # odd H, Cout not a multiple of 64
+    (1, 13, 24, 40, 3, 1, 1),    # small odd channel counts
+]
+
+
+@pytest.mark.parametrize("prec", ["fp32", "bf16"])
+@pytest.mark.parametrize("case", CONV_CASES)
+def test_conv_fprop_dgrad_wgrad(prec, case):
+    from b200net import ops
+    N, H, C, K, R, stride, pad = case
+    dt = DT[prec]
+    x = _rand((N, C, H, H), dt, 11)
+    w = _rand((K, C, R, R), torch.float32, 12, scale=1.0 / math.sqrt(C * R * R))
+    wq = w.to(dt)  # what the kernel sees after packing
+    xd = x.double().requires_grad_(True)
+    wd = wq.double().requires_grad_(True)
+    yref = TF.conv2d(xd, wd, stride=stride, padding=pad)
+    dy = _rand(tuple(yref.shape), dt, 13)
+    yref.backward(dy.double())
+
+    xh = _nhwc(x, dt)
+    wp = ops.pack_weight(w, dt)
+    y = ops.conv_fprop(xh, wp, K, R, R, stride, pad)
+    assert y.shape == (N, yref.shape[2], yref.shape[3], K)
+    tol = TOL[prec]
+    assert _rel(y.permute(0, 3, 1, 2), yref) < tol
+
+    dyh = _nhwc(dy, dt)
+    dx = ops.conv_dgrad(dyh, wp, xh.shape, K, R, R, stride, pad)
+    assert _rel(dx.permute(0, 3, 1, 2), xd.grad) < tol
+    base = _rand(tuple(xh.shape), dt, 14)
+    acc = base.clone()
+    ops.conv_dgrad(dyh, wp, xh.shape, K, R, R, stride, pad, out=acc, accumulate=True)
+    assert _rel(acc.permute(0, 3, 1, 2), xd.grad + base.double().permute(0, 3, 1, 2)) < tol
+
+    dw = ops.conv_wgrad(xh, dyh, K, R, R, stride, pad)
+    assert dw.shape == w.shape and dw.dtype == torch.float32
+    assert _rel(dw, wd.grad) < (1e-4 if prec == "fp32" else 5e-3)
+
+
+# ---------------------------------------------------------------------------------------------- batch norm
+@pytest.mark.parametrize("prec", ["fp32", "bf16"])
+@pytest.mark.parametrize("rows,C", [(2 * 20 * 20, 64), (3 * 7 * 5, 2048), (1000, 24), (50, 130)])
+@pytest.mark.parametrize("relu,residual", [(True, False), (True, True), (False, False)])
+def test_batchnorm_train_fwd_bwd(prec, rows, C, relu, residual):
+    from b200net import ops
+    dt = DT[prec]
+    x = _rand((rows, C), dt, 21, scale=2.0) + 0.5
+    res = _rand((rows, C), dt, 22) if residual else None
+    gamma = _rand((C,), torch.float32, 23).abs() + 0.5
+    beta = _rand((C,), torch.float32, 24)
+    rm = torch.zeros(C, device=_dev())
+    rv = torch.ones(C, device=_dev())
+    mean, invstd, scale, shift = ops.bn_train_stats(x, gamma, beta, rm, rv, 0.1, 1e-5)
+    z = ops.bn_apply(x, scale, shift, relu, res)
+
+    xd = x.double().requires_grad_(True)
+    gd = gamma.double().requires_grad_(True)
+    bd = beta.double().requires_grad_(True)
+    rmd, rvd = torch.zeros(C, dtype=torch.float64, device=_dev()), torch.ones(C, dtype=torch.float64, device=_dev())
+    resd = res.double().requires_grad_(True) if residual else None
+    zr = TF.batch_norm(xd, rmd, rvd, gd, bd, True, 0.1, 1e-5)
+    if residual:
+        zr = zr + resd
+    if relu:
+        zr = torch.relu(zr)
+    tol = TOL[prec] if prec == "bf16" else 1e-5
+    assert _rel(z, zr) < tol
+    assert _rel(mean, xd.mean(0)) < 1e-5 and _rel(invstd, 1 / torch.sqrt(xd.var(0, unbiased=False) + 1e-5)) < 1e-5
+    assert _rel(rm, rmd) < 1e-5 and _rel(rv, rvd) < 1e-5
+
+    dz = _rand((rows, C), dt, 25)
+    # the kernel derives the ReLU mask from ITS OWN saved output z, as the backbone does
+    mask = (z > 0).double() if relu else torch.ones_like(zr)
+    (zr_lin,) = (TF.batch_norm(xd, None, None, gd, bd, True, 0.1, 1e-5),)
+    g = dz.double() * mask
+    zr_lin.backward(g)
+    dx, dres, dgamma, dbeta = ops.bn_backward(dz, z if relu else None, x, gamma, mean, invstd, relu, want_dres=residual)
+    assert _rel(dx, xd.grad) < (tol if prec == "bf16" else 2e-4)
+    assert _rel(dgamma, gd.grad) < 2e-4 and _rel(dbeta, bd.grad) < 2e-4
+    if residual:
+        assert _rel(dres, g) < tol
+
+
+def test_batchnorm_eval_coeffs():
+    from b200net import ops
+    C = 96
+    x = _rand((77, C), torch.float32, 31)
+    gamma, beta = _rand((C,), torch.float32, 32), _rand((C,), torch.float32, 33)
+    rm, rv = _rand((C,), torch.float32, 34), _rand((C,), torch.float32, 35).abs() + 0.1
+    scale, shift = ops.bn_eval_coeffs(gamma, beta, rm, rv, 1e-5)
+    z = ops.bn_apply(x, scale, shift, False)
+    ref = TF.batch_norm(x.double(), rm.double(), rv.double(), gamma.double(), beta.double(), False, 0.1, 1e-5)
+    assert _rel(z, ref) < 1e-5
+
+
+# ---------------------------------------------------------------------------------------------- pooling
+@pytest.mark.parametrize("prec", ["fp32", "bf16"])
+@pytest.mark.parametrize("N,H,W,C", [(2, 80, 80, 64), (1, 7, 9, 24), (3, 6, 6, 8)])
+def test_maxpool_avgpool(prec, N, H, W, C):
+    from b200net import ops
+    dt = DT[prec]
+    x = torch.relu(_rand((N, C, H, W), dt, 41))  # post-ReLU input: exact ties at zero, like the stem
+    xd = x.double().requires_grad_(True)
+    yr = TF.max_pool2d(xd, 3, 2, 1)
+    dy = _rand(tuple(yr.shape), dt, 42)
+    yr.backward(dy.double())
+    xh = _nhwc(x, dt)
+    y, idx = ops.maxpool_fwd(xh, True)
+    assert torch.equal(y.permute(0, 3, 1, 2).double(), yr.detach())
+    dx = ops.maxpool_bwd(_nhwc(dy, dt), idx, xh.shape)
+    assert _rel(dx.permute(0, 3, 1, 2), xd.grad) < TOL[prec]
+    a = ops.avgpool_fwd(xh)
+    assert _rel(a, x.double().mean((2, 3))) < 1e-5
+    da = _rand((N, C), torch.float32, 43)
+    dxa = ops.avgpool_bwd(da, xh.shape, dt)
+    assert _rel(dxa, (da.double() / (H * W))[:, None, None, :].expand(N, H, W, C)) < TOL[prec]
+
+
+# ---------------------------------------------------------------------------------------------- head
+def test_head_functions_match_torch():
+    import b200net
+    F = b200net.functional
+    x = _rand((37, 2048), torch.float32, 51).requires_grad_(True)
+    lin1 = torch.nn.Linear(2048, 512).to(_dev())
+    lin2 = torch.nn.Linear(512, 10).to(_dev())
+    labels = torch.randint(0, 10, (37,), device=_dev())
+    h = F.relu(F.linear(x, lin1.weight, lin1.bias))
+    logp = F.log_softmax(F.linear(h, lin2.weight, lin2.bias), 1)
+    loss = F.nll_loss(logp, labels)
+    loss.backward()
+    got = [x.grad.clone(), lin1.weight.grad.clone(), lin1.bias.grad.clone(), lin2.weight.grad.clone(), lin2.bias.grad.clone()]
+    xd = x.detach().double().requires_grad_(True)
+    l1, l2 = torch.nn.Linear(2048, 512).to(_dev()).double(), torch.nn.Linear(512, 10).to(_dev()).double()
+    l1.load_state_dict({k: v.double() for k, v in lin1.state_dict().items()})
+    l2.load_state_dict({k: v.double() for k, v in lin2.state_dict().items()})
+    lr = TF.log_softmax(l2(torch.relu(l1(xd))), 1)
+    lossr = TF.nll_loss(lr, labels)
+    lossr.backward()
+    assert _rel(logp, lr) < 1e-5 and abs(loss.item() - lossr.item()) < 1e-5
+    for a, b in zip(got, [xd.grad, l1.weight.grad, l1.bias.grad, l2.weight.grad, l2.bias.grad]):
+        assert _rel(a, b) < 1e-4
+
+
+def test_dropout_mask_replay_and_rate():
+    import b200net
+    F = b200net.functional
+    x = torch.ones(1 << 20, device=_dev(), requires_grad=True)
+    y = F.dropout(x, 0.2, True)
+    keep = (y > 0).float().mean().item()
+    assert abs(keep - 0.8) < 5e-3
+    assert torch.allclose(y[y > 0], torch.tensor(1.25, device=_dev()))
+    y.sum().backward()
+    assert torch.equal(x.grad > 0, y > 0)          # backward replays the forward mask
+    y2 = F.dropout(x, 0.2, True)
+    assert not torch.equal(y2 > 0, y > 0)          # the Philox offset advances between calls
+    assert F.dropout(x, 0.2, False) is x           # eval mode: identity
+
+
+# ---------------------------------------------------------------------------------------------- optimizers
+def _param_set(seed):
+    g = torch.Generator().manual_seed(seed)
+    shapes = [(64, 3, 7, 7), (64,), (256, 64, 1, 1), (2048, 512), (10,), (1,)] + [(17,)] * 60
+    return [torch.randn(s, generator=g) for s in shapes]
+
+
+@pytest.mark.parametrize("name,kw", [
+    ("SGD", dict(lr=0.001)),
+    ("SGD", dict(lr=0.05, momentum=0.9, weight_decay=1e-4)),
+    ("SGD", dict(lr=0.05, momentum=0.9, nesterov=True)),
+    ("Adam", dict(lr=0.003)),
+    ("Adam", dict(lr=0.003, weight_decay=1e-2)),
+    ("AdamW", dict(lr=2e-5, eps=1e-8, weight_decay=0.0)),
+    ("AdamW", dict(lr=1e-3, weight_decay=0.1)),
+])
+def test_optimizers_match_torch(name, kw):
+    import b200net
+    ours = [torch.nn.Parameter(t.clone().to(_dev())) for t in _param_set(61)]
+    ref = [torch.nn.Parameter(t.clone().double().to(_dev())) for t in _param_set(61)]
+    o1 = getattr(b200net.optim, name)(ours, **kw)
+    o2 = getattr(torch.optim, name)(ref, **kw)
+    for step in range(4):
+        grads = _param_set(100 + step)
+        for p, q, g in zip(ours, ref, grads):
+            p.grad = g.to(_dev())
+            q.grad = g.double().to(_dev())
+        v0 = ours[0]._version
+        o1.step()
+        o2.step()
+        assert ours[0]._version > v0          # packed-weight caches key on the version counter
+    for p, q in zip(ours, ref):
+        assert _rel(p, q) < 1e-5
+
+
+def test_clip_grad_norm():
+    import b200net
+    ours = [torch.nn.Parameter(t.clone().to(_dev())) for t in _param_set(71)]
+    ref = [torch.nn.Parameter(t.clone().to(_dev())) for t in _param_set(71)]
+    for p, q, g in zip(ours, ref, _param_set(72)):
+        p.grad = g.clone().to(_dev())
+        q.grad = g.clone().to(_dev())
+    n1 = b200net.utils.clip_grad_norm_(ours, 1.0)
+    n2 = torch.nn.utils.clip_grad_norm_(ref, 1.0)
+    assert abs(n1.item() - n2.item()) < 1e-4 * n2.item()
+    for p, q in zip(ours, ref):
+        assert _rel(p.grad, q.grad) < 1e-5
+    n3 = b200net.utils.clip_grad_norm_(ours, 1e9)     # below the threshold: untouched
+    assert abs(n3.item() - 1.0) < 1e-3
