@@ -101,6 +101,23 @@ int32_t b200_bn_train_stats(const void* x, int64_t rows, int32_t C, int32_t dtyp
                             const float* beta, float* running_mean, float* running_var, float momentum, float eps,
                             float* save_mean, float* save_invstd, float* scale, float* shift, void* ws,
                             int64_t ws_bytes, void* stream);
+/* Same computation and outputs as b200_bn_train_stats, for callers that have no workspace to give and must not
+ * allocate one.  (No counterpart in the reference: it exists for hosts of this library that cannot call
+ * cudaMalloc -- a serving process whose framework claimed all device memory for its own pool at start-up, or a
+ * latency-bound loop that cannot afford cudaMalloc's device-wide synchronisation.)  The per-block partial sums
+ * live in a 2 MiB array that is part of the library image itself (every GPU that loads the library holds those
+ * 2 MiB until the process exits); the call makes no cudaMalloc / cudaFree / allocating library call.
+ *   limit  : C <= B200_BN_NOALLOC_MAX_C; anything larger is rejected with B200_UNSUPPORTED and a message.
+ *   set-up : the first call on each device looks up the array's device address (cudaGetSymbolAddress), with that
+ *            device current; make that first call before starting any stream capture.
+ *   sharing: every call on a device uses the same array, which keeps whatever the previous call left in it
+ *            (nothing in it has to start at zero: each launch overwrites every slot it later reads).  Two calls
+ *            that overlap on the GPU (different streams, no ordering between them) race on it: serialise them. */
+#define B200_BN_NOALLOC_MAX_C 4096
+int32_t b200_bn_train_stats_noalloc(const void* x, int64_t rows, int32_t C, int32_t dtype, const float* gamma,
+                                    const float* beta, float* running_mean, float* running_var, float momentum,
+                                    float eps, float* save_mean, float* save_invstd, float* scale, float* shift,
+                                    void* stream);
 /* eval mode: scale/shift from running statistics */
 int32_t b200_bn_eval_coeffs(const float* gamma, const float* beta, const float* running_mean,
                             const float* running_var, float eps, float* scale, float* shift, int32_t C, void* stream);

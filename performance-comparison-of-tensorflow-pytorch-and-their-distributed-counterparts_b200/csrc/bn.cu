@@ -364,3 +364,86 @@ extern "C" int32_t b200_relu_bwd(const void* dz, const void* z, void* dx, int64_
   else return fail(B200_INVALID_ARG, "relu_bwd: bad dtype");
   return check_launch("relu_bwd");
 }
+
+// ------------------------------------------------------------------------------------------------------------------
+// Allocation-free variant of b200_bn_train_stats.
+//
+// Some hosts of this library cannot hand us a workspace and cannot allocate one either: a serving process in which
+// the framework took all device memory for its own pool when it started, or a latency-bound loop where the
+// device-wide synchronisation inside cudaMalloc is not acceptable.  For them the per-block partial sums live in the
+// array below, which is part of the library image: each GPU that loads the library carries these 2 MiB until the
+// process exits.  Nothing here calls cudaMalloc, cudaFree or any routine that allocates.
+//
+// `g_bn_noalloc_scratch` names a DEVICE array.  In host code that name is only a handle for the runtime, not an
+// address a kernel can use, so the host side asks the runtime for the real device address once per device
+// (bn_noalloc_scratch_ptr) and passes that pointer to the kernels.
+constexpr size_t BN_NOALLOC_FLOATS = (2u << 20) / sizeof(float);  // 2 MiB
+static __device__ __align__(256) float g_bn_noalloc_scratch[BN_NOALLOC_FLOATS];
+
+namespace b200 {
+
+// Device address of the scratch array for the CURRENT device; looked up on the first call per device.
+// Do that first call before any stream capture begins.
+static int32_t bn_noalloc_scratch_ptr(float** out) {
+  constexpr int MAX_DEV = 64;
+  static float* ptrs[MAX_DEV] = {nullptr};
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return fail(B200_CUDA_ERROR, "bn_train_stats_noalloc: cudaGetDevice: %s", cudaGetErrorString(e));
+  if (dev < 0 || dev >= MAX_DEV) return fail(B200_UNSUPPORTED, "bn_train_stats_noalloc: device index %d out of range", dev);
+  if (!ptrs[dev]) {
+    float* p = nullptr;
+    e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_bn_noalloc_scratch);
+    if (e != cudaSuccess || !p)
+      return fail(B200_CUDA_ERROR, "bn_train_stats_noalloc: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+    ptrs[dev] = p;  // racing first calls store the same value
+  }
+  *out = ptrs[dev];
+  return B200_OK;
+}
+
+template <typename T>
+static int32_t bn_stats_noalloc_impl(const T* x, long long rows, int C, const float* gamma, const float* beta,
+                                     float* rm, float* rv, float momentum, float eps, float* save_mean,
+                                     float* save_invstd, float* scale, float* shift, float* part, cudaStream_t st) {
+  // same kernels as the workspace variant; only the number of row blocks is capped so that the
+  // [nblk][2][C] partial sums fit the fixed array.  Every slot that the finalize kernel reads is written by this
+  // launch, so the contents left behind by an earlier call never matter and nothing needs clearing.
+  BnPlan p = bn_plan<T>(rows, C);
+  const long long max_blk = (long long)(BN_NOALLOC_FLOATS / (2 * (size_t)C));
+  if (p.nblk > max_blk) {
+    const int ry = BN_THREADS / p.cx;
+    long long rpb = (rows + max_blk - 1) / max_blk;
+    rpb = (rpb + ry - 1) / ry * ry;
+    p.rows_per_block = rpb;
+    p.nblk = (int)((rows + rpb - 1) / rpb);
+  }
+  if (p.vec == 1)
+    bn_partial_kernel<T, 1, false><<<p.nblk, BN_THREADS, 0, st>>>(x, nullptr, nullptr, nullptr, rows, C, p.cx, p.rows_per_block, 0, part);
+  else
+    bn_partial_kernel<T, VecTraits<T>::W, false><<<p.nblk, BN_THREADS, 0, st>>>(x, nullptr, nullptr, nullptr, rows, C, p.cx, p.rows_per_block, 0, part);
+  bn_finalize_fwd_kernel<<<(C + 127) / 128, 128, 0, st>>>(part, p.nblk, C, (double)rows, gamma, beta, rm, rv, momentum, eps, save_mean, save_invstd, scale, shift);
+  return check_launch("bn_train_stats_noalloc", 2);
+}
+
+}  // namespace b200
+
+extern "C" int32_t b200_bn_train_stats_noalloc(const void* x, int64_t rows, int32_t C, int32_t dtype,
+                                               const float* gamma, const float* beta, float* running_mean,
+                                               float* running_var, float momentum, float eps, float* save_mean,
+                                               float* save_invstd, float* scale, float* shift, void* stream) {
+  if (!x || rows <= 0 || C <= 0 || !save_mean || !save_invstd || !scale || !shift)
+    return fail(B200_INVALID_ARG, "bn_train_stats_noalloc: bad arguments");
+  if (C > B200_BN_NOALLOC_MAX_C)
+    return fail(B200_UNSUPPORTED, "bn_train_stats_noalloc: C=%d exceeds the built-in scratch limit of %d channels; "
+                "use b200_bn_train_stats with a caller-provided workspace", (int)C, B200_BN_NOALLOC_MAX_C);
+  if ((reinterpret_cast<uintptr_t>(x) & 15) != 0) return fail(B200_INVALID_ARG, "bn_train_stats_noalloc: x must be 16-byte aligned");
+  float* part = nullptr;
+  if (int32_t rc = bn_noalloc_scratch_ptr(&part)) return rc;
+  cudaStream_t st = as_stream(stream);
+  if (dtype == B200_F32)
+    return bn_stats_noalloc_impl<float>((const float*)x, rows, C, gamma, beta, running_mean, running_var, momentum, eps, save_mean, save_invstd, scale, shift, part, st);
+  if (dtype == B200_BF16)
+    return bn_stats_noalloc_impl<__nv_bfloat16>((const __nv_bfloat16*)x, rows, C, gamma, beta, running_mean, running_var, momentum, eps, save_mean, save_invstd, scale, shift, part, st);
+  return fail(B200_INVALID_ARG, "bn_train_stats_noalloc: bad dtype");
+}
