@@ -6,7 +6,9 @@
 // path validated by tools/umma_probe.cu replaces the staging for the bf16 3x3 convolutions).
 #include "common.cuh"
 #include "gemm_sm100.cuh"
+#include "conv_sm100.cuh"
 #include <vector>
+#include <stdlib.h>
 #include <utility>
 
 namespace b200 {
@@ -102,6 +104,189 @@ static int32_t gemm_bf16_run(const void* A, const void* B, void* C, int M, int N
   return B200_OK;
 }
 
+
+// ------------------------------------------------------------------------------------------------ implicit path
+// bf16, channel counts that are multiples of 64, filters up to 3x3, stride 1 or 2: everything in ResNet-50 except the
+// 3-channel stem.  Other shapes keep the staged (im2col) path above.
+static inline bool implicit_ok(const b200_conv_desc* d) {
+  static const bool disabled = getenv("B200_NO_IMPLICIT_CONV") != nullptr;
+  return !disabled && d->dtype == B200_BF16 && d->C % 64 == 0 && d->K % 64 == 0 && d->R <= 3 && d->S <= 3 &&
+         (d->stride == 1 || d->stride == 2) && d->pad < d->R && d->pad < d->S;
+}
+static inline bool is_flat(const b200_conv_desc* d) { return d->R == 1 && d->S == 1 && d->stride == 1 && d->pad == 0; }
+
+struct WgradPlan {
+  PixelBox box;
+  int Wq, Hq, Nq, bn_tile, nsplits, pb_total, pb_per;
+};
+static inline WgradPlan wgrad_plan(const b200_conv_desc* d, const ConvGeom& g) {
+  WgradPlan w;
+  if (is_flat(d)) { w.Wq = (int)g.M; w.Hq = 1; w.Nq = 1; }
+  else { w.Wq = g.Wo; w.Hq = g.Ho; w.Nq = d->N; }
+  w.box = choose_pixel_box(w.Wq, w.Hq, w.Nq, CONV_KR_MAX, 16, d->stride);
+  w.bn_tile = d->C >= 128 ? 128 : 64;
+  w.pb_total = w.box.tiles_w * w.box.tiles_h * w.box.tiles_n;
+  const long long ctas = (long long)((d->C + w.bn_tile - 1) / w.bn_tile) * ((d->K + 127) / 128) * (d->R * d->S);
+  long long s = (2LL * num_sms() + ctas - 1) / ctas;
+  if (s > w.pb_total) s = w.pb_total;
+  if (s > 1024) s = 1024;
+  const long long slab = (long long)d->K * g.ldw * 4;
+  while (s > 1 && s * slab > (1024LL << 20)) --s;
+  if (s < 1) s = 1;
+  w.pb_per = (int)((w.pb_total + s - 1) / s);
+  w.nsplits = (w.pb_total + w.pb_per - 1) / w.pb_per;
+  return w;
+}
+
+template <int MODE>
+static int launch_conv_mode(int bn, const CUtensorMap& ta, const CUtensorMap& tb, const ConvParams& P, dim3 grid,
+                            cudaStream_t st) {
+  if (MODE == MODE_WGRAD) {
+    if (bn == 128) return launch_conv_cfg<128, 3, MODE>(ta, tb, P, grid, st);
+    return launch_conv_cfg<64, 4, MODE>(ta, tb, P, grid, st);
+  }
+  if (bn == 256) return launch_conv_cfg<256, 4, MODE>(ta, tb, P, grid, st);
+  if (bn == 128) return launch_conv_cfg<128, 6, MODE>(ta, tb, P, grid, st);
+  return launch_conv_cfg<64, 8, MODE>(ta, tb, P, grid, st);
+}
+
+static inline void timing_begin(cudaEvent_t& e0, cudaEvent_t& e1, cudaStream_t st) {
+  if (gemm_timing().on) {
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    cudaEventRecord(e0, st);
+  }
+}
+static inline void timing_end(cudaEvent_t e0, cudaEvent_t e1, double flops, cudaStream_t st) {
+  GemmTiming& gt = gemm_timing();
+  if (gt.on) {
+    cudaEventRecord(e1, st);
+    gt.ev.emplace_back(e0, e1);
+    gt.flops += flops;
+  }
+  launch_counter() += 1;
+}
+
+// fprop (mode 0) and dgrad (mode 1) of one pixel grid / tap set
+static int32_t implicit_fprop(const b200_conv_desc* d, const ConvGeom& g, const void* x, const void* w, void* y,
+                              cudaStream_t st) {
+  ConvParams P{};
+  const bool flat = is_flat(d);
+  const int Wq = flat ? (int)g.M : g.Wo, Hq = flat ? 1 : g.Ho, Nq = flat ? 1 : d->N;
+  const PixelBox b = choose_pixel_box(Wq, Hq, Nq, GEMM_BM, 1, d->stride);
+  P.bw = b.bw; P.bh = b.bh; P.bn = b.bn; P.tiles_w = b.tiles_w; P.tiles_h = b.tiles_h; P.tiles_n = b.tiles_n;
+  P.a_mul = d->stride;
+  P.ntaps = d->R * d->S;
+  P.cchunks = d->C / 64;
+  for (int r = 0; r < d->R; ++r)
+    for (int s2 = 0; s2 < d->S; ++s2) P.taps[r * d->S + s2] = ConvTap{s2 - d->pad, r - d->pad, (r * d->S + s2) * d->C};
+  P.out = y; P.ldo = d->K; P.Wout = Wq; P.Hout = Hq; P.Nout = Nq; P.o_mul = 1; P.o_off_w = 0; P.o_off_h = 0;
+  P.ncols = d->K; P.out_fp32 = 0; P.accumulate = 0;
+  P.vec_ok = (reinterpret_cast<uintptr_t>(y) & 15) == 0 && d->K % 8 == 0;
+  CUtensorMap ta, tb;
+  int rc = flat ? make_tmap_bf16_nhwc(&ta, x, 1, 1, (int)g.M, d->C, b.bw, b.bh, b.bn, 1)
+                : make_tmap_bf16_nhwc(&ta, x, d->N, d->H, d->W, d->C, b.bw, b.bh, b.bn, d->stride);
+  if (rc) return fail(B200_CUDA_ERROR, "conv_fprop: activation tensor map failed (%d)", rc);
+  const int bn = d->K > 128 ? 256 : (d->K > 64 ? 128 : 64);
+  rc = make_tmap_bf16_2d(&tb, w, g.RSC, d->K, g.ldw, 64, bn);
+  if (rc) return fail(B200_CUDA_ERROR, "conv_fprop: weight tensor map failed (%d)", rc);
+  const long long tiles = (long long)b.tiles_w * b.tiles_h * b.tiles_n;
+  if (tiles > 65535) return fail(B200_UNSUPPORTED, "conv_fprop: too many pixel tiles (%lld)", tiles);
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  timing_begin(e0, e1, st);
+  rc = launch_conv_mode<MODE_FPROP>(bn, ta, tb, P, dim3((d->K + bn - 1) / bn, (unsigned)tiles, 1), st);
+  timing_end(e0, e1, 2.0 * g.M * d->K * g.RSC, st);
+  if (rc) return fail(B200_CUDA_ERROR, "conv_fprop: launch failed (%d)", rc);
+  return B200_OK;
+}
+
+static int32_t implicit_dgrad(const b200_conv_desc* d, const ConvGeom& g, const void* dy, const void* w, void* dx,
+                              int accumulate, cudaStream_t st) {
+  const bool flat = is_flat(d);
+  CUtensorMap tb;
+  int rc = make_tmap_bf16_2d(&tb, w, g.RSC, d->K, g.ldw, 64, 64);
+  if (rc) return fail(B200_CUDA_ERROR, "conv_dgrad: weight tensor map failed (%d)", rc);
+  const int bn = d->C > 128 ? 256 : (d->C > 64 ? 128 : 64);
+  const int classes = d->stride == 1 ? 1 : 4;
+  for (int cls = 0; cls < classes; ++cls) {
+    const int ph = d->stride == 1 ? 0 : cls / 2, pw = d->stride == 1 ? 0 : cls % 2;
+    ConvParams P{};
+    int Wq, Hq, Nq;
+    if (flat) { Wq = (int)g.M; Hq = 1; Nq = 1; }
+    else {
+      Wq = (d->W - pw + d->stride - 1) / d->stride;
+      Hq = (d->H - ph + d->stride - 1) / d->stride;
+      Nq = d->N;
+    }
+    if (Wq <= 0 || Hq <= 0) continue;
+    P.ntaps = 0;
+    for (int r = 0; r < d->R; ++r) {
+      const int vh = ph + d->pad - r;
+      if (vh % d->stride) continue;
+      for (int s2 = 0; s2 < d->S; ++s2) {
+        const int vw = pw + d->pad - s2;
+        if (vw % d->stride) continue;
+        P.taps[P.ntaps++] = ConvTap{vw / d->stride, vh / d->stride, (r * d->S + s2) * d->C};
+      }
+    }
+    if (P.ntaps == 0 && accumulate) continue;  // nothing to add for this parity class
+    const PixelBox b = choose_pixel_box(Wq, Hq, Nq, GEMM_BM, 1, 1);
+    P.bw = b.bw; P.bh = b.bh; P.bn = b.bn; P.tiles_w = b.tiles_w; P.tiles_h = b.tiles_h; P.tiles_n = b.tiles_n;
+    P.a_mul = 1;
+    P.cchunks = d->K / 64;
+    P.out = dx; P.ldo = d->C;
+    P.Wout = flat ? (int)g.M : d->W; P.Hout = flat ? 1 : d->H; P.Nout = flat ? 1 : d->N;
+    P.o_mul = d->stride; P.o_off_w = pw; P.o_off_h = ph;
+    P.ncols = d->C; P.out_fp32 = 0; P.accumulate = accumulate;
+    P.vec_ok = (reinterpret_cast<uintptr_t>(dx) & 15) == 0 && d->C % 8 == 0;
+    CUtensorMap ta;
+    rc = flat ? make_tmap_bf16_nhwc(&ta, dy, 1, 1, (int)g.M, d->K, b.bw, b.bh, b.bn, 1)
+              : make_tmap_bf16_nhwc(&ta, dy, d->N, g.Ho, g.Wo, d->K, b.bw, b.bh, b.bn, 1);
+    if (rc) return fail(B200_CUDA_ERROR, "conv_dgrad: gradient tensor map failed (%d)", rc);
+    const long long tiles = (long long)b.tiles_w * b.tiles_h * b.tiles_n;
+    if (tiles > 65535) return fail(B200_UNSUPPORTED, "conv_dgrad: too many pixel tiles (%lld)", tiles);
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    timing_begin(e0, e1, st);
+    rc = launch_conv_mode<MODE_DGRAD>(bn, ta, tb, P, dim3((d->C + bn - 1) / bn, (unsigned)tiles, 1), st);
+    timing_end(e0, e1, 2.0 * Wq * Hq * Nq * (double)d->C * d->K * P.ntaps, st);
+    if (rc) return fail(B200_CUDA_ERROR, "conv_dgrad: launch failed (%d)", rc);
+  }
+  return B200_OK;
+}
+
+static int32_t implicit_wgrad(const b200_conv_desc* d, const ConvGeom& g, const void* x, const void* dy, float* dw,
+                              void* ws, cudaStream_t st) {
+  const WgradPlan wp = wgrad_plan(d, g);
+  const bool flat = is_flat(d);
+  ConvParams P{};
+  P.bw = wp.box.bw; P.bh = wp.box.bh; P.bn = wp.box.bn;
+  P.tiles_w = wp.box.tiles_w; P.tiles_h = wp.box.tiles_h; P.tiles_n = wp.box.tiles_n;
+  P.ntaps = d->R * d->S;
+  for (int r = 0; r < d->R; ++r)
+    for (int s2 = 0; s2 < d->S; ++s2) P.taps[r * d->S + s2] = ConvTap{s2 - d->pad, r - d->pad, (r * d->S + s2) * d->C};
+  P.out = ws; P.ldo = g.ldw; P.split_stride = (long long)d->K * g.ldw;
+  P.ncols = d->C; P.out_fp32 = 1; P.accumulate = 0;
+  P.vec_ok = (reinterpret_cast<uintptr_t>(ws) & 15) == 0;   // ldw % 8 == 0 and tap offsets are multiples of 64
+  P.nsplits = wp.nsplits; P.pb_total = wp.pb_total; P.pb_per_split = wp.pb_per; P.x_mul = d->stride;
+  P.kr = wp.box.bw * wp.box.bh * wp.box.bn;
+  P.mrows = d->K;
+  CUtensorMap ta, tb;
+  int rc = flat ? make_tmap_bf16_nhwc(&ta, dy, 1, 1, (int)g.M, d->K, P.bw, P.bh, P.bn, 1)
+                : make_tmap_bf16_nhwc(&ta, dy, d->N, g.Ho, g.Wo, d->K, P.bw, P.bh, P.bn, 1);
+  if (rc) return fail(B200_CUDA_ERROR, "conv_wgrad: gradient tensor map failed (%d)", rc);
+  rc = flat ? make_tmap_bf16_nhwc(&tb, x, 1, 1, (int)g.M, d->C, P.bw, P.bh, P.bn, 1)
+            : make_tmap_bf16_nhwc(&tb, x, d->N, d->H, d->W, d->C, P.bw, P.bh, P.bn, d->stride);
+  if (rc) return fail(B200_CUDA_ERROR, "conv_wgrad: activation tensor map failed (%d)", rc);
+  dim3 grid((d->C + wp.bn_tile - 1) / wp.bn_tile, (d->K + 127) / 128, P.ntaps * wp.nsplits);
+  if (grid.z > 65535) return fail(B200_UNSUPPORTED, "conv_wgrad: too many split-K slabs");
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  timing_begin(e0, e1, st);
+  rc = launch_conv_mode<MODE_WGRAD>(wp.bn_tile, ta, tb, P, grid, st);
+  timing_end(e0, e1, 2.0 * g.M * d->K * g.RSC, st);
+  if (rc) return fail(B200_CUDA_ERROR, "conv_wgrad: launch failed (%d)", rc);
+  return launch_reduce_wgrad((const float*)ws, wp.nsplits, P.split_stride, d->K, d->C, d->R * d->S, g.ldw, dw, st);
+}
+
 }  // namespace b200
 
 using namespace b200;
@@ -111,6 +296,11 @@ extern "C" int32_t b200_conv_weight_ld(int32_t R, int32_t S, int32_t C) { return
 extern "C" int64_t b200_conv_workspace_bytes(const b200_conv_desc* d, int32_t which) {
   if (check_desc(d)) return -1;
   const ConvGeom g = geom(d);
+  if (implicit_ok(d)) {
+    if (which == B200_CONV_FPROP || which == B200_CONV_DGRAD) return 0;
+    if (which == B200_CONV_WGRAD) return (int64_t)align_up((size_t)wgrad_plan(d, g).nsplits * d->K * g.ldw * 4, 256);
+    return -1;
+  }
   size_t col = g.direct ? 0 : align_up((size_t)g.M * g.ldw * g.esz, 256);
   if (which == B200_CONV_FPROP) return (int64_t)col;
   if (which == B200_CONV_DGRAD) return g.direct ? 0 : (int64_t)align_up((size_t)g.M * g.ldw * 4, 256);
@@ -127,6 +317,7 @@ extern "C" int32_t b200_conv_fprop(const b200_conv_desc* d, const void* x, const
   if (!x || !w || !y) return fail(B200_INVALID_ARG, "conv_fprop: null pointer");
   const ConvGeom g = geom(d);
   cudaStream_t st = as_stream(stream);
+  if (implicit_ok(d)) return implicit_fprop(d, g, x, w, y, st);
   const void* A = x;
   long long lda = d->C;
   int Kred = d->C;
@@ -152,6 +343,7 @@ extern "C" int32_t b200_conv_dgrad(const b200_conv_desc* d, const void* dy, cons
   if (!dy || !w || !dx) return fail(B200_INVALID_ARG, "conv_dgrad: null pointer");
   const ConvGeom g = geom(d);
   cudaStream_t st = as_stream(stream);
+  if (implicit_ok(d)) return implicit_dgrad(d, g, dy, w, dx, accumulate, st);
   if (g.direct) {
     // dx[M][C] (+)= dy[M][K] * W[K][C]
     if (d->dtype == B200_F32)
@@ -182,6 +374,7 @@ extern "C" int32_t b200_conv_wgrad(const b200_conv_desc* d, const void* x, const
   cudaStream_t st = as_stream(stream);
   if (ws_bytes < b200_conv_workspace_bytes(d, B200_CONV_WGRAD) || !ws)
     return fail(B200_WORKSPACE_TOO_SMALL, "conv_wgrad: workspace too small");
+  if (implicit_ok(d)) return implicit_wgrad(d, g, x, dy, dw, ws, st);
   const size_t col_bytes = g.direct ? 0 : align_up((size_t)g.M * g.ldw * g.esz, 256);
   const void* Bm = x;
   long long ldb = d->C;

@@ -1,0 +1,358 @@
+// Implicit-GEMM convolution on tcgen05 for sm_100a: fprop, dgrad and wgrad over NHWC bf16 activations with NO
+// im2col / col2im staging.  The A operand of each k-block is fetched straight from the activation tensor by a 4-D
+// tiled TMA box {64 channels, bw, bh, bn pixels}:
+//   * the filter tap (r,s) is a coordinate shift of the box; out-of-bounds rows/columns (the padding halo, ragged
+//     tile tails, images past N) are zero-filled by the TMA unit;
+//   * the convolution stride is the tensor map's elementStrides (the box walks every stride-th pixel);
+//   * a 1x1/stride-1 convolution is the same code with the image flattened to one row of N*H*W pixels.
+// The M tile of the MMA is the pixel box (up to 128 pixels; rows past the box are stale smem and only ever reach
+// accumulator rows that are never stored).  Verified on hardware by tools/umma_probe.cu (4-D TMA cases).
+//
+//   MODE_FPROP : D[pix][cout] = sum_{tap,c} X[pix shifted by tap][c] * W[cout][tap][c]      (B K-major)
+//   MODE_DGRAD : D[pix][cin]  = sum_{tap,k} dY[pix shifted][k]       * W[k][tap][cin]       (B MN-major)
+//                stride-2 convolutions are decomposed into the four output-parity classes, each a stride-1 problem
+//                over the taps of matching parity (no wasted MACs), written to the interleaved output positions
+//   MODE_WGRAD : D[cout][cin] (one tap) = sum_{pixel boxes} dY[pix][cout]^T * X[pix shifted][cin]
+//                both operands MN-major (pixel index outermost), split-K over pixel boxes into fp32 slabs
+#pragma once
+#include "sm100_ptx.cuh"
+#include "gemm_sm100.cuh"
+
+namespace b200 {
+
+enum { MODE_FPROP = 0, MODE_DGRAD = 1, MODE_WGRAD = 2 };
+constexpr int CONV_MAX_TAPS = 9;
+constexpr int CONV_KR_MAX = 128;  // wgrad: pixel rows per k-block (multiple of 16)
+
+struct ConvTap {
+  int dw, dh;  // shift of the activation box (input-pixel units) for this tap
+  int bcol;    // column offset of this tap in the packed weight matrix [K][R*S*C]
+};
+
+struct ConvParams {
+  int bw, bh, bn;                    // pixel box extents
+  int tiles_w, tiles_h, tiles_n;     // number of boxes along each pixel dimension
+  int a_mul;                         // A box origin = tile origin * a_mul + tap shift
+  int ntaps, cchunks;                // reduction: taps x 64-channel chunks (fprop/dgrad)
+  ConvTap taps[CONV_MAX_TAPS];
+  void* out;                         // fprop/dgrad: NHWC tensor; wgrad: fp32 slabs [split][K][ld]
+  long long ldo;                     // elements per output pixel (fprop/dgrad) / per cout row (wgrad)
+  long long split_stride;            // wgrad: elements per slab
+  int Wout, Hout, Nout;              // output tensor extents (fprop/dgrad)
+  int o_mul, o_off_w, o_off_h;       // output pixel = tile pixel * o_mul + offset
+  int ncols;                         // valid output columns (cout / cin)
+  int out_fp32, accumulate, vec_ok;
+  // wgrad only
+  int nsplits, pb_total, pb_per_split, x_mul;  // x_mul = conv stride (X box origin = tile origin * x_mul + shift)
+  int kr;                                       // pixel rows per box = bw*bh*bn
+  int mrows;                                    // valid cout rows
+};
+
+template <int BN, int STAGES, int MODE>
+constexpr int conv_smem_bytes() {
+  constexpr int a = MODE == MODE_WGRAD ? 2 * CONV_KR_MAX * 128 : GEMM_BM * 128;
+  constexpr int b = MODE == MODE_WGRAD ? (BN / 64) * CONV_KR_MAX * 128 : BN * 128;
+  return STAGES * (a + b) + 1024 + 256;
+}
+
+template <int BN, int STAGES, int MODE>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                  const __grid_constant__ ConvParams P) {
+  constexpr int A_BYTES = MODE == MODE_WGRAD ? 2 * CONV_KR_MAX * 128 : GEMM_BM * 128;
+  constexpr int B_BYTES = MODE == MODE_WGRAD ? (BN / 64) * CONV_KR_MAX * 128 : BN * 128;
+  constexpr uint32_t TMEM_COLS = BN < 32 ? 32 : BN;
+
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t s0 = smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + ((1024u - (s0 & 1023u)) & 1023u);
+  uint8_t* smA = smem;
+  uint8_t* smB = smem + STAGES * A_BYTES;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + STAGES * (A_BYTES + B_BYTES));
+  uint64_t* empty = full + STAGES;
+  uint64_t* tmem_full = empty + STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int n0 = blockIdx.x * BN;  // output-column tile (cout for fprop, cin for dgrad / wgrad)
+
+  // ---- tile decode
+  int q0 = 0, p0 = 0, i0 = 0;      // pixel-box origin (fprop/dgrad)
+  int m0 = 0, tap = 0, split = 0;  // wgrad
+  int kb_begin = 0, kb_end = 0;
+  if (MODE != MODE_WGRAD) {
+    int t = blockIdx.y;
+    const int tw = t % P.tiles_w;
+    t /= P.tiles_w;
+    const int th = t % P.tiles_h;
+    const int tn = t / P.tiles_h;
+    q0 = tw * P.bw;
+    p0 = th * P.bh;
+    i0 = tn * P.bn;
+    kb_end = P.ntaps * P.cchunks;
+  } else {
+    m0 = blockIdx.y * GEMM_BM;
+    tap = blockIdx.z / P.nsplits;
+    split = blockIdx.z % P.nsplits;
+    kb_begin = split * P.pb_per_split;
+    kb_end = kb_begin + P.pb_per_split;
+    if (kb_end > P.pb_total) kb_end = P.pb_total;
+  }
+  const uint32_t box_bytes = static_cast<uint32_t>(P.bw * P.bh * P.bn) * 128u;
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+#pragma unroll
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], 1);
+    }
+    mbar_init(tmem_full, 1);
+    mbar_fence_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, TMEM_COLS);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const bool have_work = kb_end > kb_begin;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      int i = 0;
+      for (int kb = kb_begin; kb < kb_end; ++kb, ++i) {
+        const int s = i % STAGES;
+        const uint32_t ph = (i / STAGES) & 1;
+        mbar_wait(&empty[s], ph ^ 1);
+        uint8_t* a = smA + s * A_BYTES;
+        uint8_t* b = smB + s * B_BYTES;
+        if (MODE != MODE_WGRAD) {
+          const int t = kb / P.cchunks, cc = kb - t * P.cchunks;
+          mbar_expect_tx(&full[s], box_bytes + B_BYTES);
+          tma_load_4d(a, &tmA, &full[s], cc * 64, q0 * P.a_mul + P.taps[t].dw, p0 * P.a_mul + P.taps[t].dh, i0);
+          if (MODE == MODE_FPROP) {
+            tma_load_2d(b, &tmB, &full[s], P.taps[t].bcol + cc * 64, n0);  // box {64 c, BN cout}
+          } else {
+#pragma unroll
+            for (int h = 0; h < BN / 64; ++h)
+              tma_load_2d(b + h * 8192, &tmB, &full[s], P.taps[t].bcol + n0 + h * 64, cc * 64);  // {64 cin, 64 k}
+          }
+        } else {
+          int t = kb;
+          const int tw = t % P.tiles_w;
+          t /= P.tiles_w;
+          const int th = t % P.tiles_h;
+          const int tn = t / P.tiles_h;
+          const int bq = tw * P.bw, bp = th * P.bh, bi = tn * P.bn;
+          mbar_expect_tx(&full[s], box_bytes * (2 + BN / 64));
+#pragma unroll
+          for (int h = 0; h < 2; ++h) tma_load_4d(a + h * box_bytes, &tmA, &full[s], m0 + h * 64, bq, bp, bi);
+#pragma unroll
+          for (int h = 0; h < BN / 64; ++h)
+            tma_load_4d(b + h * box_bytes, &tmB, &full[s], n0 + h * 64, bq * P.x_mul + P.taps[tap].dw,
+                        bp * P.x_mul + P.taps[tap].dh, bi);
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ------------------------------------------------------------ MMA issuer
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(GEMM_BM, BN, MODE == MODE_WGRAD, MODE != MODE_FPROP);
+      int i = 0;
+      for (int kb = kb_begin; kb < kb_end; ++kb, ++i) {
+        const int s = i % STAGES;
+        const uint32_t ph = (i / STAGES) & 1;
+        mbar_wait(&full[s], ph);
+        tc_fence_after();
+        const uint32_t a_addr = smem_u32(smA + s * A_BYTES);
+        const uint32_t b_addr = smem_u32(smB + s * B_BYTES);
+        if (MODE != MODE_WGRAD) {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const uint64_t adesc = umma_smem_desc(a_addr + k * 32, 16, 1024);
+            const uint64_t bdesc = MODE == MODE_FPROP ? umma_smem_desc(b_addr + k * 32, 16, 1024)
+                                                      : umma_smem_desc(b_addr + k * 2048, 8192, 1024);
+            umma_f16(tmem_base, adesc, bdesc, idesc, (i > 0 || k > 0) ? 1u : 0u);
+          }
+        } else {
+          const int ksteps = P.kr >> 4;
+          for (int k = 0; k < ksteps; ++k) {
+            const uint64_t adesc = umma_smem_desc(a_addr + k * 2048, box_bytes, 1024);
+            const uint64_t bdesc = umma_smem_desc(b_addr + k * 2048, box_bytes, 1024);
+            umma_f16(tmem_base, adesc, bdesc, idesc, (i > 0 || k > 0) ? 1u : 0u);
+          }
+        }
+        umma_commit(&empty[s]);
+      }
+      umma_commit(tmem_full);
+    }
+    __syncwarp();
+  } else {
+    // ------------------------------------------------------------ epilogue warps
+    const int q = warp & 3;
+    const int l = q * 32 + lane;  // accumulator row
+    if (have_work) {
+      mbar_wait(tmem_full, 0);
+      tc_fence_after();
+    }
+    bool row_ok;
+    long long row_off;
+    if (MODE != MODE_WGRAD) {
+      const int iw = l % P.bw;
+      const int t = l / P.bw;
+      const int ih = t % P.bh;
+      const int in = t / P.bh;
+      const int ow = (q0 + iw) * P.o_mul + P.o_off_w;
+      const int oh = (p0 + ih) * P.o_mul + P.o_off_h;
+      const int on = i0 + in;
+      row_ok = in < P.bn && ow < P.Wout && oh < P.Hout && on < P.Nout;
+      row_off = ((static_cast<long long>(on) * P.Hout + oh) * P.Wout + ow) * P.ldo;
+    } else {
+      row_ok = (m0 + l) < P.mrows;
+      row_off = static_cast<long long>(blockIdx.z % P.nsplits) * P.split_stride +
+                static_cast<long long>(m0 + l) * P.ldo + P.taps[tap].bcol;
+    }
+#pragma unroll 1
+    for (int c = 0; c < BN / 32; ++c) {
+      uint32_t r[32];
+      if (have_work) {
+        tmem_ld_32x32b_x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(c * 32), r);
+        tmem_ld_wait();
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) r[j] = 0u;
+      }
+      const int col0 = n0 + c * 32;
+      if (!row_ok || col0 >= P.ncols) continue;
+      if (P.out_fp32) {
+        float* p = reinterpret_cast<float*>(P.out) + row_off + col0;
+        if (P.vec_ok && col0 + 32 <= P.ncols) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            float4 v = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]),
+                                   __uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3]));
+            if (P.accumulate) {
+              float4 o = reinterpret_cast<float4*>(p)[j];
+              v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w;
+            }
+            reinterpret_cast<float4*>(p)[j] = v;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (col0 + j < P.ncols) p[j] = (P.accumulate ? p[j] : 0.f) + __uint_as_float(r[j]);
+        }
+      } else {
+        __nv_bfloat16* p = reinterpret_cast<__nv_bfloat16*>(P.out) + row_off + col0;
+        if (P.vec_ok && col0 + 32 <= P.ncols) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            float f[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(r[8 * j + e]);
+            if (P.accumulate) {
+              uint4 o = reinterpret_cast<uint4*>(p)[j];
+              const __nv_bfloat162* ob = reinterpret_cast<const __nv_bfloat162*>(&o);
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                float2 t2 = __bfloat1622float2(ob[e]);
+                f[2 * e] += t2.x;
+                f[2 * e + 1] += t2.y;
+              }
+            }
+            uint4 v;
+            v.x = pack_bf16x2(f[0], f[1]);
+            v.y = pack_bf16x2(f[2], f[3]);
+            v.z = pack_bf16x2(f[4], f[5]);
+            v.w = pack_bf16x2(f[6], f[7]);
+            reinterpret_cast<uint4*>(p)[j] = v;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (col0 + j < P.ncols) {
+              float f = __uint_as_float(r[j]);
+              if (P.accumulate) f += __bfloat162float(p[j]);
+              p[j] = __float2bfloat16_rn(f);
+            }
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ host side
+// bf16 4-D map over an NHWC tensor [N][H][W][C]: box {64, bw*es, bh*es, bn}, traversal stride es along W and H.
+inline int make_tmap_bf16_nhwc(CUtensorMap* m, const void* base, int N, int H, int W, int C, int bw, int bh, int bn,
+                               int es) {
+  EncodeTiledFn enc = tma_encode_fn();
+  if (!enc) return -1;
+  cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+  cuuint64_t strides[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+  cuuint32_t box[4] = {64, (cuuint32_t)(bw * es), (cuuint32_t)(bh * es), (cuuint32_t)bn};
+  cuuint32_t estr[4] = {1, (cuuint32_t)es, (cuuint32_t)es, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : static_cast<int>(r);
+}
+
+struct PixelBox {
+  int bw, bh, bn, tiles_w, tiles_h, tiles_n;
+};
+// Chooses the pixel box {bw,bh,bn} (bw*bh*bn <= max_rows, multiple of `mult`, each TMA box dim <= 256 after the
+// element stride) that covers a W x H x N pixel grid with the fewest box rows in total.
+inline PixelBox choose_pixel_box(int W, int H, int N, int max_rows, int mult, int es) {
+  PixelBox best{1, 1, 1, W, H, N};
+  long long best_rows = -1;
+  const int wlim = 256 / es;
+  for (int bw = 1; bw <= W && bw <= max_rows && bw <= wlim; ++bw) {
+    for (int bh = 1; bh <= H && bw * bh <= max_rows && bh <= wlim; ++bh) {
+      int bn = max_rows / (bw * bh);
+      if (bn > N) bn = N;
+      if (bn > 256) bn = 256;
+      for (; bn >= 1; --bn)
+        if ((bw * bh * bn) % mult == 0) break;
+      if (bn < 1) continue;
+      const long long tw = (W + bw - 1) / bw, th = (H + bh - 1) / bh, tn = (N + bn - 1) / bn;
+      const long long rows = tw * th * tn * (mult == 1 ? (long long)max_rows : (long long)bw * bh * bn);
+      if (best_rows < 0 || rows < best_rows || (rows == best_rows && bw > best.bw)) {
+        best_rows = rows;
+        best = PixelBox{bw, bh, bn, (int)tw, (int)th, (int)tn};
+      }
+    }
+  }
+  return best;
+}
+
+template <int BN, int STAGES, int MODE>
+inline int launch_conv_cfg(const CUtensorMap& ta, const CUtensorMap& tb, const ConvParams& P, dim3 grid,
+                           cudaStream_t st) {
+  auto kern = conv_sm100_kernel<BN, STAGES, MODE>;
+  constexpr int smem = conv_smem_bytes<BN, STAGES, MODE>();
+  static bool attr_done = false;
+  if (!attr_done) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return 300 + static_cast<int>(e);
+    attr_done = true;
+  }
+  kern<<<grid, GEMM_THREADS, smem, st>>>(ta, tb, P);
+  cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? 0 : 400 + static_cast<int>(e);
+}
+
+}  // namespace b200

@@ -108,6 +108,12 @@ CONV_CASES = [
     (4, 5, 512, 2048, 1, 1, 0),  # s  tiny M
     (1, 21, 64, 72, 3, 2, 1),    # odd H, Cout not a multiple of 64
     (1, 13, 24, 40, 3, 1, 1),    # small odd channel counts
+    (2, 14, 128, 128, 3, 1, 1),  # 224-px family: 14x14
+    (1, 21, 64, 128, 3, 2, 1),   # odd H, stride 2 (implicit path: parity classes with ragged extents)
+    (3, 7, 512, 512, 3, 1, 1),   # 7x7 map
+    (1, 11, 64, 64, 1, 2, 0),    # odd H, 1x1 stride 2
+    (5, 5, 512, 512, 3, 1, 1),   # 5x5 map, N not a multiple of the pixel box
+    (2, 10, 512, 512, 3, 2, 1),  # r  10 -> 5
 ]
 
 
