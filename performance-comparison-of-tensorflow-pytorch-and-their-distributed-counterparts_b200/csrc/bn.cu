@@ -81,19 +81,41 @@ bn_partial_kernel(const T* __restrict__ x, const T* __restrict__ dz, const T* __
   }
 }
 
-__global__ void bn_finalize_fwd_kernel(const float* __restrict__ part, int nblk, int C, double n,
-                                       const float* __restrict__ gamma, const float* __restrict__ beta,
-                                       float* __restrict__ running_mean, float* __restrict__ running_var,
-                                       float momentum, float eps, float* __restrict__ save_mean,
-                                       float* __restrict__ save_invstd, float* __restrict__ scale,
-                                       float* __restrict__ shift) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
-  double s = 0, q = 0;
-  for (int b = 0; b < nblk; ++b) {
-    s += part[((long long)b * 2 + 0) * C + c];
-    q += part[((long long)b * 2 + 1) * C + c];
+// Sums the per-block partials: a block owns 32 channels (coalesced across x) and 16 partial-lanes (y).
+constexpr int FIN_CX = 32, FIN_RY = 16;
+__device__ __forceinline__ void bn_sum_partials(const float* __restrict__ part, int nblk, int C, int c, double& s,
+                                                double& q) {
+  __shared__ double red[2][FIN_RY][FIN_CX + 1];
+  double a = 0, b = 0;
+  if (c < C) {
+    for (int i = threadIdx.y; i < nblk; i += FIN_RY) {
+      a += part[((long long)i * 2 + 0) * C + c];
+      b += part[((long long)i * 2 + 1) * C + c];
+    }
   }
+  red[0][threadIdx.y][threadIdx.x] = a;
+  red[1][threadIdx.y][threadIdx.x] = b;
+  __syncthreads();
+  s = 0;
+  q = 0;
+  if (threadIdx.y == 0) {
+#pragma unroll
+    for (int j = 0; j < FIN_RY; ++j) {
+      s += red[0][j][threadIdx.x];
+      q += red[1][j][threadIdx.x];
+    }
+  }
+}
+
+__global__ void __launch_bounds__(FIN_CX * FIN_RY)
+bn_finalize_fwd_kernel(const float* __restrict__ part, int nblk, int C, double n, const float* __restrict__ gamma,
+                       const float* __restrict__ beta, float* __restrict__ running_mean,
+                       float* __restrict__ running_var, float momentum, float eps, float* __restrict__ save_mean,
+                       float* __restrict__ save_invstd, float* __restrict__ scale, float* __restrict__ shift) {
+  const int c = blockIdx.x * FIN_CX + threadIdx.x;
+  double s, q;
+  bn_sum_partials(part, nblk, C, c, s, q);
+  if (threadIdx.y != 0 || c >= C) return;
   const double mean = s / n;
   double var = q / n - mean * mean;
   if (var < 0) var = 0;
@@ -112,17 +134,14 @@ __global__ void bn_finalize_fwd_kernel(const float* __restrict__ part, int nblk,
 }
 
 // coef layout: [3][C] : A = gamma*invstd ; B = gamma*invstd^3*S2/n ; Cc = A*dbeta/n
-__global__ void bn_finalize_bwd_kernel(const float* __restrict__ part, int nblk, int C, double n,
-                                       const float* __restrict__ gamma, const float* __restrict__ invstd,
-                                       float* __restrict__ dgamma, float* __restrict__ dbeta,
-                                       float* __restrict__ coef) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
-  double s = 0, q = 0;
-  for (int b = 0; b < nblk; ++b) {
-    s += part[((long long)b * 2 + 0) * C + c];
-    q += part[((long long)b * 2 + 1) * C + c];
-  }
+__global__ void __launch_bounds__(FIN_CX * FIN_RY)
+bn_finalize_bwd_kernel(const float* __restrict__ part, int nblk, int C, double n, const float* __restrict__ gamma,
+                       const float* __restrict__ invstd, float* __restrict__ dgamma, float* __restrict__ dbeta,
+                       float* __restrict__ coef) {
+  const int c = blockIdx.x * FIN_CX + threadIdx.x;
+  double s, q;
+  bn_sum_partials(part, nblk, C, c, s, q);
+  if (threadIdx.y != 0 || c >= C) return;
   const double is = invstd[c], g = gamma ? gamma[c] : 1.0;
   if (dgamma) dgamma[c] = (float)(q * is);
   if (dbeta) dbeta[c] = (float)s;
@@ -132,13 +151,26 @@ __global__ void bn_finalize_bwd_kernel(const float* __restrict__ part, int nblk,
   coef[2 * C + c] = (float)(A * s / n);
 }
 
-template <typename T, int VEC>
-__global__ void bn_apply_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __restrict__ y,
-                                long long nvec_total, int nvec, const float* __restrict__ scale,
-                                const float* __restrict__ shift, int relu) {
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < nvec_total;
-       i += (long long)gridDim.x * blockDim.x) {
+// FIXEDC: the grid stride is a multiple of nvec, so a thread always lands on the same channel vector and keeps its
+// per-channel constants in registers (the streaming loop is then loads + FMAs + store only).
+template <typename T, int VEC, bool FIXEDC>
+__global__ void __launch_bounds__(BN_THREADS)
+bn_apply_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __restrict__ y, long long nvec_total, int nvec,
+                const float* __restrict__ scale, const float* __restrict__ shift, int relu) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  float sc[VEC], sh[VEC];
+  if (FIXEDC) {
     const int c = (int)(i % nvec) * VEC;
+#pragma unroll
+    for (int e = 0; e < VEC; ++e) { sc[e] = scale[c + e]; sh[e] = shift[c + e]; }
+  }
+  for (; i < nvec_total; i += stride) {
+    if (!FIXEDC) {
+      const int c = (int)(i % nvec) * VEC;
+#pragma unroll
+      for (int e = 0; e < VEC; ++e) { sc[e] = scale[c + e]; sh[e] = shift[c + e]; }
+    }
     const long long off = i * VEC;
     float xv[VEC], rv[VEC];
     if constexpr (VEC == 1) { xv[0] = to_f(x[off]); if (res) rv[0] = to_f(res[off]); }
@@ -148,7 +180,7 @@ __global__ void bn_apply_kernel(const T* __restrict__ x, const T* __restrict__ r
     }
 #pragma unroll
     for (int e = 0; e < VEC; ++e) {
-      float v = fmaf(xv[e], scale[c + e], shift[c + e]);
+      float v = fmaf(xv[e], sc[e], sh[e]);
       if (res) v += rv[e];
       if (relu) v = fmaxf(v, 0.f);
       xv[e] = v;
@@ -158,13 +190,25 @@ __global__ void bn_apply_kernel(const T* __restrict__ x, const T* __restrict__ r
   }
 }
 
-template <typename T, int VEC>
-__global__ void bn_bwd_dx_kernel(const T* __restrict__ dz, const T* __restrict__ z, const T* __restrict__ x,
-                                 T* __restrict__ dx, T* __restrict__ dres, long long nvec_total, int nvec, int C,
-                                 const float* __restrict__ mean, const float* __restrict__ coef, int relu) {
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < nvec_total;
-       i += (long long)gridDim.x * blockDim.x) {
+template <typename T, int VEC, bool FIXEDC>
+__global__ void __launch_bounds__(BN_THREADS)
+bn_bwd_dx_kernel(const T* __restrict__ dz, const T* __restrict__ z, const T* __restrict__ x, T* __restrict__ dx,
+                 T* __restrict__ dres, long long nvec_total, int nvec, int C, const float* __restrict__ mean,
+                 const float* __restrict__ coef, int relu) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  float cA[VEC], cB[VEC], cC[VEC], mu[VEC];
+  if (FIXEDC) {
     const int c = (int)(i % nvec) * VEC;
+#pragma unroll
+    for (int e = 0; e < VEC; ++e) { cA[e] = coef[c + e]; cB[e] = coef[C + c + e]; cC[e] = coef[2 * C + c + e]; mu[e] = mean[c + e]; }
+  }
+  for (; i < nvec_total; i += stride) {
+    if (!FIXEDC) {
+      const int c = (int)(i % nvec) * VEC;
+#pragma unroll
+      for (int e = 0; e < VEC; ++e) { cA[e] = coef[c + e]; cB[e] = coef[C + c + e]; cC[e] = coef[2 * C + c + e]; mu[e] = mean[c + e]; }
+    }
     const long long off = i * VEC;
     float gv[VEC], zv[VEC], xv[VEC];
     if constexpr (VEC == 1) { gv[0] = to_f(dz[off]); xv[0] = to_f(x[off]); zv[0] = relu ? to_f(z[off]) : 1.f; }
@@ -177,7 +221,7 @@ __global__ void bn_bwd_dx_kernel(const T* __restrict__ dz, const T* __restrict__
     for (int e = 0; e < VEC; ++e) {
       const float g = (!relu || zv[e] > 0.f) ? gv[e] : 0.f;
       gv[e] = g;
-      xv[e] = coef[c + e] * g - coef[2 * C + c + e] - coef[C + c + e] * (xv[e] - mean[c + e]);
+      xv[e] = cA[e] * g - cC[e] - cB[e] * (xv[e] - mu[e]);
     }
     if constexpr (VEC == 1) { dx[off] = from_f<T>(xv[0]); if (dres) dres[off] = from_f<T>(gv[0]); }
     else {
@@ -203,6 +247,20 @@ static inline int ew_grid(long long total) {
   const long long cap = (long long)num_sms() * 8;
   if (b > cap) b = cap;
   return (int)(b < 1 ? 1 : b);
+}
+
+// grid for the streaming kernels; `fixed` tells whether gridDim*blockDim is a multiple of nvec
+static inline int ew_grid_fixed(long long total, int nvec, bool* fixed) {
+  int g = ew_grid(total);
+  *fixed = false;
+  if (nvec <= 0) return g;
+  // smallest multiple m of (nvec / gcd(nvec, BN_THREADS)) blocks keeps every thread on one channel vector
+  int a = nvec, b = BN_THREADS;
+  while (b) { int t = a % b; a = b; b = t; }
+  const int per = nvec / a;
+  if (per <= g) { g = g / per * per; *fixed = true; }
+  else if (per <= 4096 && (long long)per * BN_THREADS <= total * 2) { g = per; *fixed = true; }
+  return g;
 }
 
 struct BnPlan {
@@ -239,7 +297,7 @@ static int32_t bn_stats_impl(const T* x, long long rows, int C, const float* gam
     bn_partial_kernel<T, 1, false><<<p.nblk, BN_THREADS, 0, st>>>(x, nullptr, nullptr, nullptr, rows, C, p.cx, p.rows_per_block, 0, part);
   else
     bn_partial_kernel<T, VecTraits<T>::W, false><<<p.nblk, BN_THREADS, 0, st>>>(x, nullptr, nullptr, nullptr, rows, C, p.cx, p.rows_per_block, 0, part);
-  bn_finalize_fwd_kernel<<<(C + 127) / 128, 128, 0, st>>>(part, p.nblk, C, (double)rows, gamma, beta, rm, rv, momentum, eps, save_mean, save_invstd, scale, shift);
+  bn_finalize_fwd_kernel<<<(C + FIN_CX - 1) / FIN_CX, dim3(FIN_CX, FIN_RY), 0, st>>>(part, p.nblk, C, (double)rows, gamma, beta, rm, rv, momentum, eps, save_mean, save_invstd, scale, shift);
   return check_launch("bn_train_stats", 2);
 }
 
@@ -249,9 +307,12 @@ static int32_t bn_apply_impl(const T* x, const T* res, T* y, long long rows, int
   const bool aligned = ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y) | reinterpret_cast<uintptr_t>(res)) & 15) == 0;
   if (C % VecTraits<T>::W == 0 && aligned) {
     constexpr int V = VecTraits<T>::W;
-    bn_apply_kernel<T, V><<<ew_grid(rows * (C / V)), BN_THREADS, 0, st>>>(x, res, y, rows * (C / V), C / V, scale, shift, relu);
+    bool fixed;
+    const int grid = ew_grid_fixed(rows * (C / V), C / V, &fixed);
+    if (fixed) bn_apply_kernel<T, V, true><<<grid, BN_THREADS, 0, st>>>(x, res, y, rows * (C / V), C / V, scale, shift, relu);
+    else bn_apply_kernel<T, V, false><<<grid, BN_THREADS, 0, st>>>(x, res, y, rows * (C / V), C / V, scale, shift, relu);
   } else {
-    bn_apply_kernel<T, 1><<<ew_grid(rows * C), BN_THREADS, 0, st>>>(x, res, y, rows * C, C, scale, shift, relu);
+    bn_apply_kernel<T, 1, false><<<ew_grid(rows * C), BN_THREADS, 0, st>>>(x, res, y, rows * C, C, scale, shift, relu);
   }
   return check_launch("bn_apply");
 }
@@ -267,14 +328,17 @@ static int32_t bn_bwd_impl(const T* dz, const T* z, const T* x, T* dx, T* dres, 
     bn_partial_kernel<T, 1, true><<<p.nblk, BN_THREADS, 0, st>>>(x, dz, z, mean, rows, C, p.cx, p.rows_per_block, relu, part);
   else
     bn_partial_kernel<T, VecTraits<T>::W, true><<<p.nblk, BN_THREADS, 0, st>>>(x, dz, z, mean, rows, C, p.cx, p.rows_per_block, relu, part);
-  bn_finalize_bwd_kernel<<<(C + 127) / 128, 128, 0, st>>>(part, p.nblk, C, (double)rows, gamma, invstd, dgamma, dbeta, coef);
+  bn_finalize_bwd_kernel<<<(C + FIN_CX - 1) / FIN_CX, dim3(FIN_CX, FIN_RY), 0, st>>>(part, p.nblk, C, (double)rows, gamma, invstd, dgamma, dbeta, coef);
   const bool aligned = ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(dz) | reinterpret_cast<uintptr_t>(z) |
                          reinterpret_cast<uintptr_t>(dx) | reinterpret_cast<uintptr_t>(dres)) & 15) == 0;
   if (p.vec != 1 && aligned) {
     constexpr int V = VecTraits<T>::W;
-    bn_bwd_dx_kernel<T, V><<<ew_grid(rows * (C / V)), BN_THREADS, 0, st>>>(dz, z, x, dx, dres, rows * (C / V), C / V, C, mean, coef, relu);
+    bool fixed;
+    const int grid = ew_grid_fixed(rows * (C / V), C / V, &fixed);
+    if (fixed) bn_bwd_dx_kernel<T, V, true><<<grid, BN_THREADS, 0, st>>>(dz, z, x, dx, dres, rows * (C / V), C / V, C, mean, coef, relu);
+    else bn_bwd_dx_kernel<T, V, false><<<grid, BN_THREADS, 0, st>>>(dz, z, x, dx, dres, rows * (C / V), C / V, C, mean, coef, relu);
   } else {
-    bn_bwd_dx_kernel<T, 1><<<ew_grid(rows * C), BN_THREADS, 0, st>>>(dz, z, x, dx, dres, rows * C, C, C, mean, coef, relu);
+    bn_bwd_dx_kernel<T, 1, false><<<ew_grid(rows * C), BN_THREADS, 0, st>>>(dz, z, x, dx, dres, rows * C, C, C, mean, coef, relu);
   }
   return check_launch("bn_backward", 3);
 }
@@ -422,7 +486,7 @@ static int32_t bn_stats_noalloc_impl(const T* x, long long rows, int C, const fl
     bn_partial_kernel<T, 1, false><<<p.nblk, BN_THREADS, 0, st>>>(x, nullptr, nullptr, nullptr, rows, C, p.cx, p.rows_per_block, 0, part);
   else
     bn_partial_kernel<T, VecTraits<T>::W, false><<<p.nblk, BN_THREADS, 0, st>>>(x, nullptr, nullptr, nullptr, rows, C, p.cx, p.rows_per_block, 0, part);
-  bn_finalize_fwd_kernel<<<(C + 127) / 128, 128, 0, st>>>(part, p.nblk, C, (double)rows, gamma, beta, rm, rv, momentum, eps, save_mean, save_invstd, scale, shift);
+  bn_finalize_fwd_kernel<<<(C + FIN_CX - 1) / FIN_CX, dim3(FIN_CX, FIN_RY), 0, st>>>(part, p.nblk, C, (double)rows, gamma, beta, rm, rv, momentum, eps, save_mean, save_invstd, scale, shift);
   return check_launch("bn_train_stats_noalloc", 2);
 }
 

@@ -72,6 +72,86 @@ __global__ void maxpool_bwd_kernel(const T* __restrict__ dy, const uint8_t* __re
   }
 }
 
+// vectorised variants (C % VEC == 0, 16-byte aligned): one thread = VEC channels of one pixel
+template <typename T, int VEC>
+__global__ void maxpool_fwd_vec_kernel(const T* __restrict__ x, T* __restrict__ y, uint8_t* __restrict__ amax, int N,
+                                       int H, int W, int C, int Ho, int Wo) {
+  const int cv = C / VEC;
+  const long long total = (long long)N * Ho * Wo * cv;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % cv) * VEC;
+    long long t = i / cv;
+    const int q = (int)(t % Wo);
+    t /= Wo;
+    const int p = (int)(t % Ho);
+    const int n = (int)(t / Ho);
+    float best[VEC];
+    int bi[VEC];
+    bool any = false;
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      const int h = 2 * p - 1 + r;
+      if (h < 0 || h >= H) continue;
+#pragma unroll
+      for (int s = 0; s < 3; ++s) {
+        const int w = 2 * q - 1 + s;
+        if (w < 0 || w >= W) continue;
+        float v[VEC];
+        load_vec(x + (((long long)n * H + h) * W + w) * C + c, v);
+#pragma unroll
+        for (int e = 0; e < VEC; ++e)
+          if (!any || v[e] > best[e] || v[e] != v[e]) { best[e] = v[e]; bi[e] = r * 3 + s; }
+        any = true;
+      }
+    }
+    const long long o = (((long long)n * Ho + p) * Wo + q) * C + c;
+    store_vec(y + o, best);
+    if (amax) {
+#pragma unroll
+      for (int e = 0; e < VEC; ++e) amax[o + e] = (uint8_t)bi[e];
+    }
+  }
+}
+
+template <typename T, int VEC>
+__global__ void maxpool_bwd_vec_kernel(const T* __restrict__ dy, const uint8_t* __restrict__ amax,
+                                       T* __restrict__ dx, int N, int H, int W, int C, int Ho, int Wo) {
+  const int cv = C / VEC;
+  const long long total = (long long)N * H * W * cv;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % cv) * VEC;
+    long long t = i / cv;
+    const int w = (int)(t % W);
+    t /= W;
+    const int h = (int)(t % H);
+    const int n = (int)(t / H);
+    float acc[VEC];
+#pragma unroll
+    for (int e = 0; e < VEC; ++e) acc[e] = 0.f;
+    const int p_lo = h / 2, p_hi = (h + 1) / 2, q_lo = w / 2, q_hi = (w + 1) / 2;
+    for (int p = p_lo; p <= p_hi; ++p) {
+      if (p >= Ho) continue;
+      const int r = h - (2 * p - 1);
+      for (int q = q_lo; q <= q_hi; ++q) {
+        if (q >= Wo) continue;
+        const int want = r * 3 + (w - (2 * q - 1));
+        const long long o = (((long long)n * Ho + p) * Wo + q) * C + c;
+        uint8_t idx[VEC];
+        if (VEC == 8) *reinterpret_cast<uint2*>(idx) = *reinterpret_cast<const uint2*>(amax + o);
+        else *reinterpret_cast<uint32_t*>(idx) = *reinterpret_cast<const uint32_t*>(amax + o);
+        float g[VEC];
+        load_vec(dy + o, g);
+#pragma unroll
+        for (int e = 0; e < VEC; ++e)
+          if (idx[e] == want) acc[e] += g[e];
+      }
+    }
+    store_vec(dx + (((long long)n * H + h) * W + w) * C + c, acc);
+  }
+}
+
 template <typename T>
 __global__ void avgpool_fwd_kernel(const T* __restrict__ x, float* __restrict__ y, int N, int HW, int C) {
   const long long total = (long long)N * C;
@@ -113,7 +193,10 @@ extern "C" int32_t b200_maxpool3x3s2_fwd(const void* x, void* y, uint8_t* argmax
   const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;
   const long long total = (long long)N * Ho * Wo * C;
   cudaStream_t st = as_stream(stream);
-  if (dtype == B200_F32) maxpool_fwd_kernel<float><<<pgrid(total), 256, 0, st>>>((const float*)x, (float*)y, argmax, N, H, W, C, Ho, Wo);
+  const bool al = ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y) | reinterpret_cast<uintptr_t>(argmax)) & 15) == 0;
+  if (dtype == B200_F32 && al && C % 4 == 0) maxpool_fwd_vec_kernel<float, 4><<<pgrid(total / 4), 256, 0, st>>>((const float*)x, (float*)y, argmax, N, H, W, C, Ho, Wo);
+  else if (dtype == B200_BF16 && al && C % 8 == 0) maxpool_fwd_vec_kernel<__nv_bfloat16, 8><<<pgrid(total / 8), 256, 0, st>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, argmax, N, H, W, C, Ho, Wo);
+  else if (dtype == B200_F32) maxpool_fwd_kernel<float><<<pgrid(total), 256, 0, st>>>((const float*)x, (float*)y, argmax, N, H, W, C, Ho, Wo);
   else if (dtype == B200_BF16) maxpool_fwd_kernel<__nv_bfloat16><<<pgrid(total), 256, 0, st>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, argmax, N, H, W, C, Ho, Wo);
   else return fail(B200_INVALID_ARG, "maxpool_fwd: bad dtype");
   return check_launch("maxpool_fwd");
@@ -125,7 +208,10 @@ extern "C" int32_t b200_maxpool3x3s2_bwd(const void* dy, const uint8_t* argmax, 
   const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;
   const long long total = (long long)N * H * W * C;
   cudaStream_t st = as_stream(stream);
-  if (dtype == B200_F32) maxpool_bwd_kernel<float><<<pgrid(total), 256, 0, st>>>((const float*)dy, argmax, (float*)dx, N, H, W, C, Ho, Wo);
+  const bool al = ((reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(dx) | reinterpret_cast<uintptr_t>(argmax)) & 15) == 0;
+  if (dtype == B200_F32 && al && C % 4 == 0) maxpool_bwd_vec_kernel<float, 4><<<pgrid(total / 4), 256, 0, st>>>((const float*)dy, argmax, (float*)dx, N, H, W, C, Ho, Wo);
+  else if (dtype == B200_BF16 && al && C % 8 == 0) maxpool_bwd_vec_kernel<__nv_bfloat16, 8><<<pgrid(total / 8), 256, 0, st>>>((const __nv_bfloat16*)dy, argmax, (__nv_bfloat16*)dx, N, H, W, C, Ho, Wo);
+  else if (dtype == B200_F32) maxpool_bwd_kernel<float><<<pgrid(total), 256, 0, st>>>((const float*)dy, argmax, (float*)dx, N, H, W, C, Ho, Wo);
   else if (dtype == B200_BF16) maxpool_bwd_kernel<__nv_bfloat16><<<pgrid(total), 256, 0, st>>>((const __nv_bfloat16*)dy, argmax, (__nv_bfloat16*)dx, N, H, W, C, Ho, Wo);
   else return fail(B200_INVALID_ARG, "maxpool_bwd: bad dtype");
   return check_launch("maxpool_bwd");
