@@ -82,16 +82,26 @@ bn_partial_kernel(const T* __restrict__ x, const T* __restrict__ dz, const T* __
 }
 
 // Sums the per-block partials: a block owns 32 channels (coalesced across x) and 16 partial-lanes (y).
-constexpr int FIN_CX = 32, FIN_RY = 16;
+constexpr int FIN_CX = 32, FIN_RY = 32;
 __device__ __forceinline__ void bn_sum_partials(const float* __restrict__ part, int nblk, int C, int c, double& s,
                                                 double& q) {
   __shared__ double red[2][FIN_RY][FIN_CX + 1];
   double a = 0, b = 0;
   if (c < C) {
-    for (int i = threadIdx.y; i < nblk; i += FIN_RY) {
+    // two independent accumulation chains and all four loads of an iteration issued together
+    double a1 = 0, b1 = 0;
+    int i = threadIdx.y;
+    for (; i + FIN_RY < nblk; i += 2 * FIN_RY) {
+      const float x0 = part[((long long)i * 2 + 0) * C + c], y0 = part[((long long)i * 2 + 1) * C + c];
+      const float x1 = part[((long long)(i + FIN_RY) * 2 + 0) * C + c], y1 = part[((long long)(i + FIN_RY) * 2 + 1) * C + c];
+      a += x0; b += y0; a1 += x1; b1 += y1;
+    }
+    if (i < nblk) {
       a += part[((long long)i * 2 + 0) * C + c];
       b += part[((long long)i * 2 + 1) * C + c];
     }
+    a += a1;
+    b += b1;
   }
   red[0][threadIdx.y][threadIdx.x] = a;
   red[1][threadIdx.y][threadIdx.x] = b;

@@ -139,15 +139,16 @@ static inline WgradPlan wgrad_plan(const b200_conv_desc* d, const ConvGeom& g) {
 }
 
 template <int MODE>
-static int launch_conv_mode(int bn, const CUtensorMap& ta, const CUtensorMap& tb, const ConvParams& P, dim3 grid,
+static int launch_conv_mode(int bn, const CUtensorMap& ta, const CUtensorMap& tb, const ConvParams& P,
                             cudaStream_t st) {
+  const int ctas = num_sms();   // persistent: one CTA per SM
   if (MODE == MODE_WGRAD) {
-    if (bn == 128) return launch_conv_cfg<128, 3, MODE>(ta, tb, P, grid, st);
-    return launch_conv_cfg<64, 4, MODE>(ta, tb, P, grid, st);
+    if (bn == 128) return launch_conv_cfg<128, 3, MODE>(ta, tb, P, ctas, st);
+    return launch_conv_cfg<64, 4, MODE>(ta, tb, P, ctas, st);
   }
-  if (bn == 256) return launch_conv_cfg<256, 4, MODE>(ta, tb, P, grid, st);
-  if (bn == 128) return launch_conv_cfg<128, 6, MODE>(ta, tb, P, grid, st);
-  return launch_conv_cfg<64, 8, MODE>(ta, tb, P, grid, st);
+  if (bn == 256) return launch_conv_cfg<256, 4, MODE>(ta, tb, P, ctas, st);
+  if (bn == 128) return launch_conv_cfg<128, 6, MODE>(ta, tb, P, ctas, st);
+  return launch_conv_cfg<64, 8, MODE>(ta, tb, P, ctas, st);
 }
 
 static inline void timing_begin(cudaEvent_t& e0, cudaEvent_t& e1, cudaStream_t st) {
@@ -191,10 +192,13 @@ static int32_t implicit_fprop(const b200_conv_desc* d, const ConvGeom& g, const 
   rc = make_tmap_bf16_2d(&tb, w, g.RSC, d->K, g.ldw, 64, bn);
   if (rc) return fail(B200_CUDA_ERROR, "conv_fprop: weight tensor map failed (%d)", rc);
   const long long tiles = (long long)b.tiles_w * b.tiles_h * b.tiles_n;
-  if (tiles > 65535) return fail(B200_UNSUPPORTED, "conv_fprop: too many pixel tiles (%lld)", tiles);
+  P.n_tiles = (d->K + bn - 1) / bn;
+  P.m_tiles = 1;
+  if (tiles * P.n_tiles > 0x7fffffffLL) return fail(B200_UNSUPPORTED, "conv_fprop: too many tiles");
+  P.total_tiles = (int)(tiles * P.n_tiles);
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   timing_begin(e0, e1, st);
-  rc = launch_conv_mode<MODE_FPROP>(bn, ta, tb, P, dim3((d->K + bn - 1) / bn, (unsigned)tiles, 1), st);
+  rc = launch_conv_mode<MODE_FPROP>(bn, ta, tb, P, st);
   timing_end(e0, e1, 2.0 * g.M * d->K * g.RSC, st);
   if (rc) return fail(B200_CUDA_ERROR, "conv_fprop: launch failed (%d)", rc);
   return B200_OK;
@@ -244,10 +248,13 @@ static int32_t implicit_dgrad(const b200_conv_desc* d, const ConvGeom& g, const 
               : make_tmap_bf16_nhwc(&ta, dy, d->N, g.Ho, g.Wo, d->K, b.bw, b.bh, b.bn, 1);
     if (rc) return fail(B200_CUDA_ERROR, "conv_dgrad: gradient tensor map failed (%d)", rc);
     const long long tiles = (long long)b.tiles_w * b.tiles_h * b.tiles_n;
-    if (tiles > 65535) return fail(B200_UNSUPPORTED, "conv_dgrad: too many pixel tiles (%lld)", tiles);
+    P.n_tiles = (d->C + bn - 1) / bn;
+    P.m_tiles = 1;
+    if (tiles * P.n_tiles > 0x7fffffffLL) return fail(B200_UNSUPPORTED, "conv_dgrad: too many tiles");
+    P.total_tiles = (int)(tiles * P.n_tiles);
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     timing_begin(e0, e1, st);
-    rc = launch_conv_mode<MODE_DGRAD>(bn, ta, tb, P, dim3((d->C + bn - 1) / bn, (unsigned)tiles, 1), st);
+    rc = launch_conv_mode<MODE_DGRAD>(bn, ta, tb, P, st);
     timing_end(e0, e1, 2.0 * Wq * Hq * Nq * (double)d->C * d->K * P.ntaps, st);
     if (rc) return fail(B200_CUDA_ERROR, "conv_dgrad: launch failed (%d)", rc);
   }
@@ -277,11 +284,12 @@ static int32_t implicit_wgrad(const b200_conv_desc* d, const ConvGeom& g, const 
   rc = flat ? make_tmap_bf16_nhwc(&tb, x, 1, 1, (int)g.M, d->C, P.bw, P.bh, P.bn, 1)
             : make_tmap_bf16_nhwc(&tb, x, d->N, d->H, d->W, d->C, P.bw, P.bh, P.bn, d->stride);
   if (rc) return fail(B200_CUDA_ERROR, "conv_wgrad: activation tensor map failed (%d)", rc);
-  dim3 grid((d->C + wp.bn_tile - 1) / wp.bn_tile, (d->K + 127) / 128, P.ntaps * wp.nsplits);
-  if (grid.z > 65535) return fail(B200_UNSUPPORTED, "conv_wgrad: too many split-K slabs");
+  P.n_tiles = (d->C + wp.bn_tile - 1) / wp.bn_tile;
+  P.m_tiles = (d->K + 127) / 128;
+  P.total_tiles = P.n_tiles * P.m_tiles * P.ntaps * wp.nsplits;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   timing_begin(e0, e1, st);
-  rc = launch_conv_mode<MODE_WGRAD>(wp.bn_tile, ta, tb, P, grid, st);
+  rc = launch_conv_mode<MODE_WGRAD>(wp.bn_tile, ta, tb, P, st);
   timing_end(e0, e1, 2.0 * g.M * d->K * g.RSC, st);
   if (rc) return fail(B200_CUDA_ERROR, "conv_wgrad: launch failed (%d)", rc);
   return launch_reduce_wgrad((const float*)ws, wp.nsplits, P.split_stride, d->K, d->C, d->R * d->S, g.ldw, dw, st);

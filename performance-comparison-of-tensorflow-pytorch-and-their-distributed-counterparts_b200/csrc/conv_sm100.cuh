@@ -46,6 +46,8 @@ struct ConvParams {
   int nsplits, pb_total, pb_per_split, x_mul;  // x_mul = conv stride (X box origin = tile origin * x_mul + shift)
   int kr;                                       // pixel rows per box = bw*bh*bn
   int mrows;                                    // valid cout rows
+  // persistent tile walk: tile = n_tile + n_tiles * (pixel tile | m_tile + m_tiles * (tap*nsplits + split))
+  int n_tiles, m_tiles, total_tiles;
 };
 
 template <int BN, int STAGES, int MODE>
@@ -55,13 +57,52 @@ constexpr int conv_smem_bytes() {
   return STAGES * (a + b) + 1024 + 256;
 }
 
+// Persistent kernel: grid = min(#tiles, #SMs); every CTA walks tiles blockIdx.x, blockIdx.x + gridDim.x, ...
+// TMEM holds TWO accumulators (2*BN columns) so the epilogue of tile i (TMEM -> registers -> global) overlaps the
+// TMA/MMA mainloop of tile i+1; the smem ring and its mbarrier phases run continuously across tiles.
+struct ConvTile {
+  int n0;                   // output-column tile origin
+  int q0, p0, i0;           // pixel-box origin (fprop/dgrad)
+  int m0, tap, split;       // wgrad
+  int kb_begin, kb_end;
+};
+template <int BN, int MODE>
+__device__ __forceinline__ ConvTile conv_decode_tile(const ConvParams& P, int tile) {
+  ConvTile t{};
+  const int nt = tile % P.n_tiles;
+  int rest = tile / P.n_tiles;
+  t.n0 = nt * BN;
+  if (MODE != MODE_WGRAD) {
+    const int tw = rest % P.tiles_w;
+    rest /= P.tiles_w;
+    const int th = rest % P.tiles_h;
+    const int tn = rest / P.tiles_h;
+    t.q0 = tw * P.bw;
+    t.p0 = th * P.bh;
+    t.i0 = tn * P.bn;
+    t.kb_begin = 0;
+    t.kb_end = P.ntaps * P.cchunks;
+  } else {
+    const int mt = rest % P.m_tiles;
+    rest /= P.m_tiles;
+    t.m0 = mt * GEMM_BM;
+    t.tap = rest / P.nsplits;
+    t.split = rest % P.nsplits;
+    t.kb_begin = t.split * P.pb_per_split;
+    t.kb_end = t.kb_begin + P.pb_per_split;
+    if (t.kb_end > P.pb_total) t.kb_end = P.pb_total;
+  }
+  return t;
+}
+
 template <int BN, int STAGES, int MODE>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                   const __grid_constant__ ConvParams P) {
   constexpr int A_BYTES = MODE == MODE_WGRAD ? 2 * CONV_KR_MAX * 128 : GEMM_BM * 128;
   constexpr int B_BYTES = MODE == MODE_WGRAD ? (BN / 64) * CONV_KR_MAX * 128 : BN * 128;
-  constexpr uint32_t TMEM_COLS = BN < 32 ? 32 : BN;
+  constexpr uint32_t TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;   // two accumulators
+  static_assert(2 * BN <= 512, "two accumulators must fit TMEM");
 
   extern __shared__ uint8_t smem_raw[];
   const uint32_t s0 = smem_u32(smem_raw);
@@ -70,35 +111,12 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   uint8_t* smB = smem + STAGES * A_BYTES;
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + STAGES * (A_BYTES + B_BYTES));
   uint64_t* empty = full + STAGES;
-  uint64_t* tmem_full = empty + STAGES;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+  uint64_t* tmem_full = empty + STAGES;    // [2]
+  uint64_t* tmem_empty = tmem_full + 2;    // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int n0 = blockIdx.x * BN;  // output-column tile (cout for fprop, cin for dgrad / wgrad)
-
-  // ---- tile decode
-  int q0 = 0, p0 = 0, i0 = 0;      // pixel-box origin (fprop/dgrad)
-  int m0 = 0, tap = 0, split = 0;  // wgrad
-  int kb_begin = 0, kb_end = 0;
-  if (MODE != MODE_WGRAD) {
-    int t = blockIdx.y;
-    const int tw = t % P.tiles_w;
-    t /= P.tiles_w;
-    const int th = t % P.tiles_h;
-    const int tn = t / P.tiles_h;
-    q0 = tw * P.bw;
-    p0 = th * P.bh;
-    i0 = tn * P.bn;
-    kb_end = P.ntaps * P.cchunks;
-  } else {
-    m0 = blockIdx.y * GEMM_BM;
-    tap = blockIdx.z / P.nsplits;
-    split = blockIdx.z % P.nsplits;
-    kb_begin = split * P.pb_per_split;
-    kb_end = kb_begin + P.pb_per_split;
-    if (kb_end > P.pb_total) kb_end = P.pb_total;
-  }
   const uint32_t box_bytes = static_cast<uint32_t>(P.bw * P.bh * P.bn) * 128u;
 
   if (threadIdx.x == 0) {
@@ -109,7 +127,11 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       mbar_init(&full[s], 1);
       mbar_init(&empty[s], 1);
     }
-    mbar_init(tmem_full, 1);
+#pragma unroll
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&tmem_full[b], 1);
+      mbar_init(&tmem_empty[b], 4);   // one arrive per epilogue warp
+    }
     mbar_fence_init();
   }
   if (warp == 1) {
@@ -120,43 +142,46 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const bool have_work = kb_end > kb_begin;
 
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer
     if (lane == 0) {
-      int i = 0;
-      for (int kb = kb_begin; kb < kb_end; ++kb, ++i) {
-        const int s = i % STAGES;
-        const uint32_t ph = (i / STAGES) & 1;
-        mbar_wait(&empty[s], ph ^ 1);
-        uint8_t* a = smA + s * A_BYTES;
-        uint8_t* b = smB + s * B_BYTES;
-        if (MODE != MODE_WGRAD) {
-          const int t = kb / P.cchunks, cc = kb - t * P.cchunks;
-          mbar_expect_tx(&full[s], box_bytes + B_BYTES);
-          tma_load_4d(a, &tmA, &full[s], cc * 64, q0 * P.a_mul + P.taps[t].dw, p0 * P.a_mul + P.taps[t].dh, i0);
-          if (MODE == MODE_FPROP) {
-            tma_load_2d(b, &tmB, &full[s], P.taps[t].bcol + cc * 64, n0);  // box {64 c, BN cout}
+      uint32_t i = 0;   // running k-block counter across tiles (ring position / phase)
+      for (int tile = blockIdx.x; tile < P.total_tiles; tile += gridDim.x) {
+        const ConvTile T = conv_decode_tile<BN, MODE>(P, tile);
+        for (int kb = T.kb_begin; kb < T.kb_end; ++kb, ++i) {
+          const int s = i % STAGES;
+          const uint32_t ph = (i / STAGES) & 1;
+          mbar_wait(&empty[s], ph ^ 1);
+          uint8_t* a = smA + s * A_BYTES;
+          uint8_t* b = smB + s * B_BYTES;
+          if (MODE != MODE_WGRAD) {
+            const int t = kb / P.cchunks, cc = kb - t * P.cchunks;
+            mbar_expect_tx(&full[s], box_bytes + B_BYTES);
+            tma_load_4d(a, &tmA, &full[s], cc * 64, T.q0 * P.a_mul + P.taps[t].dw, T.p0 * P.a_mul + P.taps[t].dh,
+                        T.i0);
+            if (MODE == MODE_FPROP) {
+              tma_load_2d(b, &tmB, &full[s], P.taps[t].bcol + cc * 64, T.n0);  // box {64 c, BN cout}
+            } else {
+#pragma unroll
+              for (int h = 0; h < BN / 64; ++h)
+                tma_load_2d(b + h * 8192, &tmB, &full[s], P.taps[t].bcol + T.n0 + h * 64, cc * 64);  // {64 cin, 64 k}
+            }
           } else {
+            int t = kb;
+            const int tw = t % P.tiles_w;
+            t /= P.tiles_w;
+            const int th = t % P.tiles_h;
+            const int tn = t / P.tiles_h;
+            const int bq = tw * P.bw, bp = th * P.bh, bi = tn * P.bn;
+            mbar_expect_tx(&full[s], box_bytes * (2 + BN / 64));
+#pragma unroll
+            for (int h = 0; h < 2; ++h) tma_load_4d(a + h * box_bytes, &tmA, &full[s], T.m0 + h * 64, bq, bp, bi);
 #pragma unroll
             for (int h = 0; h < BN / 64; ++h)
-              tma_load_2d(b + h * 8192, &tmB, &full[s], P.taps[t].bcol + n0 + h * 64, cc * 64);  // {64 cin, 64 k}
+              tma_load_4d(b + h * box_bytes, &tmB, &full[s], T.n0 + h * 64, bq * P.x_mul + P.taps[T.tap].dw,
+                          bp * P.x_mul + P.taps[T.tap].dh, bi);
           }
-        } else {
-          int t = kb;
-          const int tw = t % P.tiles_w;
-          t /= P.tiles_w;
-          const int th = t % P.tiles_h;
-          const int tn = t / P.tiles_h;
-          const int bq = tw * P.bw, bp = th * P.bh, bi = tn * P.bn;
-          mbar_expect_tx(&full[s], box_bytes * (2 + BN / 64));
-#pragma unroll
-          for (int h = 0; h < 2; ++h) tma_load_4d(a + h * box_bytes, &tmA, &full[s], m0 + h * 64, bq, bp, bi);
-#pragma unroll
-          for (int h = 0; h < BN / 64; ++h)
-            tma_load_4d(b + h * box_bytes, &tmB, &full[s], n0 + h * 64, bq * P.x_mul + P.taps[tap].dw,
-                        bp * P.x_mul + P.taps[tap].dh, bi);
         }
       }
     }
@@ -165,125 +190,143 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     // ------------------------------------------------------------ MMA issuer
     if (lane == 0) {
       constexpr uint32_t idesc = umma_idesc_bf16(GEMM_BM, BN, MODE == MODE_WGRAD, MODE != MODE_FPROP);
-      int i = 0;
-      for (int kb = kb_begin; kb < kb_end; ++kb, ++i) {
-        const int s = i % STAGES;
-        const uint32_t ph = (i / STAGES) & 1;
-        mbar_wait(&full[s], ph);
+      uint32_t i = 0;
+      uint32_t it = 0;   // local tile counter
+      for (int tile = blockIdx.x; tile < P.total_tiles; tile += gridDim.x, ++it) {
+        const ConvTile T = conv_decode_tile<BN, MODE>(P, tile);
+        const uint32_t buf = it & 1, use = it >> 1;
+        mbar_wait(&tmem_empty[buf], (use & 1) ^ 1);   // epilogue has drained this accumulator
         tc_fence_after();
-        const uint32_t a_addr = smem_u32(smA + s * A_BYTES);
-        const uint32_t b_addr = smem_u32(smB + s * B_BYTES);
-        if (MODE != MODE_WGRAD) {
+        const uint32_t d_tmem = tmem_base + buf * BN;
+        bool first = true;
+        for (int kb = T.kb_begin; kb < T.kb_end; ++kb, ++i) {
+          const int s = i % STAGES;
+          const uint32_t ph = (i / STAGES) & 1;
+          mbar_wait(&full[s], ph);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(smA + s * A_BYTES);
+          const uint32_t b_addr = smem_u32(smB + s * B_BYTES);
+          if (MODE != MODE_WGRAD) {
 #pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            const uint64_t adesc = umma_smem_desc(a_addr + k * 32, 16, 1024);
-            const uint64_t bdesc = MODE == MODE_FPROP ? umma_smem_desc(b_addr + k * 32, 16, 1024)
-                                                      : umma_smem_desc(b_addr + k * 2048, 8192, 1024);
-            umma_f16(tmem_base, adesc, bdesc, idesc, (i > 0 || k > 0) ? 1u : 0u);
+            for (int k = 0; k < 4; ++k) {
+              const uint64_t adesc = umma_smem_desc(a_addr + k * 32, 16, 1024);
+              const uint64_t bdesc = MODE == MODE_FPROP ? umma_smem_desc(b_addr + k * 32, 16, 1024)
+                                                        : umma_smem_desc(b_addr + k * 2048, 8192, 1024);
+              umma_f16(d_tmem, adesc, bdesc, idesc, (!first || k > 0) ? 1u : 0u);
+            }
+          } else {
+            const int ksteps = P.kr >> 4;
+            for (int k = 0; k < ksteps; ++k) {
+              const uint64_t adesc = umma_smem_desc(a_addr + k * 2048, box_bytes, 1024);
+              const uint64_t bdesc = umma_smem_desc(b_addr + k * 2048, box_bytes, 1024);
+              umma_f16(d_tmem, adesc, bdesc, idesc, (!first || k > 0) ? 1u : 0u);
+            }
           }
-        } else {
-          const int ksteps = P.kr >> 4;
-          for (int k = 0; k < ksteps; ++k) {
-            const uint64_t adesc = umma_smem_desc(a_addr + k * 2048, box_bytes, 1024);
-            const uint64_t bdesc = umma_smem_desc(b_addr + k * 2048, box_bytes, 1024);
-            umma_f16(tmem_base, adesc, bdesc, idesc, (i > 0 || k > 0) ? 1u : 0u);
-          }
+          first = false;
+          umma_commit(&empty[s]);
         }
-        umma_commit(&empty[s]);
+        umma_commit(&tmem_full[buf]);
       }
-      umma_commit(tmem_full);
     }
     __syncwarp();
   } else {
     // ------------------------------------------------------------ epilogue warps
     const int q = warp & 3;
     const int l = q * 32 + lane;  // accumulator row
-    if (have_work) {
-      mbar_wait(tmem_full, 0);
+    uint32_t it = 0;
+    for (int tile = blockIdx.x; tile < P.total_tiles; tile += gridDim.x, ++it) {
+      const ConvTile T = conv_decode_tile<BN, MODE>(P, tile);
+      const uint32_t buf = it & 1, use = it >> 1;
+      const bool have_work = T.kb_end > T.kb_begin;
+      mbar_wait(&tmem_full[buf], use & 1);
       tc_fence_after();
-    }
-    bool row_ok;
-    long long row_off;
-    if (MODE != MODE_WGRAD) {
-      const int iw = l % P.bw;
-      const int t = l / P.bw;
-      const int ih = t % P.bh;
-      const int in = t / P.bh;
-      const int ow = (q0 + iw) * P.o_mul + P.o_off_w;
-      const int oh = (p0 + ih) * P.o_mul + P.o_off_h;
-      const int on = i0 + in;
-      row_ok = in < P.bn && ow < P.Wout && oh < P.Hout && on < P.Nout;
-      row_off = ((static_cast<long long>(on) * P.Hout + oh) * P.Wout + ow) * P.ldo;
-    } else {
-      row_ok = (m0 + l) < P.mrows;
-      row_off = static_cast<long long>(blockIdx.z % P.nsplits) * P.split_stride +
-                static_cast<long long>(m0 + l) * P.ldo + P.taps[tap].bcol;
-    }
+      bool row_ok;
+      long long row_off;
+      if (MODE != MODE_WGRAD) {
+        const int iw = l % P.bw;
+        const int t = l / P.bw;
+        const int ih = t % P.bh;
+        const int in = t / P.bh;
+        const int ow = (T.q0 + iw) * P.o_mul + P.o_off_w;
+        const int oh = (T.p0 + ih) * P.o_mul + P.o_off_h;
+        const int on = T.i0 + in;
+        row_ok = in < P.bn && ow < P.Wout && oh < P.Hout && on < P.Nout;
+        row_off = ((static_cast<long long>(on) * P.Hout + oh) * P.Wout + ow) * P.ldo;
+      } else {
+        row_ok = (T.m0 + l) < P.mrows;
+        row_off = static_cast<long long>(T.split) * P.split_stride + static_cast<long long>(T.m0 + l) * P.ldo +
+                  P.taps[T.tap].bcol;
+      }
 #pragma unroll 1
-    for (int c = 0; c < BN / 32; ++c) {
-      uint32_t r[32];
-      if (have_work) {
-        tmem_ld_32x32b_x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(c * 32), r);
-        tmem_ld_wait();
-      } else {
-#pragma unroll
-        for (int j = 0; j < 32; ++j) r[j] = 0u;
-      }
-      const int col0 = n0 + c * 32;
-      if (!row_ok || col0 >= P.ncols) continue;
-      if (P.out_fp32) {
-        float* p = reinterpret_cast<float*>(P.out) + row_off + col0;
-        if (P.vec_ok && col0 + 32 <= P.ncols) {
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            float4 v = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]),
-                                   __uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3]));
-            if (P.accumulate) {
-              float4 o = reinterpret_cast<float4*>(p)[j];
-              v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w;
-            }
-            reinterpret_cast<float4*>(p)[j] = v;
-          }
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t r[32];
+        if (have_work) {
+          tmem_ld_32x32b_x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * BN + static_cast<uint32_t>(c * 32), r);
+          tmem_ld_wait();
         } else {
 #pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (col0 + j < P.ncols) p[j] = (P.accumulate ? p[j] : 0.f) + __uint_as_float(r[j]);
+          for (int j = 0; j < 32; ++j) r[j] = 0u;
         }
-      } else {
-        __nv_bfloat16* p = reinterpret_cast<__nv_bfloat16*>(P.out) + row_off + col0;
-        if (P.vec_ok && col0 + 32 <= P.ncols) {
+        const int col0 = T.n0 + c * 32;
+        if (!row_ok || col0 >= P.ncols) continue;
+        if (P.out_fp32) {
+          float* p = reinterpret_cast<float*>(P.out) + row_off + col0;
+          if (P.vec_ok && col0 + 32 <= P.ncols) {
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            float f[8];
-#pragma unroll
-            for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(r[8 * j + e]);
-            if (P.accumulate) {
-              uint4 o = reinterpret_cast<uint4*>(p)[j];
-              const __nv_bfloat162* ob = reinterpret_cast<const __nv_bfloat162*>(&o);
-#pragma unroll
-              for (int e = 0; e < 4; ++e) {
-                float2 t2 = __bfloat1622float2(ob[e]);
-                f[2 * e] += t2.x;
-                f[2 * e + 1] += t2.y;
+            for (int j = 0; j < 8; ++j) {
+              float4 v = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]),
+                                     __uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3]));
+              if (P.accumulate) {
+                float4 o = reinterpret_cast<float4*>(p)[j];
+                v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w;
               }
+              reinterpret_cast<float4*>(p)[j] = v;
             }
-            uint4 v;
-            v.x = pack_bf16x2(f[0], f[1]);
-            v.y = pack_bf16x2(f[2], f[3]);
-            v.z = pack_bf16x2(f[4], f[5]);
-            v.w = pack_bf16x2(f[6], f[7]);
-            reinterpret_cast<uint4*>(p)[j] = v;
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (col0 + j < P.ncols) p[j] = (P.accumulate ? p[j] : 0.f) + __uint_as_float(r[j]);
           }
         } else {
+          __nv_bfloat16* p = reinterpret_cast<__nv_bfloat16*>(P.out) + row_off + col0;
+          if (P.vec_ok && col0 + 32 <= P.ncols) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (col0 + j < P.ncols) {
-              float f = __uint_as_float(r[j]);
-              if (P.accumulate) f += __bfloat162float(p[j]);
-              p[j] = __float2bfloat16_rn(f);
+            for (int j = 0; j < 4; ++j) {
+              float f[8];
+#pragma unroll
+              for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(r[8 * j + e]);
+              if (P.accumulate) {
+                uint4 o = reinterpret_cast<uint4*>(p)[j];
+                const __nv_bfloat162* ob = reinterpret_cast<const __nv_bfloat162*>(&o);
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                  float2 t2 = __bfloat1622float2(ob[e]);
+                  f[2 * e] += t2.x;
+                  f[2 * e + 1] += t2.y;
+                }
+              }
+              uint4 v;
+              v.x = pack_bf16x2(f[0], f[1]);
+              v.y = pack_bf16x2(f[2], f[3]);
+              v.z = pack_bf16x2(f[4], f[5]);
+              v.w = pack_bf16x2(f[6], f[7]);
+              reinterpret_cast<uint4*>(p)[j] = v;
             }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (col0 + j < P.ncols) {
+                float f = __uint_as_float(r[j]);
+                if (P.accumulate) f += __bfloat162float(p[j]);
+                p[j] = __float2bfloat16_rn(f);
+              }
+          }
         }
       }
+      // this warp has finished reading the accumulator: hand it back to the MMA issuer
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tmem_empty[buf]);
     }
   }
 
@@ -340,7 +383,7 @@ inline PixelBox choose_pixel_box(int W, int H, int N, int max_rows, int mult, in
 }
 
 template <int BN, int STAGES, int MODE>
-inline int launch_conv_cfg(const CUtensorMap& ta, const CUtensorMap& tb, const ConvParams& P, dim3 grid,
+inline int launch_conv_cfg(const CUtensorMap& ta, const CUtensorMap& tb, const ConvParams& P, int num_ctas,
                            cudaStream_t st) {
   auto kern = conv_sm100_kernel<BN, STAGES, MODE>;
   constexpr int smem = conv_smem_bytes<BN, STAGES, MODE>();
@@ -350,6 +393,7 @@ inline int launch_conv_cfg(const CUtensorMap& ta, const CUtensorMap& tb, const C
     if (e != cudaSuccess) return 300 + static_cast<int>(e);
     attr_done = true;
   }
+  const int grid = P.total_tiles < num_ctas ? P.total_tiles : num_ctas;
   kern<<<grid, GEMM_THREADS, smem, st>>>(ta, tb, P);
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? 0 : 400 + static_cast<int>(e);
