@@ -40,16 +40,19 @@ int32_t b200_gemm_timing_read(double* total_ms, int64_t* launches, double* flops
 /* ------------------------------------------------------------------ layout / packing
  * inputs.to(device) hands the model NCHW fp32 (pytorch_training_inference_on_image.ipynb:667); the first kernel
  * converts to the internal NHWC layout (and to bf16 in bf16 mode). */
+/* Cpad >= C: channels of the NHWC output (extra channels are written as zero; used to widen the 3-channel
+ * image to 8-byte pixels for the stem convolution). */
 int32_t b200_nchw_to_nhwc(const float* x_nchw, void* y_nhwc, int32_t N, int32_t C, int32_t H, int32_t W,
-                          int32_t out_dtype, void* stream);
+                          int32_t Cpad, int32_t out_dtype, void* stream);
 int32_t b200_nhwc_to_nchw(const void* x_nhwc, float* y_nchw, int32_t N, int32_t C, int32_t H, int32_t W,
                           int32_t in_dtype, void* stream);
 /* OIHW fp32 parameter -> [K][ld] (dtype) with column (r*S+s)*C+c: the K-major operand of the implicit GEMM.
  * ld >= R*S*C is the row stride, zero-filled past R*S*C (b200_conv_weight_ld gives the value the conv entry
  * points expect: R*S*C rounded up to a multiple of 8). */
 int32_t b200_conv_weight_ld(int32_t R, int32_t S, int32_t C);
-int32_t b200_pack_weight(const float* w_oihw, void* w_krsc, int32_t K, int32_t C, int32_t R, int32_t S,
-                         int32_t ld, int32_t out_dtype, void* stream);
+/* Cw = channels of the parameter, C >= Cw = channels of the packed operand (zero-filled beyond Cw). */
+int32_t b200_pack_weight(const float* w_oihw, void* w_krsc, int32_t K, int32_t Cw, int32_t R, int32_t S,
+                         int32_t C, int32_t ld, int32_t out_dtype, void* stream);
 /* dtype cast of a flat buffer (fp32 <-> bf16) */
 int32_t b200_cast(const void* x, void* y, int64_t n, int32_t in_dtype, int32_t out_dtype, void* stream);
 

@@ -38,10 +38,10 @@ SIGNATURES = {
     "b200_launch_count": (I64, []),
     "b200_gemm_timing_enable": (I32, [I32]),
     "b200_gemm_timing_read": (I32, [POINTER(ctypes.c_double), POINTER(c_int64), POINTER(ctypes.c_double)]),
-    "b200_nchw_to_nhwc": (I32, [P, P, I32, I32, I32, I32, I32, P]),
+    "b200_nchw_to_nhwc": (I32, [P, P, I32, I32, I32, I32, I32, I32, P]),
     "b200_nhwc_to_nchw": (I32, [P, P, I32, I32, I32, I32, I32, P]),
     "b200_conv_weight_ld": (I32, [I32, I32, I32]),
-    "b200_pack_weight": (I32, [P, P, I32, I32, I32, I32, I32, I32, P]),
+    "b200_pack_weight": (I32, [P, P, I32, I32, I32, I32, I32, I32, I32, P]),
     "b200_cast": (I32, [P, P, I64, I32, I32, P]),
     "b200_conv_workspace_bytes": (I64, [POINTER(ConvDesc), I32]),
     "b200_conv_fprop": (I32, [POINTER(ConvDesc), P, P, P, P, I64, P]),

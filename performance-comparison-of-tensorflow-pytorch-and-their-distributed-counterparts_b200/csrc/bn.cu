@@ -41,26 +41,42 @@ bn_partial_kernel(const T* __restrict__ x, const T* __restrict__ dz, const T* __
 #pragma unroll
         for (int e = 0; e < VEC; ++e) mu[e] = mean[cv * VEC + e];
       }
-      for (long long r = r0 + ty; r < r1; r += ry) {
-        const long long off = r * C + (long long)cv * VEC;
-        float xv[VEC];
-        if constexpr (VEC == 1) xv[0] = to_f(x[off]);
-        else load_vec(x + off, reinterpret_cast<float(&)[VecTraits<T>::W]>(xv));
-        if (!BWD) {
+      // U rows in flight per thread: all loads of an iteration are issued before any of them is consumed
+      constexpr int U = BWD ? 2 : 4;
+      for (long long r = r0 + ty; r < r1; r += (long long)U * ry) {
+        float xv[U][VEC], gv[BWD ? U : 1][VEC], zv[BWD ? U : 1][VEC];
+        bool ok[U];
 #pragma unroll
-          for (int e = 0; e < VEC; ++e) { s0[e] += xv[e]; s1[e] = fmaf(xv[e], xv[e], s1[e]); }
-        } else {
-          float gv[VEC], zv[VEC];
-          if constexpr (VEC == 1) { gv[0] = to_f(dz[off]); zv[0] = relu ? to_f(z[off]) : 1.f; }
-          else {
-            load_vec(dz + off, reinterpret_cast<float(&)[VecTraits<T>::W]>(gv));
-            if (relu) load_vec(z + off, reinterpret_cast<float(&)[VecTraits<T>::W]>(zv));
+        for (int u = 0; u < U; ++u) {
+          const long long rr = r + (long long)u * ry;
+          ok[u] = rr < r1;
+          if (ok[u]) {
+            const long long off = rr * C + (long long)cv * VEC;
+            if constexpr (VEC == 1) {
+              xv[u][0] = to_f(x[off]);
+              if (BWD) { gv[u][0] = to_f(dz[off]); zv[u][0] = relu ? to_f(z[off]) : 1.f; }
+            } else {
+              load_vec(x + off, reinterpret_cast<float(&)[VecTraits<T>::W]>(xv[u]));
+              if (BWD) {
+                load_vec(dz + off, reinterpret_cast<float(&)[VecTraits<T>::W]>(gv[u]));
+                if (relu) load_vec(z + off, reinterpret_cast<float(&)[VecTraits<T>::W]>(zv[u]));
+              }
+            }
           }
+        }
 #pragma unroll
-          for (int e = 0; e < VEC; ++e) {
-            const float g = (!relu || zv[e] > 0.f) ? gv[e] : 0.f;
-            s0[e] += g;
-            s1[e] = fmaf(g, xv[e] - mu[e], s1[e]);
+        for (int u = 0; u < U; ++u) {
+          if (!ok[u]) continue;
+          if (!BWD) {
+#pragma unroll
+            for (int e = 0; e < VEC; ++e) { s0[e] += xv[u][e]; s1[e] = fmaf(xv[u][e], xv[u][e], s1[e]); }
+          } else {
+#pragma unroll
+            for (int e = 0; e < VEC; ++e) {
+              const float g = (!relu || zv[u][e] > 0.f) ? gv[u][e] : 0.f;
+              s0[e] += g;
+              s1[e] = fmaf(g, xv[u][e] - mu[e], s1[e]);
+            }
           }
         }
       }
@@ -285,8 +301,9 @@ static BnPlan bn_plan(long long rows, int C) {
   p.cx = pow2_ceil(nvec);
   if (p.cx > BN_THREADS) p.cx = BN_THREADS;
   const int ry = BN_THREADS / p.cx;
-  // at least 8 rows per row-lane, at most BN_MAX_BLOCKS blocks
-  long long rpb = (long long)ry * 8;
+  // at least 32 rows per row-lane (keeps the partial-sum traffic far below the tensor's own bytes when C is large),
+  // at most BN_MAX_BLOCKS blocks
+  long long rpb = (long long)ry * 16;
   long long nblk = (rows + rpb - 1) / rpb;
   if (nblk > BN_MAX_BLOCKS) {
     rpb = (rows + BN_MAX_BLOCKS - 1) / BN_MAX_BLOCKS;

@@ -7,14 +7,14 @@ namespace b200 {
 // ---------------------------------------------------------------- NCHW <-> NHWC
 // small C (images, C<=4): one thread per pixel, coalesced plane reads, contiguous pixel writes
 template <typename T>
-__global__ void nchw_to_nhwc_smallc(const float* __restrict__ x, T* __restrict__ y, int C, long long HW,
+__global__ void nchw_to_nhwc_smallc(const float* __restrict__ x, T* __restrict__ y, int C, int Cpad, long long HW,
                                     long long total_pix) {
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total_pix;
        i += (long long)gridDim.x * blockDim.x) {
     const long long n = i / HW, hw = i - n * HW;
     const float* src = x + n * C * HW + hw;
-    T* dst = y + i * C;
-    for (int c = 0; c < C; ++c) dst[c] = from_f<T>(src[c * HW]);
+    T* dst = y + i * Cpad;
+    for (int c = 0; c < Cpad; ++c) dst[c] = from_f<T>(c < C ? src[c * HW] : 0.f);
   }
 }
 // general: per image transpose [C][HW] -> [HW][C] through a 32x33 smem tile
@@ -39,8 +39,9 @@ __global__ void transpose_batched(const TI* __restrict__ x, TO* __restrict__ y, 
 
 // ---------------------------------------------------------------- weights: OIHW fp32 -> [K][ld] with (r,s,c) order
 template <typename T>
-__global__ void pack_weight_kernel(const float* __restrict__ w, T* __restrict__ out, int K, int C, int R, int S,
-                                   int ld) {
+__global__ void pack_weight_kernel(const float* __restrict__ w, T* __restrict__ out, int K, int Cw, int C, int R,
+                                   int S, int ld) {
+  // Cw = channels of the OIHW parameter, C >= Cw = channels of the packed operand (extra channels are zero)
   const long long total = (long long)K * ld;
   const int RSC = R * S * C;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
@@ -49,7 +50,7 @@ __global__ void pack_weight_kernel(const float* __restrict__ w, T* __restrict__ 
     float v = 0.f;
     if (j < RSC) {
       const int c = j % C, rs = j / C;
-      v = w[((long long)k * C + c) * (R * S) + rs];
+      if (c < Cw) v = w[((long long)k * Cw + c) * (R * S) + rs];
     }
     out[i] = from_f<T>(v);
   }
@@ -84,14 +85,12 @@ __global__ void im2col_kernel(const T* __restrict__ x, T* __restrict__ col, int 
     if (h >= 0 && h < H && w >= 0 && w < W) {
       const T* src = x + (((long long)n * H + h) * W + w) * C + c;
       if constexpr (VEC == 1) dst[0] = src[0];
-      else *reinterpret_cast<typename VecTraits<T>::V*>(dst) = *reinterpret_cast<const typename VecTraits<T>::V*>(src);
+      else if constexpr (VEC * sizeof(T) == 8) *reinterpret_cast<uint2*>(dst) = *reinterpret_cast<const uint2*>(src);
+      else *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(src);
     } else {
       if constexpr (VEC == 1) dst[0] = from_f<T>(0.f);
-      else {
-        typename VecTraits<T>::V z;
-        memset(&z, 0, sizeof(z));
-        *reinterpret_cast<typename VecTraits<T>::V*>(dst) = z;
-      }
+      else if constexpr (VEC * sizeof(T) == 8) *reinterpret_cast<uint2*>(dst) = make_uint2(0u, 0u);
+      else *reinterpret_cast<uint4*>(dst) = make_uint4(0u, 0u, 0u, 0u);
     }
   }
 }
@@ -190,6 +189,8 @@ int32_t launch_im2col(const void* x, void* col, int dtype, int N, int H, int W, 
   } else {
     if (C % 8 == 0 && ld % 8 == 0)
       im2col_kernel<__nv_bfloat16, 8><<<grid_for(M * R * S * (C / 8)), 256, 0, st>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)col, N, H, W, C, R, S, stride, pad, Ho, Wo, ld);
+    else if (C % 4 == 0 && ld % 4 == 0)   // the channel-padded stem: 8-byte pixels
+      im2col_kernel<__nv_bfloat16, 4><<<grid_for(M * R * S * (C / 4), 256, 32), 256, 0, st>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)col, N, H, W, C, R, S, stride, pad, Ho, Wo, ld);
     else
       im2col_kernel<__nv_bfloat16, 1><<<grid_for(M * R * S * C), 256, 0, st>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)col, N, H, W, C, R, S, stride, pad, Ho, Wo, ld);
     if (ld > R * S * C) im2col_pad_kernel<__nv_bfloat16><<<grid_for(M * (ld - R * S * C)), 256, 0, st>>>((__nv_bfloat16*)col, M, R * S * C, ld);
@@ -224,13 +225,14 @@ int32_t launch_reduce_plain(const float* part, int slabs, long long slab_stride,
 using namespace b200;
 
 extern "C" int32_t b200_nchw_to_nhwc(const float* x, void* y, int32_t N, int32_t C, int32_t H, int32_t W,
-                                     int32_t out_dtype, void* stream) {
-  if (!x || !y || N <= 0 || C <= 0 || H <= 0 || W <= 0) return fail(B200_INVALID_ARG, "nchw_to_nhwc: bad args");
+                                     int32_t Cpad, int32_t out_dtype, void* stream) {
+  if (!x || !y || N <= 0 || C <= 0 || H <= 0 || W <= 0 || Cpad < C) return fail(B200_INVALID_ARG, "nchw_to_nhwc: bad args");
+  if (Cpad != C && Cpad > 4) return fail(B200_UNSUPPORTED, "nchw_to_nhwc: channel padding is supported up to 4 channels");
   cudaStream_t st = as_stream(stream);
   const long long HW = (long long)H * W;
-  if (C <= 4) {
-    if (out_dtype == B200_F32) nchw_to_nhwc_smallc<float><<<grid_for(N * HW), 256, 0, st>>>(x, (float*)y, C, HW, N * HW);
-    else if (out_dtype == B200_BF16) nchw_to_nhwc_smallc<__nv_bfloat16><<<grid_for(N * HW), 256, 0, st>>>(x, (__nv_bfloat16*)y, C, HW, N * HW);
+  if (Cpad <= 4) {
+    if (out_dtype == B200_F32) nchw_to_nhwc_smallc<float><<<grid_for(N * HW), 256, 0, st>>>(x, (float*)y, C, Cpad, HW, N * HW);
+    else if (out_dtype == B200_BF16) nchw_to_nhwc_smallc<__nv_bfloat16><<<grid_for(N * HW), 256, 0, st>>>(x, (__nv_bfloat16*)y, C, Cpad, HW, N * HW);
     else return fail(B200_INVALID_ARG, "bad dtype");
   } else {
     dim3 grid((unsigned)((HW + 31) / 32), (C + 31) / 32, N), block(32, 8);
@@ -253,12 +255,12 @@ extern "C" int32_t b200_nhwc_to_nchw(const void* x, float* y, int32_t N, int32_t
   return check_launch("nhwc_to_nchw");
 }
 
-extern "C" int32_t b200_pack_weight(const float* w, void* out, int32_t K, int32_t C, int32_t R, int32_t S, int32_t ld,
-                                    int32_t out_dtype, void* stream) {
-  if (!w || !out || ld < R * S * C) return fail(B200_INVALID_ARG, "pack_weight: bad args");
+extern "C" int32_t b200_pack_weight(const float* w, void* out, int32_t K, int32_t Cw, int32_t R, int32_t S,
+                                    int32_t C, int32_t ld, int32_t out_dtype, void* stream) {
+  if (!w || !out || C < Cw || ld < R * S * C) return fail(B200_INVALID_ARG, "pack_weight: bad args");
   cudaStream_t st = as_stream(stream);
-  if (out_dtype == B200_F32) pack_weight_kernel<float><<<grid_for((long long)K * ld), 256, 0, st>>>(w, (float*)out, K, C, R, S, ld);
-  else if (out_dtype == B200_BF16) pack_weight_kernel<__nv_bfloat16><<<grid_for((long long)K * ld), 256, 0, st>>>(w, (__nv_bfloat16*)out, K, C, R, S, ld);
+  if (out_dtype == B200_F32) pack_weight_kernel<float><<<grid_for((long long)K * ld), 256, 0, st>>>(w, (float*)out, K, Cw, C, R, S, ld);
+  else if (out_dtype == B200_BF16) pack_weight_kernel<__nv_bfloat16><<<grid_for((long long)K * ld), 256, 0, st>>>(w, (__nv_bfloat16*)out, K, Cw, C, R, S, ld);
   else return fail(B200_INVALID_ARG, "bad dtype");
   return check_launch("pack_weight");
 }

@@ -119,11 +119,80 @@ sgemm_kernel(const float* __restrict__ A, const float* __restrict__ B, float* __
   }
 }
 
+// Small-problem variant: 32x32 output tiles (2x2 per thread), BK = 32.  The head's GEMMs ([256 x 2048] x [512 x 2048]^T
+// and friends) give only a handful of 128x128 tiles; 32x32 tiles spread them over every SM.
+template <bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(256)
+sgemm_small_kernel(const float* __restrict__ A, const float* __restrict__ B, float* __restrict__ C, int M, int N, int K,
+                   long long lda, long long ldb, long long ldc, const float* __restrict__ bias, int relu,
+                   int accumulate) {
+  __shared__ float As[32][33];  // [k][m]
+  __shared__ float Bs[32][33];  // [k][n]
+  const int t = threadIdx.x;
+  const int tx = t & 15, ty = t >> 4;
+  const int m0 = blockIdx.y * 32, n0 = blockIdx.x * 32;
+  float acc[2][2] = {{0.f, 0.f}, {0.f, 0.f}};
+  for (int k0 = 0; k0 < K; k0 += 32) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int idx = t + j * 256;
+      int m, k;
+      if (!A_MN) { k = idx & 31; m = idx >> 5; } else { m = idx & 31; k = idx >> 5; }
+      const int gm = m0 + m, gk = k0 + k;
+      float v = 0.f;
+      if (gm < M && gk < K) v = A_MN ? A[(long long)gk * lda + gm] : A[(long long)gm * lda + gk];
+      As[k][m] = v;
+      int n;
+      if (!B_MN) { k = idx & 31; n = idx >> 5; } else { n = idx & 31; k = idx >> 5; }
+      const int gn = n0 + n;
+      const int gk2 = k0 + k;
+      v = 0.f;
+      if (gn < N && gk2 < K) v = B_MN ? B[(long long)gk2 * ldb + gn] : B[(long long)gn * ldb + gk2];
+      Bs[k][n] = v;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < 32; ++kk) {
+      const float a0 = As[kk][ty], a1 = As[kk][ty + 16];
+      const float b0 = Bs[kk][tx], b1 = Bs[kk][tx + 16];
+      acc[0][0] = fmaf(a0, b0, acc[0][0]);
+      acc[0][1] = fmaf(a0, b1, acc[0][1]);
+      acc[1][0] = fmaf(a1, b0, acc[1][0]);
+      acc[1][1] = fmaf(a1, b1, acc[1][1]);
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    const int m = m0 + ty + i * 16;
+    if (m >= M) continue;
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const int n = n0 + tx + j * 16;
+      if (n >= N) continue;
+      float v = acc[i][j];
+      if (bias) v += bias[n];
+      float* p = C + (long long)m * ldc + n;
+      if (accumulate) v += *p;
+      if (relu) v = fmaxf(v, 0.f);
+      *p = v;
+    }
+  }
+}
+
 int32_t launch_sgemm(const float* A, const float* B, float* C, int M, int N, int K, long long lda, long long ldb,
                      long long ldc, bool a_mn, bool b_mn, const float* bias, int relu, int accumulate, int splits,
                      long long split_stride, cudaStream_t st) {
   if (M <= 0 || N <= 0 || K <= 0) return fail(B200_INVALID_ARG, "sgemm: empty problem");
   if (splits < 1) splits = 1;
+  if (splits == 1 && (long long)((M + SG_BM - 1) / SG_BM) * ((N + SG_BN - 1) / SG_BN) < num_sms() / 2) {
+    dim3 g((N + 31) / 32, (M + 31) / 32);
+    if (!a_mn && !b_mn) sgemm_small_kernel<false, false><<<g, 256, 0, st>>>(A, B, C, M, N, K, lda, ldb, ldc, bias, relu, accumulate);
+    else if (!a_mn && b_mn) sgemm_small_kernel<false, true><<<g, 256, 0, st>>>(A, B, C, M, N, K, lda, ldb, ldc, bias, relu, accumulate);
+    else if (a_mn && !b_mn) sgemm_small_kernel<true, false><<<g, 256, 0, st>>>(A, B, C, M, N, K, lda, ldb, ldc, bias, relu, accumulate);
+    else sgemm_small_kernel<true, true><<<g, 256, 0, st>>>(A, B, C, M, N, K, lda, ldb, ldc, bias, relu, accumulate);
+    return check_launch("sgemm_small");
+  }
   int k_per = ((K + splits - 1) / splits + SG_BK - 1) / SG_BK * SG_BK;
   splits = (K + k_per - 1) / k_per;
   const int a_vec = ((reinterpret_cast<uintptr_t>(A) & 15) == 0) && (lda % 4 == 0);

@@ -54,14 +54,20 @@ def set_grad_sink(fn):
 _PACKED = {}
 
 
-def packed_weight(w, dtype):
+def packed_weight(w, dtype, cpad=None):
     key = id(w)
     e = _PACKED.get(key)
-    if e is not None and e[0] == w.data_ptr() and e[1] == w._version and e[2] == dtype:
+    if e is not None and e[0] == w.data_ptr() and e[1] == w._version and e[2] == dtype and e[4] == cpad:
         return e[3]
-    p = ops.pack_weight(w, dtype)
-    _PACKED[key] = (w.data_ptr(), w._version, dtype, p)
+    p = ops.pack_weight(w, dtype, cpad)
+    _PACKED[key] = (w.data_ptr(), w._version, dtype, p, cpad)
     return p
+
+
+def _stem_cpad(conv, dtype):
+    """3-channel images are widened to 4 channels (8-byte pixels) in bf16 mode so the stem's staging copies move
+    8 bytes at a time; the fourth channel and its weights are zero."""
+    return 4 if (dtype == torch.bfloat16 and conv.in_channels == 3) else None
 
 
 def _conv_geom(conv):
@@ -104,7 +110,7 @@ class _Unit(object):
 
 def _unit_forward(conv, bn, x, relu, residual, save):
     K, R, S, stride, pad = _conv_geom(conv)
-    wp = packed_weight(conv.weight, x.dtype)
+    wp = packed_weight(conv.weight, x.dtype, x.shape[-1] if x.shape[-1] != conv.in_channels else None)
     y = ops.conv_fprop(x, wp, K, R, S, stride, pad)
     scale, shift, mean, invstd = _bn_coeffs(bn, y, bump_nbt=False)
     # eval mode: y is dead after the apply -> write in place
@@ -145,7 +151,7 @@ class _ResNetBackbone(torch.autograd.Function):
                and m.num_batches_tracked is not None and not _under(model.fc, m, model)]
         if nbt:
             torch._foreach_add_(nbt, 1)
-        xh = ops.to_nhwc(x, dtype)
+        xh = ops.to_nhwc(x, dtype, _stem_cpad(model.conv1, dtype))
         units = []
         z, u = _unit_forward(model.conv1, model.bn1, xh, True, None, save)
         units.append(u)
@@ -200,12 +206,16 @@ class _ResNetBackbone(torch.autograd.Function):
                     emit(u.bn.weight, dgamma)
             K, R, S, stride, pad = u.geom
             if u.conv.weight.requires_grad:
-                emit(u.conv.weight, ops.conv_wgrad(u.x, dy, K, R, S, stride, pad))
+                dw = ops.conv_wgrad(u.x, dy, K, R, S, stride, pad)
+                if dw.shape[1] != u.conv.in_channels:      # channel-padded stem: drop the zero channel
+                    dw = dw[:, :u.conv.in_channels].contiguous()
+                emit(u.conv.weight, dw)
             return dy, dres
 
         def dgrad(u, dy, out=None, accumulate=False):
             K, R, S, stride, pad = u.geom
-            wp = packed_weight(u.conv.weight, dy.dtype)
+            cin = u.x.shape[-1]
+            wp = packed_weight(u.conv.weight, dy.dtype, cin if cin != u.conv.in_channels else None)
             return ops.conv_dgrad(dy, wp, u.x.shape, K, R, S, stride, pad, out=out, accumulate=accumulate)
 
         dcur = ops.avgpool_bwd(dfeat, ctx.final_shape, ctx.dtype)
@@ -226,7 +236,7 @@ class _ResNetBackbone(torch.autograd.Function):
         dy0, _ = unit_backward(u0, dz0, want_dres=False)
         dx = None
         if ctx.x_needs_grad:
-            dx = ops.to_nchw(dgrad(u0, dy0))
+            dx = ops.to_nchw(dgrad(u0, dy0))[:, :u0.conv.in_channels].contiguous()
         out = (None, dx) + tuple(grads.get(id(p)) if need else None for p, need in zip(ctx.params, ctx.param_needs))
         ctx.blocks = None
         ctx.units0 = None

@@ -43,15 +43,17 @@ def workspace(nbytes, device):
 
 
 # ------------------------------------------------------------------ layout
-def to_nhwc(x, dtype):
-    """NCHW fp32 (what the reference's loaders produce, ...on_image.ipynb:667) -> NHWC `dtype`."""
+def to_nhwc(x, dtype, cpad=None):
+    """NCHW fp32 (what the reference's loaders produce, ...on_image.ipynb:667) -> NHWC `dtype`.
+    cpad widens the channel dimension with zeros (3-channel images -> 8-byte bf16 pixels for the stem)."""
     _need_cuda(x)
     if x.dtype != torch.float32:
         x = x.float()
     x = x.contiguous()
     N, C, H, W = x.shape
-    y = torch.empty((N, H, W, C), dtype=dtype, device=x.device)
-    check(lib.b200_nchw_to_nhwc(x.data_ptr(), y.data_ptr(), N, C, H, W, _DT[dtype], _stream()), "nchw_to_nhwc")
+    cp = C if cpad is None else cpad
+    y = torch.empty((N, H, W, cp), dtype=dtype, device=x.device)
+    check(lib.b200_nchw_to_nhwc(x.data_ptr(), y.data_ptr(), N, C, H, W, cp, _DT[dtype], _stream()), "nchw_to_nhwc")
     return y
 
 
@@ -67,16 +69,18 @@ def weight_ld(R, S, C):
     return (R * S * C + 7) // 8 * 8
 
 
-def pack_weight(w, dtype):
-    """OIHW fp32 parameter -> [K][ld] `dtype`, (r,s,c) column order."""
+def pack_weight(w, dtype, cpad=None):
+    """OIHW fp32 parameter -> [K][ld] `dtype`, (r,s,c) column order; cpad >= C zero-pads the channel dimension."""
     _need_cuda(w)
-    K, C, R, S = w.shape
+    K, Cw, R, S = w.shape
+    C = Cw if cpad is None else cpad
     ld = weight_ld(R, S, C)
     out = torch.empty((K, ld), dtype=dtype, device=w.device)
     wd = w.detach()
     if wd.dtype != torch.float32 or not wd.is_contiguous():
         wd = wd.float().contiguous()
-    check(lib.b200_pack_weight(wd.data_ptr(), out.data_ptr(), K, C, R, S, ld, _DT[dtype], _stream()), "pack_weight")
+    check(lib.b200_pack_weight(wd.data_ptr(), out.data_ptr(), K, Cw, R, S, C, ld, _DT[dtype], _stream()),
+          "pack_weight")
     return out
 
 
