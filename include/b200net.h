@@ -72,6 +72,15 @@ int64_t b200_conv_workspace_bytes(const b200_conv_desc* d, int32_t which);
 /* y[N,Ho,Wo,K] = conv(x[N,H,W,C], w[K,R,S,C]) */
 int32_t b200_conv_fprop(const b200_conv_desc* d, const void* x, const void* w_krsc, void* y, void* ws,
                         int64_t ws_bytes, void* stream);
+/* Forward convolution that also emits the batch statistics the following BatchNorm2d needs (every conv of the
+ * model is followed by one: repr at pytorch_training_inference_on_image.ipynb:455-626): `partials` receives
+ * [rows][2][K] fp32 = per pixel-tile column sums and sums of squares of the bf16-rounded output, one row per pixel
+ * tile; b200_conv_fprop_bnstats_rows gives the row count (0 = this shape is not on the fused path: use
+ * b200_conv_fprop + b200_bn_train_stats).  b200_bn_finalize_stats turns the partials into mean / invstd /
+ * scale / shift and updates the running statistics. */
+int64_t b200_conv_fprop_bnstats_rows(const b200_conv_desc* d);
+int32_t b200_conv_fprop_bnstats(const b200_conv_desc* d, const void* x, const void* w_krsc, void* y,
+                                float* partials, int64_t partial_rows, void* stream);
 /* dx[N,H,W,C] (+)= conv_transpose(dy[N,Ho,Wo,K], w[K,R,S,C]);  accumulate!=0 adds into dx */
 int32_t b200_conv_dgrad(const b200_conv_desc* d, const void* dy, const void* w_krsc, void* dx, int32_t accumulate,
                         void* ws, int64_t ws_bytes, void* stream);
@@ -104,6 +113,12 @@ int32_t b200_bn_train_stats(const void* x, int64_t rows, int32_t C, int32_t dtyp
                             const float* beta, float* running_mean, float* running_var, float momentum, float eps,
                             float* save_mean, float* save_invstd, float* scale, float* shift, void* ws,
                             int64_t ws_bytes, void* stream);
+/* second half of b200_bn_train_stats for partial sums produced elsewhere (b200_conv_fprop_bnstats):
+ * partials is [partial_rows][2][C]; rows = N*H*W of the normalised tensor. */
+int32_t b200_bn_finalize_stats(const float* partials, int64_t partial_rows, int64_t rows, int32_t C,
+                               const float* gamma, const float* beta, float* running_mean, float* running_var,
+                               float momentum, float eps, float* save_mean, float* save_invstd, float* scale,
+                               float* shift, void* stream);
 /* Same computation and outputs as b200_bn_train_stats, for callers that have no workspace to give and must not
  * allocate one.  (No counterpart in the reference: it exists for hosts of this library that cannot call
  * cudaMalloc -- a serving process whose framework claimed all device memory for its own pool at start-up, or a

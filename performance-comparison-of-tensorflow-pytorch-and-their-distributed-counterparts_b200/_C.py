@@ -45,12 +45,15 @@ SIGNATURES = {
     "b200_cast": (I32, [P, P, I64, I32, I32, P]),
     "b200_conv_workspace_bytes": (I64, [POINTER(ConvDesc), I32]),
     "b200_conv_fprop": (I32, [POINTER(ConvDesc), P, P, P, P, I64, P]),
+    "b200_conv_fprop_bnstats_rows": (I64, [POINTER(ConvDesc)]),
+    "b200_conv_fprop_bnstats": (I32, [POINTER(ConvDesc), P, P, P, P, I64, P]),
     "b200_conv_dgrad": (I32, [POINTER(ConvDesc), P, P, P, I32, P, I64, P]),
     "b200_conv_wgrad": (I32, [POINTER(ConvDesc), P, P, P, P, I64, P]),
     "b200_gemm_f32": (I32, [P, P, P, I32, I32, I32, I64, I64, I64, I32, I32, P, I32, I32, P]),
     "b200_gemm_bf16": (I32, [P, P, P, I32, I32, I32, I64, I64, I64, I32, I32, I32, I32, I32, P, I64, P]),
     "b200_bn_workspace_bytes": (I64, [I64, I32]),
     "b200_bn_train_stats": (I32, [P, I64, I32, I32, P, P, P, P, F, F, P, P, P, P, P, I64, P]),
+    "b200_bn_finalize_stats": (I32, [P, I64, I64, I32, P, P, P, P, F, F, P, P, P, P, P]),
     "b200_bn_train_stats_noalloc": (I32, [P, I64, I32, I32, P, P, P, P, F, F, P, P, P, P, P]),
     "b200_bn_eval_coeffs": (I32, [P, P, P, P, F, P, P, I32, P]),
     "b200_bn_apply": (I32, [P, P, P, I64, I32, I32, P, P, I32, P]),

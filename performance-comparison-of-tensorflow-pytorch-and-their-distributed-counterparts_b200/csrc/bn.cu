@@ -405,6 +405,18 @@ extern "C" int32_t b200_bn_train_stats(const void* x, int64_t rows, int32_t C, i
   return fail(B200_INVALID_ARG, "bn_train_stats: bad dtype");
 }
 
+extern "C" int32_t b200_bn_finalize_stats(const float* partials, int64_t partial_rows, int64_t rows, int32_t C,
+                                          const float* gamma, const float* beta, float* running_mean,
+                                          float* running_var, float momentum, float eps, float* save_mean,
+                                          float* save_invstd, float* scale, float* shift, void* stream) {
+  if (!partials || partial_rows <= 0 || rows <= 0 || C <= 0 || !save_mean || !save_invstd || !scale || !shift)
+    return fail(B200_INVALID_ARG, "bn_finalize_stats: bad arguments");
+  bn_finalize_fwd_kernel<<<(C + FIN_CX - 1) / FIN_CX, dim3(FIN_CX, FIN_RY), 0, as_stream(stream)>>>(
+      partials, (int)partial_rows, C, (double)rows, gamma, beta, running_mean, running_var, momentum, eps, save_mean,
+      save_invstd, scale, shift);
+  return check_launch("bn_finalize_stats");
+}
+
 extern "C" int32_t b200_bn_eval_coeffs(const float* gamma, const float* beta, const float* running_mean,
                                        const float* running_var, float eps, float* scale, float* shift, int32_t C,
                                        void* stream) {

@@ -123,10 +123,12 @@ static inline WgradPlan wgrad_plan(const b200_conv_desc* d, const ConvGeom& g) {
   WgradPlan w;
   if (is_flat(d)) { w.Wq = (int)g.M; w.Hq = 1; w.Nq = 1; }
   else { w.Wq = g.Wo; w.Hq = g.Ho; w.Nq = d->N; }
-  w.box = choose_pixel_box(w.Wq, w.Hq, w.Nq, CONV_KR_MAX, 16, d->stride);
-  w.bn_tile = d->C >= 128 ? 128 : 64;
+  // columns of the packed [K][R*S*C] gradient per tile: 256 (four 64-channel tap groups share one dY tile) when
+  // C == 64, else 128 with twice as many pixels per k-block
+  w.bn_tile = d->C == 64 ? 256 : 128;
+  w.box = choose_pixel_box(w.Wq, w.Hq, w.Nq, w.bn_tile == 256 ? 64 : 128, 16, d->stride);
   w.pb_total = w.box.tiles_w * w.box.tiles_h * w.box.tiles_n;
-  const long long ctas = (long long)((d->C + w.bn_tile - 1) / w.bn_tile) * ((d->K + 127) / 128) * (d->R * d->S);
+  const long long ctas = (long long)((g.RSC + w.bn_tile - 1) / w.bn_tile) * ((d->K + 127) / 128);
   long long s = (2LL * num_sms() + ctas - 1) / ctas;
   if (s > w.pb_total) s = w.pb_total;
   if (s > 1024) s = 1024;
@@ -139,16 +141,17 @@ static inline WgradPlan wgrad_plan(const b200_conv_desc* d, const ConvGeom& g) {
 }
 
 template <int MODE>
-static int launch_conv_mode(int bn, const CUtensorMap& ta, const CUtensorMap& tb, const ConvParams& P,
-                            cudaStream_t st) {
+static int launch_conv_mode(int bn, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to,
+                            const ConvParams& P, cudaStream_t st) {
   const int ctas = num_sms();   // persistent: one CTA per SM
-  if (MODE == MODE_WGRAD) {
-    if (bn == 128) return launch_conv_cfg<128, 3, MODE>(ta, tb, P, ctas, st);
-    return launch_conv_cfg<64, 4, MODE>(ta, tb, P, ctas, st);
+  if constexpr (MODE == MODE_WGRAD) {
+    if (bn == 256) return launch_conv_cfg<256, 4, MODE>(ta, tb, to, P, ctas, st);
+    return launch_conv_cfg<128, 3, MODE>(ta, tb, to, P, ctas, st);
+  } else {
+    if (bn == 256) return launch_conv_cfg<256, 4, MODE>(ta, tb, to, P, ctas, st);
+    if (bn == 128) return launch_conv_cfg<128, 6, MODE>(ta, tb, to, P, ctas, st);
+    return launch_conv_cfg<64, 7, MODE>(ta, tb, to, P, ctas, st);
   }
-  if (bn == 256) return launch_conv_cfg<256, 4, MODE>(ta, tb, P, ctas, st);
-  if (bn == 128) return launch_conv_cfg<128, 6, MODE>(ta, tb, P, ctas, st);
-  return launch_conv_cfg<64, 8, MODE>(ta, tb, P, ctas, st);
 }
 
 static inline void timing_begin(cudaEvent_t& e0, cudaEvent_t& e1, cudaStream_t st) {
@@ -169,12 +172,18 @@ static inline void timing_end(cudaEvent_t e0, cudaEvent_t e1, double flops, cuda
 }
 
 // fprop (mode 0) and dgrad (mode 1) of one pixel grid / tap set
+static inline PixelBox fprop_box(const b200_conv_desc* d, const ConvGeom& g) {
+  const bool flat = is_flat(d);
+  const int Wq = flat ? (int)g.M : g.Wo, Hq = flat ? 1 : g.Ho, Nq = flat ? 1 : d->N;
+  return choose_pixel_box(Wq, Hq, Nq, GEMM_BM, 1, d->stride);
+}
+
 static int32_t implicit_fprop(const b200_conv_desc* d, const ConvGeom& g, const void* x, const void* w, void* y,
-                              cudaStream_t st) {
+                              float* stats, cudaStream_t st) {
   ConvParams P{};
   const bool flat = is_flat(d);
   const int Wq = flat ? (int)g.M : g.Wo, Hq = flat ? 1 : g.Ho, Nq = flat ? 1 : d->N;
-  const PixelBox b = choose_pixel_box(Wq, Hq, Nq, GEMM_BM, 1, d->stride);
+  const PixelBox b = fprop_box(d, g);
   P.bw = b.bw; P.bh = b.bh; P.bn = b.bn; P.tiles_w = b.tiles_w; P.tiles_h = b.tiles_h; P.tiles_n = b.tiles_n;
   P.a_mul = d->stride;
   P.ntaps = d->R * d->S;
@@ -196,9 +205,16 @@ static int32_t implicit_fprop(const b200_conv_desc* d, const ConvGeom& g, const 
   P.m_tiles = 1;
   if (tiles * P.n_tiles > 0x7fffffffLL) return fail(B200_UNSUPPORTED, "conv_fprop: too many tiles");
   P.total_tiles = (int)(tiles * P.n_tiles);
+  CUtensorMap to;
+  static const bool no_tma_store = getenv("B200_NO_TMA_STORE") != nullptr;
+  P.tma_store = !no_tma_store && P.vec_ok;
+  P.stats = stats;
+  if (stats && !P.tma_store) return fail(B200_UNSUPPORTED, "conv_fprop_bnstats: needs the TMA-store epilogue");
+  rc = make_tmap_bf16_nhwc(&to, y, Nq, Hq, Wq, d->K, b.bw, b.bh, b.bn, 1);
+  if (rc) return fail(B200_CUDA_ERROR, "conv_fprop: output tensor map failed (%d)", rc);
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   timing_begin(e0, e1, st);
-  rc = launch_conv_mode<MODE_FPROP>(bn, ta, tb, P, st);
+  rc = launch_conv_mode<MODE_FPROP>(bn, ta, tb, to, P, st);
   timing_end(e0, e1, 2.0 * g.M * d->K * g.RSC, st);
   if (rc) return fail(B200_CUDA_ERROR, "conv_fprop: launch failed (%d)", rc);
   return B200_OK;
@@ -252,9 +268,16 @@ static int32_t implicit_dgrad(const b200_conv_desc* d, const ConvGeom& g, const 
     P.m_tiles = 1;
     if (tiles * P.n_tiles > 0x7fffffffLL) return fail(B200_UNSUPPORTED, "conv_dgrad: too many tiles");
     P.total_tiles = (int)(tiles * P.n_tiles);
+    CUtensorMap to;
+    static const bool no_tma_store = getenv("B200_NO_TMA_STORE") != nullptr;
+    // strided (parity-class) outputs keep the per-thread store path; accumulation uses the TMA reduce-add
+    static const bool no_tma_reduce = getenv("B200_NO_TMA_REDUCE") != nullptr;
+    P.tma_store = !no_tma_store && P.vec_ok && d->stride == 1 && (!accumulate || !no_tma_reduce);
+    rc = make_tmap_bf16_nhwc(&to, dx, P.Nout, P.Hout, P.Wout, d->C, b.bw, b.bh, b.bn, 1);
+    if (rc) return fail(B200_CUDA_ERROR, "conv_dgrad: output tensor map failed (%d)", rc);
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     timing_begin(e0, e1, st);
-    rc = launch_conv_mode<MODE_DGRAD>(bn, ta, tb, P, st);
+    rc = launch_conv_mode<MODE_DGRAD>(bn, ta, tb, to, P, st);
     timing_end(e0, e1, 2.0 * Wq * Hq * Nq * (double)d->C * d->K * P.ntaps, st);
     if (rc) return fail(B200_CUDA_ERROR, "conv_dgrad: launch failed (%d)", rc);
   }
@@ -272,8 +295,8 @@ static int32_t implicit_wgrad(const b200_conv_desc* d, const ConvGeom& g, const 
   for (int r = 0; r < d->R; ++r)
     for (int s2 = 0; s2 < d->S; ++s2) P.taps[r * d->S + s2] = ConvTap{s2 - d->pad, r - d->pad, (r * d->S + s2) * d->C};
   P.out = ws; P.ldo = g.ldw; P.split_stride = (long long)d->K * g.ldw;
-  P.ncols = d->C; P.out_fp32 = 1; P.accumulate = 0;
-  P.vec_ok = (reinterpret_cast<uintptr_t>(ws) & 15) == 0;   // ldw % 8 == 0 and tap offsets are multiples of 64
+  P.ncols = g.RSC; P.cdim = d->C; P.out_fp32 = 1; P.accumulate = 0;
+  P.vec_ok = (reinterpret_cast<uintptr_t>(ws) & 15) == 0;   // ldw % 8 == 0 and column tiles start at multiples of 256
   P.nsplits = wp.nsplits; P.pb_total = wp.pb_total; P.pb_per_split = wp.pb_per; P.x_mul = d->stride;
   P.kr = wp.box.bw * wp.box.bh * wp.box.bn;
   P.mrows = d->K;
@@ -284,12 +307,14 @@ static int32_t implicit_wgrad(const b200_conv_desc* d, const ConvGeom& g, const 
   rc = flat ? make_tmap_bf16_nhwc(&tb, x, 1, 1, (int)g.M, d->C, P.bw, P.bh, P.bn, 1)
             : make_tmap_bf16_nhwc(&tb, x, d->N, d->H, d->W, d->C, P.bw, P.bh, P.bn, d->stride);
   if (rc) return fail(B200_CUDA_ERROR, "conv_wgrad: activation tensor map failed (%d)", rc);
-  P.n_tiles = (d->C + wp.bn_tile - 1) / wp.bn_tile;
+  P.n_tiles = (g.RSC + wp.bn_tile - 1) / wp.bn_tile;
+  P.n_inner = d->C / wp.bn_tile > 0 && P.n_tiles % (d->C / wp.bn_tile) == 0 ? d->C / wp.bn_tile : 1;
   P.m_tiles = (d->K + 127) / 128;
-  P.total_tiles = P.n_tiles * P.m_tiles * P.ntaps * wp.nsplits;
+  P.total_tiles = P.n_tiles * P.m_tiles * wp.nsplits;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   timing_begin(e0, e1, st);
-  rc = launch_conv_mode<MODE_WGRAD>(wp.bn_tile, ta, tb, P, st);
+  P.tma_store = 0;
+  rc = launch_conv_mode<MODE_WGRAD>(wp.bn_tile, ta, tb, ta, P, st);
   timing_end(e0, e1, 2.0 * g.M * d->K * g.RSC, st);
   if (rc) return fail(B200_CUDA_ERROR, "conv_wgrad: launch failed (%d)", rc);
   return launch_reduce_wgrad((const float*)ws, wp.nsplits, P.split_stride, d->K, d->C, d->R * d->S, g.ldw, dw, st);
@@ -325,7 +350,7 @@ extern "C" int32_t b200_conv_fprop(const b200_conv_desc* d, const void* x, const
   if (!x || !w || !y) return fail(B200_INVALID_ARG, "conv_fprop: null pointer");
   const ConvGeom g = geom(d);
   cudaStream_t st = as_stream(stream);
-  if (implicit_ok(d)) return implicit_fprop(d, g, x, w, y, st);
+  if (implicit_ok(d)) return implicit_fprop(d, g, x, w, y, nullptr, st);
   const void* A = x;
   long long lda = d->C;
   int Kred = d->C;
@@ -449,4 +474,26 @@ extern "C" int32_t b200_gemm_timing_read(double* total_ms, int64_t* launches, do
   if (launches) *launches = (int64_t)gt.ev.size();
   if (flops) *flops = gt.flops;
   return B200_OK;
+}
+
+// ---- convolution forward with the following BatchNorm's batch statistics fused into the epilogue
+extern "C" int64_t b200_conv_fprop_bnstats_rows(const b200_conv_desc* d) {
+  if (check_desc(d)) return -1;
+  static const bool off = getenv("B200_NO_FUSED_BNSTATS") != nullptr || getenv("B200_NO_TMA_STORE") != nullptr;
+  if (off || !implicit_ok(d)) return 0;
+  const ConvGeom g = geom(d);
+  const PixelBox b = fprop_box(d, g);
+  return (int64_t)b.tiles_w * b.tiles_h * b.tiles_n;
+}
+
+extern "C" int32_t b200_conv_fprop_bnstats(const b200_conv_desc* d, const void* x, const void* w, void* y,
+                                           float* partials, int64_t partial_rows, void* stream) {
+  if (int32_t rc = check_desc(d)) return rc;
+  if (!x || !w || !y || !partials) return fail(B200_INVALID_ARG, "conv_fprop_bnstats: null pointer");
+  const int64_t need = b200_conv_fprop_bnstats_rows(d);
+  if (need <= 0) return fail(B200_UNSUPPORTED, "conv_fprop_bnstats: shape not on the implicit tcgen05 path");
+  if (partial_rows < need) return fail(B200_WORKSPACE_TOO_SMALL, "conv_fprop_bnstats: %lld partial rows needed", (long long)need);
+  if ((reinterpret_cast<uintptr_t>(partials) & 7) || (reinterpret_cast<uintptr_t>(y) & 15))
+    return fail(B200_INVALID_ARG, "conv_fprop_bnstats: misaligned buffers");
+  return implicit_fprop(d, geom(d), x, w, y, partials, as_stream(stream));
 }

@@ -12,8 +12,10 @@
 //   MODE_DGRAD : D[pix][cin]  = sum_{tap,k} dY[pix shifted][k]       * W[k][tap][cin]       (B MN-major)
 //                stride-2 convolutions are decomposed into the four output-parity classes, each a stride-1 problem
 //                over the taps of matching parity (no wasted MACs), written to the interleaved output positions
-//   MODE_WGRAD : D[cout][cin] (one tap) = sum_{pixel boxes} dY[pix][cout]^T * X[pix shifted][cin]
-//                both operands MN-major (pixel index outermost), split-K over pixel boxes into fp32 slabs
+//   MODE_WGRAD : D[cout][(tap,cin)] = sum_{pixel boxes} dY[pix][cout]^T * X[pix shifted by tap][cin]
+//                both operands MN-major (pixel index outermost), split-K over pixel boxes into fp32 slabs.
+//                The N tile is 256 columns of the packed [K][R*S*C] gradient: each 64-column group is its own TMA
+//                box of X with its own tap shift, so one dY tile feeds up to four taps (C=64) per MMA.
 #pragma once
 #include "sm100_ptx.cuh"
 #include "gemm_sm100.cuh"
@@ -22,7 +24,9 @@ namespace b200 {
 
 enum { MODE_FPROP = 0, MODE_DGRAD = 1, MODE_WGRAD = 2 };
 constexpr int CONV_MAX_TAPS = 9;
-constexpr int CONV_KR_MAX = 128;  // wgrad: pixel rows per k-block (multiple of 16)
+constexpr int CONV_KR_MAX = 128;  // wgrad: most pixel rows per k-block (multiple of 16); 64 with 256-column tiles
+constexpr int CONV_STAGING_BYTES = 2 * 128 * 128;  // epilogue: two [128 rows][64 bf16] swizzled tiles for TMA stores
+constexpr int CONV_STATS_RED_BYTES = 3 * 64 * 2 * 4;  // epilogue: cross-warp scratch of the fused BN statistics
 
 struct ConvTap {
   int dw, dh;  // shift of the activation box (input-pixel units) for this tap
@@ -46,15 +50,23 @@ struct ConvParams {
   int nsplits, pb_total, pb_per_split, x_mul;  // x_mul = conv stride (X box origin = tile origin * x_mul + shift)
   int kr;                                       // pixel rows per box = bw*bh*bn
   int mrows;                                    // valid cout rows
+  int cdim;                                     // input channels C: output column j <-> tap j / C, channel j % C
   // persistent tile walk: tile = n_tile + n_tiles * (pixel tile | m_tile + m_tiles * (tap*nsplits + split))
   int n_tiles, m_tiles, total_tiles;
+  int n_inner;                       // wgrad: column tiles per tap (n_tiles = n_inner * tap groups)
+  int tma_store;                     // fprop/dgrad: bf16 output written by TMA from a swizzled smem staging tile
+  float* stats;                      // fprop + tma_store: per-pixel-tile column sums [pixel tile][2][ncols] of the
+                                     // bf16-rounded output (sum, sum of squares) for the BatchNorm that follows
 };
+
+// wgrad stage geometry: 128-column tiles use 128-pixel k-blocks, 256-column tiles 64-pixel k-blocks (same bytes)
+#define CONV_WGRAD_KR(BN_) ((BN_) == 256 ? 64 : 128)
 
 template <int BN, int STAGES, int MODE>
 constexpr int conv_smem_bytes() {
-  constexpr int a = MODE == MODE_WGRAD ? 2 * CONV_KR_MAX * 128 : GEMM_BM * 128;
-  constexpr int b = MODE == MODE_WGRAD ? (BN / 64) * CONV_KR_MAX * 128 : BN * 128;
-  return STAGES * (a + b) + 1024 + 256;
+  constexpr int a = MODE == MODE_WGRAD ? 2 * CONV_WGRAD_KR(BN) * 128 : GEMM_BM * 128;
+  constexpr int b = MODE == MODE_WGRAD ? (BN / 64) * CONV_WGRAD_KR(BN) * 128 : BN * 128;
+  return STAGES * (a + b) + (MODE == MODE_WGRAD ? 0 : CONV_STAGING_BYTES + CONV_STATS_RED_BYTES) + 1024 + 256;
 }
 
 // Persistent kernel: grid = min(#tiles, #SMs); every CTA walks tiles blockIdx.x, blockIdx.x + gridDim.x, ...
@@ -69,10 +81,10 @@ struct ConvTile {
 template <int BN, int MODE>
 __device__ __forceinline__ ConvTile conv_decode_tile(const ConvParams& P, int tile) {
   ConvTile t{};
-  const int nt = tile % P.n_tiles;
-  int rest = tile / P.n_tiles;
-  t.n0 = nt * BN;
   if (MODE != MODE_WGRAD) {
+    const int nt = tile % P.n_tiles;
+    int rest = tile / P.n_tiles;
+    t.n0 = nt * BN;
     const int tw = rest % P.tiles_w;
     rest /= P.tiles_w;
     const int th = rest % P.tiles_h;
@@ -83,11 +95,17 @@ __device__ __forceinline__ ConvTile conv_decode_tile(const ConvParams& P, int ti
     t.kb_begin = 0;
     t.kb_end = P.ntaps * P.cchunks;
   } else {
+    // order: column tile within a tap (fastest), cout tile, split, tap group.  Concurrent CTAs then work on
+    // different pixel ranges (splits) instead of all hitting the same dY / X lines in L2 at once.
+    const int ni = tile % P.n_inner;
+    int rest = tile / P.n_inner;
     const int mt = rest % P.m_tiles;
     rest /= P.m_tiles;
-    t.m0 = mt * GEMM_BM;
-    t.tap = rest / P.nsplits;
     t.split = rest % P.nsplits;
+    const int no = rest / P.nsplits;
+    t.n0 = (no * P.n_inner + ni) * BN;
+    t.m0 = mt * GEMM_BM;
+    t.tap = t.n0 / P.cdim;
     t.kb_begin = t.split * P.pb_per_split;
     t.kb_end = t.kb_begin + P.pb_per_split;
     if (t.kb_end > P.pb_total) t.kb_end = P.pb_total;
@@ -98,9 +116,10 @@ __device__ __forceinline__ ConvTile conv_decode_tile(const ConvParams& P, int ti
 template <int BN, int STAGES, int MODE>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                  const __grid_constant__ ConvParams P) {
-  constexpr int A_BYTES = MODE == MODE_WGRAD ? 2 * CONV_KR_MAX * 128 : GEMM_BM * 128;
-  constexpr int B_BYTES = MODE == MODE_WGRAD ? (BN / 64) * CONV_KR_MAX * 128 : BN * 128;
+                  const __grid_constant__ CUtensorMap tmO, const __grid_constant__ ConvParams P) {
+  constexpr int A_BYTES = MODE == MODE_WGRAD ? 2 * CONV_WGRAD_KR(BN) * 128 : GEMM_BM * 128;
+  constexpr int B_BYTES = MODE == MODE_WGRAD ? (BN / 64) * CONV_WGRAD_KR(BN) * 128 : BN * 128;
+  constexpr int STG_BYTES = MODE == MODE_WGRAD ? 0 : CONV_STAGING_BYTES + CONV_STATS_RED_BYTES;
   constexpr uint32_t TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;   // two accumulators
   static_assert(2 * BN <= 512, "two accumulators must fit TMEM");
 
@@ -109,7 +128,9 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   uint8_t* smem = smem_raw + ((1024u - (s0 & 1023u)) & 1023u);
   uint8_t* smA = smem;
   uint8_t* smB = smem + STAGES * A_BYTES;
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + STAGES * (A_BYTES + B_BYTES));
+  uint8_t* smStage = smem + STAGES * (A_BYTES + B_BYTES);   // 1024-aligned: stage sizes are multiples of 1024
+  float* smRed = reinterpret_cast<float*>(smStage + CONV_STAGING_BYTES);   // [3][64][2]
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + STAGES * (A_BYTES + B_BYTES) + STG_BYTES);
   uint64_t* empty = full + STAGES;
   uint64_t* tmem_full = empty + STAGES;    // [2]
   uint64_t* tmem_empty = tmem_full + 2;    // [2]
@@ -122,6 +143,7 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
+    if (MODE != MODE_WGRAD && P.tma_store) tma_prefetch_desc(&tmO);
 #pragma unroll
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(&full[s], 1);
@@ -146,42 +168,72 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer
     if (lane == 0) {
-      uint32_t i = 0;   // running k-block counter across tiles (ring position / phase)
+      int stage = 0;          // ring position and phase run continuously across tiles
+      uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < P.total_tiles; tile += gridDim.x) {
         const ConvTile T = conv_decode_tile<BN, MODE>(P, tile);
-        for (int kb = T.kb_begin; kb < T.kb_end; ++kb, ++i) {
-          const int s = i % STAGES;
-          const uint32_t ph = (i / STAGES) & 1;
-          mbar_wait(&empty[s], ph ^ 1);
+        if (MODE != MODE_WGRAD) {
+          // taps x 64-channel chunks, no per-k-block division; stage index / phase carried incrementally
+          for (int t = 0; t < P.ntaps; ++t) {
+            const int aw = T.q0 * P.a_mul + P.taps[t].dw, ah = T.p0 * P.a_mul + P.taps[t].dh;
+            const int bcol = P.taps[t].bcol;
+            for (int cc = 0; cc < P.cchunks; ++cc) {
+              mbar_wait(&empty[stage], phase ^ 1);
+              uint8_t* a = smA + stage * A_BYTES;
+              uint8_t* b = smB + stage * B_BYTES;
+              mbar_expect_tx(&full[stage], box_bytes + B_BYTES);
+              tma_load_4d(a, &tmA, &full[stage], cc * 64, aw, ah, T.i0);
+              if (MODE == MODE_FPROP) {
+                tma_load_2d(b, &tmB, &full[stage], bcol + cc * 64, T.n0);  // box {64 c, BN cout}
+              } else {
+#pragma unroll
+                for (int h = 0; h < BN / 64; ++h)
+                  tma_load_2d(b + h * 8192, &tmB, &full[stage], bcol + T.n0 + h * 64, cc * 64);  // {64 cin, 64 k}
+              }
+              if (++stage == STAGES) { stage = 0; phase ^= 1; }
+            }
+          }
+          continue;
+        }
+        // pixel-box walk (w fastest, then h, then n) carried incrementally from the first box of this split
+        int tw = T.kb_begin % P.tiles_w, th = (T.kb_begin / P.tiles_w) % P.tiles_h,
+            tn = T.kb_begin / (P.tiles_w * P.tiles_h);
+        for (int kb = T.kb_begin; kb < T.kb_end; ++kb) {
+          const int s = stage;
+          mbar_wait(&empty[s], phase ^ 1);
           uint8_t* a = smA + s * A_BYTES;
           uint8_t* b = smB + s * B_BYTES;
-          if (MODE != MODE_WGRAD) {
-            const int t = kb / P.cchunks, cc = kb - t * P.cchunks;
-            mbar_expect_tx(&full[s], box_bytes + B_BYTES);
-            tma_load_4d(a, &tmA, &full[s], cc * 64, T.q0 * P.a_mul + P.taps[t].dw, T.p0 * P.a_mul + P.taps[t].dh,
-                        T.i0);
-            if (MODE == MODE_FPROP) {
-              tma_load_2d(b, &tmB, &full[s], P.taps[t].bcol + cc * 64, T.n0);  // box {64 c, BN cout}
-            } else {
+          {
+            const int bq = tw * P.bw, bp = th * P.bh, bi = tn * P.bn;
+            if (++tw == P.tiles_w) { tw = 0; if (++th == P.tiles_h) { th = 0; ++tn; } }
+            if (BN == 128) {
+              // one tap per tile (C >= 128): fixed, fully unrolled issue sequence
+              const int cin0 = T.n0 - T.tap * P.cdim;
+              mbar_expect_tx(&full[s], box_bytes * (2 + BN / 64));
+#pragma unroll
+              for (int h = 0; h < 2; ++h) tma_load_4d(a + h * box_bytes, &tmA, &full[s], T.m0 + h * 64, bq, bp, bi);
 #pragma unroll
               for (int h = 0; h < BN / 64; ++h)
-                tma_load_2d(b + h * 8192, &tmB, &full[s], P.taps[t].bcol + T.n0 + h * 64, cc * 64);  // {64 cin, 64 k}
+                tma_load_4d(b + h * box_bytes, &tmB, &full[s], cin0 + h * 64, bq * P.x_mul + P.taps[T.tap].dw,
+                            bp * P.x_mul + P.taps[T.tap].dh, bi);
+            } else {
+              // 256-column tile of the packed gradient (C == 64): each 64-column group is its own tap
+              const int na = (T.m0 + 64 < P.mrows) ? 2 : 1;          // second 64-cout half only if it exists
+              int nb = (P.ncols - T.n0 + 63) / 64;
+              if (nb > BN / 64) nb = BN / 64;
+              mbar_expect_tx(&full[s], box_bytes * (na + nb));
+              for (int h = 0; h < na; ++h) tma_load_4d(a + h * box_bytes, &tmA, &full[s], T.m0 + h * 64, bq, bp, bi);
+#pragma unroll
+              for (int h = 0; h < BN / 64; ++h) {
+                if (h < nb) {
+                  const int tp = (T.n0 >> 6) + h;   // C == 64: column group = tap
+                  tma_load_4d(b + h * box_bytes, &tmB, &full[s], 0, bq * P.x_mul + P.taps[tp].dw,
+                              bp * P.x_mul + P.taps[tp].dh, bi);
+                }
+              }
             }
-          } else {
-            int t = kb;
-            const int tw = t % P.tiles_w;
-            t /= P.tiles_w;
-            const int th = t % P.tiles_h;
-            const int tn = t / P.tiles_h;
-            const int bq = tw * P.bw, bp = th * P.bh, bi = tn * P.bn;
-            mbar_expect_tx(&full[s], box_bytes * (2 + BN / 64));
-#pragma unroll
-            for (int h = 0; h < 2; ++h) tma_load_4d(a + h * box_bytes, &tmA, &full[s], T.m0 + h * 64, bq, bp, bi);
-#pragma unroll
-            for (int h = 0; h < BN / 64; ++h)
-              tma_load_4d(b + h * box_bytes, &tmB, &full[s], T.n0 + h * 64, bq * P.x_mul + P.taps[T.tap].dw,
-                          bp * P.x_mul + P.taps[T.tap].dh, bi);
           }
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
     }
@@ -190,7 +242,8 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     // ------------------------------------------------------------ MMA issuer
     if (lane == 0) {
       constexpr uint32_t idesc = umma_idesc_bf16(GEMM_BM, BN, MODE == MODE_WGRAD, MODE != MODE_FPROP);
-      uint32_t i = 0;
+      int stage = 0;
+      uint32_t phase = 0;
       uint32_t it = 0;   // local tile counter
       for (int tile = blockIdx.x; tile < P.total_tiles; tile += gridDim.x, ++it) {
         const ConvTile T = conv_decode_tile<BN, MODE>(P, tile);
@@ -199,10 +252,10 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + buf * BN;
         bool first = true;
-        for (int kb = T.kb_begin; kb < T.kb_end; ++kb, ++i) {
-          const int s = i % STAGES;
-          const uint32_t ph = (i / STAGES) & 1;
-          mbar_wait(&full[s], ph);
+        for (int kb = T.kb_begin; kb < T.kb_end; ++kb) {
+          const int s = stage;
+          mbar_wait(&full[s], phase);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
           tc_fence_after();
           const uint32_t a_addr = smem_u32(smA + s * A_BYTES);
           const uint32_t b_addr = smem_u32(smB + s * B_BYTES);
@@ -234,6 +287,7 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     const int q = warp & 3;
     const int l = q * 32 + lane;  // accumulator row
     uint32_t it = 0;
+    uint32_t stage_ctr = 0;       // staging-tile ring position (TMA-store epilogue)
     for (int tile = blockIdx.x; tile < P.total_tiles; tile += gridDim.x, ++it) {
       const ConvTile T = conv_decode_tile<BN, MODE>(P, tile);
       const uint32_t buf = it & 1, use = it >> 1;
@@ -254,8 +308,88 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         row_off = ((static_cast<long long>(on) * P.Hout + oh) * P.Wout + ow) * P.ldo;
       } else {
         row_ok = (T.m0 + l) < P.mrows;
-        row_off = static_cast<long long>(T.split) * P.split_stride + static_cast<long long>(T.m0 + l) * P.ldo +
-                  P.taps[T.tap].bcol;
+        row_off = static_cast<long long>(T.split) * P.split_stride + static_cast<long long>(T.m0 + l) * P.ldo;
+      }
+      if (MODE != MODE_WGRAD && P.tma_store) {
+        // ---- TMA-store epilogue: TMEM -> registers -> bf16 -> 128B-swizzled smem tile [128 px][64 ch] -> one bulk
+        // tensor store per 64-channel group (full 128-byte lines, bounds clipped by the TMA unit).  Two staging
+        // tiles alternate so the store of group g overlaps the TMEM reads / packing of group g+1.
+        const bool elected = (warp == 2 && lane == 0);
+#pragma unroll 1
+        for (int g = 0; g < BN / 64; ++g) {
+          if (T.n0 + g * 64 >= P.ncols) break;     // uniform across the CTA
+          uint8_t* stg = smStage + (stage_ctr & 1u) * (CONV_STAGING_BYTES / 2);
+          if (elected) tma_store_wait_read<1>();   // the store that last used this tile has finished reading it
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            uint32_t r[32];
+            if (have_work) {
+              tmem_ld_32x32b_x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * BN +
+                                     static_cast<uint32_t>(g * 64 + h * 32), r);
+              tmem_ld_wait();
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) r[j] = 0u;
+            }
+            uint8_t* rowp = stg + l * 128;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              uint4 v;
+              v.x = pack_bf16x2(__uint_as_float(r[8 * j + 0]), __uint_as_float(r[8 * j + 1]));
+              v.y = pack_bf16x2(__uint_as_float(r[8 * j + 2]), __uint_as_float(r[8 * j + 3]));
+              v.z = pack_bf16x2(__uint_as_float(r[8 * j + 4]), __uint_as_float(r[8 * j + 5]));
+              v.w = pack_bf16x2(__uint_as_float(r[8 * j + 6]), __uint_as_float(r[8 * j + 7]));
+              if (MODE == MODE_FPROP && !row_ok) v = make_uint4(0u, 0u, 0u, 0u);   // keep the fused statistics clean
+              const int chunk = (h * 4 + j) ^ (l & 7);
+              *reinterpret_cast<uint4*>(rowp + chunk * 16) = v;
+            }
+          }
+          fence_proxy_async_smem();
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+          if (elected) {
+            if (P.accumulate) tma_reduce_add_4d(&tmO, stg, T.n0 + g * 64, T.q0, T.p0, T.i0);
+            else tma_store_4d(&tmO, stg, T.n0 + g * 64, T.q0, T.p0, T.i0);
+            tma_store_commit();
+          }
+          if (MODE == MODE_FPROP && P.stats != nullptr) {
+            // Fused BatchNorm statistics: column sums of the bf16 tile that was just staged.  Thread (warp q, lane)
+            // owns columns 2*lane, 2*lane+1 over rows 32q..32q+31 (one conflict-free 4-byte smem read per row);
+            // warps 1..3 hand their partials to warp 0 through smem; one row of partials per pixel tile in global.
+            float s0a = 0.f, s0b = 0.f, s1a = 0.f, s1b = 0.f;
+            const int cpair = lane;
+#pragma unroll 8
+            for (int i = 0; i < 32; ++i) {
+              const int row = q * 32 + i;
+              const uint32_t w = *reinterpret_cast<const uint32_t*>(stg + row * 128 + (((cpair >> 2) ^ (row & 7)) << 4) +
+                                                                     ((cpair & 3) << 2));
+              const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w));
+              s0a += f.x; s1a = fmaf(f.x, f.x, s1a);
+              s0b += f.y; s1b = fmaf(f.y, f.y, s1b);
+            }
+            if (q != 0) {
+              float* r = smRed + ((q - 1) * 64 + 2 * cpair) * 2;
+              r[0] = s0a; r[1] = s1a; r[2] = s0b; r[3] = s1b;
+            }
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            if (q == 0) {
+#pragma unroll
+              for (int w2 = 0; w2 < 3; ++w2) {
+                const float* r = smRed + (w2 * 64 + 2 * cpair) * 2;
+                s0a += r[0]; s1a += r[1]; s0b += r[2]; s1b += r[3];
+              }
+              const int ptile = tile / P.n_tiles;
+              float* dst = P.stats + (static_cast<long long>(ptile) * 2) * P.ncols + T.n0 + g * 64 + 2 * cpair;
+              *reinterpret_cast<float2*>(dst) = make_float2(s0a, s0b);
+              *reinterpret_cast<float2*>(dst + P.ncols) = make_float2(s1a, s1b);
+            }
+          }
+          ++stage_ctr;
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tmem_empty[buf]);
+        continue;
       }
 #pragma unroll 1
       for (int c = 0; c < BN / 32; ++c) {
@@ -328,6 +462,7 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       __syncwarp();
       if (lane == 0) mbar_arrive(&tmem_empty[buf]);
     }
+    if (MODE != MODE_WGRAD && P.tma_store && warp == 2 && lane == 0) tma_store_wait<0>();  // smem must outlive the stores
   }
 
   tc_fence_before();
@@ -383,8 +518,8 @@ inline PixelBox choose_pixel_box(int W, int H, int N, int max_rows, int mult, in
 }
 
 template <int BN, int STAGES, int MODE>
-inline int launch_conv_cfg(const CUtensorMap& ta, const CUtensorMap& tb, const ConvParams& P, int num_ctas,
-                           cudaStream_t st) {
+inline int launch_conv_cfg(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, const ConvParams& P,
+                           int num_ctas, cudaStream_t st) {
   auto kern = conv_sm100_kernel<BN, STAGES, MODE>;
   constexpr int smem = conv_smem_bytes<BN, STAGES, MODE>();
   static bool attr_done = false;
@@ -394,7 +529,7 @@ inline int launch_conv_cfg(const CUtensorMap& ta, const CUtensorMap& tb, const C
     attr_done = true;
   }
   const int grid = P.total_tiles < num_ctas ? P.total_tiles : num_ctas;
-  kern<<<grid, GEMM_THREADS, smem, st>>>(ta, tb, P);
+  kern<<<grid, GEMM_THREADS, smem, st>>>(ta, tb, to, P);
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? 0 : 400 + static_cast<int>(e);
 }

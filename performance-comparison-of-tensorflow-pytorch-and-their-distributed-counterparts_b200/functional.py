@@ -84,9 +84,14 @@ def _conv_geom(conv):
 
 
 # ------------------------------------------------------------------ BN helpers shared by both granularities
-def _bn_coeffs(bn, y, bump_nbt=True):
-    """Returns (scale, shift, mean, invstd); mean/invstd are None in eval mode.  Updates running stats in train mode."""
-    use_batch = bn.training or (bn.running_mean is None and bn.running_var is None)
+def _bn_uses_batch_stats(bn):
+    return bn.training or (bn.running_mean is None and bn.running_var is None)
+
+
+def _bn_coeffs(bn, y, bump_nbt=True, partials=None):
+    """Returns (scale, shift, mean, invstd); mean/invstd are None in eval mode.  Updates running stats in train mode.
+    `partials` = per-tile column sums already produced by the convolution's epilogue (ops.conv_fprop_bnstats)."""
+    use_batch = _bn_uses_batch_stats(bn)
     if use_batch:
         momentum = 0.0
         rm, rv = bn.running_mean, bn.running_var
@@ -96,7 +101,11 @@ def _bn_coeffs(bn, y, bump_nbt=True):
             momentum = bn.momentum if bn.momentum is not None else 1.0 / float(bn.num_batches_tracked)
         else:
             rm = rv = None
-        mean, invstd, scale, shift = ops.bn_train_stats(y, bn.weight, bn.bias, rm, rv, momentum, bn.eps)
+        if partials is not None:
+            mean, invstd, scale, shift = ops.bn_finalize_stats(partials, y.numel() // y.shape[-1], bn.weight, bn.bias,
+                                                               rm, rv, momentum, bn.eps)
+        else:
+            mean, invstd, scale, shift = ops.bn_train_stats(y, bn.weight, bn.bias, rm, rv, momentum, bn.eps)
         return scale, shift, mean, invstd
     scale, shift = ops.bn_eval_coeffs(bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.eps)
     return scale, shift, None, None
@@ -111,8 +120,11 @@ class _Unit(object):
 def _unit_forward(conv, bn, x, relu, residual, save):
     K, R, S, stride, pad = _conv_geom(conv)
     wp = packed_weight(conv.weight, x.dtype, x.shape[-1] if x.shape[-1] != conv.in_channels else None)
-    y = ops.conv_fprop(x, wp, K, R, S, stride, pad)
-    scale, shift, mean, invstd = _bn_coeffs(bn, y, bump_nbt=False)
+    if _bn_uses_batch_stats(bn):
+        y, partials = ops.conv_fprop_bnstats(x, wp, K, R, S, stride, pad)   # BN statistics fused into the epilogue
+    else:
+        y, partials = ops.conv_fprop(x, wp, K, R, S, stride, pad), None
+    scale, shift, mean, invstd = _bn_coeffs(bn, y, bump_nbt=False, partials=partials)
     # eval mode: y is dead after the apply -> write in place
     z = ops.bn_apply(y, scale, shift, relu, residual, out=None if save else y)
     if not save:
@@ -226,9 +238,11 @@ class _ResNetBackbone(torch.autograd.Function):
             dz1 = dgrad(u2, dy2)
             dy1, _ = unit_backward(u1, dz1, want_dres=False)
             if ud is not None:
+                # dense branch first (plain store), then the strided downsample branch accumulates: for a 1x1
+                # stride-2 convolution only one of the four output-parity classes receives anything
                 dyd, _ = unit_backward(ud, g, want_dres=False)
-                dcur = dgrad(ud, dyd)
-                dgrad(u1, dy1, out=dcur, accumulate=True)
+                dcur = dgrad(u1, dy1)
+                dgrad(ud, dyd, out=dcur, accumulate=True)
             else:
                 dcur = dgrad(u1, dy1, out=g, accumulate=True)
         dz0 = ops.maxpool_bwd(dcur, ctx.pool_idx, ctx.stem_shape)

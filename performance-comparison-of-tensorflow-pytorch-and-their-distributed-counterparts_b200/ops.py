@@ -113,6 +113,41 @@ def conv_fprop(x, wp, K, R, S, stride, pad):
     return y
 
 
+_STATS_ROWS = {}
+
+
+def conv_fprop_bnstats(x, wp, K, R, S, stride, pad):
+    """conv forward + per-pixel-tile column statistics of the output; returns (y, partials or None).
+    partials is None when the shape is not on the fused path (caller then runs bn_train_stats on y)."""
+    N, H, W, C = x.shape
+    key = (N, H, W, C, K, R, S, stride, pad, _dt(x))
+    d, dref, ws, Ho, Wo = _desc(*key)
+    rows = _STATS_ROWS.get(key)
+    if rows is None:
+        rows = int(lib.b200_conv_fprop_bnstats_rows(dref))
+        _STATS_ROWS[key] = rows
+    if rows <= 0:
+        return conv_fprop(x, wp, K, R, S, stride, pad), None
+    y = torch.empty((N, Ho, Wo, K), dtype=x.dtype, device=x.device)
+    part = torch.empty((rows, 2, K), dtype=torch.float32, device=x.device)
+    check(lib.b200_conv_fprop_bnstats(dref, x.data_ptr(), wp.data_ptr(), y.data_ptr(), part.data_ptr(), rows,
+                                      _stream()), "conv_fprop_bnstats")
+    return y, part
+
+
+def bn_finalize_stats(part, rows, gamma, beta, running_mean, running_var, momentum, eps):
+    nblk, _, C = part.shape
+    st = torch.empty((4, C), dtype=torch.float32, device=part.device)
+    check(lib.b200_bn_finalize_stats(
+        part.data_ptr(), nblk, rows, C, gamma.data_ptr() if gamma is not None else None,
+        beta.data_ptr() if beta is not None else None,
+        running_mean.data_ptr() if running_mean is not None else None,
+        running_var.data_ptr() if running_var is not None else None,
+        float(momentum), float(eps), st[0].data_ptr(), st[1].data_ptr(), st[2].data_ptr(), st[3].data_ptr(),
+        _stream()), "bn_finalize_stats")
+    return st[0], st[1], st[2], st[3]
+
+
 def conv_dgrad(dy, wp, x_shape, K, R, S, stride, pad, out=None, accumulate=False):
     N, H, W, C = x_shape
     d, dref, ws, Ho, Wo = _desc(N, H, W, C, K, R, S, stride, pad, _dt(dy))

@@ -152,6 +152,31 @@ def test_conv_fprop_dgrad_wgrad(prec, case):
     assert _rel(dw, wd.grad) < (1e-4 if prec == "fp32" else 5e-3)
 
 
+@pytest.mark.parametrize("case", [c for c in CONV_CASES if c[2] % 64 == 0 and c[3] % 64 == 0])
+def test_conv_fprop_fused_bn_statistics(case):
+    """The fprop epilogue also emits per-pixel-tile column sums / sums of squares of the bf16 output: they must add up
+    to the statistics of the tensor it wrote, and feed b200_bn_finalize_stats to the same result as the stand-alone
+    statistics kernel."""
+    from b200net import ops
+    N, H, C, K, R, stride, pad = case
+    x = _nhwc(_rand((N, C, H, H), torch.bfloat16, 11), torch.bfloat16)
+    wp = ops.pack_weight(_rand((K, C, R, R), torch.float32, 12, scale=1.0 / math.sqrt(C * R * R)), torch.bfloat16)
+    y0 = ops.conv_fprop(x, wp, K, R, R, stride, pad)
+    y, part = ops.conv_fprop_bnstats(x, wp, K, R, R, stride, pad)
+    assert part is not None and torch.equal(y, y0)
+    yd = y.double().reshape(-1, K)
+    assert _rel(part[:, 0].double().sum(0), yd.sum(0)) < 1e-5
+    assert _rel(part[:, 1].double().sum(0), (yd * yd).sum(0)) < 1e-5
+    gamma, beta = _rand((K,), torch.float32, 13).abs() + 0.5, _rand((K,), torch.float32, 14)
+    rm1, rv1, rm2, rv2 = (torch.zeros(K, device=_dev()), torch.ones(K, device=_dev()),
+                          torch.zeros(K, device=_dev()), torch.ones(K, device=_dev()))
+    a = ops.bn_finalize_stats(part, yd.shape[0], gamma, beta, rm1, rv1, 0.1, 1e-5)
+    b = ops.bn_train_stats(y, gamma, beta, rm2, rv2, 0.1, 1e-5)
+    for u, v in zip(a, b):
+        assert _rel(u, v) < 1e-5
+    assert _rel(rm1, rm2) < 1e-5 and _rel(rv1, rv2) < 1e-5
+
+
 # ---------------------------------------------------------------------------------------------- batch norm
 @pytest.mark.parametrize("prec", ["fp32", "bf16"])
 @pytest.mark.parametrize("rows,C", [(2 * 20 * 20, 64), (3 * 7 * 5, 2048), (1000, 24), (50, 130)])
