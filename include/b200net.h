@@ -139,15 +139,20 @@ int32_t b200_bn_train_stats_noalloc(const void* x, int64_t rows, int32_t C, int3
 /* eval mode: scale/shift from running statistics */
 int32_t b200_bn_eval_coeffs(const float* gamma, const float* beta, const float* running_mean,
                             const float* running_var, float eps, float* scale, float* shift, int32_t C, void* stream);
-/* y = act(x*scale + shift (+ residual)) ; act = ReLU when relu != 0 */
-int32_t b200_bn_apply(const void* x, const void* residual, void* y, int64_t rows, int32_t C, int32_t dtype,
-                      const float* scale, const float* shift, int32_t relu, void* stream);
-/* Backward of y = act(bn(x) (+res)).  g = dz * [z>0] when relu (z = saved output), else g = dz.
+/* y = act(x*scale + shift (+ residual)) ; act = ReLU when relu != 0.
+ * mask (optional, may be NULL): receives the ReLU mask of the STORED output, one byte per 16-byte vector of y
+ * (bit e = element e of the vector is > 0; b200_bn_mask_bytes gives the size, 0 = not available for this C). */
+int64_t b200_bn_mask_bytes(int64_t rows, int32_t C, int32_t dtype);
+int32_t b200_bn_apply(const void* x, const void* residual, void* y, uint8_t* mask, int64_t rows, int32_t C,
+                      int32_t dtype, const float* scale, const float* shift, int32_t relu, void* stream);
+/* Backward of y = act(bn(x) (+res)).  g = dz * [y > 0] when relu, else g = dz.  The sign of y comes from `mask`
+ * (as written by b200_bn_apply) when it is given, otherwise from z = the saved output.
  *   dgamma = sum g*xhat, dbeta = sum g, dx = gamma*invstd*(g - dbeta/n - xhat*dgamma/n);
  *   dres (optional, may be NULL) receives g (gradient of the residual branch). */
-int32_t b200_bn_backward(const void* dz, const void* z, const void* x, void* dx, void* dres, int64_t rows, int32_t C,
-                         int32_t dtype, const float* gamma, const float* save_mean, const float* save_invstd,
-                         int32_t relu, float* dgamma, float* dbeta, void* ws, int64_t ws_bytes, void* stream);
+int32_t b200_bn_backward(const void* dz, const void* z, const uint8_t* mask, const void* x, void* dx, void* dres,
+                         int64_t rows, int32_t C, int32_t dtype, const float* gamma, const float* save_mean,
+                         const float* save_invstd, int32_t relu, float* dgamma, float* dbeta, void* ws,
+                         int64_t ws_bytes, void* stream);
 /* standalone ReLU backward / elementwise add used between blocks: y = a + b ; y = dz*[z>0] */
 int32_t b200_add(const void* a, const void* b, void* y, int64_t n, int32_t dtype, void* stream);
 int32_t b200_relu_bwd(const void* dz, const void* z, void* dx, int64_t n, int32_t dtype, void* stream);

@@ -1,7 +1,10 @@
 // BatchNorm2d (+ReLU, +residual) over NHWC activations [rows][C]: bandwidth kernels.
-//   statistics : vectorised column sums (16-byte loads), per-block partials in the workspace, fp64 finalize
-//                (deterministic: no atomics), running-stat EMA in the same finalize launch
-//   apply      : y = act(x*scale + shift (+res)), one pass, 16-byte loads/stores
+//   statistics : vectorised column sums (16-byte loads, four rows in flight per thread), per-block partials in the
+//                workspace, fp64 finalize (deterministic: no atomics), running-stat EMA in the same finalize launch.
+//                In bf16 training the forward statistics normally come from the convolution epilogue instead
+//                (b200_conv_fprop_bnstats) and only the finalize launch runs.
+//   apply      : y = act(x*scale + shift (+res)), one pass; optionally emits the ReLU mask as one byte per 16-byte
+//                vector so the backward kernels never re-read the activation just to learn its sign
 //   backward   : partial sums of g and g*(x-mean) -> finalize (dgamma, dbeta, dx coefficients) -> one dx pass that
 //                also emits the residual-branch gradient
 #include "common.cuh"
@@ -9,7 +12,7 @@
 namespace b200 {
 
 constexpr int BN_THREADS = 256;
-constexpr int BN_MAX_BLOCKS = 592;  // 4 x 148 SMs
+constexpr int BN_MAX_BLOCKS = 296;  // 2 x 148 SMs (each thread keeps four rows of 16-byte loads in flight)
 
 static inline int pow2_ceil(int v) {
   int p = 1;
@@ -17,12 +20,35 @@ static inline int pow2_ceil(int v) {
   return p;
 }
 
-// part layout: [nblk][2][C]
-template <typename T, int VEC, bool BWD>
+// raw 16-byte vector <-> floats
+__device__ __forceinline__ void unpack16(const uint4& v, float (&f)[4]) {
+  f[0] = __uint_as_float(v.x); f[1] = __uint_as_float(v.y); f[2] = __uint_as_float(v.z); f[3] = __uint_as_float(v.w);
+}
+__device__ __forceinline__ void unpack16(const uint4& v, float (&f)[8]) {
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 t = __bfloat1622float2(h[i]);
+    f[2 * i] = t.x;
+    f[2 * i + 1] = t.y;
+  }
+}
+
+// what the partial-sum kernel accumulates
+enum { PM_FWD = 0,       // sum x, sum x^2
+       PM_BWD = 1,       // g = dz                      : sum g, sum g*(x-mean)
+       PM_BWD_Z = 2,     // g = dz * [z > 0]
+       PM_BWD_MASK = 3   // g = dz * mask bit
+};
+
+// part layout: [nblk][2][C].  Vector path: a thread owns one 16-byte channel vector and walks rows.
+template <typename T, int MODE>
 __global__ void __launch_bounds__(BN_THREADS)
-bn_partial_kernel(const T* __restrict__ x, const T* __restrict__ dz, const T* __restrict__ z,
-                  const float* __restrict__ mean, long long rows, int C, int cx, long long rows_per_block, int relu,
-                  float* __restrict__ part) {
+bn_partial_vec_kernel(const T* __restrict__ x, const T* __restrict__ dz, const T* __restrict__ z,
+                      const uint8_t* __restrict__ mask, const float* __restrict__ mean, long long rows, int C, int cx,
+                      long long rows_per_block, float* __restrict__ part) {
+  constexpr int VEC = VecTraits<T>::W;
+  constexpr int U = 4;  // rows in flight per thread (raw 16-byte registers, converted only when consumed)
   __shared__ float red[BN_THREADS][2 * VEC + 1];
   const int nvec = C / VEC;
   const int ry = BN_THREADS / cx;
@@ -37,45 +63,46 @@ bn_partial_kernel(const T* __restrict__ x, const T* __restrict__ dz, const T* __
 #pragma unroll
     for (int e = 0; e < VEC; ++e) { s0[e] = 0.f; s1[e] = 0.f; mu[e] = 0.f; }
     if (active) {
-      if (BWD) {
+      if (MODE != PM_FWD) {
 #pragma unroll
         for (int e = 0; e < VEC; ++e) mu[e] = mean[cv * VEC + e];
       }
-      // U rows in flight per thread: all loads of an iteration are issued before any of them is consumed
-      constexpr int U = BWD ? 2 : 4;
       for (long long r = r0 + ty; r < r1; r += (long long)U * ry) {
-        float xv[U][VEC], gv[BWD ? U : 1][VEC], zv[BWD ? U : 1][VEC];
+        uint4 xr[U], gr[U], zr[U];
+        uint32_t mk[U];
         bool ok[U];
 #pragma unroll
         for (int u = 0; u < U; ++u) {
           const long long rr = r + (long long)u * ry;
           ok[u] = rr < r1;
           if (ok[u]) {
-            const long long off = rr * C + (long long)cv * VEC;
-            if constexpr (VEC == 1) {
-              xv[u][0] = to_f(x[off]);
-              if (BWD) { gv[u][0] = to_f(dz[off]); zv[u][0] = relu ? to_f(z[off]) : 1.f; }
-            } else {
-              load_vec(x + off, reinterpret_cast<float(&)[VecTraits<T>::W]>(xv[u]));
-              if (BWD) {
-                load_vec(dz + off, reinterpret_cast<float(&)[VecTraits<T>::W]>(gv[u]));
-                if (relu) load_vec(z + off, reinterpret_cast<float(&)[VecTraits<T>::W]>(zv[u]));
-              }
-            }
+            const long long vi = rr * nvec + cv;           // vector index
+            xr[u] = reinterpret_cast<const uint4*>(x)[vi];
+            if (MODE != PM_FWD) gr[u] = reinterpret_cast<const uint4*>(dz)[vi];
+            if (MODE == PM_BWD_Z) zr[u] = reinterpret_cast<const uint4*>(z)[vi];
+            if (MODE == PM_BWD_MASK) mk[u] = mask[vi];
           }
         }
 #pragma unroll
         for (int u = 0; u < U; ++u) {
           if (!ok[u]) continue;
-          if (!BWD) {
+          float xv[VEC];
+          unpack16(xr[u], xv);
+          if (MODE == PM_FWD) {
 #pragma unroll
-            for (int e = 0; e < VEC; ++e) { s0[e] += xv[u][e]; s1[e] = fmaf(xv[u][e], xv[u][e], s1[e]); }
+            for (int e = 0; e < VEC; ++e) { s0[e] += xv[e]; s1[e] = fmaf(xv[e], xv[e], s1[e]); }
           } else {
+            float gv[VEC], zv[VEC];
+            unpack16(gr[u], gv);
+            if (MODE == PM_BWD_Z) unpack16(zr[u], zv);
 #pragma unroll
             for (int e = 0; e < VEC; ++e) {
-              const float g = (!relu || zv[u][e] > 0.f) ? gv[u][e] : 0.f;
+              bool on = true;
+              if (MODE == PM_BWD_Z) on = zv[e] > 0.f;
+              if (MODE == PM_BWD_MASK) on = (mk[u] >> e) & 1u;
+              const float g = on ? gv[e] : 0.f;
               s0[e] += g;
-              s1[e] = fmaf(g, xv[u][e] - mu[e], s1[e]);
+              s1[e] = fmaf(g, xv[e] - mu[e], s1[e]);
             }
           }
         }
@@ -97,27 +124,72 @@ bn_partial_kernel(const T* __restrict__ x, const T* __restrict__ dz, const T* __
   }
 }
 
-// Sums the per-block partials: a block owns 32 channels (coalesced across x) and 16 partial-lanes (y).
+// scalar path (C not a multiple of the vector width): a thread owns one channel
+template <typename T, int MODE>
+__global__ void __launch_bounds__(BN_THREADS)
+bn_partial_scalar_kernel(const T* __restrict__ x, const T* __restrict__ dz, const T* __restrict__ z,
+                         const float* __restrict__ mean, long long rows, int C, int cx, long long rows_per_block,
+                         float* __restrict__ part) {
+  __shared__ float red[BN_THREADS][3];
+  const int ry = BN_THREADS / cx;
+  const int tx = threadIdx.x % cx, ty = threadIdx.x / cx;
+  const long long r0 = blockIdx.x * rows_per_block;
+  long long r1 = r0 + rows_per_block;
+  if (r1 > rows) r1 = rows;
+  for (int base = 0; base < C; base += cx) {
+    const int c = base + tx;
+    const bool active = c < C;
+    float s0 = 0.f, s1 = 0.f;
+    if (active) {
+      const float mu = MODE != PM_FWD ? mean[c] : 0.f;
+      for (long long r = r0 + ty; r < r1; r += ry) {
+        const long long off = r * C + c;
+        const float xv = to_f(x[off]);
+        if (MODE == PM_FWD) { s0 += xv; s1 = fmaf(xv, xv, s1); }
+        else {
+          float g = to_f(dz[off]);
+          if (MODE == PM_BWD_Z && !(to_f(z[off]) > 0.f)) g = 0.f;
+          s0 += g;
+          s1 = fmaf(g, xv - mu, s1);
+        }
+      }
+    }
+    red[threadIdx.x][0] = s0;
+    red[threadIdx.x][1] = s1;
+    __syncthreads();
+    if (ty == 0 && active) {
+      float a = 0.f, b = 0.f;
+      for (int yy = 0; yy < ry; ++yy) { a += red[yy * cx + tx][0]; b += red[yy * cx + tx][1]; }
+      part[((long long)blockIdx.x * 2 + 0) * C + c] = a;
+      part[((long long)blockIdx.x * 2 + 1) * C + c] = b;
+    }
+    __syncthreads();
+  }
+}
+
+// Sums the per-block partials: a block owns 32 channels (coalesced across x) and 32 partial-lanes (y).
 constexpr int FIN_CX = 32, FIN_RY = 32;
 __device__ __forceinline__ void bn_sum_partials(const float* __restrict__ part, int nblk, int C, int c, double& s,
                                                 double& q) {
   __shared__ double red[2][FIN_RY][FIN_CX + 1];
   double a = 0, b = 0;
   if (c < C) {
-    // two independent accumulation chains and all four loads of an iteration issued together
-    double a1 = 0, b1 = 0;
+    // four independent accumulation chains; the eight loads of an iteration are issued together
+    double a1 = 0, b1 = 0, a2 = 0, b2 = 0, a3 = 0, b3 = 0;
     int i = threadIdx.y;
-    for (; i + FIN_RY < nblk; i += 2 * FIN_RY) {
+    for (; i + 3 * FIN_RY < nblk; i += 4 * FIN_RY) {
       const float x0 = part[((long long)i * 2 + 0) * C + c], y0 = part[((long long)i * 2 + 1) * C + c];
       const float x1 = part[((long long)(i + FIN_RY) * 2 + 0) * C + c], y1 = part[((long long)(i + FIN_RY) * 2 + 1) * C + c];
-      a += x0; b += y0; a1 += x1; b1 += y1;
+      const float x2 = part[((long long)(i + 2 * FIN_RY) * 2 + 0) * C + c], y2 = part[((long long)(i + 2 * FIN_RY) * 2 + 1) * C + c];
+      const float x3 = part[((long long)(i + 3 * FIN_RY) * 2 + 0) * C + c], y3 = part[((long long)(i + 3 * FIN_RY) * 2 + 1) * C + c];
+      a += x0; b += y0; a1 += x1; b1 += y1; a2 += x2; b2 += y2; a3 += x3; b3 += y3;
     }
-    if (i < nblk) {
+    for (; i < nblk; i += FIN_RY) {
       a += part[((long long)i * 2 + 0) * C + c];
       b += part[((long long)i * 2 + 1) * C + c];
     }
-    a += a1;
-    b += b1;
+    a += a1 + a2 + a3;
+    b += b1 + b2 + b3;
   }
   red[0][threadIdx.y][threadIdx.x] = a;
   red[1][threadIdx.y][threadIdx.x] = b;
@@ -181,8 +253,9 @@ bn_finalize_bwd_kernel(const float* __restrict__ part, int nblk, int C, double n
 // per-channel constants in registers (the streaming loop is then loads + FMAs + store only).
 template <typename T, int VEC, bool FIXEDC>
 __global__ void __launch_bounds__(BN_THREADS)
-bn_apply_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __restrict__ y, long long nvec_total, int nvec,
-                const float* __restrict__ scale, const float* __restrict__ shift, int relu) {
+bn_apply_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __restrict__ y, uint8_t* __restrict__ mask,
+                long long nvec_total, int nvec, const float* __restrict__ scale, const float* __restrict__ shift,
+                int relu) {
   const long long stride = (long long)gridDim.x * blockDim.x;
   long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   float sc[VEC], sh[VEC];
@@ -204,6 +277,7 @@ bn_apply_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __restric
       load_vec(x + off, reinterpret_cast<float(&)[VecTraits<T>::W]>(xv));
       if (res) load_vec(res + off, reinterpret_cast<float(&)[VecTraits<T>::W]>(rv));
     }
+    uint32_t m = 0;
 #pragma unroll
     for (int e = 0; e < VEC; ++e) {
       float v = fmaf(xv[e], sc[e], sh[e]);
@@ -212,15 +286,24 @@ bn_apply_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __restric
       xv[e] = v;
     }
     if constexpr (VEC == 1) y[off] = from_f<T>(xv[0]);
-    else store_vec(y + off, reinterpret_cast<float(&)[VecTraits<T>::W]>(xv));
+    else {
+      store_vec(y + off, reinterpret_cast<float(&)[VecTraits<T>::W]>(xv));
+      if (mask) {
+        // the bit must describe the STORED value (after rounding to T), which is what "z > 0" meant before
+#pragma unroll
+        for (int e = 0; e < VEC; ++e) m |= (to_f(from_f<T>(xv[e])) > 0.f ? 1u : 0u) << e;
+        mask[i] = (uint8_t)m;
+      }
+    }
   }
 }
 
-template <typename T, int VEC, bool FIXEDC>
+enum { DM_NONE = 0, DM_Z = 1, DM_MASK = 2 };
+template <typename T, int VEC, bool FIXEDC, int DMODE>
 __global__ void __launch_bounds__(BN_THREADS)
-bn_bwd_dx_kernel(const T* __restrict__ dz, const T* __restrict__ z, const T* __restrict__ x, T* __restrict__ dx,
-                 T* __restrict__ dres, long long nvec_total, int nvec, int C, const float* __restrict__ mean,
-                 const float* __restrict__ coef, int relu) {
+bn_bwd_dx_kernel(const T* __restrict__ dz, const T* __restrict__ z, const uint8_t* __restrict__ mask,
+                 const T* __restrict__ x, T* __restrict__ dx, T* __restrict__ dres, long long nvec_total, int nvec,
+                 int C, const float* __restrict__ mean, const float* __restrict__ coef) {
   const long long stride = (long long)gridDim.x * blockDim.x;
   long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   float cA[VEC], cB[VEC], cC[VEC], mu[VEC];
@@ -237,15 +320,22 @@ bn_bwd_dx_kernel(const T* __restrict__ dz, const T* __restrict__ z, const T* __r
     }
     const long long off = i * VEC;
     float gv[VEC], zv[VEC], xv[VEC];
-    if constexpr (VEC == 1) { gv[0] = to_f(dz[off]); xv[0] = to_f(x[off]); zv[0] = relu ? to_f(z[off]) : 1.f; }
-    else {
+    uint32_t m = 0xffffffffu;
+    if constexpr (VEC == 1) {
+      gv[0] = to_f(dz[off]); xv[0] = to_f(x[off]);
+      if (DMODE == DM_Z) zv[0] = to_f(z[off]);
+    } else {
       load_vec(dz + off, reinterpret_cast<float(&)[VecTraits<T>::W]>(gv));
       load_vec(x + off, reinterpret_cast<float(&)[VecTraits<T>::W]>(xv));
-      if (relu) load_vec(z + off, reinterpret_cast<float(&)[VecTraits<T>::W]>(zv));
+      if (DMODE == DM_Z) load_vec(z + off, reinterpret_cast<float(&)[VecTraits<T>::W]>(zv));
+      if (DMODE == DM_MASK) m = mask[i];
     }
 #pragma unroll
     for (int e = 0; e < VEC; ++e) {
-      const float g = (!relu || zv[e] > 0.f) ? gv[e] : 0.f;
+      bool on = true;
+      if (DMODE == DM_Z) on = zv[e] > 0.f;
+      if (DMODE == DM_MASK) on = (m >> e) & 1u;
+      const float g = on ? gv[e] : 0.f;
       gv[e] = g;
       xv[e] = cA[e] * g - cC[e] - cB[e] * (xv[e] - mu[e]);
     }
@@ -280,10 +370,9 @@ static inline int ew_grid_fixed(long long total, int nvec, bool* fixed) {
   int g = ew_grid(total);
   *fixed = false;
   if (nvec <= 0) return g;
-  // smallest multiple m of (nvec / gcd(nvec, BN_THREADS)) blocks keeps every thread on one channel vector
   int a = nvec, b = BN_THREADS;
   while (b) { int t = a % b; a = b; b = t; }
-  const int per = nvec / a;
+  const int per = nvec / a;   // blocks per period: g must be a multiple of it
   if (per <= g) { g = g / per * per; *fixed = true; }
   else if (per <= 4096 && (long long)per * BN_THREADS <= total * 2) { g = per; *fixed = true; }
   return g;
@@ -301,7 +390,7 @@ static BnPlan bn_plan(long long rows, int C) {
   p.cx = pow2_ceil(nvec);
   if (p.cx > BN_THREADS) p.cx = BN_THREADS;
   const int ry = BN_THREADS / p.cx;
-  // at least 32 rows per row-lane (keeps the partial-sum traffic far below the tensor's own bytes when C is large),
+  // at least 16 rows per row-lane (keeps the partial-sum traffic far below the tensor's own bytes when C is large),
   // at most BN_MAX_BLOCKS blocks
   long long rpb = (long long)ry * 16;
   long long nblk = (rows + rpb - 1) / rpb;
@@ -316,56 +405,75 @@ static BnPlan bn_plan(long long rows, int C) {
 }
 
 template <typename T>
+static void launch_bn_partial(const BnPlan& p, int mode, const T* x, const T* dz, const T* z, const uint8_t* mask,
+                              const float* mean, long long rows, int C, float* part, cudaStream_t st) {
+  if (p.vec == 1) {
+    if (mode == PM_FWD) bn_partial_scalar_kernel<T, PM_FWD><<<p.nblk, BN_THREADS, 0, st>>>(x, dz, z, mean, rows, C, p.cx, p.rows_per_block, part);
+    else if (mode == PM_BWD) bn_partial_scalar_kernel<T, PM_BWD><<<p.nblk, BN_THREADS, 0, st>>>(x, dz, z, mean, rows, C, p.cx, p.rows_per_block, part);
+    else bn_partial_scalar_kernel<T, PM_BWD_Z><<<p.nblk, BN_THREADS, 0, st>>>(x, dz, z, mean, rows, C, p.cx, p.rows_per_block, part);
+    return;
+  }
+  if (mode == PM_FWD) bn_partial_vec_kernel<T, PM_FWD><<<p.nblk, BN_THREADS, 0, st>>>(x, dz, z, mask, mean, rows, C, p.cx, p.rows_per_block, part);
+  else if (mode == PM_BWD) bn_partial_vec_kernel<T, PM_BWD><<<p.nblk, BN_THREADS, 0, st>>>(x, dz, z, mask, mean, rows, C, p.cx, p.rows_per_block, part);
+  else if (mode == PM_BWD_Z) bn_partial_vec_kernel<T, PM_BWD_Z><<<p.nblk, BN_THREADS, 0, st>>>(x, dz, z, mask, mean, rows, C, p.cx, p.rows_per_block, part);
+  else bn_partial_vec_kernel<T, PM_BWD_MASK><<<p.nblk, BN_THREADS, 0, st>>>(x, dz, z, mask, mean, rows, C, p.cx, p.rows_per_block, part);
+}
+
+template <typename T>
 static int32_t bn_stats_impl(const T* x, long long rows, int C, const float* gamma, const float* beta, float* rm,
                              float* rv, float momentum, float eps, float* save_mean, float* save_invstd, float* scale,
                              float* shift, float* part, cudaStream_t st) {
   const BnPlan p = bn_plan<T>(rows, C);
-  if (p.vec == 1)
-    bn_partial_kernel<T, 1, false><<<p.nblk, BN_THREADS, 0, st>>>(x, nullptr, nullptr, nullptr, rows, C, p.cx, p.rows_per_block, 0, part);
-  else
-    bn_partial_kernel<T, VecTraits<T>::W, false><<<p.nblk, BN_THREADS, 0, st>>>(x, nullptr, nullptr, nullptr, rows, C, p.cx, p.rows_per_block, 0, part);
+  launch_bn_partial<T>(p, PM_FWD, x, nullptr, nullptr, nullptr, nullptr, rows, C, part, st);
   bn_finalize_fwd_kernel<<<(C + FIN_CX - 1) / FIN_CX, dim3(FIN_CX, FIN_RY), 0, st>>>(part, p.nblk, C, (double)rows, gamma, beta, rm, rv, momentum, eps, save_mean, save_invstd, scale, shift);
   return check_launch("bn_train_stats", 2);
 }
 
 template <typename T>
-static int32_t bn_apply_impl(const T* x, const T* res, T* y, long long rows, int C, const float* scale,
+static int32_t bn_apply_impl(const T* x, const T* res, T* y, uint8_t* mask, long long rows, int C, const float* scale,
                              const float* shift, int relu, cudaStream_t st) {
   const bool aligned = ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y) | reinterpret_cast<uintptr_t>(res)) & 15) == 0;
   if (C % VecTraits<T>::W == 0 && aligned) {
     constexpr int V = VecTraits<T>::W;
     bool fixed;
     const int grid = ew_grid_fixed(rows * (C / V), C / V, &fixed);
-    if (fixed) bn_apply_kernel<T, V, true><<<grid, BN_THREADS, 0, st>>>(x, res, y, rows * (C / V), C / V, scale, shift, relu);
-    else bn_apply_kernel<T, V, false><<<grid, BN_THREADS, 0, st>>>(x, res, y, rows * (C / V), C / V, scale, shift, relu);
+    if (fixed) bn_apply_kernel<T, V, true><<<grid, BN_THREADS, 0, st>>>(x, res, y, mask, rows * (C / V), C / V, scale, shift, relu);
+    else bn_apply_kernel<T, V, false><<<grid, BN_THREADS, 0, st>>>(x, res, y, mask, rows * (C / V), C / V, scale, shift, relu);
   } else {
-    bn_apply_kernel<T, 1, false><<<ew_grid(rows * C), BN_THREADS, 0, st>>>(x, res, y, rows * C, C, scale, shift, relu);
+    if (mask) return fail(B200_UNSUPPORTED, "bn_apply: the ReLU mask needs C %% %d == 0 and 16-byte aligned tensors", VecTraits<T>::W);
+    bn_apply_kernel<T, 1, false><<<ew_grid(rows * C), BN_THREADS, 0, st>>>(x, res, y, nullptr, rows * C, C, scale, shift, relu);
   }
   return check_launch("bn_apply");
 }
 
 template <typename T>
-static int32_t bn_bwd_impl(const T* dz, const T* z, const T* x, T* dx, T* dres, long long rows, int C,
-                           const float* gamma, const float* mean, const float* invstd, int relu, float* dgamma,
+static int32_t bn_bwd_impl(const T* dz, const T* z, const uint8_t* mask, const T* x, T* dx, T* dres, long long rows,
+                           int C, const float* gamma, const float* mean, const float* invstd, int relu, float* dgamma,
                            float* dbeta, float* ws, cudaStream_t st) {
   const BnPlan p = bn_plan<T>(rows, C);
   float* part = ws;
   float* coef = ws + (size_t)BN_MAX_BLOCKS * 2 * C;
-  if (p.vec == 1)
-    bn_partial_kernel<T, 1, true><<<p.nblk, BN_THREADS, 0, st>>>(x, dz, z, mean, rows, C, p.cx, p.rows_per_block, relu, part);
-  else
-    bn_partial_kernel<T, VecTraits<T>::W, true><<<p.nblk, BN_THREADS, 0, st>>>(x, dz, z, mean, rows, C, p.cx, p.rows_per_block, relu, part);
-  bn_finalize_bwd_kernel<<<(C + FIN_CX - 1) / FIN_CX, dim3(FIN_CX, FIN_RY), 0, st>>>(part, p.nblk, C, (double)rows, gamma, invstd, dgamma, dbeta, coef);
   const bool aligned = ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(dz) | reinterpret_cast<uintptr_t>(z) |
                          reinterpret_cast<uintptr_t>(dx) | reinterpret_cast<uintptr_t>(dres)) & 15) == 0;
-  if (p.vec != 1 && aligned) {
+  if (mask && (p.vec == 1 || !aligned))
+    return fail(B200_UNSUPPORTED, "bn_backward: the ReLU mask needs C %% %d == 0 and 16-byte aligned tensors", VecTraits<T>::W);
+  if (p.vec != 1 && !aligned) return fail(B200_INVALID_ARG, "bn_backward: tensors must be 16-byte aligned");
+  const int pmode = !relu ? PM_BWD : (mask ? PM_BWD_MASK : PM_BWD_Z);
+  launch_bn_partial<T>(p, pmode, x, dz, z, mask, mean, rows, C, part, st);
+  bn_finalize_bwd_kernel<<<(C + FIN_CX - 1) / FIN_CX, dim3(FIN_CX, FIN_RY), 0, st>>>(part, p.nblk, C, (double)rows, gamma, invstd, dgamma, dbeta, coef);
+  if (p.vec != 1) {
     constexpr int V = VecTraits<T>::W;
     bool fixed;
     const int grid = ew_grid_fixed(rows * (C / V), C / V, &fixed);
-    if (fixed) bn_bwd_dx_kernel<T, V, true><<<grid, BN_THREADS, 0, st>>>(dz, z, x, dx, dres, rows * (C / V), C / V, C, mean, coef, relu);
-    else bn_bwd_dx_kernel<T, V, false><<<grid, BN_THREADS, 0, st>>>(dz, z, x, dx, dres, rows * (C / V), C / V, C, mean, coef, relu);
+    const long long nv = rows * (C / V);
+#define B200_DX(FX, DM) bn_bwd_dx_kernel<T, V, FX, DM><<<grid, BN_THREADS, 0, st>>>(dz, z, mask, x, dx, dres, nv, C / V, C, mean, coef)
+    if (!relu) { if (fixed) B200_DX(true, DM_NONE); else B200_DX(false, DM_NONE); }
+    else if (mask) { if (fixed) B200_DX(true, DM_MASK); else B200_DX(false, DM_MASK); }
+    else { if (fixed) B200_DX(true, DM_Z); else B200_DX(false, DM_Z); }
+#undef B200_DX
   } else {
-    bn_bwd_dx_kernel<T, 1, false><<<ew_grid(rows * C), BN_THREADS, 0, st>>>(dz, z, x, dx, dres, rows * C, C, C, mean, coef, relu);
+    if (!relu) bn_bwd_dx_kernel<T, 1, false, DM_NONE><<<ew_grid(rows * C), BN_THREADS, 0, st>>>(dz, z, nullptr, x, dx, dres, rows * C, C, C, mean, coef);
+    else bn_bwd_dx_kernel<T, 1, false, DM_Z><<<ew_grid(rows * C), BN_THREADS, 0, st>>>(dz, z, nullptr, x, dx, dres, rows * C, C, C, mean, coef);
   }
   return check_launch("bn_backward", 3);
 }
@@ -387,6 +495,12 @@ using namespace b200;
 extern "C" int64_t b200_bn_workspace_bytes(int64_t rows, int32_t C) {
   (void)rows;
   return (int64_t)((size_t)BN_MAX_BLOCKS * 2 * C + 3 * (size_t)C) * 4;
+}
+
+extern "C" int64_t b200_bn_mask_bytes(int64_t rows, int32_t C, int32_t dtype) {
+  const int W = dtype == B200_BF16 ? 8 : 4;
+  if (rows <= 0 || C <= 0 || C % W != 0) return 0;
+  return rows * (int64_t)(C / W);
 }
 
 extern "C" int32_t b200_bn_train_stats(const void* x, int64_t rows, int32_t C, int32_t dtype, const float* gamma,
@@ -425,28 +539,28 @@ extern "C" int32_t b200_bn_eval_coeffs(const float* gamma, const float* beta, co
   return check_launch("bn_eval_coeffs");
 }
 
-extern "C" int32_t b200_bn_apply(const void* x, const void* residual, void* y, int64_t rows, int32_t C, int32_t dtype,
-                                 const float* scale, const float* shift, int32_t relu, void* stream) {
+extern "C" int32_t b200_bn_apply(const void* x, const void* residual, void* y, uint8_t* mask, int64_t rows, int32_t C,
+                                 int32_t dtype, const float* scale, const float* shift, int32_t relu, void* stream) {
   if (!x || !y || !scale || !shift || rows <= 0 || C <= 0) return fail(B200_INVALID_ARG, "bn_apply: bad arguments");
   cudaStream_t st = as_stream(stream);
-  if (dtype == B200_F32) return bn_apply_impl<float>((const float*)x, (const float*)residual, (float*)y, rows, C, scale, shift, relu, st);
+  if (dtype == B200_F32) return bn_apply_impl<float>((const float*)x, (const float*)residual, (float*)y, mask, rows, C, scale, shift, relu, st);
   if (dtype == B200_BF16)
-    return bn_apply_impl<__nv_bfloat16>((const __nv_bfloat16*)x, (const __nv_bfloat16*)residual, (__nv_bfloat16*)y, rows, C, scale, shift, relu, st);
+    return bn_apply_impl<__nv_bfloat16>((const __nv_bfloat16*)x, (const __nv_bfloat16*)residual, (__nv_bfloat16*)y, mask, rows, C, scale, shift, relu, st);
   return fail(B200_INVALID_ARG, "bn_apply: bad dtype");
 }
 
-extern "C" int32_t b200_bn_backward(const void* dz, const void* z, const void* x, void* dx, void* dres, int64_t rows,
-                                    int32_t C, int32_t dtype, const float* gamma, const float* save_mean,
-                                    const float* save_invstd, int32_t relu, float* dgamma, float* dbeta, void* ws,
-                                    int64_t ws_bytes, void* stream) {
-  if (!dz || !x || !dx || !save_mean || !save_invstd || rows <= 0 || C <= 0 || (relu && !z))
+extern "C" int32_t b200_bn_backward(const void* dz, const void* z, const uint8_t* mask, const void* x, void* dx,
+                                    void* dres, int64_t rows, int32_t C, int32_t dtype, const float* gamma,
+                                    const float* save_mean, const float* save_invstd, int32_t relu, float* dgamma,
+                                    float* dbeta, void* ws, int64_t ws_bytes, void* stream) {
+  if (!dz || !x || !dx || !save_mean || !save_invstd || rows <= 0 || C <= 0 || (relu && !z && !mask))
     return fail(B200_INVALID_ARG, "bn_backward: bad arguments");
   if (!ws || ws_bytes < b200_bn_workspace_bytes(rows, C)) return fail(B200_WORKSPACE_TOO_SMALL, "bn_backward: workspace too small");
   cudaStream_t st = as_stream(stream);
   if (dtype == B200_F32)
-    return bn_bwd_impl<float>((const float*)dz, (const float*)z, (const float*)x, (float*)dx, (float*)dres, rows, C, gamma, save_mean, save_invstd, relu, dgamma, dbeta, (float*)ws, st);
+    return bn_bwd_impl<float>((const float*)dz, (const float*)z, mask, (const float*)x, (float*)dx, (float*)dres, rows, C, gamma, save_mean, save_invstd, relu, dgamma, dbeta, (float*)ws, st);
   if (dtype == B200_BF16)
-    return bn_bwd_impl<__nv_bfloat16>((const __nv_bfloat16*)dz, (const __nv_bfloat16*)z, (const __nv_bfloat16*)x, (__nv_bfloat16*)dx, (__nv_bfloat16*)dres, rows, C, gamma, save_mean, save_invstd, relu, dgamma, dbeta, (float*)ws, st);
+    return bn_bwd_impl<__nv_bfloat16>((const __nv_bfloat16*)dz, (const __nv_bfloat16*)z, mask, (const __nv_bfloat16*)x, (__nv_bfloat16*)dx, (__nv_bfloat16*)dres, rows, C, gamma, save_mean, save_invstd, relu, dgamma, dbeta, (float*)ws, st);
   return fail(B200_INVALID_ARG, "bn_backward: bad dtype");
 }
 
@@ -521,10 +635,7 @@ static int32_t bn_stats_noalloc_impl(const T* x, long long rows, int C, const fl
     p.rows_per_block = rpb;
     p.nblk = (int)((rows + rpb - 1) / rpb);
   }
-  if (p.vec == 1)
-    bn_partial_kernel<T, 1, false><<<p.nblk, BN_THREADS, 0, st>>>(x, nullptr, nullptr, nullptr, rows, C, p.cx, p.rows_per_block, 0, part);
-  else
-    bn_partial_kernel<T, VecTraits<T>::W, false><<<p.nblk, BN_THREADS, 0, st>>>(x, nullptr, nullptr, nullptr, rows, C, p.cx, p.rows_per_block, 0, part);
+  launch_bn_partial<T>(p, PM_FWD, x, nullptr, nullptr, nullptr, nullptr, rows, C, part, st);
   bn_finalize_fwd_kernel<<<(C + FIN_CX - 1) / FIN_CX, dim3(FIN_CX, FIN_RY), 0, st>>>(part, p.nblk, C, (double)rows, gamma, beta, rm, rv, momentum, eps, save_mean, save_invstd, scale, shift);
   return check_launch("bn_train_stats_noalloc", 2);
 }

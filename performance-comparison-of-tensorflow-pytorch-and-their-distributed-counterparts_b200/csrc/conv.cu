@@ -483,7 +483,11 @@ extern "C" int64_t b200_conv_fprop_bnstats_rows(const b200_conv_desc* d) {
   if (off || !implicit_ok(d)) return 0;
   const ConvGeom g = geom(d);
   const PixelBox b = fprop_box(d, g);
-  return (int64_t)b.tiles_w * b.tiles_h * b.tiles_n;
+  const int bn = d->K > 128 ? 256 : (d->K > 64 ? 128 : 64);
+  const int n_tiles = (d->K + bn - 1) / bn;
+  const long long total = (long long)b.tiles_w * b.tiles_h * b.tiles_n * n_tiles;
+  if (total > 0x7fffffffLL) return 0;
+  return conv_stats_grid((int)total, n_tiles, num_sms()) / n_tiles;   // rows of partial sums the launch writes
 }
 
 extern "C" int32_t b200_conv_fprop_bnstats(const b200_conv_desc* d, const void* x, const void* w, void* y,

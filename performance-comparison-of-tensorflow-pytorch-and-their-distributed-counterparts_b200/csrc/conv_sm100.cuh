@@ -288,6 +288,11 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     const int l = q * 32 + lane;  // accumulator row
     uint32_t it = 0;
     uint32_t stage_ctr = 0;       // staging-tile ring position (TMA-store epilogue)
+    // fused BatchNorm statistics: this thread's running column sums over ALL tiles of this CTA (the launcher makes
+    // gridDim a multiple of n_tiles, so a CTA only ever sees one output-column tile)
+    float st_acc[BN / 64][4];
+#pragma unroll
+    for (int g = 0; g < BN / 64; ++g) { st_acc[g][0] = 0.f; st_acc[g][1] = 0.f; st_acc[g][2] = 0.f; st_acc[g][3] = 0.f; }
     for (int tile = blockIdx.x; tile < P.total_tiles; tile += gridDim.x, ++it) {
       const ConvTile T = conv_decode_tile<BN, MODE>(P, tile);
       const uint32_t buf = it & 1, use = it >> 1;
@@ -315,7 +320,7 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         // tensor store per 64-channel group (full 128-byte lines, bounds clipped by the TMA unit).  Two staging
         // tiles alternate so the store of group g overlaps the TMEM reads / packing of group g+1.
         const bool elected = (warp == 2 && lane == 0);
-#pragma unroll 1
+#pragma unroll
         for (int g = 0; g < BN / 64; ++g) {
           if (T.n0 + g * 64 >= P.ncols) break;     // uniform across the CTA
           uint8_t* stg = smStage + (stage_ctr & 1u) * (CONV_STAGING_BYTES / 2);
@@ -354,34 +359,16 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           }
           if (MODE == MODE_FPROP && P.stats != nullptr) {
             // Fused BatchNorm statistics: column sums of the bf16 tile that was just staged.  Thread (warp q, lane)
-            // owns columns 2*lane, 2*lane+1 over rows 32q..32q+31 (one conflict-free 4-byte smem read per row);
-            // warps 1..3 hand their partials to warp 0 through smem; one row of partials per pixel tile in global.
-            float s0a = 0.f, s0b = 0.f, s1a = 0.f, s1b = 0.f;
-            const int cpair = lane;
+            // owns columns 2*lane, 2*lane+1 over rows 32q..32q+31 (one conflict-free 4-byte smem read per row) and
+            // keeps the sums in registers until the CTA has finished all of its tiles.
 #pragma unroll 8
             for (int i = 0; i < 32; ++i) {
               const int row = q * 32 + i;
-              const uint32_t w = *reinterpret_cast<const uint32_t*>(stg + row * 128 + (((cpair >> 2) ^ (row & 7)) << 4) +
-                                                                     ((cpair & 3) << 2));
+              const uint32_t w = *reinterpret_cast<const uint32_t*>(stg + row * 128 + (((lane >> 2) ^ (row & 7)) << 4) +
+                                                                     ((lane & 3) << 2));
               const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w));
-              s0a += f.x; s1a = fmaf(f.x, f.x, s1a);
-              s0b += f.y; s1b = fmaf(f.y, f.y, s1b);
-            }
-            if (q != 0) {
-              float* r = smRed + ((q - 1) * 64 + 2 * cpair) * 2;
-              r[0] = s0a; r[1] = s1a; r[2] = s0b; r[3] = s1b;
-            }
-            asm volatile("bar.sync 1, 128;" ::: "memory");
-            if (q == 0) {
-#pragma unroll
-              for (int w2 = 0; w2 < 3; ++w2) {
-                const float* r = smRed + (w2 * 64 + 2 * cpair) * 2;
-                s0a += r[0]; s1a += r[1]; s0b += r[2]; s1b += r[3];
-              }
-              const int ptile = tile / P.n_tiles;
-              float* dst = P.stats + (static_cast<long long>(ptile) * 2) * P.ncols + T.n0 + g * 64 + 2 * cpair;
-              *reinterpret_cast<float2*>(dst) = make_float2(s0a, s0b);
-              *reinterpret_cast<float2*>(dst + P.ncols) = make_float2(s1a, s1b);
+              st_acc[g][0] += f.x; st_acc[g][1] = fmaf(f.x, f.x, st_acc[g][1]);
+              st_acc[g][2] += f.y; st_acc[g][3] = fmaf(f.y, f.y, st_acc[g][3]);
             }
           }
           ++stage_ctr;
@@ -463,6 +450,32 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       if (lane == 0) mbar_arrive(&tmem_empty[buf]);
     }
     if (MODE != MODE_WGRAD && P.tma_store && warp == 2 && lane == 0) tma_store_wait<0>();  // smem must outlive the stores
+    if (MODE == MODE_FPROP && P.tma_store && P.stats != nullptr) {
+      // one row of partial statistics per CTA: warps 1..3 hand their sums to warp 0 through smem
+      const int n0 = (blockIdx.x % P.n_tiles) * BN;
+#pragma unroll
+      for (int g = 0; g < BN / 64; ++g) {
+        if (n0 + g * 64 >= P.ncols) break;
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (q != 0) {
+          float* r = smRed + ((q - 1) * 64 + 2 * lane) * 2;
+          r[0] = st_acc[g][0]; r[1] = st_acc[g][1]; r[2] = st_acc[g][2]; r[3] = st_acc[g][3];
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (q == 0) {
+          float a0 = st_acc[g][0], a1 = st_acc[g][1], b0 = st_acc[g][2], b1 = st_acc[g][3];
+#pragma unroll
+          for (int w2 = 0; w2 < 3; ++w2) {
+            const float* r = smRed + (w2 * 64 + 2 * lane) * 2;
+            a0 += r[0]; a1 += r[1]; b0 += r[2]; b1 += r[3];
+          }
+          // row = blockIdx.x / n_tiles: the n_tiles CTAs of a row cover the column tiles exactly once
+          float* dst = P.stats + (static_cast<long long>(blockIdx.x / P.n_tiles) * 2) * P.ncols + n0 + g * 64 + 2 * lane;
+          *reinterpret_cast<float2*>(dst) = make_float2(a0, b0);
+          *reinterpret_cast<float2*>(dst + P.ncols) = make_float2(a1, b1);
+        }
+      }
+    }
   }
 
   tc_fence_before();
@@ -517,6 +530,15 @@ inline PixelBox choose_pixel_box(int W, int H, int N, int max_rows, int mult, in
   return best;
 }
 
+// Grid of a fprop launch that also produces BN statistics: a multiple of n_tiles (so that tile = blockIdx.x +
+// i*gridDim keeps every CTA on one output-column tile) and never more than the number of tiles.  The launch writes
+// gridDim / n_tiles rows of partial statistics (CTA b fills its column tile of row b / n_tiles).
+inline int conv_stats_grid(int total_tiles, int n_tiles, int num_ctas) {
+  int g = total_tiles < num_ctas ? total_tiles : num_ctas;
+  g = g / n_tiles * n_tiles;
+  return g < n_tiles ? n_tiles : g;
+}
+
 template <int BN, int STAGES, int MODE>
 inline int launch_conv_cfg(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, const ConvParams& P,
                            int num_ctas, cudaStream_t st) {
@@ -528,7 +550,8 @@ inline int launch_conv_cfg(const CUtensorMap& ta, const CUtensorMap& tb, const C
     if (e != cudaSuccess) return 300 + static_cast<int>(e);
     attr_done = true;
   }
-  const int grid = P.total_tiles < num_ctas ? P.total_tiles : num_ctas;
+  int grid = P.total_tiles < num_ctas ? P.total_tiles : num_ctas;
+  if (MODE == MODE_FPROP && P.stats != nullptr) grid = conv_stats_grid(P.total_tiles, P.n_tiles, num_ctas);
   kern<<<grid, GEMM_THREADS, smem, st>>>(ta, tb, to, P);
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? 0 : 400 + static_cast<int>(e);

@@ -114,7 +114,7 @@ def _bn_coeffs(bn, y, bump_nbt=True, partials=None):
 # ------------------------------------------------------------------ the backbone as one autograd node
 class _Unit(object):
     """Saved state of one conv -> BN (-> +residual) (-> ReLU) unit."""
-    __slots__ = ("conv", "bn", "x", "y", "z", "mean", "invstd", "relu", "geom")
+    __slots__ = ("conv", "bn", "x", "y", "z", "mask", "mean", "invstd", "relu", "geom")
 
 
 def _unit_forward(conv, bn, x, relu, residual, save):
@@ -125,12 +125,13 @@ def _unit_forward(conv, bn, x, relu, residual, save):
     else:
         y, partials = ops.conv_fprop(x, wp, K, R, S, stride, pad), None
     scale, shift, mean, invstd = _bn_coeffs(bn, y, bump_nbt=False, partials=partials)
-    # eval mode: y is dead after the apply -> write in place
-    z = ops.bn_apply(y, scale, shift, relu, residual, out=None if save else y)
     if not save:
-        return z, None
+        # y is dead after the apply -> write in place
+        return ops.bn_apply(y, scale, shift, relu, residual, out=y), None
+    z, mask = ops.bn_apply(y, scale, shift, relu, residual, want_mask=True)
     u = _Unit()
     u.conv, u.bn, u.x, u.y, u.z, u.mean, u.invstd, u.relu = conv, bn, x, y, z, mean, invstd, relu
+    u.mask = mask
     u.geom = (K, R, S, stride, pad)
     return z, u
 
@@ -210,7 +211,8 @@ class _ResNetBackbone(torch.autograd.Function):
                 raise RuntimeError("b200net: backward through BatchNorm in eval mode is not supported on this path")
             need_bn = u.bn.weight is not None and (u.bn.weight.requires_grad or u.bn.bias.requires_grad)
             dy, dres, dgamma, dbeta = ops.bn_backward(dz, u.z if u.relu else None, u.y, u.bn.weight, u.mean, u.invstd,
-                                                      u.relu, want_dres=want_dres, want_param_grads=need_bn)
+                                                      u.relu, want_dres=want_dres, want_param_grads=need_bn,
+                                                      mask=u.mask)
             if need_bn:
                 if u.bn.bias.requires_grad:
                     emit(u.bn.bias, dbeta)

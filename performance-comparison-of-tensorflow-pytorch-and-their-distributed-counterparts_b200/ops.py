@@ -202,16 +202,24 @@ def bn_eval_coeffs(gamma, beta, running_mean, running_var, eps):
     return st[0], st[1]
 
 
-def bn_apply(x, scale, shift, relu, residual=None, out=None):
+def bn_apply(x, scale, shift, relu, residual=None, out=None, want_mask=False):
+    """y = act(x*scale + shift (+residual)).  With want_mask the ReLU mask of the stored output is returned too
+    (one byte per 16-byte vector; None when C does not allow it) -- the backward kernels then never re-read y."""
     C = x.shape[-1]
     rows = x.numel() // C
     y = torch.empty_like(x) if out is None else out
-    check(lib.b200_bn_apply(x.data_ptr(), residual.data_ptr() if residual is not None else None, y.data_ptr(), rows, C,
-                            _dt(x), scale.data_ptr(), shift.data_ptr(), 1 if relu else 0, _stream()), "bn_apply")
-    return y
+    mask = None
+    if want_mask and relu:
+        nb = int(lib.b200_bn_mask_bytes(rows, C, _dt(x)))
+        if nb > 0:
+            mask = torch.empty(nb, dtype=torch.uint8, device=x.device)
+    check(lib.b200_bn_apply(x.data_ptr(), residual.data_ptr() if residual is not None else None, y.data_ptr(),
+                            mask.data_ptr() if mask is not None else None, rows, C, _dt(x), scale.data_ptr(),
+                            shift.data_ptr(), 1 if relu else 0, _stream()), "bn_apply")
+    return (y, mask) if want_mask else y
 
 
-def bn_backward(dz, z, x, gamma, mean, invstd, relu, want_dres=False, want_param_grads=True):
+def bn_backward(dz, z, x, gamma, mean, invstd, relu, want_dres=False, want_param_grads=True, mask=None):
     C = x.shape[-1]
     rows = x.numel() // C
     dx = torch.empty_like(x)
@@ -219,7 +227,8 @@ def bn_backward(dz, z, x, gamma, mean, invstd, relu, want_dres=False, want_param
     pg = torch.empty((2, C), dtype=torch.float32, device=x.device) if want_param_grads else None
     ws, n = _bn_ws(rows, C, x.device)
     check(lib.b200_bn_backward(
-        dz.data_ptr(), z.data_ptr() if z is not None else None, x.data_ptr(), dx.data_ptr(),
+        dz.data_ptr(), z.data_ptr() if (z is not None and mask is None) else None,
+        mask.data_ptr() if mask is not None else None, x.data_ptr(), dx.data_ptr(),
         dres.data_ptr() if dres is not None else None, rows, C, _dt(x),
         gamma.data_ptr() if gamma is not None else None, mean.data_ptr(), invstd.data_ptr(), 1 if relu else 0,
         pg[0].data_ptr() if pg is not None else None, pg[1].data_ptr() if pg is not None else None,

@@ -219,6 +219,19 @@ def test_batchnorm_train_fwd_bwd(prec, rows, C, relu, residual):
     assert _rel(dgamma, gd.grad) < 2e-4 and _rel(dbeta, bd.grad) < 2e-4
     if residual:
         assert _rel(dres, g) < tol
+    # the same backward driven by the one-byte-per-vector ReLU mask written by bn_apply instead of by z
+    z2, mask = ops.bn_apply(x, scale, shift, relu, res, want_mask=True)
+    assert torch.equal(z2, z)
+    if relu and mask is not None:
+        W = 8 if prec == "bf16" else 4
+        bits = (mask.view(-1, 1).int() >> torch.arange(W, device=_dev()).int().view(1, W)) & 1
+        assert torch.equal(bits.view(rows, C).bool(), z > 0)
+        dx2, dres2, dgamma2, dbeta2 = ops.bn_backward(dz, None, x, gamma, mean, invstd, relu, want_dres=residual, mask=mask)
+        assert torch.equal(dx2, dx) and torch.equal(dgamma2, dgamma) and torch.equal(dbeta2, dbeta)
+        if residual:
+            assert torch.equal(dres2, dres)
+    else:
+        assert mask is None
 
 
 def test_batchnorm_eval_coeffs():
