@@ -53,6 +53,12 @@ int32_t b200_conv_weight_ld(int32_t R, int32_t S, int32_t C);
 /* Cw = channels of the parameter, C >= Cw = channels of the packed operand (zero-filled beyond Cw). */
 int32_t b200_pack_weight(const float* w_oihw, void* w_krsc, int32_t K, int32_t Cw, int32_t R, int32_t S,
                          int32_t C, int32_t ld, int32_t out_dtype, void* stream);
+/* Explicit im2col staging: col[m][(r*S+s)*C + c] for output pixel m = (n*Ho + p)*Wo + q, row stride ld >= R*S*C
+ * (tail zero-filled).  Used for the 3-channel stem: the image is widened to 4 channels, staged once per step with
+ * ld = 256, and the stem then runs as a 1x1 convolution over 256 "channels" on the implicit tcgen05 path (forward
+ * and weight gradient share the staged matrix). */
+int32_t b200_im2col(const void* x, void* col, int32_t N, int32_t H, int32_t W, int32_t C, int32_t R, int32_t S,
+                    int32_t stride, int32_t pad, int32_t ld, int32_t dtype, void* stream);
 /* dtype cast of a flat buffer (fp32 <-> bf16) */
 int32_t b200_cast(const void* x, void* y, int64_t n, int32_t in_dtype, int32_t out_dtype, void* stream);
 

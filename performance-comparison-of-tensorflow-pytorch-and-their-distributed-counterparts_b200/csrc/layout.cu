@@ -94,6 +94,36 @@ __global__ void im2col_kernel(const T* __restrict__ x, T* __restrict__ col, int 
     }
   }
 }
+// 8-byte pixels (bf16, C = 4: the channel-padded image): one warp per output pixel, lane l writes the 8-byte slots
+// l, l+32, ... of the pixel's row (slot t < R*S is filter tap t, the remaining slots up to ld are zero).  Writes are
+// fully coalesced, reads hit L1/L2 (neighbouring pixels share most of their window), index math is per warp.
+__global__ void __launch_bounds__(256)
+im2col_px8_kernel(const uint2* __restrict__ x, uint2* __restrict__ col, int N, int H, int W, int R, int S, int stride,
+                  int pad, int Ho, int Wo, int slots) {
+  const int lane = threadIdx.x & 31;
+  const long long M = (long long)N * Ho * Wo;
+  const int taps = R * S;
+  for (long long m = blockIdx.x * (long long)(blockDim.x >> 5) + (threadIdx.x >> 5); m < M;
+       m += (long long)gridDim.x * (blockDim.x >> 5)) {
+    const int q = (int)(m % Wo);
+    const long long t2 = m / Wo;
+    const int p = (int)(t2 % Ho);
+    const int n = (int)(t2 / Ho);
+    const int h0 = p * stride - pad, w0 = q * stride - pad;
+    const uint2* xn = x + (long long)n * H * W;
+    uint2* dst = col + m * slots;
+    for (int t = lane; t < slots; t += 32) {
+      uint2 v = make_uint2(0u, 0u);
+      if (t < taps) {
+        const int r = t / S, s2 = t - r * S;
+        const int h = h0 + r, w = w0 + s2;
+        if (h >= 0 && h < H && w >= 0 && w < W) v = xn[(long long)h * W + w];
+      }
+      dst[t] = v;
+    }
+  }
+}
+
 template <typename T>
 __global__ void im2col_pad_kernel(T* __restrict__ col, long long M, int used, int ld) {
   const int padw = ld - used;
@@ -187,6 +217,13 @@ int32_t launch_im2col(const void* x, void* col, int dtype, int N, int H, int W, 
       im2col_kernel<float, 1><<<grid_for(M * R * S * C), 256, 0, st>>>((const float*)x, (float*)col, N, H, W, C, R, S, stride, pad, Ho, Wo, ld);
     if (ld > R * S * C) im2col_pad_kernel<float><<<grid_for(M * (ld - R * S * C)), 256, 0, st>>>((float*)col, M, R * S * C, ld);
   } else {
+    if (C == 4 && ld % 4 == 0 && ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(col)) & 7) == 0) {
+      const int warps_per_block = 8;
+      long long blocks = (M + warps_per_block - 1) / warps_per_block;
+      if (blocks > (long long)num_sms() * 32) blocks = (long long)num_sms() * 32;
+      im2col_px8_kernel<<<(int)blocks, 256, 0, st>>>((const uint2*)x, (uint2*)col, N, H, W, R, S, stride, pad, Ho, Wo, ld / 4);
+      return check_launch("im2col");
+    }
     if (C % 8 == 0 && ld % 8 == 0)
       im2col_kernel<__nv_bfloat16, 8><<<grid_for(M * R * S * (C / 8)), 256, 0, st>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)col, N, H, W, C, R, S, stride, pad, Ho, Wo, ld);
     else if (C % 4 == 0 && ld % 4 == 0)   // the channel-padded stem: 8-byte pixels
@@ -278,4 +315,15 @@ extern "C" int32_t b200_cast(const void* x, void* y, int64_t n, int32_t in_dtype
     cast_kernel<__nv_bfloat16, __nv_bfloat16><<<grid_for(n), 256, 0, st>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, n);
   else return fail(B200_INVALID_ARG, "cast: bad dtypes");
   return check_launch("cast");
+}
+
+/* explicit staging of a convolution's A operand: col[m][(r*S+s)*C + c], row stride ld >= R*S*C, zero-filled tail */
+extern "C" int32_t b200_im2col(const void* x, void* col, int32_t N, int32_t H, int32_t W, int32_t C, int32_t R,
+                               int32_t S, int32_t stride, int32_t pad, int32_t ld, int32_t dtype, void* stream) {
+  if (!x || !col || N <= 0 || H <= 0 || W <= 0 || C <= 0 || R <= 0 || S <= 0 || stride <= 0 || pad < 0 || ld < R * S * C)
+    return fail(B200_INVALID_ARG, "im2col: bad arguments");
+  if (dtype != B200_F32 && dtype != B200_BF16) return fail(B200_INVALID_ARG, "im2col: bad dtype");
+  const int Ho = (H + 2 * pad - R) / stride + 1, Wo = (W + 2 * pad - S) / stride + 1;
+  if (Ho <= 0 || Wo <= 0) return fail(B200_INVALID_ARG, "im2col: filter larger than input");
+  return launch_im2col(x, col, dtype, N, H, W, C, R, S, stride, pad, Ho, Wo, ld, as_stream(stream));
 }

@@ -54,13 +54,13 @@ def set_grad_sink(fn):
 _PACKED = {}
 
 
-def packed_weight(w, dtype, cpad=None):
+def packed_weight(w, dtype, cpad=None, ld=None):
     key = id(w)
     e = _PACKED.get(key)
-    if e is not None and e[0] == w.data_ptr() and e[1] == w._version and e[2] == dtype and e[4] == cpad:
+    if e is not None and e[0] == w.data_ptr() and e[1] == w._version and e[2] == dtype and e[4] == (cpad, ld):
         return e[3]
-    p = ops.pack_weight(w, dtype, cpad)
-    _PACKED[key] = (w.data_ptr(), w._version, dtype, p, cpad)
+    p = ops.pack_weight(w, dtype, cpad) if ld is None else ops.pack_weight_ld(w, dtype, cpad, ld)
+    _PACKED[key] = (w.data_ptr(), w._version, dtype, p, (cpad, ld))
     return p
 
 
@@ -114,12 +114,24 @@ def _bn_coeffs(bn, y, bump_nbt=True, partials=None):
 # ------------------------------------------------------------------ the backbone as one autograd node
 class _Unit(object):
     """Saved state of one conv -> BN (-> +residual) (-> ReLU) unit."""
-    __slots__ = ("conv", "bn", "x", "y", "z", "mask", "mean", "invstd", "relu", "geom")
+    __slots__ = ("conv", "bn", "x", "y", "z", "mask", "mean", "invstd", "relu", "geom", "staged")
 
 
-def _unit_forward(conv, bn, x, relu, residual, save):
+def _unit_forward(conv, bn, x, relu, residual, save, stage=False):
     K, R, S, stride, pad = _conv_geom(conv)
-    wp = packed_weight(conv.weight, x.dtype, x.shape[-1] if x.shape[-1] != conv.in_channels else None)
+    staged = None
+    if stage:
+        # Stem (3 -> 64, 7x7/2) in bf16 mode: the channel-padded image is staged ONCE as an im2col matrix with 256
+        # columns and the convolution becomes a 1x1 convolution over 256 "channels" on the implicit tcgen05 path
+        # (persistent kernel, TMA-store epilogue, fused BN statistics); the weight gradient reuses the staged matrix.
+        cp = x.shape[-1]
+        ld = (R * S * cp + 63) // 64 * 64
+        wp = packed_weight(conv.weight, x.dtype, cp, ld)
+        staged = (R, S, stride, pad, cp, x.shape)
+        x = ops.im2col(x, R, S, stride, pad, ld)
+        R, S, stride, pad = 1, 1, 1, 0
+    else:
+        wp = packed_weight(conv.weight, x.dtype, x.shape[-1] if x.shape[-1] != conv.in_channels else None)
     if _bn_uses_batch_stats(bn):
         y, partials = ops.conv_fprop_bnstats(x, wp, K, R, S, stride, pad)   # BN statistics fused into the epilogue
     else:
@@ -132,6 +144,7 @@ def _unit_forward(conv, bn, x, relu, residual, save):
     u = _Unit()
     u.conv, u.bn, u.x, u.y, u.z, u.mean, u.invstd, u.relu = conv, bn, x, y, z, mean, invstd, relu
     u.mask = mask
+    u.staged = staged
     u.geom = (K, R, S, stride, pad)
     return z, u
 
@@ -164,9 +177,11 @@ class _ResNetBackbone(torch.autograd.Function):
                and m.num_batches_tracked is not None and not _under(model.fc, m, model)]
         if nbt:
             torch._foreach_add_(nbt, 1)
-        xh = ops.to_nhwc(x, dtype, _stem_cpad(model.conv1, dtype))
+        cp = _stem_cpad(model.conv1, dtype)
+        xh = ops.to_nhwc(x, dtype, cp)
         units = []
-        z, u = _unit_forward(model.conv1, model.bn1, xh, True, None, save)
+        z, u = _unit_forward(model.conv1, model.bn1, xh, True, None, save,
+                             stage=cp is not None and not ctx.needs_input_grad[1])
         units.append(u)
         stem_shape = z.shape
         cur, pool_idx = ops.maxpool_fwd(z, save)
@@ -221,7 +236,11 @@ class _ResNetBackbone(torch.autograd.Function):
             K, R, S, stride, pad = u.geom
             if u.conv.weight.requires_grad:
                 dw = ops.conv_wgrad(u.x, dy, K, R, S, stride, pad)
-                if dw.shape[1] != u.conv.in_channels:      # channel-padded stem: drop the zero channel
+                if u.staged is not None:                   # staged stem: [K][R*S*cp (+pad)] -> OIHW
+                    r0, s0, _, _, cp0, _ = u.staged
+                    dw = dw.reshape(K, -1)[:, :r0 * s0 * cp0].reshape(K, r0, s0, cp0)
+                    dw = dw[..., :u.conv.in_channels].permute(0, 3, 1, 2).contiguous()
+                elif dw.shape[1] != u.conv.in_channels:    # channel-padded stem: drop the zero channel
                     dw = dw[:, :u.conv.in_channels].contiguous()
                 emit(u.conv.weight, dw)
             return dy, dres

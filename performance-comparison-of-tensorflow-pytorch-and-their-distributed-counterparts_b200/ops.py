@@ -84,6 +84,27 @@ def pack_weight(w, dtype, cpad=None):
     return out
 
 
+def im2col(x, R, S, stride, pad, ld):
+    """NHWC [N,H,W,C] -> staged matrix [N,Ho,Wo,ld] (column (r*S+s)*C+c, zero tail)."""
+    N, H, W, C = x.shape
+    Ho, Wo = (H + 2 * pad - R) // stride + 1, (W + 2 * pad - S) // stride + 1
+    col = torch.empty((N, Ho, Wo, ld), dtype=x.dtype, device=x.device)
+    check(lib.b200_im2col(x.data_ptr(), col.data_ptr(), N, H, W, C, R, S, stride, pad, ld, _dt(x), _stream()), "im2col")
+    return col
+
+
+def pack_weight_ld(w, dtype, cpad, ld):
+    """pack_weight with an explicit row stride (the stem's staged-1x1 form needs ld = 256)."""
+    K, Cw, R, S = w.shape
+    out = torch.empty((K, ld), dtype=dtype, device=w.device)
+    wd = w.detach()
+    if wd.dtype != torch.float32 or not wd.is_contiguous():
+        wd = wd.float().contiguous()
+    check(lib.b200_pack_weight(wd.data_ptr(), out.data_ptr(), K, Cw, R, S, cpad, ld, _DT[dtype], _stream()),
+          "pack_weight")
+    return out
+
+
 # ------------------------------------------------------------------ convolution
 _DESC = {}
 
