@@ -13,6 +13,6 @@ library raises.
 """
 from . import _C  # noqa: F401  (fails loudly when libb200net.so is missing)
 from . import ops, functional, nn, models, optim, utils, parallel  # noqa: F401
-from .functional import set_precision, get_precision  # noqa: F401
+from .functional import set_precision, get_precision, set_cuda_graphs  # noqa: F401
 
 __version__ = "0.1.0"

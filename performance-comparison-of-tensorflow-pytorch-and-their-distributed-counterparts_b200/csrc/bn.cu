@@ -264,6 +264,42 @@ bn_apply_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __restric
 #pragma unroll
     for (int e = 0; e < VEC; ++e) { sc[e] = scale[c + e]; sh[e] = shift[c + e]; }
   }
+  if constexpr (FIXEDC && VEC > 1) {
+    // streaming loop, two 16-byte vectors (plus residuals) in flight per thread
+    for (; i < nvec_total; i += 2 * stride) {
+      const long long i1 = i + stride;
+      const bool has1 = i1 < nvec_total;
+      float x0[VEC], x1[VEC], r0[VEC], r1[VEC];
+      load_vec(x + i * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(x0));
+      if (has1) load_vec(x + i1 * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(x1));
+      if (res) {
+        load_vec(res + i * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(r0));
+        if (has1) load_vec(res + i1 * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(r1));
+      }
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        if (half == 1 && !has1) break;
+        float (&xv)[VEC] = half ? x1 : x0;
+        float (&rv)[VEC] = half ? r1 : r0;
+        const long long ii = half ? i1 : i;
+        uint32_t m = 0;
+#pragma unroll
+        for (int e = 0; e < VEC; ++e) {
+          float v = fmaf(xv[e], sc[e], sh[e]);
+          if (res) v += rv[e];
+          if (relu) v = fmaxf(v, 0.f);
+          xv[e] = v;
+        }
+        store_vec(y + ii * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(xv));
+        if (mask) {
+#pragma unroll
+          for (int e = 0; e < VEC; ++e) m |= (to_f(from_f<T>(xv[e])) > 0.f ? 1u : 0u) << e;
+          mask[ii] = (uint8_t)m;
+        }
+      }
+    }
+    return;
+  }
   for (; i < nvec_total; i += stride) {
     if (!FIXEDC) {
       const int c = (int)(i % nvec) * VEC;
@@ -311,6 +347,46 @@ bn_bwd_dx_kernel(const T* __restrict__ dz, const T* __restrict__ z, const uint8_
     const int c = (int)(i % nvec) * VEC;
 #pragma unroll
     for (int e = 0; e < VEC; ++e) { cA[e] = coef[c + e]; cB[e] = coef[C + c + e]; cC[e] = coef[2 * C + c + e]; mu[e] = mean[c + e]; }
+  }
+  if constexpr (FIXEDC && VEC > 1) {
+    // streaming loop, two vectors of each input in flight per thread
+    for (; i < nvec_total; i += 2 * stride) {
+      const long long i1 = i + stride;
+      const bool has1 = i1 < nvec_total;
+      float g0[VEC], g1[VEC], x0[VEC], x1[VEC], z0[VEC], z1[VEC];
+      uint32_t m0 = 0xffffffffu, m1 = 0xffffffffu;
+      load_vec(dz + i * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(g0));
+      load_vec(x + i * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(x0));
+      if (DMODE == DM_Z) load_vec(z + i * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(z0));
+      if (DMODE == DM_MASK) m0 = mask[i];
+      if (has1) {
+        load_vec(dz + i1 * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(g1));
+        load_vec(x + i1 * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(x1));
+        if (DMODE == DM_Z) load_vec(z + i1 * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(z1));
+        if (DMODE == DM_MASK) m1 = mask[i1];
+      }
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        if (half == 1 && !has1) break;
+        float (&gv)[VEC] = half ? g1 : g0;
+        float (&xv)[VEC] = half ? x1 : x0;
+        float (&zv)[VEC] = half ? z1 : z0;
+        const uint32_t m = half ? m1 : m0;
+        const long long ii = half ? i1 : i;
+#pragma unroll
+        for (int e = 0; e < VEC; ++e) {
+          bool on = true;
+          if (DMODE == DM_Z) on = zv[e] > 0.f;
+          if (DMODE == DM_MASK) on = (m >> e) & 1u;
+          const float g = on ? gv[e] : 0.f;
+          gv[e] = g;
+          xv[e] = cA[e] * g - cC[e] - cB[e] * (xv[e] - mu[e]);
+        }
+        store_vec(dx + ii * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(xv));
+        if (dres) store_vec(dres + ii * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(gv));
+      }
+    }
+    return;
   }
   for (; i < nvec_total; i += stride) {
     if (!FIXEDC) {

@@ -52,10 +52,19 @@ def set_grad_sink(fn):
 # key: id(param) -> (data_ptr, version, dtype, packed).  Our optimizers bump the parameter version after the raw
 # in-place update (torch.autograd.graph.increment_version), stock optimizers do it through ATen.
 _PACKED = {}
+_CAPTURE_PACKED = {}   # packed buffers of the graph being captured (one pack per weight per graph)
 
 
 def packed_weight(w, dtype, cpad=None, ld=None):
     key = id(w)
+    if _CAPTURING[0]:
+        # inside a graph capture the repack has to be recorded (the weights change between replays) and must not
+        # leak into the eager cache (the buffer belongs to the graph's memory pool)
+        cached = _CAPTURE_PACKED.get((key, dtype, cpad, ld))
+        if cached is None:
+            cached = ops.pack_weight(w, dtype, cpad) if ld is None else ops.pack_weight_ld(w, dtype, cpad, ld)
+            _CAPTURE_PACKED[(key, dtype, cpad, ld)] = cached
+        return cached
     e = _PACKED.get(key)
     if e is not None and e[0] == w.data_ptr() and e[1] == w._version and e[2] == dtype and e[4] == (cpad, ld):
         return e[3]
@@ -165,123 +174,266 @@ def _under(fc, m, model):
     return any(m is x for x in fc.modules()) if isinstance(fc, torch.nn.Module) else False
 
 
+class _BackboneState(object):
+    """What the backbone's backward needs from its forward."""
+    __slots__ = ("unit0", "blocks", "pool_idx", "stem_shape", "final_shape", "dtype")
+
+
+def _backbone_fwd(model, x, save, x_needs_grad):
+    """Stem -> layer1..4 -> avgpool on NHWC activations.  Returns (features [N,2048] fp32, state or None)."""
+    dtype = act_dtype()
+    # num_batches_tracked += 1 for every BatchNorm in train mode: one multi-tensor launch instead of 53
+    nbt = [m.num_batches_tracked for m in model.modules()
+           if isinstance(m, torch.nn.BatchNorm2d) and m.training and m.track_running_stats
+           and m.num_batches_tracked is not None and not _under(model.fc, m, model)]
+    if nbt:
+        torch._foreach_add_(nbt, 1)
+    cp = _stem_cpad(model.conv1, dtype)
+    xh = ops.to_nhwc(x, dtype, cp)
+    z, u0 = _unit_forward(model.conv1, model.bn1, xh, True, None, save, stage=cp is not None and not x_needs_grad)
+    stem_shape = z.shape
+    cur, pool_idx = ops.maxpool_fwd(z, save)
+    blocks = []
+    for layer in (model.layer1, model.layer2, model.layer3, model.layer4):
+        for blk in layer:
+            z1, u1 = _unit_forward(blk.conv1, blk.bn1, cur, True, None, save)
+            z2, u2 = _unit_forward(blk.conv2, blk.bn2, z1, True, None, save)
+            ud = None
+            if blk.downsample is not None:
+                res, ud = _unit_forward(blk.downsample[0], blk.downsample[1], cur, False, None, save)
+            else:
+                res = cur
+            cur, u3 = _unit_forward(blk.conv3, blk.bn3, z2, True, res, save)
+            blocks.append((u1, u2, u3, ud))
+    feat = ops.avgpool_fwd(cur)
+    if not save:
+        return feat, None
+    st = _BackboneState()
+    st.unit0, st.blocks, st.pool_idx, st.stem_shape, st.final_shape, st.dtype = u0, blocks, pool_idx, stem_shape, \
+        cur.shape, dtype
+    return feat, st
+
+
+def _backbone_bwd(st, dfeat, params, param_needs, x_needs_grad, sink):
+    """Reverse walk: BN backward (mask from the saved byte mask) -> wgrad -> dgrad; the block-input gradient is the
+    residual gradient with conv1's dgrad accumulated in the GEMM epilogue.  Returns (dx or None, [grad per param])."""
+    dfeat = dfeat.contiguous().float()
+    grads = {}  # id(param) -> grad
+
+    def emit(p, g):
+        grads[id(p)] = sink(p, g) if sink is not None else g
+
+    def unit_backward(u, dz, want_dres):
+        if u.mean is None:
+            raise RuntimeError("b200net: backward through BatchNorm in eval mode is not supported on this path")
+        need_bn = u.bn.weight is not None and (u.bn.weight.requires_grad or u.bn.bias.requires_grad)
+        dy, dres, dgamma, dbeta = ops.bn_backward(dz, u.z if u.relu else None, u.y, u.bn.weight, u.mean, u.invstd,
+                                                  u.relu, want_dres=want_dres, want_param_grads=need_bn, mask=u.mask)
+        if need_bn:
+            if u.bn.bias.requires_grad:
+                emit(u.bn.bias, dbeta)
+            if u.bn.weight.requires_grad:
+                emit(u.bn.weight, dgamma)
+        K, R, S, stride, pad = u.geom
+        if u.conv.weight.requires_grad:
+            dw = ops.conv_wgrad(u.x, dy, K, R, S, stride, pad)
+            if u.staged is not None:                   # staged stem: [K][R*S*cp (+pad)] -> OIHW
+                r0, s0, _, _, cp0, _ = u.staged
+                dw = dw.reshape(K, -1)[:, :r0 * s0 * cp0].reshape(K, r0, s0, cp0)
+                dw = dw[..., :u.conv.in_channels].permute(0, 3, 1, 2).contiguous()
+            elif dw.shape[1] != u.conv.in_channels:    # channel-padded stem: drop the zero channel
+                dw = dw[:, :u.conv.in_channels].contiguous()
+            emit(u.conv.weight, dw)
+        return dy, dres
+
+    def dgrad(u, dy, out=None, accumulate=False):
+        K, R, S, stride, pad = u.geom
+        cin = u.x.shape[-1]
+        wp = packed_weight(u.conv.weight, dy.dtype, cin if cin != u.conv.in_channels else None)
+        return ops.conv_dgrad(dy, wp, u.x.shape, K, R, S, stride, pad, out=out, accumulate=accumulate)
+
+    dcur = ops.avgpool_bwd(dfeat, st.final_shape, st.dtype)
+    for (u1, u2, u3, ud) in reversed(st.blocks):
+        dy3, g = unit_backward(u3, dcur, want_dres=True)
+        dz2 = dgrad(u3, dy3)
+        dy2, _ = unit_backward(u2, dz2, want_dres=False)
+        dz1 = dgrad(u2, dy2)
+        dy1, _ = unit_backward(u1, dz1, want_dres=False)
+        if ud is not None:
+            # dense branch first (plain store), then the strided downsample branch accumulates: for a 1x1
+            # stride-2 convolution only one of the four output-parity classes receives anything
+            dyd, _ = unit_backward(ud, g, want_dres=False)
+            dcur = dgrad(u1, dy1)
+            dgrad(ud, dyd, out=dcur, accumulate=True)
+        else:
+            dcur = dgrad(u1, dy1, out=g, accumulate=True)
+    dz0 = ops.maxpool_bwd(dcur, st.pool_idx, st.stem_shape)
+    u0 = st.unit0
+    dy0, _ = unit_backward(u0, dz0, want_dres=False)
+    dx = None
+    if x_needs_grad:
+        dx = ops.to_nchw(dgrad(u0, dy0))[:, :u0.conv.in_channels].contiguous()
+    return dx, [grads.get(id(p)) if need else None for p, need in zip(params, param_needs)]
+
+
 class _ResNetBackbone(torch.autograd.Function):
+    """Eager path: every kernel is enqueued from Python on each call."""
+
     @staticmethod
     def forward(ctx, model, x, *params):
         # forward() runs with grad mode off; needs_input_grad already folds in the caller's grad mode
         save = any(ctx.needs_input_grad)
-        dtype = act_dtype()
-        # num_batches_tracked += 1 for every BatchNorm in train mode: one multi-tensor launch instead of 53
-        nbt = [m.num_batches_tracked for m in model.modules()
-               if isinstance(m, torch.nn.BatchNorm2d) and m.training and m.track_running_stats
-               and m.num_batches_tracked is not None and not _under(model.fc, m, model)]
-        if nbt:
-            torch._foreach_add_(nbt, 1)
-        cp = _stem_cpad(model.conv1, dtype)
-        xh = ops.to_nhwc(x, dtype, cp)
-        units = []
-        z, u = _unit_forward(model.conv1, model.bn1, xh, True, None, save,
-                             stage=cp is not None and not ctx.needs_input_grad[1])
-        units.append(u)
-        stem_shape = z.shape
-        cur, pool_idx = ops.maxpool_fwd(z, save)
-        blocks = []
-        for layer in (model.layer1, model.layer2, model.layer3, model.layer4):
-            for blk in layer:
-                z1, u1 = _unit_forward(blk.conv1, blk.bn1, cur, True, None, save)
-                z2, u2 = _unit_forward(blk.conv2, blk.bn2, z1, True, None, save)
-                ud = None
-                if blk.downsample is not None:
-                    res, ud = _unit_forward(blk.downsample[0], blk.downsample[1], cur, False, None, save)
-                else:
-                    res = cur
-                cur, u3 = _unit_forward(blk.conv3, blk.bn3, z2, True, res, save)
-                blocks.append((u1, u2, u3, ud))
-        feat = ops.avgpool_fwd(cur)
+        feat, st = _backbone_fwd(model, x, save, ctx.needs_input_grad[1])
         if save:
-            ctx.units0 = units[0]
-            ctx.blocks = blocks
-            ctx.pool_idx = pool_idx
-            ctx.stem_shape = stem_shape
-            ctx.final_shape = cur.shape
-            ctx.dtype = dtype
-            ctx.x_needs_grad = ctx.needs_input_grad[1]
+            ctx.state = st
             ctx.params = params
             ctx.param_needs = list(ctx.needs_input_grad[2:])
+            ctx.x_needs_grad = ctx.needs_input_grad[1]
         return feat
 
     @staticmethod
     @once_differentiable
     def backward(ctx, dfeat):
-        dfeat = dfeat.contiguous().float()
-        grads = {}  # id(param) -> grad
-        sink = _GRAD_SINK
-
-        def emit(p, g):
-            grads[id(p)] = sink(p, g) if sink is not None else g
-
-        def unit_backward(u, dz, want_dres, need_dx=True):
-            """dz: grad w.r.t. the unit output. Returns (dx_of_conv_input or None, dres)."""
-            if u.mean is None:
-                raise RuntimeError("b200net: backward through BatchNorm in eval mode is not supported on this path")
-            need_bn = u.bn.weight is not None and (u.bn.weight.requires_grad or u.bn.bias.requires_grad)
-            dy, dres, dgamma, dbeta = ops.bn_backward(dz, u.z if u.relu else None, u.y, u.bn.weight, u.mean, u.invstd,
-                                                      u.relu, want_dres=want_dres, want_param_grads=need_bn,
-                                                      mask=u.mask)
-            if need_bn:
-                if u.bn.bias.requires_grad:
-                    emit(u.bn.bias, dbeta)
-                if u.bn.weight.requires_grad:
-                    emit(u.bn.weight, dgamma)
-            K, R, S, stride, pad = u.geom
-            if u.conv.weight.requires_grad:
-                dw = ops.conv_wgrad(u.x, dy, K, R, S, stride, pad)
-                if u.staged is not None:                   # staged stem: [K][R*S*cp (+pad)] -> OIHW
-                    r0, s0, _, _, cp0, _ = u.staged
-                    dw = dw.reshape(K, -1)[:, :r0 * s0 * cp0].reshape(K, r0, s0, cp0)
-                    dw = dw[..., :u.conv.in_channels].permute(0, 3, 1, 2).contiguous()
-                elif dw.shape[1] != u.conv.in_channels:    # channel-padded stem: drop the zero channel
-                    dw = dw[:, :u.conv.in_channels].contiguous()
-                emit(u.conv.weight, dw)
-            return dy, dres
-
-        def dgrad(u, dy, out=None, accumulate=False):
-            K, R, S, stride, pad = u.geom
-            cin = u.x.shape[-1]
-            wp = packed_weight(u.conv.weight, dy.dtype, cin if cin != u.conv.in_channels else None)
-            return ops.conv_dgrad(dy, wp, u.x.shape, K, R, S, stride, pad, out=out, accumulate=accumulate)
-
-        dcur = ops.avgpool_bwd(dfeat, ctx.final_shape, ctx.dtype)
-        for (u1, u2, u3, ud) in reversed(ctx.blocks):
-            dy3, g = unit_backward(u3, dcur, want_dres=True)
-            dz2 = dgrad(u3, dy3)
-            dy2, _ = unit_backward(u2, dz2, want_dres=False)
-            dz1 = dgrad(u2, dy2)
-            dy1, _ = unit_backward(u1, dz1, want_dres=False)
-            if ud is not None:
-                # dense branch first (plain store), then the strided downsample branch accumulates: for a 1x1
-                # stride-2 convolution only one of the four output-parity classes receives anything
-                dyd, _ = unit_backward(ud, g, want_dres=False)
-                dcur = dgrad(u1, dy1)
-                dgrad(ud, dyd, out=dcur, accumulate=True)
-            else:
-                dcur = dgrad(u1, dy1, out=g, accumulate=True)
-        dz0 = ops.maxpool_bwd(dcur, ctx.pool_idx, ctx.stem_shape)
-        u0 = ctx.units0
-        dy0, _ = unit_backward(u0, dz0, want_dres=False)
-        dx = None
-        if ctx.x_needs_grad:
-            dx = ops.to_nchw(dgrad(u0, dy0))[:, :u0.conv.in_channels].contiguous()
-        out = (None, dx) + tuple(grads.get(id(p)) if need else None for p, need in zip(ctx.params, ctx.param_needs))
-        ctx.blocks = None
-        ctx.units0 = None
+        dx, grads = _backbone_bwd(ctx.state, dfeat, ctx.params, ctx.param_needs, ctx.x_needs_grad, _GRAD_SINK)
+        ctx.state = None
         ctx.params = None
-        return out
+        return (None, dx) + tuple(grads)
+
+
+# ------------------------------------------------------------------ CUDA-graph replay of the backbone
+# The backbone is ~170 (forward) + ~400 (backward) kernel launches; enqueuing them from Python costs about as much
+# CPU time as the GPU needs to run them, and at batch 1 far more.  After GRAPH_WARMUP eager calls with the same
+# (model, input shape, mode, precision, set of trainable parameters) the forward and the backward are each captured
+# into a CUDA graph once and replayed from then on: the reference's loop
+# (pytorch_training_inference_on_image.ipynb:664-673, :855-861) is unchanged, only what happens inside
+# model.forward / loss.backward differs.  B200_CUDA_GRAPHS=0 disables it; DDP (per-parameter gradient hand-off to the
+# communication stream) keeps the eager path.
+GRAPH_WARMUP = 3
+GRAPH_CACHE = 6
+_GRAPHS_ON = os.environ.get("B200_CUDA_GRAPHS", "1") != "0"
+_GRAPHS = {}     # key -> _GraphRecord | "failed"
+_GRAPH_SEEN = {}  # key -> number of eager calls so far
+_CAPTURING = [False]
+
+
+def set_cuda_graphs(on):
+    global _GRAPHS_ON
+    _GRAPHS_ON = bool(on)
+    if not on:
+        _GRAPHS.clear()
+        _GRAPH_SEEN.clear()
+
+
+class _GraphRecord(object):
+    __slots__ = ("fwd", "bwd", "x", "feat", "dfeat", "grads", "dx", "state", "ptrs", "ws", "uses")
+
+
+def _graph_key(model, x, params, needs_x):
+    bn_flags = tuple(m.training for m in model.modules() if isinstance(m, torch.nn.BatchNorm2d))
+    needs = tuple(p.requires_grad for p in params) if torch.is_grad_enabled() else ()
+    return (id(model), tuple(x.shape), x.device.index, _PRECISION, bn_flags, needs, bool(needs_x))
+
+
+def _tensor_ptrs(model):
+    return tuple(t.data_ptr() for t in list(model.parameters()) + list(model.buffers()))
+
+
+def _capture(model, x, params, key):
+    needs = key[5]
+    needs_x = key[6]
+    save = any(needs) or needs_x
+    rec = _GraphRecord()
+    rec.x = x.detach().clone()
+    rec.ptrs = _tensor_ptrs(model)
+    rec.uses = 0
+    pool = torch.cuda.graph_pool_handle()
+    _CAPTURE_PACKED.clear()
+    _CAPTURING[0] = True
+    ops.NO_WORKSPACE_GROWTH[0] = True   # the warm-up calls sized the workspace; growing it now would move it into
+    try:                                # the graph's private pool
+        torch.cuda.synchronize()
+        rec.fwd = torch.cuda.CUDAGraph()
+        with torch.no_grad():
+            with torch.cuda.graph(rec.fwd, pool=pool):
+                rec.feat, rec.state = _backbone_fwd(model, rec.x, save, needs_x)
+        rec.bwd = None
+        if save:
+            rec.dfeat = torch.zeros_like(rec.feat)
+            rec.bwd = torch.cuda.CUDAGraph()
+            with torch.no_grad():
+                with torch.cuda.graph(rec.bwd, pool=pool):
+                    rec.dx, rec.grads = _backbone_bwd(rec.state, rec.dfeat, params, list(needs), needs_x, None)
+        rec.ws = dict(ops._WS)   # the graphs hold raw pointers into the workspace: keep it alive
+    finally:
+        _CAPTURING[0] = False
+        ops.NO_WORKSPACE_GROWTH[0] = False
+        _CAPTURE_PACKED.clear()
+    return rec
+
+
+class _GraphedBackbone(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, rec, x, *params):
+        rec.x.copy_(x)
+        rec.fwd.replay()
+        ctx.rec = rec
+        ctx.saved_params = params
+        return rec.feat.clone()
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dfeat):
+        rec = ctx.rec
+        if rec.bwd is None:
+            raise RuntimeError("b200net: this backbone graph was captured without a backward pass")
+        rec.dfeat.copy_(dfeat)
+        rec.bwd.replay()
+        # The gradients live in graph-owned memory that the next replay overwrites.  With the usual
+        # zero_grad() -> backward() -> step() cycle they are consumed before that, so they are handed out as they
+        # are; a parameter that still holds a .grad (gradient accumulation) gets a private copy instead, because
+        # autograd would otherwise add the buffer to itself.
+        params = ctx.saved_params
+        out = [None if g is None else (g if p.grad is None else g.clone()) for p, g in zip(params, rec.grads)]
+        return (None, rec.dx.clone() if rec.dx is not None else None) + tuple(out)
 
 
 def resnet_backbone(model, x):
     """[N,3,H,W] fp32 NCHW -> [N,2048] fp32 features (everything up to and including avgpool + flatten)."""
-    return _ResNetBackbone.apply(model, x, *_backbone_params(model))
+    params = _backbone_params(model)
+    if not (_GRAPHS_ON and _GRAD_SINK is None and x.is_cuda and not torch.cuda.is_current_stream_capturing()):
+        return _ResNetBackbone.apply(model, x, *params)
+    needs_x = x.requires_grad and torch.is_grad_enabled()
+    key = _graph_key(model, x, params, needs_x)
+    rec = _GRAPHS.get(key)
+    if rec is not None and rec != "failed":
+        if rec.ptrs == _tensor_ptrs(model):
+            rec.uses += 1
+            return _GraphedBackbone.apply(rec, x, *params)
+        del _GRAPHS[key]          # parameters were re-allocated (model.to(), new tensors): recapture
+        _GRAPH_SEEN[key] = 0
+        rec = None
+    if rec is None:
+        seen = _GRAPH_SEEN.get(key, 0)
+        if seen >= GRAPH_WARMUP:
+            try:
+                if len(_GRAPHS) >= GRAPH_CACHE:      # bounded cache: drop the least used graph
+                    victim = min((k for k in _GRAPHS if _GRAPHS[k] != "failed"), key=lambda k: _GRAPHS[k].uses,
+                                 default=None)
+                    if victim is not None:
+                        del _GRAPHS[victim]
+                rec = _capture(model, x, params, key)
+                _GRAPHS[key] = rec
+                rec.uses = 1
+                return _GraphedBackbone.apply(rec, x, *params)
+            except Exception as e:                    # capture is an optimisation: never fatal
+                import warnings
+                warnings.warn("b200net: CUDA-graph capture of the backbone failed (%s); staying on the eager path" % e)
+                _GRAPHS[key] = "failed"
+        else:
+            if len(_GRAPH_SEEN) > 256:               # variable-size inference: do not grow without bound
+                _GRAPH_SEEN.clear()
+            _GRAPH_SEEN[key] = seen + 1
+    return _ResNetBackbone.apply(model, x, *params)
 
 
 # ------------------------------------------------------------------ classifier head (fp32, [rows][features])

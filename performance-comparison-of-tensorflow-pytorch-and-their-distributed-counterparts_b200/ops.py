@@ -30,12 +30,15 @@ def _stream():
 
 # ------------------------------------------------------------------ workspace (one growing buffer per device)
 _WS = {}
+NO_WORKSPACE_GROWTH = [False]   # set while a CUDA graph is being captured
 
 
 def workspace(nbytes, device):
     key = device.index if device.index is not None else torch.cuda.current_device()
     buf = _WS.get(key)
     if buf is None or buf.numel() < nbytes:
+        if NO_WORKSPACE_GROWTH[0]:
+            raise RuntimeError("b200net: workspace would have to grow during CUDA-graph capture")
         # stream-ordered reuse: every consumer runs on the current stream
         buf = torch.empty(max(int(nbytes), 1 << 20), dtype=torch.uint8, device=device)
         _WS[key] = buf

@@ -221,6 +221,50 @@ def test_reference_loops_run_verbatim_bf16():
         assert torch.equal(m2(one), model.eval()(one))
 
 
+def test_cuda_graph_replay_equals_eager():
+    """After a few eager calls the backbone forward/backward are replayed as CUDA graphs.  Same kernels in the same
+    order: losses and weights must be bit-identical to a run with the graphs switched off -- in training (Mode A and
+    frozen-backbone Mode F), with gradient accumulation, and for repeated batch-1 inference."""
+    import b200net
+    from b200net import functional as F
+
+    def run(graphs, mode):
+        b200net.set_cuda_graphs(graphs)
+        ref = O.build_reference_model(dropout=False)
+        m = _ours_from(ref)
+        opt, crit = _make_opt(m, mode)
+        x, y = O.make_batch(8, 64, 3, DEV)
+        m.train()
+        losses = []
+        for step in range(8):
+            if step != 5:                      # step 5 accumulates on top of step 4's gradients
+                opt.zero_grad()
+            loss = crit(m(x), y)
+            loss.backward()
+            opt.step()
+            losses.append(loss.item())
+        used = sum(1 for k, r in F._GRAPHS.items() if r != "failed")
+        m.eval()
+        with torch.no_grad():
+            one = torch.rand(1, 3, 96, 96, device=DEV)
+            outs = [m(one).clone() for _ in range(6)]
+        return losses, m.state_dict(), outs, used
+
+    try:
+        for mode in ("A", "F"):
+            le, sde, oe, _ = run(False, mode)
+            lg, sdg, og, used = run(True, mode)
+            assert used >= 1, "graphs were never captured"
+            assert le == lg, (mode, le, lg)
+            for k in sde:
+                assert torch.equal(sde[k], sdg[k]), (mode, k)
+            for a, b in zip(oe, og):
+                assert torch.equal(a, b)
+            assert all(torch.equal(og[0], o) for o in og)
+    finally:
+        b200net.set_cuda_graphs(True)
+
+
 def test_standalone_modules_match_torch_fp32():
     """Layer-by-layer use (NCHW in/out) of the drop-in modules: Bottleneck forward/backward vs torchvision."""
     import b200net
