@@ -249,6 +249,30 @@ def main():
                 "launches_per_step": n.value // prof_steps, "kernel_ms_per_step": ms.value / prof_steps,
                 "executed_gemm_tflop_per_step": fl.value / prof_steps / 1e12}
 
+    # inference leg (BASELINE.json configs[3] and the reference's per-image loop, ...on_image.ipynb:855-861):
+    # eval mode, no_grad; every rank runs an independent replica on its own shard (no collective)
+    infer = None
+    if args.precision == "bf16":
+        net = model.module if distributed else model
+        net.eval()
+        with torch.no_grad():
+            xi = torch.rand(1024, 3, HW, HW, device=dev)
+            for _ in range(6):
+                net(xi)
+            t_inf = timed(lambda: net(xi).argmax(1), 10)
+            x1 = torch.rand(1, 3, 224, 224, device=dev)
+            for _ in range(8):
+                net(x1)
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for _ in range(100):
+                int(net(x1).data.cpu().numpy().argmax())       # predict_image(): one D2H sync per image
+            lat = (time.perf_counter() - t0) / 100 * 1e3
+        net.train()
+        infer = {"batch": 1024, "img_s": world * 1024 * 10 / (t_inf * 1e-3), "ms_per_batch": t_inf / 10,
+                 "batch1_224px_latency_ms": lat, "tensor_util": 4.1727e9 * 1024 * 10 / (t_inf * 1e-3) / 1e12 / peaks()["tflops"]}
+        del xi
+
     if rank == 0:
         ips = world * B * args.steps / (total_ms * 1e-3)
         e2e_ips = world * B * args.steps / (e2e_ms * 1e-3)
@@ -271,6 +295,8 @@ def main():
         }
         if roof:
             out["roofline"] = roof
+        if infer:
+            out["infer"] = infer
         if world == 1 and not args.no_cpu_baseline:
             cips, cms, cores = cpu_reference_run(steps=5, warmup=2)
             out["cpu_baseline"] = {"value": cips, "unit": UNIT, "cores": cores, "kind": "port",

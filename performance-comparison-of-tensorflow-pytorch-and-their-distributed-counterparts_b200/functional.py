@@ -331,7 +331,10 @@ class _GraphRecord(object):
 def _graph_key(model, x, params, needs_x):
     bn_flags = tuple(m.training for m in model.modules() if isinstance(m, torch.nn.BatchNorm2d))
     needs = tuple(p.requires_grad for p in params) if torch.is_grad_enabled() else ()
-    return (id(model), tuple(x.shape), x.device.index, _PRECISION, bn_flags, needs, bool(needs_x))
+    # forward-only graphs (inference, frozen backbone) use weights packed OUTSIDE the graph, so they are only valid
+    # for the weight versions they were captured with
+    wver = -1 if (any(needs) or needs_x) else sum(p._version for p in params)
+    return (id(model), tuple(x.shape), x.device.index, _PRECISION, bn_flags, needs, bool(needs_x), wver)
 
 
 def _tensor_ptrs(model):
@@ -348,7 +351,9 @@ def _capture(model, x, params, key):
     rec.uses = 0
     pool = torch.cuda.graph_pool_handle()
     _CAPTURE_PACKED.clear()
-    _CAPTURING[0] = True
+    # training graphs re-pack the weights on every replay (they change every step); forward-only graphs read the
+    # packed copies the warm-up calls left in the eager cache (their validity is part of the key)
+    _CAPTURING[0] = save
     ops.NO_WORKSPACE_GROWTH[0] = True   # the warm-up calls sized the workspace; growing it now would move it into
     try:                                # the graph's private pool
         torch.cuda.synchronize()
@@ -363,7 +368,7 @@ def _capture(model, x, params, key):
             with torch.no_grad():
                 with torch.cuda.graph(rec.bwd, pool=pool):
                     rec.dx, rec.grads = _backbone_bwd(rec.state, rec.dfeat, params, list(needs), needs_x, None)
-        rec.ws = dict(ops._WS)   # the graphs hold raw pointers into the workspace: keep it alive
+        rec.ws = (dict(ops._WS), [e[3] for e in _PACKED.values()])   # raw pointers captured: keep the memory alive
     finally:
         _CAPTURING[0] = False
         ops.NO_WORKSPACE_GROWTH[0] = False
