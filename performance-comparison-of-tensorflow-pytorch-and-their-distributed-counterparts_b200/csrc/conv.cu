@@ -125,7 +125,8 @@ static inline WgradPlan wgrad_plan(const b200_conv_desc* d, const ConvGeom& g) {
   else { w.Wq = g.Wo; w.Hq = g.Ho; w.Nq = d->N; }
   // columns of the packed [K][R*S*C] gradient per tile: 256 (four 64-channel tap groups share one dY tile) when
   // C == 64, else 128 with twice as many pixels per k-block
-  w.bn_tile = d->C == 64 ? 256 : 128;
+  static const int force256 = getenv("B200_WGRAD_BN256") ? atoi(getenv("B200_WGRAD_BN256")) : 0;
+  w.bn_tile = (d->C == 64 || (force256 && d->C % 256 == 0)) ? 256 : 128;
   w.box = choose_pixel_box(w.Wq, w.Hq, w.Nq, w.bn_tile == 256 ? 64 : 128, 16, d->stride);
   w.pb_total = w.box.tiles_w * w.box.tiles_h * w.box.tiles_n;
   const long long ctas = (long long)((g.RSC + w.bn_tile - 1) / w.bn_tile) * ((d->K + 127) / 128);

@@ -223,13 +223,22 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
               if (nb > BN / 64) nb = BN / 64;
               mbar_expect_tx(&full[s], box_bytes * (na + nb));
               for (int h = 0; h < na; ++h) tma_load_4d(a + h * box_bytes, &tmA, &full[s], T.m0 + h * 64, bq, bp, bi);
+              if (P.cdim == 64) {
 #pragma unroll
-              for (int h = 0; h < BN / 64; ++h) {
-                if (h < nb) {
-                  const int tp = (T.n0 >> 6) + h;   // C == 64: column group = tap
-                  tma_load_4d(b + h * box_bytes, &tmB, &full[s], 0, bq * P.x_mul + P.taps[tp].dw,
-                              bp * P.x_mul + P.taps[tp].dh, bi);
+                for (int h = 0; h < BN / 64; ++h) {
+                  if (h < nb) {
+                    const int tp = (T.n0 >> 6) + h;   // C == 64: column group = tap
+                    tma_load_4d(b + h * box_bytes, &tmB, &full[s], 0, bq * P.x_mul + P.taps[tp].dw,
+                                bp * P.x_mul + P.taps[tp].dh, bi);
+                  }
                 }
+              } else {
+                // C is a multiple of 256: the whole 256-column tile lies inside one tap
+                const int cin0 = T.n0 - T.tap * P.cdim;
+                const int xw = bq * P.x_mul + P.taps[T.tap].dw, xh = bp * P.x_mul + P.taps[T.tap].dh;
+#pragma unroll
+                for (int h = 0; h < BN / 64; ++h)
+                  if (h < nb) tma_load_4d(b + h * box_bytes, &tmB, &full[s], cin0 + h * 64, xw, xh, bi);
               }
             }
           }
