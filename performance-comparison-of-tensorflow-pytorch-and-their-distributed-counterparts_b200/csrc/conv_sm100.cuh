@@ -55,6 +55,9 @@ struct ConvParams {
   int n_tiles, m_tiles, total_tiles;
   int n_inner;                       // wgrad: column tiles per tap (n_tiles = n_inner * tap groups)
   int tma_store;                     // fprop/dgrad: bf16 output written by TMA from a swizzled smem staging tile
+  const float* ep_scale;             // fprop + tma_store (eval-mode BatchNorm folded into the epilogue):
+  const float* ep_shift;             //   out = act(acc * ep_scale[col] + ep_shift[col]), act = ReLU when ep_relu
+  int ep_relu;
   float* stats;                      // fprop + tma_store: per-pixel-tile column sums [pixel tile][2][ncols] of the
                                      // bf16-rounded output (sum, sum of squares) for the BatchNorm that follows
 };
@@ -334,6 +337,11 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           if (T.n0 + g * 64 >= P.ncols) break;     // uniform across the CTA
           uint8_t* stg = smStage + (stage_ctr & 1u) * (CONV_STAGING_BYTES / 2);
           if (elected) tma_store_wait_read<1>();   // the store that last used this tile has finished reading it
+          const bool affine = MODE == MODE_FPROP && P.ep_scale != nullptr;
+          if (affine) {   // this group's 64 per-channel scales and shifts -> smem (read back as broadcasts)
+            const int col = T.n0 + g * 64 + (l & 63);
+            smRed[l] = l < 64 ? P.ep_scale[col] : P.ep_shift[col];
+          }
           asm volatile("bar.sync 1, 128;" ::: "memory");
 #pragma unroll
           for (int h = 0; h < 2; ++h) {
@@ -345,6 +353,14 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             } else {
 #pragma unroll
               for (int j = 0; j < 32; ++j) r[j] = 0u;
+            }
+            if (affine) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) {
+                float v = fmaf(__uint_as_float(r[j]), smRed[h * 32 + j], smRed[64 + h * 32 + j]);
+                if (P.ep_relu) v = fmaxf(v, 0.f);
+                r[j] = __float_as_uint(v);
+              }
             }
             uint8_t* rowp = stg + l * 128;
 #pragma unroll

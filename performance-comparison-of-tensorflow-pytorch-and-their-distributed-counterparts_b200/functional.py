@@ -126,6 +126,10 @@ class _Unit(object):
     __slots__ = ("conv", "bn", "x", "y", "z", "mask", "mean", "invstd", "relu", "geom", "staged")
 
 
+_FOLD_EVAL_BN = os.environ.get("B200_NO_FOLD_EVAL_BN") is None
+_KEEPALIVE = [] if os.environ.get("B200_KEEPALIVE") else None
+
+
 def _unit_forward(conv, bn, x, relu, residual, save, stage=False):
     K, R, S, stride, pad = _conv_geom(conv)
     staged = None
@@ -144,6 +148,14 @@ def _unit_forward(conv, bn, x, relu, residual, save, stage=False):
     if _bn_uses_batch_stats(bn):
         y, partials = ops.conv_fprop_bnstats(x, wp, K, R, S, stride, pad)   # BN statistics fused into the epilogue
     else:
+        if residual is None and not save and _FOLD_EVAL_BN:
+            # eval mode: BatchNorm (running statistics) + ReLU folded into the conv epilogue, no extra pass
+            scale, shift = ops.bn_eval_coeffs(bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.eps)
+            z = ops.conv_fprop_affine(x, wp, K, R, S, stride, pad, scale, shift, relu)
+            if _KEEPALIVE is not None:
+                _KEEPALIVE.append((scale, shift))
+            if z is not None:
+                return z, None
         y, partials = ops.conv_fprop(x, wp, K, R, S, stride, pad), None
     scale, shift, mean, invstd = _bn_coeffs(bn, y, bump_nbt=False, partials=partials)
     if not save:
@@ -280,15 +292,17 @@ class _ResNetBackbone(torch.autograd.Function):
     """Eager path: every kernel is enqueued from Python on each call."""
 
     @staticmethod
-    def forward(ctx, model, x, *params):
-        # forward() runs with grad mode off; needs_input_grad already folds in the caller's grad mode
-        save = any(ctx.needs_input_grad)
-        feat, st = _backbone_fwd(model, x, save, ctx.needs_input_grad[1])
+    def forward(ctx, model, grad_on, x, *params):
+        # forward() itself always runs with grad mode off and needs_input_grad ignores torch.no_grad(), so the
+        # caller's grad mode comes in explicitly
+        nig = ctx.needs_input_grad[2:]
+        save = grad_on and any(nig)
+        feat, st = _backbone_fwd(model, x, save, grad_on and nig[0])
         if save:
             ctx.state = st
             ctx.params = params
-            ctx.param_needs = list(ctx.needs_input_grad[2:])
-            ctx.x_needs_grad = ctx.needs_input_grad[1]
+            ctx.param_needs = list(nig[1:])
+            ctx.x_needs_grad = nig[0]
         return feat
 
     @staticmethod
@@ -297,7 +311,7 @@ class _ResNetBackbone(torch.autograd.Function):
         dx, grads = _backbone_bwd(ctx.state, dfeat, ctx.params, ctx.param_needs, ctx.x_needs_grad, _GRAD_SINK)
         ctx.state = None
         ctx.params = None
-        return (None, dx) + tuple(grads)
+        return (None, None, dx) + tuple(grads)
 
 
 # ------------------------------------------------------------------ CUDA-graph replay of the backbone
@@ -406,7 +420,7 @@ def resnet_backbone(model, x):
     """[N,3,H,W] fp32 NCHW -> [N,2048] fp32 features (everything up to and including avgpool + flatten)."""
     params = _backbone_params(model)
     if not (_GRAPHS_ON and _GRAD_SINK is None and x.is_cuda and not torch.cuda.is_current_stream_capturing()):
-        return _ResNetBackbone.apply(model, x, *params)
+        return _ResNetBackbone.apply(model, torch.is_grad_enabled(), x, *params)
     needs_x = x.requires_grad and torch.is_grad_enabled()
     key = _graph_key(model, x, params, needs_x)
     rec = _GRAPHS.get(key)
@@ -438,7 +452,7 @@ def resnet_backbone(model, x):
             if len(_GRAPH_SEEN) > 256:               # variable-size inference: do not grow without bound
                 _GRAPH_SEEN.clear()
             _GRAPH_SEEN[key] = seen + 1
-    return _ResNetBackbone.apply(model, x, *params)
+    return _ResNetBackbone.apply(model, torch.is_grad_enabled(), x, *params)
 
 
 # ------------------------------------------------------------------ classifier head (fp32, [rows][features])

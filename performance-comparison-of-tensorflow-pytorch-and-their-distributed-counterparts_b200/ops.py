@@ -159,6 +159,24 @@ def conv_fprop_bnstats(x, wp, K, R, S, stride, pad):
     return y, part
 
 
+def conv_fprop_affine(x, wp, K, R, S, stride, pad, scale, shift, relu):
+    """conv forward with y = act(conv * scale + shift) applied in the epilogue (eval-mode BN folded in).
+    Returns None when the shape is not on the fused path."""
+    N, H, W, C = x.shape
+    key = (N, H, W, C, K, R, S, stride, pad, _dt(x))
+    d, dref, ws, Ho, Wo = _desc(*key)
+    rows = _STATS_ROWS.get(key)
+    if rows is None:
+        rows = int(lib.b200_conv_fprop_bnstats_rows(dref))
+        _STATS_ROWS[key] = rows
+    if rows <= 0:
+        return None
+    y = torch.empty((N, Ho, Wo, K), dtype=x.dtype, device=x.device)
+    check(lib.b200_conv_fprop_affine(dref, x.data_ptr(), wp.data_ptr(), y.data_ptr(), scale.data_ptr(),
+                                     shift.data_ptr(), 1 if relu else 0, _stream()), "conv_fprop_affine")
+    return y
+
+
 def bn_finalize_stats(part, rows, gamma, beta, running_mean, running_var, momentum, eps):
     nblk, _, C = part.shape
     st = torch.empty((4, C), dtype=torch.float32, device=part.device)

@@ -177,6 +177,27 @@ def test_conv_fprop_fused_bn_statistics(case):
     assert _rel(rm1, rm2) < 1e-5 and _rel(rv1, rv2) < 1e-5
 
 
+@pytest.mark.parametrize("case", [c for c in CONV_CASES if c[2] % 64 == 0 and c[3] % 64 == 0][:6])
+@pytest.mark.parametrize("relu", [True, False])
+def test_conv_fprop_affine_epilogue(case, relu):
+    """Eval-mode BatchNorm (+ReLU) folded into the fprop epilogue == conv followed by the separate apply kernel,
+    up to the one bf16 rounding the fused path saves."""
+    from b200net import ops
+    N, H, C, K, R, stride, pad = case
+    x = _nhwc(_rand((N, C, H, H), torch.bfloat16, 11), torch.bfloat16)
+    wp = ops.pack_weight(_rand((K, C, R, R), torch.float32, 12, scale=1.0 / math.sqrt(C * R * R)), torch.bfloat16)
+    scale = _rand((K,), torch.float32, 13).abs() + 0.5
+    shift = _rand((K,), torch.float32, 14)
+    z = ops.conv_fprop_affine(x, wp, K, R, R, stride, pad, scale, shift, relu)
+    assert z is not None
+    y = ops.conv_fprop(x, wp, K, R, R, stride, pad)
+    ref = y.double() * scale.double() + shift.double()
+    if relu:
+        ref = torch.relu(ref)
+    assert _rel(z, ref) < 2e-2
+    assert (z >= 0).all() if relu else True
+
+
 # ---------------------------------------------------------------------------------------------- batch norm
 @pytest.mark.parametrize("prec", ["fp32", "bf16"])
 @pytest.mark.parametrize("rows,C", [(2 * 20 * 20, 64), (3 * 7 * 5, 2048), (1000, 24), (50, 130)])

@@ -246,7 +246,7 @@ def test_cuda_graph_replay_equals_eager():
         used = sum(1 for k, r in F._GRAPHS.items() if r != "failed")
         m.eval()
         with torch.no_grad():
-            one = torch.rand(1, 3, 96, 96, device=DEV)
+            one = O.make_batch(1, 96, 11, DEV)[0]
             outs = [m(one).clone() for _ in range(6)]
         return losses, m.state_dict(), outs, used
 
