@@ -88,10 +88,12 @@ int64_t b200_conv_fprop_bnstats_rows(const b200_conv_desc* d);
 int32_t b200_conv_fprop_bnstats(const b200_conv_desc* d, const void* x, const void* w_krsc, void* y,
                                 float* partials, int64_t partial_rows, void* stream);
 /* Forward convolution with an eval-mode BatchNorm2d (+ReLU) folded into the epilogue (model.eval() paths:
- * pytorch_training_inference_on_image.ipynb:678-690, :853-861): y = act(conv(x,w) * scale[k] + shift[k]), scale/shift
- * from b200_bn_eval_coeffs.  Same shape support as b200_conv_fprop_bnstats (rows query > 0). */
+ * pytorch_training_inference_on_image.ipynb:678-690, :853-861): y = act(conv(x,w) * scale[k] + shift[k] (+ residual)),
+ * scale/shift from b200_bn_eval_coeffs, residual (optional, may be NULL) = the block's identity / downsample branch,
+ * same shape as y.  Same shape support as b200_conv_fprop_bnstats (rows query > 0). */
 int32_t b200_conv_fprop_affine(const b200_conv_desc* d, const void* x, const void* w_krsc, void* y,
-                               const float* scale, const float* shift, int32_t relu, void* stream);
+                               const float* scale, const float* shift, const void* residual, int32_t relu,
+                               void* stream);
 /* dx[N,H,W,C] (+)= conv_transpose(dy[N,Ho,Wo,K], w[K,R,S,C]);  accumulate!=0 adds into dx */
 int32_t b200_conv_dgrad(const b200_conv_desc* d, const void* dy, const void* w_krsc, void* dx, int32_t accumulate,
                         void* ws, int64_t ws_bytes, void* stream);

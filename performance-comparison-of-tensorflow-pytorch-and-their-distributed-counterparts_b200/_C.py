@@ -48,7 +48,7 @@ SIGNATURES = {
     "b200_conv_fprop": (I32, [POINTER(ConvDesc), P, P, P, P, I64, P]),
     "b200_conv_fprop_bnstats_rows": (I64, [POINTER(ConvDesc)]),
     "b200_conv_fprop_bnstats": (I32, [POINTER(ConvDesc), P, P, P, P, I64, P]),
-    "b200_conv_fprop_affine": (I32, [POINTER(ConvDesc), P, P, P, P, P, I32, P]),
+    "b200_conv_fprop_affine": (I32, [POINTER(ConvDesc), P, P, P, P, P, P, I32, P]),
     "b200_conv_dgrad": (I32, [POINTER(ConvDesc), P, P, P, I32, P, I64, P]),
     "b200_conv_wgrad": (I32, [POINTER(ConvDesc), P, P, P, P, I64, P]),
     "b200_gemm_f32": (I32, [P, P, P, I32, I32, I32, I64, I64, I64, I32, I32, P, I32, I32, P]),

@@ -181,7 +181,7 @@ static inline PixelBox fprop_box(const b200_conv_desc* d, const ConvGeom& g) {
 
 static int32_t implicit_fprop(const b200_conv_desc* d, const ConvGeom& g, const void* x, const void* w, void* y,
                               float* stats, cudaStream_t st, const float* ep_scale = nullptr,
-                              const float* ep_shift = nullptr, int ep_relu = 0) {
+                              const float* ep_shift = nullptr, int ep_relu = 0, const void* ep_res = nullptr) {
   ConvParams P{};
   const bool flat = is_flat(d);
   const int Wq = flat ? (int)g.M : g.Wo, Hq = flat ? 1 : g.Ho, Nq = flat ? 1 : d->N;
@@ -211,7 +211,7 @@ static int32_t implicit_fprop(const b200_conv_desc* d, const ConvGeom& g, const 
   static const bool no_tma_store = getenv("B200_NO_TMA_STORE") != nullptr;
   P.tma_store = !no_tma_store && P.vec_ok;
   P.stats = stats;
-  P.ep_scale = ep_scale; P.ep_shift = ep_shift; P.ep_relu = ep_relu;
+  P.ep_scale = ep_scale; P.ep_shift = ep_shift; P.ep_relu = ep_relu; P.ep_res = ep_res;
   if (ep_scale && !P.tma_store) return fail(B200_UNSUPPORTED, "conv_fprop_affine: needs the TMA-store epilogue");
   if (stats && !P.tma_store) return fail(B200_UNSUPPORTED, "conv_fprop_bnstats: needs the TMA-store epilogue");
   rc = make_tmap_bf16_nhwc(&to, y, Nq, Hq, Wq, d->K, b.bw, b.bh, b.bn, 1);
@@ -508,10 +508,12 @@ extern "C" int32_t b200_conv_fprop_bnstats(const b200_conv_desc* d, const void* 
 
 // ---- convolution forward with an eval-mode BatchNorm (+ReLU) folded into the epilogue
 extern "C" int32_t b200_conv_fprop_affine(const b200_conv_desc* d, const void* x, const void* w, void* y,
-                                          const float* scale, const float* shift, int32_t relu, void* stream) {
+                                          const float* scale, const float* shift, const void* residual,
+                                          int32_t relu, void* stream) {
   if (int32_t rc = check_desc(d)) return rc;
   if (!x || !w || !y || !scale || !shift) return fail(B200_INVALID_ARG, "conv_fprop_affine: null pointer");
   if (b200_conv_fprop_bnstats_rows(d) <= 0) return fail(B200_UNSUPPORTED, "conv_fprop_affine: shape not on the implicit tcgen05 path");
-  if (reinterpret_cast<uintptr_t>(y) & 15) return fail(B200_INVALID_ARG, "conv_fprop_affine: misaligned output");
-  return implicit_fprop(d, geom(d), x, w, y, nullptr, as_stream(stream), scale, shift, relu);
+  if ((reinterpret_cast<uintptr_t>(y) | reinterpret_cast<uintptr_t>(residual)) & 15)
+    return fail(B200_INVALID_ARG, "conv_fprop_affine: misaligned output / residual");
+  return implicit_fprop(d, geom(d), x, w, y, nullptr, as_stream(stream), scale, shift, relu, residual);
 }

@@ -58,6 +58,7 @@ struct ConvParams {
   const float* ep_scale;             // fprop + tma_store (eval-mode BatchNorm folded into the epilogue):
   const float* ep_shift;             //   out = act(acc * ep_scale[col] + ep_shift[col]), act = ReLU when ep_relu
   int ep_relu;
+  const void* ep_res;                //   optional residual tensor (same NHWC shape as the output), added before act
   float* stats;                      // fprop + tma_store: per-pixel-tile column sums [pixel tile][2][ncols] of the
                                      // bf16-rounded output (sum, sum of squares) for the BatchNorm that follows
 };
@@ -343,6 +344,15 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             smRed[l] = l < 64 ? P.ep_scale[col] : P.ep_shift[col];
           }
           asm volatile("bar.sync 1, 128;" ::: "memory");
+          // residual (eval-mode block output): this thread's 64 channels of its pixel, issued before the TMEM reads
+          uint4 resv[8];
+          const bool has_res = affine && P.ep_res != nullptr;
+          if (has_res && row_ok) {
+            const uint4* rp = reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(P.ep_res) +
+                                                             row_off + T.n0 + g * 64);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) resv[j] = rp[j];
+          }
 #pragma unroll
           for (int h = 0; h < 2; ++h) {
             uint32_t r[32];
@@ -358,6 +368,10 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 #pragma unroll
               for (int j = 0; j < 32; ++j) {
                 float v = fmaf(__uint_as_float(r[j]), smRed[h * 32 + j], smRed[64 + h * 32 + j]);
+                if (has_res && row_ok) {
+                  const __nv_bfloat16* rb = reinterpret_cast<const __nv_bfloat16*>(&resv[h * 4 + (j >> 3)]);
+                  v += __bfloat162float(rb[j & 7]);
+                }
                 if (P.ep_relu) v = fmaxf(v, 0.f);
                 r[j] = __float_as_uint(v);
               }

@@ -159,8 +159,8 @@ def conv_fprop_bnstats(x, wp, K, R, S, stride, pad):
     return y, part
 
 
-def conv_fprop_affine(x, wp, K, R, S, stride, pad, scale, shift, relu):
-    """conv forward with y = act(conv * scale + shift) applied in the epilogue (eval-mode BN folded in).
+def conv_fprop_affine(x, wp, K, R, S, stride, pad, scale, shift, relu, residual=None):
+    """conv forward with y = act(conv * scale + shift (+ residual)) applied in the epilogue (eval-mode BN folded in).
     Returns None when the shape is not on the fused path."""
     N, H, W, C = x.shape
     key = (N, H, W, C, K, R, S, stride, pad, _dt(x))
@@ -173,7 +173,8 @@ def conv_fprop_affine(x, wp, K, R, S, stride, pad, scale, shift, relu):
         return None
     y = torch.empty((N, Ho, Wo, K), dtype=x.dtype, device=x.device)
     check(lib.b200_conv_fprop_affine(dref, x.data_ptr(), wp.data_ptr(), y.data_ptr(), scale.data_ptr(),
-                                     shift.data_ptr(), 1 if relu else 0, _stream()), "conv_fprop_affine")
+                                     shift.data_ptr(), residual.data_ptr() if residual is not None else None,
+                                     1 if relu else 0, _stream()), "conv_fprop_affine")
     return y
 
 

@@ -192,9 +192,12 @@ def test_conv_fprop_affine_epilogue(case, relu):
     assert z is not None
     y = ops.conv_fprop(x, wp, K, R, R, stride, pad)
     ref = y.double() * scale.double() + shift.double()
+    res = _rand(tuple(y.shape), torch.bfloat16, 15)
+    zr = ops.conv_fprop_affine(x, wp, K, R, R, stride, pad, scale, shift, relu, residual=res)
+    refr = ref + res.double()
     if relu:
-        ref = torch.relu(ref)
-    assert _rel(z, ref) < 2e-2
+        ref, refr = torch.relu(ref), torch.relu(refr)
+    assert _rel(z, ref) < 2e-2 and _rel(zr, refr) < 2e-2
     assert (z >= 0).all() if relu else True
 
 
