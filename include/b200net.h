@@ -225,6 +225,67 @@ int32_t b200_bucket_pack(int32_t n, const float* const* srcs, const int64_t* siz
 int32_t b200_bucket_unpack(int32_t n, float* const* dsts, const int64_t* sizes, const float* flat, float scale,
                            void* stream);
 
+/* ------------------------------------------------------------------ BERT-base encoder (IMDB fine-tuning step)
+ * model = BertForSequenceClassification.from_pretrained("bert-base-uncased", num_labels=2, ...)
+ * (pytorch_on_language_distr.py:155-161); one step = model(b_input_ids, token_type_ids=None,
+ * attention_mask=b_input_mask, labels=b_labels) (:258-261), loss.backward() (:268).  The Linear layers run on
+ * b200_conv_fprop_affine / b200_conv_dgrad / b200_conv_wgrad as flat 1x1 problems (bias in the epilogue); these
+ * entry points are everything else.  Activations are [tokens][hidden] in `dtype`; parameters and statistics fp32.
+ * Dropout masks are never stored: forward and backward derive them from (seed, offset, flat element index) with
+ * Philox4x32-10, so the same (seed, offset) must be passed to the matching backward call. */
+
+/* BertEmbeddings: s = (word[ids] + type[type_ids]) + pos[0..S) ; y = dropout(LayerNorm(s)).  type_ids may be NULL
+ * (token_type_ids=None at :259 = all zeros).  sum_out receives s (saved for the backward), *status is set to 1 if an
+ * id is outside [0, vocab) (torch raises a device-side assert there). */
+int32_t b200_embed_ln_fwd(const int64_t* ids, const int64_t* type_ids, const float* word, const float* pos,
+                          const float* type, const float* gamma, const float* beta, float eps, int32_t N, int32_t S,
+                          int32_t H, int32_t vocab, int32_t max_pos, float p_drop, uint64_t seed, uint64_t offset,
+                          void* sum_out, void* y, float* mean, float* rstd, int32_t* status, int32_t dtype,
+                          void* stream);
+/* gradient of the three tables from ds = dL/ds: dword (fp32 atomics, table zeroed here), dpos, dtype_tab.
+ * ws: b200_colsum_workspace_bytes(N*S, H). */
+int32_t b200_embed_bwd(const int64_t* ids, const int64_t* type_ids, const void* dsum, int32_t N, int32_t S, int32_t H,
+                       int32_t vocab, int32_t max_pos, float* dword, float* dpos, float* dtype_tab, void* ws,
+                       int64_t ws_bytes, int32_t dtype, void* stream);
+/* BertSelfOutput / BertOutput: s = dropout(x) + residual ; y = LayerNorm(s) (eps 1e-12).  sum_out receives s (may
+ * alias x); residual may be NULL. */
+int32_t b200_ln_fwd(const void* x, const void* residual, void* sum_out, void* y, float* mean, float* rstd,
+                    const float* gamma, const float* beta, float eps, int64_t rows, int32_t H, float p_drop,
+                    uint64_t seed, uint64_t offset, int32_t dtype, void* stream);
+/* dy = dy_a (+ dy_b, may be NULL: the two consumers of a hidden state).  drop_after == 0: dres = dL/ds,
+ * dx = dres * dropout mask (dx may be NULL when p_drop == 0: it then equals dres), dbias = column sums of dx (bias
+ * gradient of the Linear that produced x; may be NULL).  drop_after != 0 (embeddings): dy is first multiplied by the
+ * dropout mask, dres = dL/ds, dx / dbias unused. */
+int64_t b200_ln_bwd_workspace_bytes(int64_t rows, int32_t H);
+int32_t b200_ln_bwd(const void* dy_a, const void* dy_b, const void* sum, const float* mean, const float* rstd,
+                    const float* gamma, int64_t rows, int32_t H, float p_drop, uint64_t seed, uint64_t offset,
+                    int32_t drop_after, void* dres, void* dx, float* dgamma, float* dbeta, float* dbias, void* ws,
+                    int64_t ws_bytes, int32_t dtype, void* stream);
+/* BertIntermediate activation: erf-GELU (hidden_act = "gelu") and its derivative; n % (16 bytes / element) == 0 */
+int32_t b200_gelu_fwd(const void* x, void* y, int64_t n, int32_t dtype, void* stream);
+int32_t b200_gelu_bwd(const void* dy, const void* x, void* dx, int64_t n, int32_t dtype, void* stream);
+/* out[cols] fp32 = column sums of x[rows][cols] (bias gradients; deterministic two-stage) */
+int64_t b200_colsum_workspace_bytes(int64_t rows, int32_t cols);
+int32_t b200_colsum(const void* x, float* out, int64_t rows, int32_t cols, int32_t dtype, void* ws, int64_t ws_bytes,
+                    void* stream);
+/* BertSelfAttention: qkv [N*S][3*heads*D] = (q | k | v) from the fused QKV Linear; mask [N][S] (attention_mask at
+ * :260, 0 = padded key, may be NULL); probs [N][heads][S][S] = softmax(q k^T / sqrt(D)) before dropout (saved);
+ * ctx [N*S][heads*D] = dropout(probs) v.  D must be 64, S <= 512 and a multiple of 4. */
+int32_t b200_attention_fwd(const void* qkv, const int64_t* mask, void* probs, void* ctx, int32_t N, int32_t S,
+                           int32_t heads, int32_t D, float p_drop, uint64_t seed, uint64_t offset, int32_t dtype,
+                           void* stream);
+/* dqkv from dctx; dscores is scratch of the size of probs */
+int32_t b200_attention_bwd(const void* qkv, const void* probs, const void* dctx, void* dscores, void* dqkv, int32_t N,
+                           int32_t S, int32_t heads, int32_t D, float p_drop, uint64_t seed, uint64_t offset,
+                           int32_t dtype, void* stream);
+/* BertPooler: tanh on fp32 [rows][H]; first-token gather (out[n] = x[n*row_stride ..], to fp32) and its scatter */
+int32_t b200_tanh_fwd_f32(const float* x, float* y, int64_t n, void* stream);
+int32_t b200_tanh_bwd_f32(const float* dy, const float* y, float* dx, int64_t n, void* stream);
+int32_t b200_gather_rows(const void* x, float* out, int32_t N, int64_t row_stride, int32_t H, int32_t dtype,
+                         void* stream);
+int32_t b200_scatter_rows(const float* d, void* out, int32_t N, int64_t row_stride, int32_t H, int32_t dtype,
+                          void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,707 @@
+// BERT-base encoder kernels other than the Linear GEMMs (those run on the tcgen05 implicit-GEMM kernel as flat 1x1
+// problems): embedding gather + LayerNorm, (dropout +) residual + LayerNorm forward / backward, erf-GELU, column
+// sums for bias gradients, tanh for the pooler.  Replaces what `model(b_input_ids, token_type_ids=None,
+// attention_mask=b_input_mask, labels=b_labels)` (pytorch_on_language_distr.py:258-261) and `loss.backward()` (:268)
+// dispatch to ATen for BertEmbeddings / BertSelfOutput / BertIntermediate / BertOutput / BertPooler.
+// All of these are HBM-bound row kernels: one warp owns a token row (hidden = NV*32 vectors of 16 bytes), statistics
+// and every reduction in fp32, activations in the storage dtype (bf16 or fp32).  Dropout masks are never stored: the
+// backward kernels regenerate them from (seed, offset, element index) with Philox.
+#include "common.cuh"
+#include "philox.cuh"
+
+namespace b200 {
+
+// multipliers (0 or 1/(1-p)) for W consecutive elements starting at flat index `base` (base % 4 == 0)
+template <int W>
+__device__ __forceinline__ void dropout_scale_vec(uint64_t seed, uint64_t offset, long long base, float p,
+                                                  float inv_keep, float (&m)[W]) {
+#pragma unroll
+  for (int g = 0; g < W / 4; ++g) {
+    uint32_t r[4];
+    philox4x32_10(seed, offset + (uint64_t)(base / 4 + g), r);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) m[4 * g + e] = philox_uniform(r[e]) >= p ? inv_keep : 0.f;
+  }
+}
+
+template <typename T> __device__ __forceinline__ float round_to(float v) { return to_f(from_f<T>(v)); }
+
+// row statistics of v[NV][W] held by one warp: mean and 1/sqrt(var + eps) (two-pass, in registers)
+template <int NV, int W>
+__device__ __forceinline__ void warp_row_stats(const float (&v)[NV][W], int H, float eps, float& mean, float& rstd) {
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < NV; ++i)
+#pragma unroll
+    for (int e = 0; e < W; ++e) s += v[i][e];
+  mean = warp_sum(s) / (float)H;
+  float q = 0.f;
+#pragma unroll
+  for (int i = 0; i < NV; ++i)
+#pragma unroll
+    for (int e = 0; e < W; ++e) {
+      const float d = v[i][e] - mean;
+      q += d * d;
+    }
+  rstd = rsqrtf(warp_sum(q) / (float)H + eps);
+}
+
+// ---------------------------------------------------------------- LayerNorm forward
+// s = dropout(x) + residual ; y = LN(s).   s (rounded to the storage dtype) is what backward needs: it is written to
+// sum_out (may alias x).
+template <typename T, int NV>
+__global__ void __launch_bounds__(256)
+ln_fwd_kernel(const T* __restrict__ x, const T* __restrict__ res, T* sum_out, T* __restrict__ y,
+              float* __restrict__ mean_out, float* __restrict__ rstd_out, const float* __restrict__ gamma,
+              const float* __restrict__ beta, float eps, long long rows, float p, float inv_keep, uint64_t seed,
+              uint64_t offset) {
+  constexpr int W = VecTraits<T>::W;
+  constexpr int H = NV * 32 * W;
+  const int lane = threadIdx.x & 31;
+  const long long warp = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
+  const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+  float g[NV][W], b[NV][W];
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int col = (lane + 32 * i) * W;
+#pragma unroll
+    for (int e = 0; e < W; ++e) {
+      g[i][e] = gamma[col + e];
+      b[i][e] = beta[col + e];
+    }
+  }
+  for (long long row = warp; row < rows; row += nwarps) {
+    float v[NV][W];
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const long long o = row * H + (lane + 32 * i) * W;
+      load_vec(x + o, v[i]);
+      if (p > 0.f) {
+        float m[W];
+        dropout_scale_vec<W>(seed, offset, o, p, inv_keep, m);
+#pragma unroll
+        for (int e = 0; e < W; ++e) v[i][e] *= m[e];
+      }
+      if (res != nullptr) {
+        float r[W];
+        load_vec(res + o, r);
+#pragma unroll
+        for (int e = 0; e < W; ++e) v[i][e] += r[e];
+      }
+#pragma unroll
+      for (int e = 0; e < W; ++e) v[i][e] = round_to<T>(v[i][e]);
+      if (sum_out != nullptr) store_vec(sum_out + o, v[i]);
+    }
+    float mean, rstd;
+    warp_row_stats<NV, W>(v, H, eps, mean, rstd);
+    if (lane == 0) {
+      mean_out[row] = mean;
+      rstd_out[row] = rstd;
+    }
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      float o_[W];
+#pragma unroll
+      for (int e = 0; e < W; ++e) o_[e] = (v[i][e] - mean) * rstd * g[i][e] + b[i][e];
+      store_vec(y + row * H + (lane + 32 * i) * W, o_);
+    }
+  }
+}
+
+// ---------------------------------------------------------------- embeddings: gather + LayerNorm + dropout
+// s = (word[id] + type[t]) + pos[position] (the association order of BertEmbeddings.forward), y = dropout(LN(s)).
+template <typename T, int NV>
+__global__ void __launch_bounds__(256)
+embed_ln_fwd_kernel(const long long* __restrict__ ids, const long long* __restrict__ type_ids,
+                    const float* __restrict__ word, const float* __restrict__ pos, const float* __restrict__ type,
+                    T* __restrict__ sum_out, T* __restrict__ y, float* __restrict__ mean_out,
+                    float* __restrict__ rstd_out, const float* __restrict__ gamma, const float* __restrict__ beta,
+                    float eps, long long rows, int S, int vocab, float p, float inv_keep, uint64_t seed,
+                    uint64_t offset, int* __restrict__ bad_index) {
+  constexpr int W = VecTraits<T>::W;
+  constexpr int H = NV * 32 * W;
+  const int lane = threadIdx.x & 31;
+  const long long warp = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
+  const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+  for (long long row = warp; row < rows; row += nwarps) {
+    long long id = ids[row];
+    const long long tt = type_ids != nullptr ? type_ids[row] : 0;
+    if (id < 0 || id >= vocab || tt < 0 || tt > 1) {   // torch raises a device assert here; we flag and clamp
+      if (lane == 0) atomicExch(bad_index, 1);
+      id = 0;
+    }
+    const int s = (int)(row % S);
+    float v[NV][W];
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int col = (lane + 32 * i) * W;
+#pragma unroll
+      for (int q = 0; q < W / 4; ++q) {
+        const float4 a = *reinterpret_cast<const float4*>(word + id * H + col + 4 * q);
+        const float4 t = *reinterpret_cast<const float4*>(type + (tt > 0 ? H : 0) + col + 4 * q);
+        const float4 c = *reinterpret_cast<const float4*>(pos + (long long)s * H + col + 4 * q);
+        v[i][4 * q + 0] = round_to<T>((a.x + t.x) + c.x);
+        v[i][4 * q + 1] = round_to<T>((a.y + t.y) + c.y);
+        v[i][4 * q + 2] = round_to<T>((a.z + t.z) + c.z);
+        v[i][4 * q + 3] = round_to<T>((a.w + t.w) + c.w);
+      }
+      store_vec(sum_out + row * H + col, v[i]);
+    }
+    float mean, rstd;
+    warp_row_stats<NV, W>(v, H, eps, mean, rstd);
+    if (lane == 0) {
+      mean_out[row] = mean;
+      rstd_out[row] = rstd;
+    }
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int col = (lane + 32 * i) * W;
+      float o_[W];
+#pragma unroll
+      for (int e = 0; e < W; ++e) o_[e] = (v[i][e] - mean) * rstd * gamma[col + e] + beta[col + e];
+      if (p > 0.f) {
+        float m[W];
+        dropout_scale_vec<W>(seed, offset, row * H + col, p, inv_keep, m);
+#pragma unroll
+        for (int e = 0; e < W; ++e) o_[e] *= m[e];
+      }
+      store_vec(y + row * H + col, o_);
+    }
+  }
+}
+
+// ---------------------------------------------------------------- LayerNorm backward
+// dy = dy_a (+ dy_b)            [drop_after: dy *= dropout mask, the embedding's y = dropout(LN(s))]
+// xhat = (s - mean) * rstd ; g = dy * gamma ; ds = rstd * (g - mean_row(g) - xhat * mean_row(g * xhat))
+// dres = ds ; dx = ds * dropout mask (the branch that went through dropout; same buffer as dres when p == 0)
+// per-block partial column sums: [block][3][H] = (sum dy*xhat, sum dy, sum dx)  -> dgamma, dbeta, bias grad of the
+// Linear that produced x.  Lanes own the same columns for every row, so the sums accumulate in registers.
+template <typename T, int NV>
+__global__ void __launch_bounds__(256)
+ln_bwd_kernel(const T* __restrict__ dy_a, const T* __restrict__ dy_b, const T* __restrict__ s,
+              const float* __restrict__ mean_in, const float* __restrict__ rstd_in, const float* __restrict__ gamma,
+              T* __restrict__ dres, T* __restrict__ dx, float* __restrict__ partials, long long rows, float p,
+              float inv_keep, uint64_t seed, uint64_t offset, int drop_after) {
+  constexpr int W = VecTraits<T>::W;
+  constexpr int H = NV * 32 * W;
+  extern __shared__ float red[];  // [3][H]
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, nwib = blockDim.x >> 5;
+  const long long warp = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
+  const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+  float gm[NV][W], ag[NV][W], ab[NV][W], ad[NV][W];
+#pragma unroll
+  for (int i = 0; i < NV; ++i)
+#pragma unroll
+    for (int e = 0; e < W; ++e) {
+      gm[i][e] = gamma[(lane + 32 * i) * W + e];
+      ag[i][e] = ab[i][e] = ad[i][e] = 0.f;
+    }
+  for (long long row = warp; row < rows; row += nwarps) {
+    const float mean = mean_in[row], rstd = rstd_in[row];
+    float d[NV][W], xh[NV][W];
+    float c1 = 0.f, c2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const long long o = row * H + (lane + 32 * i) * W;
+      load_vec(dy_a + o, d[i]);
+      if (dy_b != nullptr) {
+        float t[W];
+        load_vec(dy_b + o, t);
+#pragma unroll
+        for (int e = 0; e < W; ++e) d[i][e] += t[e];
+      }
+      if (drop_after && p > 0.f) {
+        float m[W];
+        dropout_scale_vec<W>(seed, offset, o, p, inv_keep, m);
+#pragma unroll
+        for (int e = 0; e < W; ++e) d[i][e] *= m[e];
+      }
+      load_vec(s + o, xh[i]);
+#pragma unroll
+      for (int e = 0; e < W; ++e) {
+        xh[i][e] = (xh[i][e] - mean) * rstd;
+        ab[i][e] += d[i][e];
+        ag[i][e] += d[i][e] * xh[i][e];
+        d[i][e] *= gm[i][e];
+        c1 += d[i][e];
+        c2 += d[i][e] * xh[i][e];
+      }
+    }
+    c1 = warp_sum(c1) / (float)H;
+    c2 = warp_sum(c2) / (float)H;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const long long o = row * H + (lane + 32 * i) * W;
+#pragma unroll
+      for (int e = 0; e < W; ++e) d[i][e] = rstd * (d[i][e] - c1 - xh[i][e] * c2);
+      store_vec(dres + o, d[i]);
+      if (!drop_after) {
+        if (p > 0.f) {
+          float m[W];
+          dropout_scale_vec<W>(seed, offset, o, p, inv_keep, m);
+#pragma unroll
+          for (int e = 0; e < W; ++e) d[i][e] *= m[e];
+          store_vec(dx + o, d[i]);
+        }
+#pragma unroll
+        for (int e = 0; e < W; ++e) ad[i][e] += round_to<T>(d[i][e]);
+      }
+    }
+  }
+  // deterministic cross-warp sum: warps add into shared memory one after the other
+  for (int w = 0; w < nwib; ++w) {
+    if (wib == w) {
+#pragma unroll
+      for (int i = 0; i < NV; ++i)
+#pragma unroll
+        for (int e = 0; e < W; ++e) {
+          const int col = (lane + 32 * i) * W + e;
+          if (w == 0) {
+            red[col] = ag[i][e];
+            red[H + col] = ab[i][e];
+            red[2 * H + col] = ad[i][e];
+          } else {
+            red[col] += ag[i][e];
+            red[H + col] += ab[i][e];
+            red[2 * H + col] += ad[i][e];
+          }
+        }
+    }
+    __syncthreads();
+  }
+  float* out = partials + (long long)blockIdx.x * 3 * H;
+  for (int i = threadIdx.x; i < 3 * H; i += blockDim.x) out[i] = red[i];
+}
+
+// out[c] = sum_b part[b][c]   (fixed order: deterministic)
+__global__ void sum_partials_kernel(const float* __restrict__ part, int nparts, int cols, float* __restrict__ o0,
+                                    float* __restrict__ o1, float* __restrict__ o2, int H) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= cols) return;
+  float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+  int b = 0;
+  for (; b + 4 <= nparts; b += 4) {
+    a0 += part[(long long)b * cols + c];
+    a1 += part[(long long)(b + 1) * cols + c];
+    a2 += part[(long long)(b + 2) * cols + c];
+    a3 += part[(long long)(b + 3) * cols + c];
+  }
+  for (; b < nparts; ++b) a0 += part[(long long)b * cols + c];
+  const float v = (a0 + a1) + (a2 + a3);
+  // cols = 3*H laid out [3][H] (LayerNorm backward) or a single vector (H == cols, o1 == o2 == NULL)
+  float* dst = c < H ? o0 : (c < 2 * H ? o1 : o2);
+  if (dst != nullptr) dst[c % H] = v;
+}
+
+// ---------------------------------------------------------------- embedding backward
+// dword[id] += ds (fp32 atomics: the only non-deterministic summation order in the library, as in ATen's
+// embedding_dense_backward without sorting); dtype[t] likewise after a per-block pre-reduction is not worth it for
+// two rows, so the type table takes the same path; dpos[s] = sum_n ds[n, s] in fixed order.
+template <typename T>
+__global__ void embed_bwd_scatter_kernel(const long long* __restrict__ ids, const long long* __restrict__ type_ids,
+                                         const T* __restrict__ ds, float* __restrict__ dword,
+                                         float* __restrict__ dtype_tab, long long rows, int H, int vocab) {
+  constexpr int W = VecTraits<T>::W;
+  const int nvec = H / W;
+  const long long total = rows * nvec;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long row = i / nvec;
+    const int col = (int)(i % nvec) * W;
+    long long id = ids[row];
+    if (id < 0 || id >= vocab) continue;
+    const long long tt = type_ids != nullptr ? type_ids[row] : 0;
+    float v[W];
+    load_vec(ds + row * H + col, v);
+#pragma unroll
+    for (int e = 0; e < W; ++e) {
+      atomicAdd(dword + id * H + col + e, v[e]);
+      if (type_ids != nullptr) atomicAdd(dtype_tab + (tt > 0 ? H : 0) + col + e, v[e]);
+    }
+  }
+}
+// dpos[s][c] = sum_n ds[n][s][c]; rows s >= S of the table get zero.  One thread per (s, column vector).
+template <typename T>
+__global__ void embed_bwd_pos_kernel(const T* __restrict__ ds, float* __restrict__ dpos, int N, int S, int H,
+                                     int max_pos) {
+  constexpr int W = VecTraits<T>::W;
+  const int nvec = H / W;
+  const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (i >= (long long)max_pos * nvec) return;
+  const int s = (int)(i / nvec), col = (int)(i % nvec) * W;
+  float acc[W];
+#pragma unroll
+  for (int e = 0; e < W; ++e) acc[e] = 0.f;
+  if (s < S)
+    for (int n = 0; n < N; ++n) {
+      float v[W];
+      load_vec(ds + ((long long)n * S + s) * H + col, v);
+#pragma unroll
+      for (int e = 0; e < W; ++e) acc[e] += v[e];
+    }
+#pragma unroll
+  for (int e = 0; e < W; ++e) dpos[(long long)s * H + col + e] = acc[e];
+}
+
+// ---------------------------------------------------------------- erf-GELU (config hidden_act = "gelu")
+__device__ __forceinline__ float gelu_f(float x) { return 0.5f * x * (1.f + erff(x * 0.70710678118654752f)); }
+__device__ __forceinline__ float gelu_grad_f(float x) {
+  return 0.5f * (1.f + erff(x * 0.70710678118654752f)) + x * 0.3989422804014327f * __expf(-0.5f * x * x);
+}
+template <typename T>
+__global__ void gelu_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, long long nvec) {
+  constexpr int W = VecTraits<T>::W;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < nvec;
+       i += (long long)gridDim.x * blockDim.x) {
+    float v[W];
+    load_vec(x + i * W, v);
+#pragma unroll
+    for (int e = 0; e < W; ++e) v[e] = gelu_f(v[e]);
+    store_vec(y + i * W, v);
+  }
+}
+template <typename T>
+__global__ void gelu_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x, T* __restrict__ dx,
+                                long long nvec) {
+  constexpr int W = VecTraits<T>::W;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < nvec;
+       i += (long long)gridDim.x * blockDim.x) {
+    float v[W], d[W];
+    load_vec(x + i * W, v);
+    load_vec(dy + i * W, d);
+#pragma unroll
+    for (int e = 0; e < W; ++e) d[e] *= gelu_grad_f(v[e]);
+    store_vec(dx + i * W, d);
+  }
+}
+
+// ---------------------------------------------------------------- column sums (bias gradients), two-stage
+// block = 32 column vectors x 8 row lanes over one row chunk; partial[chunk][cols]
+template <typename T>
+__global__ void __launch_bounds__(256)
+colsum_partial_kernel(const T* __restrict__ x, float* __restrict__ part, long long rows, int cols,
+                      long long rows_per_chunk) {
+  constexpr int W = VecTraits<T>::W;
+  __shared__ float red[8][32 * W + 1];
+  const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
+  const int col = (blockIdx.x * 32 + cx) * W;
+  const long long r0 = blockIdx.y * rows_per_chunk;
+  long long r1 = r0 + rows_per_chunk;
+  if (r1 > rows) r1 = rows;
+  float acc[W];
+#pragma unroll
+  for (int e = 0; e < W; ++e) acc[e] = 0.f;
+  if (col < cols)
+    for (long long r = r0 + ry; r < r1; r += 8) {
+      float v[W];
+      load_vec(x + r * cols + col, v);
+#pragma unroll
+      for (int e = 0; e < W; ++e) acc[e] += v[e];
+    }
+#pragma unroll
+  for (int e = 0; e < W; ++e) red[ry][cx * W + e] = acc[e];
+  __syncthreads();
+  for (int c = threadIdx.x; c < 32 * W; c += 256) {
+    float s = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s += red[j][c];
+    const int gc = blockIdx.x * 32 * W + c;
+    if (gc < cols) part[(long long)blockIdx.y * cols + gc] = s;
+  }
+}
+
+__global__ void tanh_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, long long n) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    y[i] = tanhf(x[i]);
+}
+__global__ void tanh_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ y, float* __restrict__ dx,
+                                long long n) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    dx[i] = dy[i] * (1.f - y[i] * y[i]);
+}
+// rows[n][:] = x[n*S][:] as fp32 ([CLS] token of every sequence) and its transpose-scatter for the backward
+template <typename T>
+__global__ void gather_rows_kernel(const T* __restrict__ x, float* __restrict__ out, int N, long long row_stride,
+                                   int H) {
+  const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (i >= (long long)N * H) return;
+  out[i] = to_f(x[(i / H) * row_stride + (i % H)]);
+}
+template <typename T>
+__global__ void scatter_rows_kernel(const float* __restrict__ d, T* __restrict__ out, int N, long long row_stride,
+                                    int H) {
+  const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (i >= (long long)N * H) return;
+  out[(i / H) * row_stride + (i % H)] = from_f<T>(d[i]);
+}
+
+// ---------------------------------------------------------------- host-side helpers
+static inline int row_grid(long long rows, int warps_per_block, int blocks_per_sm) {
+  const long long want = (rows + warps_per_block - 1) / warps_per_block;
+  const long long cap = (long long)num_sms() * blocks_per_sm;
+  return (int)(want < cap ? (want < 1 ? 1 : want) : cap);
+}
+static inline int ew_grid(long long n, int threads) {
+  const long long want = (n + threads - 1) / threads;
+  const long long cap = (long long)num_sms() * 8;
+  return (int)(want < cap ? (want < 1 ? 1 : want) : cap);
+}
+constexpr int LN_BWD_BLOCKS_PER_SM = 2;
+static inline int ln_bwd_grid(long long rows) { return row_grid(rows, 8, LN_BWD_BLOCKS_PER_SM); }
+static inline int ln_nv(int H, int W) { return (H % (32 * W) == 0) ? H / (32 * W) : 0; }
+
+}  // namespace b200
+
+using namespace b200;
+
+#define B200_LN_DISPATCH_NV(NV_, CALL)                 \
+  switch (NV_) {                                       \
+    case 1: { constexpr int NV = 1; CALL; } break;     \
+    case 2: { constexpr int NV = 2; CALL; } break;     \
+    case 3: { constexpr int NV = 3; CALL; } break;     \
+    case 4: { constexpr int NV = 4; CALL; } break;     \
+    case 6: { constexpr int NV = 6; CALL; } break;     \
+    case 8: { constexpr int NV = 8; CALL; } break;     \
+    default: return fail(B200_UNSUPPORTED, "layernorm: hidden size %d not supported (needs 32*vec*{1,2,3,4,6,8})", H); \
+  }
+
+template <typename T>
+static int32_t ln_fwd_t(const T* x, const T* res, T* sum_out, T* y, float* mean, float* rstd, const float* gamma,
+                        const float* beta, float eps, long long rows, int H, float p, uint64_t seed, uint64_t offset,
+                        cudaStream_t st) {
+  const int nv = ln_nv(H, VecTraits<T>::W);
+  const float ik = p > 0.f ? 1.f / (1.f - p) : 1.f;
+  const int grid = row_grid(rows, 8, 8);
+  B200_LN_DISPATCH_NV(nv, (ln_fwd_kernel<T, NV><<<grid, 256, 0, st>>>(x, res, sum_out, y, mean, rstd, gamma, beta, eps,
+                                                                    rows, p, ik, seed, offset)));
+  return check_launch("ln_fwd");
+}
+
+template <typename T>
+static int32_t embed_fwd_t(const long long* ids, const long long* tt, const float* word, const float* pos,
+                           const float* type, T* sum_out, T* y, float* mean, float* rstd, const float* gamma,
+                           const float* beta, float eps, long long rows, int S, int H, int vocab, float p,
+                           uint64_t seed, uint64_t offset, int* status, cudaStream_t st) {
+  const int nv = ln_nv(H, VecTraits<T>::W);
+  const float ik = p > 0.f ? 1.f / (1.f - p) : 1.f;
+  const int grid = row_grid(rows, 8, 8);
+  B200_LN_DISPATCH_NV(nv, (embed_ln_fwd_kernel<T, NV><<<grid, 256, 0, st>>>(ids, tt, word, pos, type, sum_out, y, mean,
+                                                                          rstd, gamma, beta, eps, rows, S, vocab, p,
+                                                                          ik, seed, offset, status)));
+  return check_launch("embed_ln_fwd");
+}
+
+template <typename T>
+static int32_t ln_bwd_t(const T* dy_a, const T* dy_b, const T* s, const float* mean, const float* rstd,
+                        const float* gamma, long long rows, int H, float p, uint64_t seed, uint64_t offset,
+                        int drop_after, T* dres, T* dx, float* dgamma, float* dbeta, float* dbias, float* ws,
+                        cudaStream_t st) {
+  const int nv = ln_nv(H, VecTraits<T>::W);
+  const float ik = p > 0.f ? 1.f / (1.f - p) : 1.f;
+  const int grid = ln_bwd_grid(rows);
+  const size_t smem = (size_t)3 * H * sizeof(float);
+  B200_LN_DISPATCH_NV(nv, (ln_bwd_kernel<T, NV><<<grid, 256, smem, st>>>(dy_a, dy_b, s, mean, rstd, gamma, dres, dx, ws,
+                                                                       rows, p, ik, seed, offset, drop_after)));
+  sum_partials_kernel<<<(3 * H + 255) / 256, 256, 0, st>>>(ws, grid, 3 * H, dgamma, dbeta, dbias, H);
+  return check_launch("ln_bwd", 2);
+}
+
+template <typename T>
+static int32_t colsum_t(const T* x, float* out, long long rows, int cols, float* ws, long long ws_floats,
+                        cudaStream_t st) {
+  constexpr int W = VecTraits<T>::W;
+  const int cblocks = (cols + 32 * W - 1) / (32 * W);
+  int chunks = (2 * num_sms() + cblocks - 1) / cblocks;
+  if (chunks > (rows + 63) / 64) chunks = (int)((rows + 63) / 64);
+  if (chunks < 1) chunks = 1;
+  if ((long long)chunks * cols > ws_floats) return fail(B200_WORKSPACE_TOO_SMALL, "colsum: workspace too small");
+  const long long rpc = (rows + chunks - 1) / chunks;
+  colsum_partial_kernel<T><<<dim3(cblocks, chunks), 256, 0, st>>>(x, ws, rows, cols, rpc);
+  sum_partials_kernel<<<(cols + 255) / 256, 256, 0, st>>>(ws, chunks, cols, out, nullptr, nullptr, cols);
+  return check_launch("colsum", 2);
+}
+
+extern "C" {
+
+int32_t b200_embed_ln_fwd(const int64_t* ids, const int64_t* type_ids, const float* word, const float* pos,
+                          const float* type, const float* gamma, const float* beta, float eps, int32_t N, int32_t S,
+                          int32_t H, int32_t vocab, int32_t max_pos, float p_drop, uint64_t seed, uint64_t offset,
+                          void* sum_out, void* y, float* mean, float* rstd, int32_t* status, int32_t dtype,
+                          void* stream) {
+  if (!ids || !word || !pos || !type || !gamma || !beta || !sum_out || !y || !mean || !rstd || !status)
+    return fail(B200_INVALID_ARG, "embed_ln_fwd: null pointer");
+  if (N <= 0 || S <= 0 || S > max_pos) return fail(B200_INVALID_ARG, "embed_ln_fwd: sequence length %d exceeds the position table (%d)", S, max_pos);
+  if (p_drop < 0.f || p_drop >= 1.f) return fail(B200_INVALID_ARG, "embed_ln_fwd: bad dropout probability");
+  const long long rows = (long long)N * S;
+  if (dtype == B200_F32)
+    return embed_fwd_t<float>((const long long*)ids, (const long long*)type_ids, word, pos, type, (float*)sum_out,
+                              (float*)y, mean, rstd, gamma, beta, eps, rows, S, H, vocab, p_drop, seed, offset, status,
+                              as_stream(stream));
+  if (dtype == B200_BF16)
+    return embed_fwd_t<__nv_bfloat16>((const long long*)ids, (const long long*)type_ids, word, pos, type,
+                                      (__nv_bfloat16*)sum_out, (__nv_bfloat16*)y, mean, rstd, gamma, beta, eps, rows,
+                                      S, H, vocab, p_drop, seed, offset, status, as_stream(stream));
+  return fail(B200_INVALID_ARG, "embed_ln_fwd: bad dtype");
+}
+
+int32_t b200_embed_bwd(const int64_t* ids, const int64_t* type_ids, const void* dsum, int32_t N, int32_t S, int32_t H,
+                       int32_t vocab, int32_t max_pos, float* dword, float* dpos, float* dtype_tab, void* ws,
+                       int64_t ws_bytes, int32_t dtype, void* stream) {
+  if (!ids || !dsum || !dword || !dpos || !dtype_tab) return fail(B200_INVALID_ARG, "embed_bwd: null pointer");
+  if (dtype != B200_F32 && dtype != B200_BF16) return fail(B200_INVALID_ARG, "embed_bwd: bad dtype");
+  const int W = dtype == B200_F32 ? 4 : 8;
+  if (H % W != 0) return fail(B200_UNSUPPORTED, "embed_bwd: hidden size %d", H);
+  cudaStream_t st = as_stream(stream);
+  const long long rows = (long long)N * S;
+  cudaMemsetAsync(dword, 0, (size_t)vocab * H * sizeof(float), st);
+  cudaMemsetAsync(dtype_tab, 0, (size_t)2 * H * sizeof(float), st);
+  const long long total = rows * (H / W);
+  const int grid = ew_grid(total, 256);
+  const int pgrid = (int)(((long long)max_pos * (H / W) + 255) / 256);
+  int32_t rc;
+  if (dtype == B200_F32) {
+    embed_bwd_scatter_kernel<float><<<grid, 256, 0, st>>>((const long long*)ids, (const long long*)type_ids,
+                                                         (const float*)dsum, dword, dtype_tab, rows, H, vocab);
+    embed_bwd_pos_kernel<float><<<pgrid, 256, 0, st>>>((const float*)dsum, dpos, N, S, H, max_pos);
+    rc = check_launch("embed_bwd", 2);
+    if (rc == B200_OK && type_ids == nullptr)
+      rc = colsum_t<float>((const float*)dsum, dtype_tab, rows, H, (float*)ws, ws_bytes / 4, st);
+  } else {
+    embed_bwd_scatter_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((const long long*)ids, (const long long*)type_ids,
+                                                                 (const __nv_bfloat16*)dsum, dword, dtype_tab, rows,
+                                                                 H, vocab);
+    embed_bwd_pos_kernel<__nv_bfloat16><<<pgrid, 256, 0, st>>>((const __nv_bfloat16*)dsum, dpos, N, S, H, max_pos);
+    rc = check_launch("embed_bwd", 2);
+    if (rc == B200_OK && type_ids == nullptr)
+      rc = colsum_t<__nv_bfloat16>((const __nv_bfloat16*)dsum, dtype_tab, rows, H, (float*)ws, ws_bytes / 4, st);
+  }
+  return rc;
+}
+
+int32_t b200_ln_fwd(const void* x, const void* residual, void* sum_out, void* y, float* mean, float* rstd,
+                    const float* gamma, const float* beta, float eps, int64_t rows, int32_t H, float p_drop,
+                    uint64_t seed, uint64_t offset, int32_t dtype, void* stream) {
+  if (!x || !y || !mean || !rstd || !gamma || !beta || rows <= 0) return fail(B200_INVALID_ARG, "ln_fwd: bad argument");
+  if (p_drop < 0.f || p_drop >= 1.f) return fail(B200_INVALID_ARG, "ln_fwd: bad dropout probability");
+  if (dtype == B200_F32)
+    return ln_fwd_t<float>((const float*)x, (const float*)residual, (float*)sum_out, (float*)y, mean, rstd, gamma, beta,
+                           eps, rows, H, p_drop, seed, offset, as_stream(stream));
+  if (dtype == B200_BF16)
+    return ln_fwd_t<__nv_bfloat16>((const __nv_bfloat16*)x, (const __nv_bfloat16*)residual, (__nv_bfloat16*)sum_out,
+                                   (__nv_bfloat16*)y, mean, rstd, gamma, beta, eps, rows, H, p_drop, seed, offset,
+                                   as_stream(stream));
+  return fail(B200_INVALID_ARG, "ln_fwd: bad dtype");
+}
+
+int64_t b200_ln_bwd_workspace_bytes(int64_t rows, int32_t H) {
+  return (int64_t)ln_bwd_grid(rows) * 3 * H * (int64_t)sizeof(float);
+}
+
+int32_t b200_ln_bwd(const void* dy_a, const void* dy_b, const void* sum, const float* mean, const float* rstd,
+                    const float* gamma, int64_t rows, int32_t H, float p_drop, uint64_t seed, uint64_t offset,
+                    int32_t drop_after, void* dres, void* dx, float* dgamma, float* dbeta, float* dbias, void* ws,
+                    int64_t ws_bytes, int32_t dtype, void* stream) {
+  if (!dy_a || !sum || !mean || !rstd || !gamma || !dres || !dgamma || !dbeta || rows <= 0)
+    return fail(B200_INVALID_ARG, "ln_bwd: bad argument");
+  if (p_drop < 0.f || p_drop >= 1.f) return fail(B200_INVALID_ARG, "ln_bwd: bad dropout probability");
+  if (!drop_after && p_drop > 0.f && !dx) return fail(B200_INVALID_ARG, "ln_bwd: dx required when dropout is on");
+  if (!ws || ws_bytes < b200_ln_bwd_workspace_bytes(rows, H))
+    return fail(B200_WORKSPACE_TOO_SMALL, "ln_bwd: workspace too small");
+  if (dtype == B200_F32)
+    return ln_bwd_t<float>((const float*)dy_a, (const float*)dy_b, (const float*)sum, mean, rstd, gamma, rows, H,
+                           p_drop, seed, offset, drop_after, (float*)dres, (float*)dx, dgamma, dbeta, dbias, (float*)ws,
+                           as_stream(stream));
+  if (dtype == B200_BF16)
+    return ln_bwd_t<__nv_bfloat16>((const __nv_bfloat16*)dy_a, (const __nv_bfloat16*)dy_b, (const __nv_bfloat16*)sum,
+                                   mean, rstd, gamma, rows, H, p_drop, seed, offset, drop_after, (__nv_bfloat16*)dres,
+                                   (__nv_bfloat16*)dx, dgamma, dbeta, dbias, (float*)ws, as_stream(stream));
+  return fail(B200_INVALID_ARG, "ln_bwd: bad dtype");
+}
+
+int32_t b200_gelu_fwd(const void* x, void* y, int64_t n, int32_t dtype, void* stream) {
+  if (!x || !y || n < 0) return fail(B200_INVALID_ARG, "gelu_fwd: bad argument");
+  const int W = dtype == B200_F32 ? 4 : 8;
+  if (n % W != 0) return fail(B200_UNSUPPORTED, "gelu_fwd: element count must be a multiple of %d", W);
+  if (n == 0) return B200_OK;
+  const int grid = ew_grid(n / W, 256);
+  if (dtype == B200_F32)
+    gelu_fwd_kernel<float><<<grid, 256, 0, as_stream(stream)>>>((const float*)x, (float*)y, n / W);
+  else if (dtype == B200_BF16)
+    gelu_fwd_kernel<__nv_bfloat16><<<grid, 256, 0, as_stream(stream)>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y,
+                                                                       n / W);
+  else
+    return fail(B200_INVALID_ARG, "gelu_fwd: bad dtype");
+  return check_launch("gelu_fwd");
+}
+
+int32_t b200_gelu_bwd(const void* dy, const void* x, void* dx, int64_t n, int32_t dtype, void* stream) {
+  if (!dy || !x || !dx || n < 0) return fail(B200_INVALID_ARG, "gelu_bwd: bad argument");
+  const int W = dtype == B200_F32 ? 4 : 8;
+  if (n % W != 0) return fail(B200_UNSUPPORTED, "gelu_bwd: element count must be a multiple of %d", W);
+  if (n == 0) return B200_OK;
+  const int grid = ew_grid(n / W, 256);
+  if (dtype == B200_F32)
+    gelu_bwd_kernel<float><<<grid, 256, 0, as_stream(stream)>>>((const float*)dy, (const float*)x, (float*)dx, n / W);
+  else if (dtype == B200_BF16)
+    gelu_bwd_kernel<__nv_bfloat16><<<grid, 256, 0, as_stream(stream)>>>(
+        (const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, (__nv_bfloat16*)dx, n / W);
+  else
+    return fail(B200_INVALID_ARG, "gelu_bwd: bad dtype");
+  return check_launch("gelu_bwd");
+}
+
+int64_t b200_colsum_workspace_bytes(int64_t rows, int32_t cols) {
+  (void)rows;
+  return (int64_t)(2 * num_sms() + 8) * cols * (int64_t)sizeof(float);
+}
+
+int32_t b200_colsum(const void* x, float* out, int64_t rows, int32_t cols, int32_t dtype, void* ws, int64_t ws_bytes,
+                    void* stream) {
+  if (!x || !out || !ws || rows <= 0 || cols <= 0) return fail(B200_INVALID_ARG, "colsum: bad argument");
+  const int W = dtype == B200_F32 ? 4 : 8;
+  if (cols % W != 0) return fail(B200_UNSUPPORTED, "colsum: column count must be a multiple of %d", W);
+  if (dtype == B200_F32) return colsum_t<float>((const float*)x, out, rows, cols, (float*)ws, ws_bytes / 4, as_stream(stream));
+  if (dtype == B200_BF16)
+    return colsum_t<__nv_bfloat16>((const __nv_bfloat16*)x, out, rows, cols, (float*)ws, ws_bytes / 4, as_stream(stream));
+  return fail(B200_INVALID_ARG, "colsum: bad dtype");
+}
+
+int32_t b200_tanh_fwd_f32(const float* x, float* y, int64_t n, void* stream) {
+  if (!x || !y || n < 0) return fail(B200_INVALID_ARG, "tanh_fwd: bad argument");
+  if (n == 0) return B200_OK;
+  tanh_fwd_kernel<<<ew_grid(n, 256), 256, 0, as_stream(stream)>>>(x, y, n);
+  return check_launch("tanh_fwd");
+}
+int32_t b200_tanh_bwd_f32(const float* dy, const float* y, float* dx, int64_t n, void* stream) {
+  if (!dy || !y || !dx || n < 0) return fail(B200_INVALID_ARG, "tanh_bwd: bad argument");
+  if (n == 0) return B200_OK;
+  tanh_bwd_kernel<<<ew_grid(n, 256), 256, 0, as_stream(stream)>>>(dy, y, dx, n);
+  return check_launch("tanh_bwd");
+}
+
+int32_t b200_gather_rows(const void* x, float* out, int32_t N, int64_t row_stride, int32_t H, int32_t dtype,
+                         void* stream) {
+  if (!x || !out || N <= 0 || H <= 0) return fail(B200_INVALID_ARG, "gather_rows: bad argument");
+  const int grid = (int)(((long long)N * H + 255) / 256);
+  if (dtype == B200_F32)
+    gather_rows_kernel<float><<<grid, 256, 0, as_stream(stream)>>>((const float*)x, out, N, row_stride, H);
+  else if (dtype == B200_BF16)
+    gather_rows_kernel<__nv_bfloat16><<<grid, 256, 0, as_stream(stream)>>>((const __nv_bfloat16*)x, out, N, row_stride, H);
+  else
+    return fail(B200_INVALID_ARG, "gather_rows: bad dtype");
+  return check_launch("gather_rows");
+}
+int32_t b200_scatter_rows(const float* d, void* out, int32_t N, int64_t row_stride, int32_t H, int32_t dtype,
+                          void* stream) {
+  if (!d || !out || N <= 0 || H <= 0) return fail(B200_INVALID_ARG, "scatter_rows: bad argument");
+  const int grid = (int)(((long long)N * H + 255) / 256);
+  if (dtype == B200_F32)
+    scatter_rows_kernel<float><<<grid, 256, 0, as_stream(stream)>>>(d, (float*)out, N, row_stride, H);
+  else if (dtype == B200_BF16)
+    scatter_rows_kernel<__nv_bfloat16><<<grid, 256, 0, as_stream(stream)>>>(d, (__nv_bfloat16*)out, N, row_stride, H);
+  else
+    return fail(B200_INVALID_ARG, "scatter_rows: bad dtype");
+  return check_launch("scatter_rows");
+}
+
+}  // extern "C"

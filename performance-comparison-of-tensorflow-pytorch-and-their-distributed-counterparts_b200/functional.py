@@ -508,6 +508,25 @@ def relu(x):
     return _ReLU.apply(x)
 
 
+class _Tanh(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        y = ops.tanh_fwd(_c2d(x))
+        ctx.save_for_backward(y)
+        return y
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dy):
+        (y,) = ctx.saved_tensors
+        return ops.tanh_bwd(_c2d(dy), y)
+
+
+def tanh(x):
+    """BertPooler activation (fp32)"""
+    return _Tanh.apply(x)
+
+
 _DROPOUT_CALLS = [0]
 
 

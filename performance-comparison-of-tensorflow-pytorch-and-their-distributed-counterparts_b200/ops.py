@@ -412,3 +412,178 @@ def nll_loss_bwd(dloss, labels, rows, cols):
     check(lib.b200_nll_loss_bwd(dloss.data_ptr(), labels.data_ptr(), d.data_ptr(), rows, cols, _stream()),
           "nll_loss_bwd")
     return d
+
+
+# ------------------------------------------------------------------ BERT encoder ops ([tokens][hidden] matrices)
+def _p(t):
+    return t.data_ptr() if t is not None else None
+
+
+def embed_ln_fwd(ids, type_ids, word, pos, type_tab, gamma, beta, eps, p, seed, offset, dtype, status):
+    """BertEmbeddings forward; returns (s, y, mean, rstd) with s the pre-LayerNorm sum (saved for backward)."""
+    _need_cuda(ids)
+    N, S = ids.shape
+    V, H = word.shape
+    s = torch.empty((N * S, H), dtype=dtype, device=ids.device)
+    y = torch.empty_like(s)
+    st = torch.empty((2, N * S), dtype=torch.float32, device=ids.device)
+    check(lib.b200_embed_ln_fwd(ids.data_ptr(), _p(type_ids), word.data_ptr(), pos.data_ptr(), type_tab.data_ptr(),
+                                gamma.data_ptr(), beta.data_ptr(), float(eps), N, S, H, V, pos.shape[0], float(p),
+                                seed, offset, s.data_ptr(), y.data_ptr(), st[0].data_ptr(), st[1].data_ptr(),
+                                status.data_ptr(), _DT[dtype], _stream()), "embed_ln_fwd")
+    return s, y, st[0], st[1]
+
+
+def embed_bwd(ids, type_ids, dsum, vocab, max_pos):
+    N, S = ids.shape
+    H = dsum.shape[-1]
+    dword = torch.empty((vocab, H), dtype=torch.float32, device=dsum.device)
+    dpos = torch.empty((max_pos, H), dtype=torch.float32, device=dsum.device)
+    dtyp = torch.empty((2, H), dtype=torch.float32, device=dsum.device)
+    n = int(lib.b200_colsum_workspace_bytes(N * S, H))
+    ws = workspace(n, dsum.device)
+    check(lib.b200_embed_bwd(ids.data_ptr(), _p(type_ids), dsum.data_ptr(), N, S, H, vocab, max_pos, dword.data_ptr(),
+                             dpos.data_ptr(), dtyp.data_ptr(), ws.data_ptr(), n, _dt(dsum), _stream()), "embed_bwd")
+    return dword, dpos, dtyp
+
+
+def ln_fwd(x, residual, gamma, beta, eps, p=0.0, seed=0, offset=0, inplace_sum=True):
+    """s = dropout(x) + residual ; y = LayerNorm(s).  Returns (s, y, mean, rstd); s overwrites x when inplace_sum."""
+    rows, H = x.shape
+    s = x if inplace_sum else torch.empty_like(x)
+    y = torch.empty_like(x)
+    st = torch.empty((2, rows), dtype=torch.float32, device=x.device)
+    check(lib.b200_ln_fwd(x.data_ptr(), _p(residual), s.data_ptr(), y.data_ptr(), st[0].data_ptr(), st[1].data_ptr(),
+                          gamma.data_ptr(), beta.data_ptr(), float(eps), rows, H, float(p), seed, offset, _dt(x),
+                          _stream()), "ln_fwd")
+    return s, y, st[0], st[1]
+
+
+def ln_bwd(dy_a, dy_b, s, mean, rstd, gamma, p=0.0, seed=0, offset=0, drop_after=False, want_dbias=True):
+    """Returns (dres, dx, dgamma, dbeta, dbias): dres = dL/ds, dx = gradient of the dropped branch (is dres when
+    p == 0), dbias = column sums of dx."""
+    rows, H = s.shape
+    dres = torch.empty_like(s)
+    dx = torch.empty_like(s) if (p > 0.0 and not drop_after) else None
+    pg = torch.empty((3, H), dtype=torch.float32, device=s.device)
+    n = int(lib.b200_ln_bwd_workspace_bytes(rows, H))
+    ws = workspace(n, s.device)
+    check(lib.b200_ln_bwd(dy_a.data_ptr(), _p(dy_b), s.data_ptr(), mean.data_ptr(), rstd.data_ptr(), gamma.data_ptr(),
+                          rows, H, float(p), seed, offset, 1 if drop_after else 0, dres.data_ptr(), _p(dx),
+                          pg[0].data_ptr(), pg[1].data_ptr(), pg[2].data_ptr() if want_dbias else None,
+                          ws.data_ptr(), n, _dt(s), _stream()), "ln_bwd")
+    return dres, (dx if dx is not None else dres), pg[0], pg[1], (pg[2] if want_dbias else None)
+
+
+def gelu_fwd(x):
+    y = torch.empty_like(x)
+    check(lib.b200_gelu_fwd(x.data_ptr(), y.data_ptr(), x.numel(), _dt(x), _stream()), "gelu_fwd")
+    return y
+
+
+def gelu_bwd(dy, x, out=None):
+    dx = torch.empty_like(x) if out is None else out
+    check(lib.b200_gelu_bwd(dy.data_ptr(), x.data_ptr(), dx.data_ptr(), x.numel(), _dt(x), _stream()), "gelu_bwd")
+    return dx
+
+
+def colsum_any(x):
+    """fp32 column sums of a [rows][cols] matrix in either dtype (bias gradients)."""
+    rows, cols = x.shape
+    out = torch.empty((cols,), dtype=torch.float32, device=x.device)
+    n = int(lib.b200_colsum_workspace_bytes(rows, cols))
+    ws = workspace(n, x.device)
+    check(lib.b200_colsum(x.data_ptr(), out.data_ptr(), rows, cols, _dt(x), ws.data_ptr(), n, _stream()), "colsum")
+    return out
+
+
+def attention_fwd(qkv, mask, N, S, heads, p=0.0, seed=0, offset=0):
+    """qkv [N*S][3*heads*64] -> (probs [N,heads,S,S] (pre-dropout, saved), ctx [N*S][heads*64])"""
+    D = qkv.shape[1] // (3 * heads)
+    probs = torch.empty((N, heads, S, S), dtype=qkv.dtype, device=qkv.device)
+    ctx = torch.empty((N * S, heads * D), dtype=qkv.dtype, device=qkv.device)
+    check(lib.b200_attention_fwd(qkv.data_ptr(), _p(mask), probs.data_ptr(), ctx.data_ptr(), N, S, heads, D, float(p),
+                                 seed, offset, _dt(qkv), _stream()), "attention_fwd")
+    return probs, ctx
+
+
+def attention_bwd(qkv, probs, dctx, N, S, heads, p=0.0, seed=0, offset=0):
+    D = qkv.shape[1] // (3 * heads)
+    dqkv = torch.empty_like(qkv)
+    ws = workspace(probs.numel() * probs.element_size(), qkv.device)
+    check(lib.b200_attention_bwd(qkv.data_ptr(), probs.data_ptr(), dctx.data_ptr(), ws.data_ptr(), dqkv.data_ptr(),
+                                 N, S, heads, D, float(p), seed, offset, _dt(qkv), _stream()), "attention_bwd")
+    return dqkv
+
+
+def tanh_fwd(x):
+    y = torch.empty_like(x)
+    check(lib.b200_tanh_fwd_f32(x.data_ptr(), y.data_ptr(), x.numel(), _stream()), "tanh_fwd")
+    return y
+
+
+def tanh_bwd(dy, y):
+    dx = torch.empty_like(y)
+    check(lib.b200_tanh_bwd_f32(dy.data_ptr(), y.data_ptr(), dx.data_ptr(), y.numel(), _stream()), "tanh_bwd")
+    return dx
+
+
+def gather_rows(x, N, row_stride):
+    """out[n] = x[n*row_stride] as fp32 (the [CLS] row of every sequence)"""
+    H = x.shape[-1]
+    out = torch.empty((N, H), dtype=torch.float32, device=x.device)
+    check(lib.b200_gather_rows(x.data_ptr(), out.data_ptr(), N, row_stride * H, H, _dt(x), _stream()), "gather_rows")
+    return out
+
+
+def scatter_rows(d, rows, row_stride, dtype):
+    """zeros([rows][H]) with row n*row_stride = d[n]"""
+    N, H = d.shape
+    out = torch.zeros((rows, H), dtype=dtype, device=d.device)
+    check(lib.b200_scatter_rows(d.data_ptr(), out.data_ptr(), N, row_stride * H, H, _DT[dtype], _stream()),
+          "scatter_rows")
+    return out
+
+
+# Linear layers of the encoder: y[M][out] = x[M][in] @ w[out][in]^T + b.  bf16: flat 1x1 problems on the tcgen05
+# implicit-GEMM kernel (bias added in its epilogue); fp32: the FFMA GEMM.
+_ONES = {}
+
+
+def _ones(n, device):
+    key = (n, device)
+    t = _ONES.get(key)
+    if t is None:
+        t = torch.ones(n, dtype=torch.float32, device=device)
+        _ONES[key] = t
+    return t
+
+
+def dense_fwd(x, wp, bias, w_f32=None):
+    """wp: packed [out][in] operand in x.dtype (for fp32 this is the parameter itself)."""
+    M, K = x.shape
+    N = wp.shape[0]
+    if x.dtype == torch.float32:
+        return gemm_f32(x, wp, M, N, K, K, K, False, False, bias=bias)
+    y = conv_fprop_affine(x.view(1, 1, M, K), wp, N, 1, 1, 1, 0, _ones(N, x.device), bias, False)
+    if y is None:
+        raise RuntimeError("b200net dense_fwd: shape [%d,%d]x[%d] is not on the tensor-core path" % (M, K, N))
+    return y.view(M, N)
+
+
+def dense_bwd_input(dy, wp, K, out=None, accumulate=False):
+    """dx[M][in] (+)= dy[M][out] @ w[out][in]"""
+    M, N = dy.shape
+    if dy.dtype == torch.float32:
+        return gemm_f32(dy, wp, M, K, N, N, K, False, True, out=out, accumulate=accumulate)
+    o = None if out is None else out.view(1, 1, M, K)
+    return conv_dgrad(dy.view(1, 1, M, N), wp, (1, 1, M, K), N, 1, 1, 1, 0, out=o, accumulate=accumulate).view(M, K)
+
+
+def dense_bwd_weight(dy, x):
+    """dw[out][in] fp32 = dy[M][out]^T @ x[M][in]"""
+    M, N = dy.shape
+    K = x.shape[1]
+    if dy.dtype == torch.float32:
+        return gemm_f32(dy, x, N, K, M, N, K, True, True)
+    return conv_wgrad(x.view(1, 1, M, K), dy.view(1, 1, M, N), N, 1, 1, 1, 0).view(N, K)
