@@ -174,6 +174,7 @@ _CALLS = [0]
 _STATUS = {}
 _CHECK_IDS = os.environ.get("B200_CHECK_IDS") is not None
 _M64 = 0xFFFFFFFFFFFFFFFF
+_FLASH = os.environ.get("B200_NO_FLASH_ATTENTION") is None
 
 
 def _cast_into(src, dst):
@@ -252,12 +253,18 @@ def _encoder_fwd(model, ids, type_ids, mask, save, training):
         raise IndexError("b200net BertEmbeddings: input id out of range")
     st = _EncoderState()
     st.layers = []
+    # bf16 at S in {128, 256}: fused tcgen05 attention (saves the log-sum-exp); otherwise the fp32-arithmetic kernel
+    # (saves the probabilities)
+    flash = _FLASH and ops.attention_flash_ok(dt, S)
     for li, L in enumerate(model.bert.encoder.layer):
         a, o = L.attention, L.output
         wqkv = _operand((a.self.query.weight, a.self.key.weight, a.self.value.weight), dt)
         bqkv = _operand((a.self.query.bias, a.self.key.bias, a.self.value.bias), torch.float32)
         qkv = ops.dense_fwd(h, wqkv, bqkv)
-        probs, ctx = ops.attention_fwd(qkv, mask, N, S, heads, p_a, seed, _site(call, 1 + 3 * li))
+        if flash:
+            probs, ctx = ops.attention_flash_fwd(qkv, mask, N, S, heads, p_a, seed, _site(call, 1 + 3 * li))
+        else:
+            probs, ctx = ops.attention_fwd(qkv, mask, N, S, heads, p_a, seed, _site(call, 1 + 3 * li))
         ao = ops.dense_fwd(ctx, _operand((a.output.dense.weight,), dt), a.output.dense.bias.detach())
         ln1 = a.output.LayerNorm
         s1, h1, m1, r1 = ops.ln_fwd(ao, h, ln1.weight.detach(), ln1.bias.detach(), ln1.eps, p_h, seed,
@@ -277,6 +284,7 @@ def _encoder_fwd(model, ids, type_ids, mask, save, training):
         st.ids, st.type_ids = ids, type_ids
         st.N, st.S, st.dtype = N, S, dt
         st.p_h, st.p_a, st.seed, st.call = p_h, p_a, seed, call
+        st.flash, st.mask = flash, mask
     return cls, st
 
 
@@ -314,7 +322,11 @@ def _encoder_bwd(model, st, dcls, emit):
         emit(a.output.dense.bias, dbias)
         emit(a.output.dense.weight, ops.dense_bwd_weight(dao, ctx))
         dctx = ops.dense_bwd_input(dao, _operand((a.output.dense.weight,), dt), H)
-        dqkv = ops.attention_bwd(qkv, probs, dctx, N, S, heads, p_a, seed, _site(call, 1 + 3 * li))
+        if st.flash:
+            dqkv = ops.attention_flash_bwd(qkv, st.mask, probs, ctx, dctx, N, S, heads, p_a, seed,
+                                           _site(call, 1 + 3 * li))
+        else:
+            dqkv = ops.attention_bwd(qkv, probs, dctx, N, S, heads, p_a, seed, _site(call, 1 + 3 * li))
         dbqkv = ops.colsum_any(dqkv)
         dwqkv = ops.dense_bwd_weight(dqkv, h_in)
         for j, lin in enumerate((a.self.query, a.self.key, a.self.value)):

@@ -516,6 +516,30 @@ def attention_bwd(qkv, probs, dctx, N, S, heads, p=0.0, seed=0, offset=0):
     return dqkv
 
 
+def attention_flash_ok(dtype, S, D=64):
+    return dtype == torch.bfloat16 and bool(lib.b200_attention_flash_supported(S, D))
+
+
+def attention_flash_fwd(qkv, mask, N, S, heads, p=0.0, seed=0, offset=0):
+    """Fused tcgen05 attention: returns (lse [N,heads,S] fp32, ctx [N*S][heads*64]); no S x S tensor is stored."""
+    D = qkv.shape[1] // (3 * heads)
+    lse = torch.empty((N, heads, S), dtype=torch.float32, device=qkv.device)
+    ctx = torch.empty((N * S, heads * D), dtype=qkv.dtype, device=qkv.device)
+    check(lib.b200_attention_flash_fwd(qkv.data_ptr(), _p(mask), lse.data_ptr(), ctx.data_ptr(), N, S, heads, D,
+                                       float(p), seed, offset, _stream()), "attention_flash_fwd")
+    return lse, ctx
+
+
+def attention_flash_bwd(qkv, mask, lse, ctx, dctx, N, S, heads, p=0.0, seed=0, offset=0):
+    D = qkv.shape[1] // (3 * heads)
+    dqkv = torch.empty_like(qkv)
+    dvec = torch.empty_like(lse)
+    check(lib.b200_attention_flash_bwd(qkv.data_ptr(), _p(mask), lse.data_ptr(), ctx.data_ptr(), dctx.data_ptr(),
+                                       dvec.data_ptr(), dqkv.data_ptr(), N, S, heads, D, float(p), seed, offset,
+                                       _stream()), "attention_flash_bwd")
+    return dqkv
+
+
 def tanh_fwd(x):
     y = torch.empty_like(x)
     check(lib.b200_tanh_fwd_f32(x.data_ptr(), y.data_ptr(), x.numel(), _stream()), "tanh_fwd")

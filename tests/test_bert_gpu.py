@@ -232,6 +232,42 @@ def test_attention_dropout_replay(prec):
     assert _rel(dqkv, qd.grad) < (1e-4 if prec == "fp32" else 3e-2)
 
 
+@pytest.mark.parametrize("N,S,heads", [(2, 128, 12), (3, 256, 4), (1, 256, 1)])
+@pytest.mark.parametrize("p", [0.0, 0.1])
+def test_attention_flash_matches_reference_path(N, S, heads, p):
+    """tcgen05 fused attention (no S x S tensor in HBM) against float64 torch (p = 0) and against the
+    fp32-arithmetic kernels on the same (seed, offset): both derive the dropout mask from the same Philox indices."""
+    from b200net import ops
+    dt = torch.bfloat16
+    assert ops.attention_flash_ok(dt, S)
+    qkv = _rand((N * S, 3 * heads * 64), dt, 1)
+    g = torch.Generator().manual_seed(3)
+    lens = torch.randint(S // 2, S + 1, (N,), generator=g)
+    mask = (torch.arange(S)[None, :] < lens[:, None]).long().to(_dev())
+    dctx = _rand((N * S, heads * 64), dt, 2)
+    seed, off = 4242, 9 << 34
+    lse, ctx = ops.attention_flash_fwd(qkv, mask, N, S, heads, p, seed, off)
+    probs, ctx_ref = ops.attention_fwd(qkv, mask, N, S, heads, p, seed, off)
+    assert _rel(ctx, ctx_ref) < 2e-2
+    dq = ops.attention_flash_bwd(qkv, mask, lse, ctx, dctx, N, S, heads, p, seed, off)
+    dq_ref = ops.attention_bwd(qkv, probs, dctx, N, S, heads, p, seed, off)
+    for j, name in enumerate("qkv"):
+        a = dq.reshape(N * S, 3, heads * 64)[:, j]
+        b = dq_ref.reshape(N * S, 3, heads * 64)[:, j]
+        assert _rel(a, b) < 3e-2, name
+    if p == 0.0:
+        qd = qkv.double().requires_grad_(True)
+        pr, cref = _attention_ref(qd, mask, N, S, heads)
+        assert _rel(ctx, cref) < 2e-2
+        lse_ref = torch.logsumexp((torch.log(pr.clamp_min(1e-300))), -1)   # == 0: probabilities are normalised
+        assert lse_ref.abs().max().item() < 1e-9
+        cref.backward(dctx.double())
+        assert _rel(dq, qd.grad) < 3e-2
+    # padded keys: exactly zero gradient for their K and V rows
+    pad = (mask == 0).reshape(-1)
+    assert dq.reshape(N * S, 3, -1)[pad][:, 1:].float().abs().sum().item() == 0.0
+
+
 # ---------------------------------------------------------------------------------------------- dense layers
 @pytest.mark.parametrize("prec", ["fp32", "bf16"])
 @pytest.mark.parametrize("M,K,N", [(512, 768, 2304), (300, 768, 768), (256, 3072, 768), (128, 768, 3072)])
