@@ -123,6 +123,129 @@ def run_reference(args, rank):
     }), flush=True)
 
 
+# ------------------------------------------------------------------ BERT / IMDB leg (BASELINE.json configs[4], C5)
+BERT_BATCH, BERT_SEQ = 32, 256          # per GPU (pytorch_on_language_distr.py:134 batch_size=32; SURVEY C5 S=256)
+BERT_GFLOP_PER_SEQ_TRAIN = 137.7        # 3 x 12 x (2 x 7 077 888 + 4 x S x 768) x S at S=256
+BERT_WORKLOAD = ("bert-base-uncased sequence classifier train step (pytorch_on_language_distr.py:257-275: forward with "
+                 "labels, backward, clip_grad_norm_ 1.0, AdamW 2e-5/1e-8, linear schedule), batch %d/GPU, seq %d, "
+                 "dropout 0.1 (BASELINE.json configs[4])")
+
+
+def bert_cpu_reference_run(steps, warmup, batch, seq=BERT_SEQ):
+    """The reference's BERT train-step statements on transformers + stock torch CPU fp32, all host threads."""
+    import torch
+    from oracle import bert_oracle as BO
+    from oracle.torch_oracle import cpu_threads
+    cores = cpu_threads()
+    torch.set_num_threads(cores)
+    model = BO.build_reference_model(dropout=0.1)
+    opt, sched = BO.make_optimizer(model, 1000)
+    ids, mask, labels = BO.make_batch(batch, seq, 0)
+    model.train()
+    for _ in range(warmup):
+        BO.train_step(model, opt, sched, ids, mask, labels)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        BO.train_step(model, opt, sched, ids, mask, labels)
+    dt = time.perf_counter() - t0
+    return batch * steps / dt, dt / steps * 1e3, cores
+
+
+def bert_leg(dev, rank, world, distributed, steps, warmup, timed, with_roofline):
+    """One rank's share of the C5 step through the reference's own statements; returns the numbers of the leg."""
+    import ctypes
+    import torch
+    import b200net
+    from b200net import bert
+    from oracle import bert_oracle as BO     # synthetic batch generator only
+    lib = b200net._C.lib
+    torch.manual_seed(BO.SEED_WEIGHTS)
+    model = bert.BertForSequenceClassification(bert.BertConfig(num_labels=2)).to(dev).train()
+    optimizer = bert.AdamW(model.parameters(), lr=2e-5, eps=1e-8)
+    scheduler = bert.get_linear_schedule_with_warmup(optimizer, num_warmup_steps=0, num_training_steps=10000)
+    net = model
+    if distributed:
+        net = b200net.parallel.DistributedDataParallel(model, device_ids=[dev.index], output_device=dev.index)
+    ids_h, mask_h, lab_h = BO.make_batch(BERT_BATCH, BERT_SEQ, 2000 + rank)
+    ids_h, mask_h, lab_h = ids_h.pin_memory(), mask_h.pin_memory(), lab_h.pin_memory()
+    ids_d, mask_d, lab_d = ids_h.to(dev), mask_h.to(dev), lab_h.to(dev)
+
+    def body(b_input_ids, b_input_mask, b_labels):
+        # pytorch_on_language_distr.py:257-275
+        net.zero_grad()
+        outputs = net(b_input_ids, token_type_ids=None, attention_mask=b_input_mask, labels=b_labels)
+        loss = outputs[0]
+        loss.backward()
+        b200net.utils.clip_grad_norm_(model.parameters(), 1.0)
+        optimizer.step()
+        scheduler.step()
+        return loss
+
+    def step_resident():
+        return body(ids_d, mask_d, lab_d)
+
+    def step_e2e():
+        return body(ids_h.to(dev, non_blocking=True), mask_h.to(dev, non_blocking=True),
+                    lab_h.to(dev, non_blocking=True)).item()
+
+    step_resident()
+    torch.cuda.synchronize()
+    l0 = lib.b200_launch_count()
+    step_resident()
+    launches = lib.b200_launch_count() - l0
+    for _ in range(max(warmup, 3)):
+        step_resident()
+    ms = timed(step_resident, steps)
+    for _ in range(3):
+        step_e2e()
+    e2e_ms = timed(step_e2e, steps)
+    out = {"workload": BERT_WORKLOAD % (BERT_BATCH, BERT_SEQ), "batch_per_gpu": BERT_BATCH, "seq_len": BERT_SEQ,
+           "seq_s": world * BERT_BATCH * steps / (ms * 1e-3), "tokens_s": world * BERT_BATCH * BERT_SEQ * steps / (ms * 1e-3),
+           "ms_per_step": ms / steps,
+           "e2e": {"value": world * BERT_BATCH * steps / (e2e_ms * 1e-3), "unit": "seq/s",
+                   "h2d_bytes_per_step": (ids_h.numel() + mask_h.numel() + lab_h.numel()) * 8, "d2h_bytes_per_step": 4,
+                   "ms_per_step": e2e_ms / steps},
+           "gpu_launches_per_step": int(launches),
+           "tensor_util_step": BERT_GFLOP_PER_SEQ_TRAIN * 1e9 * BERT_BATCH * steps / (ms * 1e-3) / 1e12 / peaks()["tflops"]}
+    if with_roofline:
+        prof_steps = 2
+        torch.cuda.synchronize()
+        lib.b200_gemm_timing_enable(1)
+        for _ in range(prof_steps):
+            step_resident()
+        torch.cuda.synchronize()
+        tms, n, fl = ctypes.c_double(), ctypes.c_int64(), ctypes.c_double()
+        lib.b200_gemm_timing_read(ctypes.byref(tms), ctypes.byref(n), ctypes.byref(fl))
+        lib.b200_gemm_timing_enable(0)
+        pk = peaks()
+        achieved = fl.value / (tms.value * 1e-3) / 1e12
+        out["roofline"] = {"bound": "tensor", "kernel": "conv_sm100_kernel as flat 1x1 (the encoder's Linear layers: "
+                           "fprop / dgrad / wgrad)", "achieved": achieved, "peak": pk["tflops"], "unit": "TFLOP/s",
+                           "frac": achieved / pk["tflops"], "peak_source": pk["src"] + " sustained bf16", "traffic": None,
+                           "launches_per_step": n.value // prof_steps, "kernel_ms_per_step": tms.value / prof_steps,
+                           "gemm_tflop_per_step": fl.value / prof_steps / 1e12}
+    del net, model, optimizer
+    torch.cuda.empty_cache()
+    return out
+
+
+def run_bert_reference(args, rank):
+    if rank != 0:
+        return
+    sps, ms, cores = bert_cpu_reference_run(args.steps, args.warmup, batch=8)
+    sample = ("transformers BertForSequenceClassification + torch.optim.AdamW on stock torch %s CPU fp32 executing "
+              "pytorch_on_language_distr.py:257-275; each step = 8 sequences of the %dx%d workload"
+              % (__import__("torch").__version__, BERT_BATCH, BERT_SEQ))
+    print(json.dumps({
+        "impl": "reference", "metric": "bert_base_train_sequences_per_sec", "value": sps, "unit": "seq/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": BERT_WORKLOAD % (BERT_BATCH, BERT_SEQ), "cpu_sample_batch": 8},
+        "cpu_baseline": {"value": sps, "unit": "seq/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": sps, "unit": "seq/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }), flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -132,6 +255,9 @@ def main():
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--batch", type=int, default=PER_GPU_BATCH)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="resnet", choices=["resnet", "bert"],
+                    help="resnet = the headline line (BASELINE.json metric); bert = a full line for configs[4]")
+    ap.add_argument("--no-bert", action="store_true", help="skip the BERT leg of the default line")
     ap.add_argument("--local_rank", type=int, default=0)     # torch.distributed.launch compatibility
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -139,7 +265,7 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", str(args.local_rank)))
 
     if args.impl == "reference":
-        return run_reference(args, rank)
+        return run_bert_reference(args, rank) if args.workload == "bert" else run_reference(args, rank)
 
     import torch
     import torch.distributed as dist
@@ -156,6 +282,56 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
 
     b200net.set_precision(args.precision)
+
+    def barrier():
+        if distributed:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if distributed:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return ms.item()
+
+    if args.workload == "bert":
+        if args.precision != "bf16":
+            raise SystemExit("bench.py --workload bert: bf16 only")
+        sampler = ClockSampler(local_rank)
+        sampler.start()
+        leg = bert_leg(dev, rank, world, distributed, args.steps, args.warmup, timed, with_roofline=True)
+        clocks = sampler.stop()
+        if rank == 0:
+            out = {"metric": "bert_base_train_sequences_per_sec", "value": leg["seq_s"], "unit": "seq/s",
+                   "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": leg["ms_per_step"],
+                   "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
+                   "data": "synthetic",
+                   "config": {"workload": leg["workload"], "global_batch": world * BERT_BATCH, "seq_len": BERT_SEQ,
+                              "parallelism": "dp%d" % world, "tokens_s": leg["tokens_s"],
+                              "l2": "per-step working set (saved activations ~3 GB, 440 MB of weights) exceeds the "
+                                    "126 MB L2; no explicit flush",
+                              "tensor_util_step": leg["tensor_util_step"]},
+                   "clocks": clocks, "e2e": leg["e2e"], "gpu_launches": leg["gpu_launches_per_step"] * args.steps,
+                   "gpu_launches_per_step": leg["gpu_launches_per_step"], "roofline": leg["roofline"]}
+            if world == 1 and not args.no_cpu_baseline:
+                sps, cms, cores = bert_cpu_reference_run(steps=2, warmup=1, batch=8)
+                out["cpu_baseline"] = {"value": sps, "unit": "seq/s", "cores": cores, "kind": "port",
+                                       "sample": "oracle (transformers + stock torch CPU fp32, the reference's "
+                                                 "train-step statements) on 8 sequences of length %d per step, "
+                                                 "1 warm-up + 2 timed steps" % BERT_SEQ}
+            print(json.dumps(out), flush=True)
+        if distributed:
+            dist.barrier()
+            dist.destroy_process_group()
+        return
+
     torch.manual_seed(O.SEED_WEIGHTS)
     model = b200net.models.resnet50(pretrained=False)
     model.fc = b200net.nn.Sequential(b200net.nn.Linear(2048, 512), b200net.nn.ReLU(), b200net.nn.Dropout(0.2),
@@ -188,24 +364,6 @@ def main():
         loss.backward()
         optimizer.step()
         return loss.item()
-
-    def barrier():
-        if distributed:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def timed(fn, steps):
-        barrier()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for _ in range(steps):
-            fn()
-        e1.record()
-        barrier()
-        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
-        if distributed:
-            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-        return ms.item()
 
     lib = b200net._C.lib
     # kernels per step, counted on one eager step (later steps replay the backbone as CUDA graphs: same kernels,
@@ -273,6 +431,13 @@ def main():
                  "batch1_224px_latency_ms": lat, "tensor_util": 4.1727e9 * 1024 * 10 / (t_inf * 1e-3) / 1e12 / peaks()["tflops"]}
         del xi
 
+    # BERT / IMDB leg (configs[4]): the same reference statements on the second model of the harness
+    bert_out = None
+    if args.precision == "bf16" and not args.no_bert:
+        del x_dev
+        torch.cuda.empty_cache()
+        bert_out = bert_leg(dev, rank, world, distributed, 10, 3, timed, with_roofline=False)
+
     if rank == 0:
         ips = world * B * args.steps / (total_ms * 1e-3)
         e2e_ips = world * B * args.steps / (e2e_ms * 1e-3)
@@ -297,6 +462,8 @@ def main():
             out["roofline"] = roof
         if infer:
             out["infer"] = infer
+        if bert_out:
+            out["bert"] = bert_out
         if world == 1 and not args.no_cpu_baseline:
             cips, cms, cores = cpu_reference_run(steps=5, warmup=2)
             out["cpu_baseline"] = {"value": cips, "unit": UNIT, "cores": cores, "kind": "port",

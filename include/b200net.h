@@ -279,15 +279,17 @@ int32_t b200_attention_bwd(const void* qkv, const void* probs, const void* dctx,
                            int32_t S, int32_t heads, int32_t D, float p_drop, uint64_t seed, uint64_t offset,
                            int32_t dtype, void* stream);
 /* Fused tensor-core attention (bf16 only; S in {128, 256}, D = 64: b200_attention_flash_supported says which
- * shapes qualify, others use the two entry points above).  Nothing of size S*S reaches HBM: forward saves
- * lse [N][heads][S] (log2 units) and backward recomputes the probabilities from it.  dvec: scratch [N][heads][S]. */
+ * shapes qualify, others use the two entry points above).  Nothing of size S*S*2 bytes reaches HBM: forward saves
+ * lse [N][heads][S] (log2 units) and, when p_drop > 0, the dropout keep mask as bits keep_bits [N][heads][S][S/32]
+ * (same Philox indices as above; may be NULL when p_drop == 0); backward recomputes the probabilities.
+ * dvec: scratch [N][heads][S]. */
 int32_t b200_attention_flash_supported(int32_t S, int32_t D);
-int32_t b200_attention_flash_fwd(const void* qkv, const int64_t* mask, float* lse, void* ctx, int32_t N, int32_t S,
-                                 int32_t heads, int32_t D, float p_drop, uint64_t seed, uint64_t offset,
-                                 void* stream);
-int32_t b200_attention_flash_bwd(const void* qkv, const int64_t* mask, const float* lse, const void* ctx,
-                                 const void* dctx, float* dvec, void* dqkv, int32_t N, int32_t S, int32_t heads,
-                                 int32_t D, float p_drop, uint64_t seed, uint64_t offset, void* stream);
+int32_t b200_attention_flash_fwd(const void* qkv, const int64_t* mask, float* lse, uint32_t* keep_bits, void* ctx,
+                                 int32_t N, int32_t S, int32_t heads, int32_t D, float p_drop, uint64_t seed,
+                                 uint64_t offset, void* stream);
+int32_t b200_attention_flash_bwd(const void* qkv, const int64_t* mask, const float* lse, const uint32_t* keep_bits,
+                                 const void* ctx, const void* dctx, float* dvec, void* dqkv, int32_t N, int32_t S,
+                                 int32_t heads, int32_t D, float p_drop, void* stream);
 /* BertPooler: tanh on fp32 [rows][H]; first-token gather (out[n] = x[n*row_stride ..], to fp32) and its scatter */
 int32_t b200_tanh_fwd_f32(const float* x, float* y, int64_t n, void* stream);
 int32_t b200_tanh_bwd_f32(const float* dy, const float* y, float* dx, int64_t n, void* stream);

@@ -95,8 +95,8 @@ SIGNATURES = {
     "b200_attention_fwd": (I32, [P, P, P, P, I32, I32, I32, I32, F, U64, U64, I32, P]),
     "b200_attention_bwd": (I32, [P, P, P, P, P, I32, I32, I32, I32, F, U64, U64, I32, P]),
     "b200_attention_flash_supported": (I32, [I32, I32]),
-    "b200_attention_flash_fwd": (I32, [P, P, P, P, I32, I32, I32, I32, F, U64, U64, P]),
-    "b200_attention_flash_bwd": (I32, [P, P, P, P, P, P, P, I32, I32, I32, I32, F, U64, U64, P]),
+    "b200_attention_flash_fwd": (I32, [P, P, P, P, P, I32, I32, I32, I32, F, U64, U64, P]),
+    "b200_attention_flash_bwd": (I32, [P, P, P, P, P, P, P, P, I32, I32, I32, I32, F, P]),
     "b200_tanh_fwd_f32": (I32, [P, P, I64, P]),
     "b200_tanh_bwd_f32": (I32, [P, P, P, I64, P]),
     "b200_gather_rows": (I32, [P, P, I32, I64, I32, I32, P]),

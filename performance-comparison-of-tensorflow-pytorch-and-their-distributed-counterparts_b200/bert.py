@@ -323,8 +323,7 @@ def _encoder_bwd(model, st, dcls, emit):
         emit(a.output.dense.weight, ops.dense_bwd_weight(dao, ctx))
         dctx = ops.dense_bwd_input(dao, _operand((a.output.dense.weight,), dt), H)
         if st.flash:
-            dqkv = ops.attention_flash_bwd(qkv, st.mask, probs, ctx, dctx, N, S, heads, p_a, seed,
-                                           _site(call, 1 + 3 * li))
+            dqkv = ops.attention_flash_bwd(qkv, st.mask, probs, ctx, dctx, N, S, heads, p_a)
         else:
             dqkv = ops.attention_bwd(qkv, probs, dctx, N, S, heads, p_a, seed, _site(call, 1 + 3 * li))
         dbqkv = ops.colsum_any(dqkv)

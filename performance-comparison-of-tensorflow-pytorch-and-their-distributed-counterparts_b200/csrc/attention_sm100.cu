@@ -16,7 +16,10 @@
 //   forward   : acc = Q_i K^T ; P = exp2(acc*c + keybias - rowmax) ; O = (dropout(P) V) / rowsum ; lse saved
 //   backward Q: acc1 = Q_i K^T, acc2 = dO_i V^T ; dS = P (acc2*drop - D) ; dQ = scale * dS K      (D = rowsum(dO*O))
 //   backward K: acc1 = K_j Q^T, acc2 = V_j dO^T (transposed problem: rows are keys) ; dV = Pd^T dO ; dK = scale dS^T Q
-// The probabilities are never written to HBM: backward recomputes them from the saved log-sum-exp.
+// The probabilities are never written to HBM: backward recomputes them from the saved log-sum-exp.  With dropout the
+// forward also leaves the keep mask as one bit per probability (Philox, same indices as the fp32-arithmetic path);
+// the backward kernels read bits instead of re-running the generator (the key-side kernel would need one Philox
+// call per element, since its rows run across the generator's groups of four).
 #include "common.cuh"
 #include "philox.cuh"
 #include "sm100_ptx.cuh"
@@ -43,6 +46,7 @@ struct AttParams {
   __nv_bfloat16* ctx;             // forward output / backward input [N*S][heads*64]
   const __nv_bfloat16* dctx;
   __nv_bfloat16* dqkv;
+  uint32_t* keep_bits;            // [N][heads][S][S/32] dropout keep mask (bit j of word w = key 32w+j); p > 0 only
 };
 
 template <int MODE>
@@ -52,7 +56,7 @@ __host__ __device__ constexpr int att_tc_smem_bytes(int S) {
   if (MODE == ATT_FWD) bytes = a2 + S * 128;                                              // P | V   (Q,K under P)
   if (MODE == ATT_BWD_Q) bytes = (a2 > 2 * ATC_TILE + S * 128 ? a2 : 2 * ATC_TILE + S * 128) + S * 128;  // dS | K
   if (MODE == ATT_BWD_KV) bytes = 2 * a2 + 2 * S * 128;                                    // PdT dST | Q dO
-  return bytes + 2 * S * 4 + 64 + 1024;
+  return bytes + 2 * S * 4 + (MODE == ATT_BWD_KV ? S * 16 : 0) + 64 + 1024;
 }
 
 __device__ __forceinline__ void att_store_chunk32(uint8_t* tile_base, int row, int chunk32, const float (&v)[32]) {
@@ -128,7 +132,8 @@ att_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__
   }
   float* vecA = reinterpret_cast<float*>(tail);         // fwd / bwd_q: key bias [S]; bwd_kv: lse [S]
   float* vecB = vecA + S;                               // bwd_kv: D [S]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(vecB + S);   // [0] loads, [1] MMA 1, [2] MMA 2
+  uint32_t* bitsT = reinterpret_cast<uint32_t*>(vecB + S);  // bwd_kv: keep words [S queries][4] of this key tile
+  uint64_t* bars = reinterpret_cast<uint64_t*>(bitsT + (MODE == ATT_BWD_KV ? S * 4 : 0));   // loads, MMA 1, MMA 2
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3);
 
   const uint32_t tmem_cols = MODE == ATT_FWD ? (uint32_t)S : (uint32_t)(2 * S);
@@ -189,6 +194,9 @@ att_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__
       vecB[i] = P.dvec[vrow + i];
     }
     row_bias = (P.mask != nullptr && P.mask[(long long)n * S + row] == 0) ? ATC_MASKED : 0.f;
+    if (P.p > 0.f)
+      for (int i = tid; i < S * 4; i += ATC_ROWS)
+        bitsT[i] = P.keep_bits[(vrow + (i >> 2)) * (S / 32) + (r0 >> 5) + (i & 3)];
   } else {
     for (int i = tid; i < S; i += ATC_ROWS)
       vecA[i] = (P.mask != nullptr && P.mask[(long long)n * S + i] == 0) ? ATC_MASKED : 0.f;
@@ -266,40 +274,39 @@ att_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__
         rsum += v[j];
       }
       if (drop) {
+        uint32_t word = 0u;
 #pragma unroll
         for (int g = 0; g < 8; ++g) {
           float mk[4];
           dropout_scale4(P.seed, P.offset, pbase + ch * 32 + g * 4, P.p, 1.f, mk);
 #pragma unroll
-          for (int e = 0; e < 4; ++e) v[g * 4 + e] *= mk[e];
+          for (int e = 0; e < 4; ++e) {
+            v[g * 4 + e] *= mk[e];
+            word |= (mk[e] != 0.f ? 1u : 0u) << (g * 4 + e);
+          }
         }
+        P.keep_bits[(vrow + row) * (S / 32) + ch] = word;   // the backward kernels read the mask instead of Philox
       }
       att_store_chunk32(smA2a + (ch >> 1) * ATC_TILE, tid, ch & 1, v);
     }
   } else if (MODE == ATT_BWD_Q) {
-    const long long pbase = (pbase_head + row) * S;
     for (int ch = 0; ch < S / 32; ++ch) {
       uint32_t r[32], d[32];
       tmem_ld_32x32b_x32(trow + ch * 32, r);
       tmem_ld_32x32b_x32(trow + S + ch * 32, d);
       tmem_ld_wait();
       float v[32];
+      const uint32_t word = drop ? P.keep_bits[(vrow + row) * (S / 32) + ch] : 0xFFFFFFFFu;
 #pragma unroll
-      for (int g = 0; g < 8; ++g) {
-        float mk[4] = {1.f, 1.f, 1.f, 1.f};
-        if (drop) dropout_scale4(P.seed, P.offset, pbase + ch * 32 + g * 4, P.p, P.inv_keep, mk);
-#pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          const int j = g * 4 + e;
-          const float pv = exp2f(fmaf(__uint_as_float(r[j]), P.c, vecA[ch * 32 + j]) - row_lse);
-          v[j] = pv * (__uint_as_float(d[j]) * mk[e] - row_D);
-        }
+      for (int j = 0; j < 32; ++j) {
+        const float keep = ((word >> j) & 1u) ? P.inv_keep : 0.f;
+        const float pv = exp2f(fmaf(__uint_as_float(r[j]), P.c, vecA[ch * 32 + j]) - row_lse);
+        v[j] = pv * (__uint_as_float(d[j]) * keep - row_D);
       }
       att_store_chunk32(smA2a + (ch >> 1) * ATC_TILE, tid, ch & 1, v);
     }
   } else {
-    // rows are keys, columns are queries: the Philox group of (q, key) is the key's group of four in row q
-    const int kq = row & ~3, ke = row & 3;
+    // rows are keys, columns are queries: bit `lane` of keep word [q][warp] is this key's mask in query row q
     for (int ch = 0; ch < S / 32; ++ch) {
       uint32_t r[32], d[32];
       tmem_ld_32x32b_x32(trow + ch * 32, r);
@@ -310,11 +317,7 @@ att_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__
       for (int j = 0; j < 32; ++j) {
         const int q = ch * 32 + j;
         float keep = 1.f;
-        if (drop) {
-          float mk[4];
-          dropout_scale4(P.seed, P.offset, (pbase_head + q) * S + kq, P.p, P.inv_keep, mk);
-          keep = ke == 0 ? mk[0] : (ke == 1 ? mk[1] : (ke == 2 ? mk[2] : mk[3]));
-        }
+        if (drop) keep = ((bitsT[q * 4 + warp] >> (tid & 31)) & 1u) ? P.inv_keep : 0.f;
         const float pv = exp2f(fmaf(__uint_as_float(r[j]), P.c, row_bias) - vecA[q]);
         pd[j] = pv * keep;
         ds[j] = pv * (__uint_as_float(d[j]) * keep - vecB[q]);
@@ -386,10 +389,11 @@ extern "C" {
 
 int32_t b200_attention_flash_supported(int32_t S, int32_t D) { return att_tc_supported(S, D) ? 1 : 0; }
 
-int32_t b200_attention_flash_fwd(const void* qkv, const int64_t* mask, float* lse, void* ctx, int32_t N, int32_t S,
-                                 int32_t heads, int32_t D, float p_drop, uint64_t seed, uint64_t offset,
-                                 void* stream) {
-  if (!qkv || !lse || !ctx || N <= 0 || heads <= 0) return fail(B200_INVALID_ARG, "attention_flash_fwd: bad argument");
+int32_t b200_attention_flash_fwd(const void* qkv, const int64_t* mask, float* lse, uint32_t* keep_bits, void* ctx,
+                                 int32_t N, int32_t S, int32_t heads, int32_t D, float p_drop, uint64_t seed,
+                                 uint64_t offset, void* stream) {
+  if (!qkv || !lse || !ctx || N <= 0 || heads <= 0 || (p_drop > 0.f && !keep_bits))
+    return fail(B200_INVALID_ARG, "attention_flash_fwd: bad argument");
   if (!att_tc_supported(S, D) || p_drop < 0.f || p_drop >= 1.f)
     return fail(B200_UNSUPPORTED, "attention_flash_fwd: needs head dim 64 and S in {128, 256} (got D=%d S=%d)", D, S);
   CUtensorMap tq;
@@ -398,14 +402,14 @@ int32_t b200_attention_flash_fwd(const void* qkv, const int64_t* mask, float* ls
   AttParams P{};
   P.S = S; P.heads = heads; P.scale = 0.125f; P.c = 0.125f * 1.4426950408889634f;
   P.p = p_drop; P.inv_keep = p_drop > 0.f ? 1.f / (1.f - p_drop) : 1.f; P.seed = seed; P.offset = offset;
-  P.mask = (const long long*)mask; P.lse = lse; P.ctx = (__nv_bfloat16*)ctx;
+  P.mask = (const long long*)mask; P.lse = lse; P.ctx = (__nv_bfloat16*)ctx; P.keep_bits = keep_bits;
   return att_tc_launch<ATT_FWD>(tq, tq, P, N, as_stream(stream));
 }
 
-int32_t b200_attention_flash_bwd(const void* qkv, const int64_t* mask, const float* lse, const void* ctx,
-                                 const void* dctx, float* dvec, void* dqkv, int32_t N, int32_t S, int32_t heads,
-                                 int32_t D, float p_drop, uint64_t seed, uint64_t offset, void* stream) {
-  if (!qkv || !lse || !ctx || !dctx || !dvec || !dqkv || N <= 0 || heads <= 0)
+int32_t b200_attention_flash_bwd(const void* qkv, const int64_t* mask, const float* lse, const uint32_t* keep_bits,
+                                 const void* ctx, const void* dctx, float* dvec, void* dqkv, int32_t N, int32_t S,
+                                 int32_t heads, int32_t D, float p_drop, void* stream) {
+  if (!qkv || !lse || !ctx || !dctx || !dvec || !dqkv || N <= 0 || heads <= 0 || (p_drop > 0.f && !keep_bits))
     return fail(B200_INVALID_ARG, "attention_flash_bwd: bad argument");
   if (!att_tc_supported(S, D) || p_drop < 0.f || p_drop >= 1.f)
     return fail(B200_UNSUPPORTED, "attention_flash_bwd: needs head dim 64 and S in {128, 256} (got D=%d S=%d)", D, S);
@@ -416,7 +420,8 @@ int32_t b200_attention_flash_bwd(const void* qkv, const int64_t* mask, const flo
   if (rc) return fail(B200_CUDA_ERROR, "attention_flash_bwd: tensor map failed (%d)", rc);
   AttParams P{};
   P.S = S; P.heads = heads; P.scale = 0.125f; P.c = 0.125f * 1.4426950408889634f;
-  P.p = p_drop; P.inv_keep = p_drop > 0.f ? 1.f / (1.f - p_drop) : 1.f; P.seed = seed; P.offset = offset;
+  P.p = p_drop; P.inv_keep = p_drop > 0.f ? 1.f / (1.f - p_drop) : 1.f;
+  P.keep_bits = const_cast<uint32_t*>(keep_bits);
   P.mask = (const long long*)mask; P.lse = const_cast<float*>(lse); P.dvec = dvec;
   P.ctx = (__nv_bfloat16*)const_cast<void*>(ctx); P.dctx = (const __nv_bfloat16*)dctx; P.dqkv = (__nv_bfloat16*)dqkv;
   int32_t r = att_tc_launch<ATT_BWD_Q>(tq, tdo, P, N, as_stream(stream));

@@ -60,16 +60,6 @@ ln_fwd_kernel(const T* __restrict__ x, const T* __restrict__ res, T* sum_out, T*
   const int lane = threadIdx.x & 31;
   const long long warp = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
   const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
-  float g[NV][W], b[NV][W];
-#pragma unroll
-  for (int i = 0; i < NV; ++i) {
-    const int col = (lane + 32 * i) * W;
-#pragma unroll
-    for (int e = 0; e < W; ++e) {
-      g[i][e] = gamma[col + e];
-      b[i][e] = beta[col + e];
-    }
-  }
   for (long long row = warp; row < rows; row += nwarps) {
     float v[NV][W];
 #pragma unroll
@@ -100,10 +90,11 @@ ln_fwd_kernel(const T* __restrict__ x, const T* __restrict__ res, T* sum_out, T*
     }
 #pragma unroll
     for (int i = 0; i < NV; ++i) {
+      const int col = (lane + 32 * i) * W;
       float o_[W];
 #pragma unroll
-      for (int e = 0; e < W; ++e) o_[e] = (v[i][e] - mean) * rstd * g[i][e] + b[i][e];
-      store_vec(y + row * H + (lane + 32 * i) * W, o_);
+      for (int e = 0; e < W; ++e) o_[e] = (v[i][e] - mean) * rstd * __ldg(gamma + col + e) + __ldg(beta + col + e);
+      store_vec(y + row * H + col, o_);
     }
   }
 }
@@ -176,121 +167,137 @@ embed_ln_fwd_kernel(const long long* __restrict__ ids, const long long* __restri
 // dres = ds ; dx = ds * dropout mask (the branch that went through dropout; same buffer as dres when p == 0)
 // per-block partial column sums: [block][3][H] = (sum dy*xhat, sum dy, sum dx)  -> dgamma, dbeta, bias grad of the
 // Linear that produced x.  Lanes own the same columns for every row, so the sums accumulate in registers.
-template <typename T, int NV>
-__global__ void __launch_bounds__(256)
+// One row is spread over TPR = H / (16-byte vector) threads (3 warps at H = 768 bf16), G rows per block: every thread
+// keeps only its own vector's three column accumulators, so the kernel stays at ~60 registers and ~24 warps per SM.
+// The two row sums cross warps through shared memory and one named barrier per row (slots alternate between rows).
+template <typename T, int TPR, int G>
+__global__ void __launch_bounds__(TPR * G)
 ln_bwd_kernel(const T* __restrict__ dy_a, const T* __restrict__ dy_b, const T* __restrict__ s,
               const float* __restrict__ mean_in, const float* __restrict__ rstd_in, const float* __restrict__ gamma,
               T* __restrict__ dres, T* __restrict__ dx, float* __restrict__ partials, long long rows, float p,
               float inv_keep, uint64_t seed, uint64_t offset, int drop_after) {
   constexpr int W = VecTraits<T>::W;
-  constexpr int H = NV * 32 * W;
-  extern __shared__ float red[];  // [3][H]
-  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, nwib = blockDim.x >> 5;
-  const long long warp = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
-  const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
-  float gm[NV][W], ag[NV][W], ab[NV][W], ad[NV][W];
+  constexpr int H = TPR * W;
+  constexpr int WPR = TPR / 32;
+  __shared__ float red[G][2][WPR][2];
+  __shared__ float fin[3 * H];
+  const int grp = threadIdx.x / TPR, t = threadIdx.x % TPR, lane = threadIdx.x & 31, wr = t >> 5;
+  const int col = t * W;
+  float gm[W], ag[W], ab[W], ad[W];
 #pragma unroll
-  for (int i = 0; i < NV; ++i)
-#pragma unroll
-    for (int e = 0; e < W; ++e) {
-      gm[i][e] = gamma[(lane + 32 * i) * W + e];
-      ag[i][e] = ab[i][e] = ad[i][e] = 0.f;
-    }
-  for (long long row = warp; row < rows; row += nwarps) {
+  for (int e = 0; e < W; ++e) {
+    gm[e] = gamma[col + e];
+    ag[e] = ab[e] = ad[e] = 0.f;
+  }
+  int it = 0;
+  for (long long row = (long long)blockIdx.x * G + grp; row < rows; row += (long long)gridDim.x * G, ++it) {
     const float mean = mean_in[row], rstd = rstd_in[row];
-    float d[NV][W], xh[NV][W];
+    const long long o = row * H + col;
+    float d[W], xh[W];
+    load_vec(dy_a + o, d);
+    if (dy_b != nullptr) {
+      float tb[W];
+      load_vec(dy_b + o, tb);
+#pragma unroll
+      for (int e = 0; e < W; ++e) d[e] += tb[e];
+    }
+    load_vec(s + o, xh);
+    if (drop_after && p > 0.f) {
+      float m[W];
+      dropout_scale_vec<W>(seed, offset, o, p, inv_keep, m);
+#pragma unroll
+      for (int e = 0; e < W; ++e) d[e] *= m[e];
+    }
     float c1 = 0.f, c2 = 0.f;
 #pragma unroll
-    for (int i = 0; i < NV; ++i) {
-      const long long o = row * H + (lane + 32 * i) * W;
-      load_vec(dy_a + o, d[i]);
-      if (dy_b != nullptr) {
-        float t[W];
-        load_vec(dy_b + o, t);
+    for (int e = 0; e < W; ++e) {
+      xh[e] = (xh[e] - mean) * rstd;
+      ab[e] += d[e];
+      ag[e] += d[e] * xh[e];
+      d[e] *= gm[e];
+      c1 += d[e];
+      c2 += d[e] * xh[e];
+    }
+    c1 = warp_sum(c1);
+    c2 = warp_sum(c2);
+    float (*slot)[2] = red[grp][it & 1];
+    if (lane == 0) {
+      slot[wr][0] = c1;
+      slot[wr][1] = c2;
+    }
+    asm volatile("bar.sync %0, %1;" ::"r"(grp + 1), "n"(TPR) : "memory");
+    c1 = 0.f;
+    c2 = 0.f;
 #pragma unroll
-        for (int e = 0; e < W; ++e) d[i][e] += t[e];
-      }
-      if (drop_after && p > 0.f) {
+    for (int w = 0; w < WPR; ++w) {
+      c1 += slot[w][0];
+      c2 += slot[w][1];
+    }
+    c1 *= 1.f / (float)H;
+    c2 *= 1.f / (float)H;
+#pragma unroll
+    for (int e = 0; e < W; ++e) d[e] = rstd * (d[e] - c1 - xh[e] * c2);
+    store_vec(dres + o, d);
+    if (!drop_after) {
+      if (p > 0.f) {
         float m[W];
         dropout_scale_vec<W>(seed, offset, o, p, inv_keep, m);
 #pragma unroll
-        for (int e = 0; e < W; ++e) d[i][e] *= m[e];
+        for (int e = 0; e < W; ++e) d[e] *= m[e];
+        store_vec(dx + o, d);
       }
-      load_vec(s + o, xh[i]);
 #pragma unroll
-      for (int e = 0; e < W; ++e) {
-        xh[i][e] = (xh[i][e] - mean) * rstd;
-        ab[i][e] += d[i][e];
-        ag[i][e] += d[i][e] * xh[i][e];
-        d[i][e] *= gm[i][e];
-        c1 += d[i][e];
-        c2 += d[i][e] * xh[i][e];
-      }
-    }
-    c1 = warp_sum(c1) / (float)H;
-    c2 = warp_sum(c2) / (float)H;
-#pragma unroll
-    for (int i = 0; i < NV; ++i) {
-      const long long o = row * H + (lane + 32 * i) * W;
-#pragma unroll
-      for (int e = 0; e < W; ++e) d[i][e] = rstd * (d[i][e] - c1 - xh[i][e] * c2);
-      store_vec(dres + o, d[i]);
-      if (!drop_after) {
-        if (p > 0.f) {
-          float m[W];
-          dropout_scale_vec<W>(seed, offset, o, p, inv_keep, m);
-#pragma unroll
-          for (int e = 0; e < W; ++e) d[i][e] *= m[e];
-          store_vec(dx + o, d[i]);
-        }
-#pragma unroll
-        for (int e = 0; e < W; ++e) ad[i][e] += round_to<T>(d[i][e]);
-      }
+      for (int e = 0; e < W; ++e) ad[e] += round_to<T>(d[e]);
     }
   }
-  // deterministic cross-warp sum: warps add into shared memory one after the other
-  for (int w = 0; w < nwib; ++w) {
-    if (wib == w) {
+  // deterministic cross-group sum: the row groups add into shared memory one after the other
+  for (int g = 0; g < G; ++g) {
+    if (grp == g) {
 #pragma unroll
-      for (int i = 0; i < NV; ++i)
-#pragma unroll
-        for (int e = 0; e < W; ++e) {
-          const int col = (lane + 32 * i) * W + e;
-          if (w == 0) {
-            red[col] = ag[i][e];
-            red[H + col] = ab[i][e];
-            red[2 * H + col] = ad[i][e];
-          } else {
-            red[col] += ag[i][e];
-            red[H + col] += ab[i][e];
-            red[2 * H + col] += ad[i][e];
-          }
+      for (int e = 0; e < W; ++e) {
+        if (g == 0) {
+          fin[col + e] = ag[e];
+          fin[H + col + e] = ab[e];
+          fin[2 * H + col + e] = ad[e];
+        } else {
+          fin[col + e] += ag[e];
+          fin[H + col + e] += ab[e];
+          fin[2 * H + col + e] += ad[e];
         }
+      }
     }
     __syncthreads();
   }
   float* out = partials + (long long)blockIdx.x * 3 * H;
-  for (int i = threadIdx.x; i < 3 * H; i += blockDim.x) out[i] = red[i];
+  for (int i = threadIdx.x; i < 3 * H; i += TPR * G) out[i] = fin[i];
 }
 
 // out[c] = sum_b part[b][c]   (fixed order: deterministic)
-__global__ void sum_partials_kernel(const float* __restrict__ part, int nparts, int cols, float* __restrict__ o0,
-                                    float* __restrict__ o1, float* __restrict__ o2, int H) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= cols) return;
-  float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-  int b = 0;
-  for (; b + 4 <= nparts; b += 4) {
-    a0 += part[(long long)b * cols + c];
-    a1 += part[(long long)(b + 1) * cols + c];
-    a2 += part[(long long)(b + 2) * cols + c];
-    a3 += part[(long long)(b + 3) * cols + c];
+__global__ void __launch_bounds__(256)
+sum_partials_kernel(const float* __restrict__ part, int nparts, int cols, float* __restrict__ o0,
+                    float* __restrict__ o1, float* __restrict__ o2, int H) {
+  __shared__ float red[8][33];
+  const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + cx;
+  float a0 = 0.f, a1 = 0.f;
+  if (c < cols) {
+    int b = ry;
+    for (; b + 8 < nparts; b += 16) {
+      a0 += part[(long long)b * cols + c];
+      a1 += part[(long long)(b + 8) * cols + c];
+    }
+    if (b < nparts) a0 += part[(long long)b * cols + c];
   }
-  for (; b < nparts; ++b) a0 += part[(long long)b * cols + c];
-  const float v = (a0 + a1) + (a2 + a3);
-  // cols = 3*H laid out [3][H] (LayerNorm backward) or a single vector (H == cols, o1 == o2 == NULL)
-  float* dst = c < H ? o0 : (c < 2 * H ? o1 : o2);
-  if (dst != nullptr) dst[c % H] = v;
+  red[ry][cx] = a0 + a1;
+  __syncthreads();
+  if (ry == 0 && c < cols) {
+    float v = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v += red[j][cx];
+    // cols = 3*H laid out [3][H] (LayerNorm backward) or a single vector (H == cols, o1 == o2 == NULL)
+    float* dst = c < H ? o0 : (c < 2 * H ? o1 : o2);
+    if (dst != nullptr) dst[c % H] = v;
+  }
 }
 
 // ---------------------------------------------------------------- embedding backward
@@ -447,7 +454,7 @@ static inline int ew_grid(long long n, int threads) {
   return (int)(want < cap ? (want < 1 ? 1 : want) : cap);
 }
 constexpr int LN_BWD_BLOCKS_PER_SM = 2;
-static inline int ln_bwd_grid(long long rows) { return row_grid(rows, 8, LN_BWD_BLOCKS_PER_SM); }
+static inline int ln_bwd_grid(long long rows) { return row_grid(rows, 2, LN_BWD_BLOCKS_PER_SM); }
 static inline int ln_nv(int H, int W) { return (H % (32 * W) == 0) ? H / (32 * W) : 0; }
 
 }  // namespace b200
@@ -496,13 +503,27 @@ static int32_t ln_bwd_t(const T* dy_a, const T* dy_b, const T* s, const float* m
                         const float* gamma, long long rows, int H, float p, uint64_t seed, uint64_t offset,
                         int drop_after, T* dres, T* dx, float* dgamma, float* dbeta, float* dbias, float* ws,
                         cudaStream_t st) {
-  const int nv = ln_nv(H, VecTraits<T>::W);
+  constexpr int W = VecTraits<T>::W;
+  const int tpr = (H % (32 * W) == 0) ? H / W : 0;
   const float ik = p > 0.f ? 1.f / (1.f - p) : 1.f;
   const int grid = ln_bwd_grid(rows);
-  const size_t smem = (size_t)3 * H * sizeof(float);
-  B200_LN_DISPATCH_NV(nv, (ln_bwd_kernel<T, NV><<<grid, 256, smem, st>>>(dy_a, dy_b, s, mean, rstd, gamma, dres, dx, ws,
-                                                                       rows, p, ik, seed, offset, drop_after)));
-  sum_partials_kernel<<<(3 * H + 255) / 256, 256, 0, st>>>(ws, grid, 3 * H, dgamma, dbeta, dbias, H);
+#define B200_LN_BWD_CASE(TPR_, G_)                                                                              \
+  case TPR_:                                                                                                     \
+    ln_bwd_kernel<T, TPR_, G_><<<grid, TPR_ * G_, 0, st>>>(dy_a, dy_b, s, mean, rstd, gamma, dres, dx, ws, rows, p, \
+                                                         ik, seed, offset, drop_after);                          \
+    break;
+  switch (tpr) {
+    B200_LN_BWD_CASE(32, 8)
+    B200_LN_BWD_CASE(64, 8)
+    B200_LN_BWD_CASE(96, 4)
+    B200_LN_BWD_CASE(128, 4)
+    B200_LN_BWD_CASE(192, 2)
+    B200_LN_BWD_CASE(256, 2)
+    default:
+      return fail(B200_UNSUPPORTED, "layernorm backward: hidden size %d not supported", H);
+  }
+#undef B200_LN_BWD_CASE
+  sum_partials_kernel<<<(3 * H + 31) / 32, 256, 0, st>>>(ws, grid, 3 * H, dgamma, dbeta, dbias, H);
   return check_launch("ln_bwd", 2);
 }
 
@@ -517,7 +538,7 @@ static int32_t colsum_t(const T* x, float* out, long long rows, int cols, float*
   if ((long long)chunks * cols > ws_floats) return fail(B200_WORKSPACE_TOO_SMALL, "colsum: workspace too small");
   const long long rpc = (rows + chunks - 1) / chunks;
   colsum_partial_kernel<T><<<dim3(cblocks, chunks), 256, 0, st>>>(x, ws, rows, cols, rpc);
-  sum_partials_kernel<<<(cols + 255) / 256, 256, 0, st>>>(ws, chunks, cols, out, nullptr, nullptr, cols);
+  sum_partials_kernel<<<(cols + 31) / 32, 256, 0, st>>>(ws, chunks, cols, out, nullptr, nullptr, cols);
   return check_launch("colsum", 2);
 }
 

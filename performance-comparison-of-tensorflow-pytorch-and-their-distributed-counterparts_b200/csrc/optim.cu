@@ -61,21 +61,39 @@ __global__ void __launch_bounds__(MT_THREADS) mt_adam_kernel(MtArgs t, AdamHyper
   }
 }
 
-__global__ void __launch_bounds__(MT_THREADS) mt_sumsq_kernel(MtArgs t, float* __restrict__ partial, int base) {
+// Sum of squares, flat work split: block b handles one chunk of `chunk` elements of the tensor whose cumulative
+// chunk range contains b (t.b[i] carries the first chunk index of tensor i), so one 23M-element embedding table and a
+// hundred 768-element vectors spread evenly over the SMs.  Eight independent 16-byte loads per thread.
+__global__ void __launch_bounds__(MT_THREADS) mt_sumsq_kernel(MtArgs t, int cnt, long long chunk,
+                                                              float* __restrict__ partial, int base) {
   __shared__ float red[MT_THREADS / 32];
-  const int ti = blockIdx.y;
+  int ti = 0;
+  while (ti + 1 < cnt && (long long)(intptr_t)t.b[ti + 1] <= (long long)blockIdx.x) ++ti;
   const float* __restrict__ x = (const float*)t.a[ti];
   const long long n = t.n[ti];
-  float s = 0.f;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
-    s = fmaf(x[i], x[i], s);
-  s = warp_sum(s);
+  const long long lo = ((long long)blockIdx.x - (long long)(intptr_t)t.b[ti]) * chunk;
+  const long long hi = lo + chunk < n ? lo + chunk : n;
+  float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+  if ((reinterpret_cast<uintptr_t>(x) & 15) == 0) {
+    const long long v0 = lo >> 2, v1 = hi >> 2;    // lo is a multiple of chunk (a multiple of 4)
+    for (long long i = v0 + threadIdx.x; i < v1; i += MT_THREADS) {
+      const float4 v = reinterpret_cast<const float4*>(x)[i];
+      s0 = fmaf(v.x, v.x, s0);
+      s1 = fmaf(v.y, v.y, s1);
+      s2 = fmaf(v.z, v.z, s2);
+      s3 = fmaf(v.w, v.w, s3);
+    }
+    for (long long i = (v1 << 2) + threadIdx.x; i < hi; i += MT_THREADS) s0 = fmaf(x[i], x[i], s0);
+  } else {
+    for (long long i = lo + threadIdx.x; i < hi; i += MT_THREADS) s0 = fmaf(x[i], x[i], s0);
+  }
+  float s = warp_sum((s0 + s1) + (s2 + s3));
   if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
   __syncthreads();
   if (threadIdx.x < 32) {
     float v = threadIdx.x < MT_THREADS / 32 ? red[threadIdx.x] : 0.f;
     v = warp_sum(v);
-    if (threadIdx.x == 0) partial[base + ti * gridDim.x + blockIdx.x] = v;
+    if (threadIdx.x == 0) partial[base + blockIdx.x] = v;
   }
 }
 __global__ void sum_partials_kernel(const float* __restrict__ partial, int count, float* __restrict__ out) {
@@ -181,22 +199,35 @@ extern "C" int32_t b200_multi_tensor_adam(int32_t n, float* const* params, const
   return check_launch("multi_tensor_adam", nlaunch);
 }
 
-constexpr int L2_BLOCKS = 32;
 constexpr int L2_MAX_PARTIALS = 16384;
+constexpr long long L2_CHUNK = 8192;     // elements per block at least (32 per thread)
 extern "C" int64_t b200_l2norm_workspace_bytes(void) { return (int64_t)L2_MAX_PARTIALS * 4; }
 
 extern "C" int32_t b200_multi_tensor_l2norm_sq(int32_t n, const float* const* tensors, const int64_t* sizes, float* out,
                                                void* ws, int64_t ws_bytes, void* stream) {
   if (n <= 0 || !tensors || !sizes || !out) return fail(B200_INVALID_ARG, "l2norm: bad arguments");
   if (!ws || ws_bytes < b200_l2norm_workspace_bytes()) return fail(B200_WORKSPACE_TOO_SMALL, "l2norm: workspace too small");
-  if ((long long)n * L2_BLOCKS > L2_MAX_PARTIALS) return fail(B200_UNSUPPORTED, "l2norm: more than %d tensors", L2_MAX_PARTIALS / L2_BLOCKS);
+  if (n > L2_MAX_PARTIALS / 2) return fail(B200_UNSUPPORTED, "l2norm: more than %d tensors", L2_MAX_PARTIALS / 2);
+  // chunk size: at most L2_MAX_PARTIALS partial sums in total (every tensor needs at least one)
+  long long total = 0;
+  for (int i = 0; i < n; ++i) total += sizes[i];
+  long long chunk = L2_CHUNK;
+  while (total / chunk + n > L2_MAX_PARTIALS) chunk *= 2;
   cudaStream_t st = as_stream(stream);
   int base = 0;
   int nlaunch = 0;
   MT_FOREACH_CHUNK(n, {
-    for (int i = 0; i < cnt; ++i) { t.a[i] = (void*)tensors[lo + i]; t.b[i] = t.c[i] = t.d[i] = nullptr; t.n[i] = sizes[lo + i]; }
-    mt_sumsq_kernel<<<dim3(L2_BLOCKS, cnt), MT_THREADS, 0, st>>>(t, (float*)ws, base);
-    base += cnt * L2_BLOCKS;
+    long long cum = 0;
+    for (int i = 0; i < cnt; ++i) {
+      t.a[i] = (void*)tensors[lo + i];
+      t.b[i] = (void*)(intptr_t)cum;
+      t.c[i] = t.d[i] = nullptr;
+      t.n[i] = sizes[lo + i];
+      const long long c = (sizes[lo + i] + chunk - 1) / chunk;
+      cum += c < 1 ? 1 : c;
+    }
+    mt_sumsq_kernel<<<(unsigned)cum, MT_THREADS, 0, st>>>(t, cnt, chunk, (float*)ws, base);
+    base += (int)cum;
   })
   sum_partials_kernel<<<1, 1024, 0, st>>>((const float*)ws, base, out);
   return check_launch("multi_tensor_l2norm_sq", nlaunch + 1);

@@ -521,21 +521,24 @@ def attention_flash_ok(dtype, S, D=64):
 
 
 def attention_flash_fwd(qkv, mask, N, S, heads, p=0.0, seed=0, offset=0):
-    """Fused tcgen05 attention: returns (lse [N,heads,S] fp32, ctx [N*S][heads*64]); no S x S tensor is stored."""
+    """Fused tcgen05 attention: returns ((lse [N,heads,S] fp32, keep bits or None), ctx [N*S][heads*64]); no S x S
+    tensor of probabilities is stored."""
     D = qkv.shape[1] // (3 * heads)
     lse = torch.empty((N, heads, S), dtype=torch.float32, device=qkv.device)
+    bits = torch.empty((N, heads, S, S // 32), dtype=torch.int32, device=qkv.device) if p > 0.0 else None
     ctx = torch.empty((N * S, heads * D), dtype=qkv.dtype, device=qkv.device)
-    check(lib.b200_attention_flash_fwd(qkv.data_ptr(), _p(mask), lse.data_ptr(), ctx.data_ptr(), N, S, heads, D,
-                                       float(p), seed, offset, _stream()), "attention_flash_fwd")
-    return lse, ctx
+    check(lib.b200_attention_flash_fwd(qkv.data_ptr(), _p(mask), lse.data_ptr(), _p(bits), ctx.data_ptr(), N, S,
+                                       heads, D, float(p), seed, offset, _stream()), "attention_flash_fwd")
+    return (lse, bits), ctx
 
 
-def attention_flash_bwd(qkv, mask, lse, ctx, dctx, N, S, heads, p=0.0, seed=0, offset=0):
+def attention_flash_bwd(qkv, mask, saved, ctx, dctx, N, S, heads, p=0.0):
+    lse, bits = saved
     D = qkv.shape[1] // (3 * heads)
     dqkv = torch.empty_like(qkv)
     dvec = torch.empty_like(lse)
-    check(lib.b200_attention_flash_bwd(qkv.data_ptr(), _p(mask), lse.data_ptr(), ctx.data_ptr(), dctx.data_ptr(),
-                                       dvec.data_ptr(), dqkv.data_ptr(), N, S, heads, D, float(p), seed, offset,
+    check(lib.b200_attention_flash_bwd(qkv.data_ptr(), _p(mask), lse.data_ptr(), _p(bits), ctx.data_ptr(),
+                                       dctx.data_ptr(), dvec.data_ptr(), dqkv.data_ptr(), N, S, heads, D, float(p),
                                        _stream()), "attention_flash_bwd")
     return dqkv
 

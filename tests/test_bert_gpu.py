@@ -249,7 +249,7 @@ def test_attention_flash_matches_reference_path(N, S, heads, p):
     lse, ctx = ops.attention_flash_fwd(qkv, mask, N, S, heads, p, seed, off)
     probs, ctx_ref = ops.attention_fwd(qkv, mask, N, S, heads, p, seed, off)
     assert _rel(ctx, ctx_ref) < 2e-2
-    dq = ops.attention_flash_bwd(qkv, mask, lse, ctx, dctx, N, S, heads, p, seed, off)
+    dq = ops.attention_flash_bwd(qkv, mask, lse, ctx, dctx, N, S, heads, p)
     dq_ref = ops.attention_bwd(qkv, probs, dctx, N, S, heads, p, seed, off)
     for j, name in enumerate("qkv"):
         a = dq.reshape(N * S, 3, heads * 64)[:, j]
