@@ -234,6 +234,12 @@ int32_t b200_bucket_unpack(int32_t n, float* const* dsts, const int64_t* sizes, 
  * Dropout masks are never stored: forward and backward derive them from (seed, offset, flat element index) with
  * Philox4x32-10, so the same (seed, offset) must be passed to the matching backward call. */
 
+/* Dropout under CUDA-graph replay: offsets passed by value are frozen into a captured graph.  While a device
+ * pointer is registered here (per calling thread; NULL clears it), every dropout site launched from this thread
+ * adds (*device_counter) << 40 to its offset when the kernel EXECUTES, so bumping the counter before a replay gives
+ * the replayed step fresh masks (and forward / backward graphs of one step agree with each other). */
+int32_t b200_dropout_counter(const uint64_t* device_counter);
+
 /* BertEmbeddings: s = (word[ids] + type[type_ids]) + pos[0..S) ; y = dropout(LayerNorm(s)).  type_ids may be NULL
  * (token_type_ids=None at :259 = all zeros).  sum_out receives s (saved for the backward), *status is set to 1 if an
  * id is outside [0, vocab) (torch raises a device-side assert there). */
@@ -264,6 +270,10 @@ int32_t b200_ln_bwd(const void* dy_a, const void* dy_b, const void* sum, const f
 /* BertIntermediate activation: erf-GELU (hidden_act = "gelu") and its derivative; n % (16 bytes / element) == 0 */
 int32_t b200_gelu_fwd(const void* x, void* y, int64_t n, int32_t dtype, void* stream);
 int32_t b200_gelu_bwd(const void* dy, const void* x, void* dx, int64_t n, int32_t dtype, void* stream);
+/* gelu_bwd fused with the bias gradient of the Linear in front of it: dx = dy * gelu'(x) on [rows][cols] and
+ * dbias[cols] = column sums of dx, one pass.  ws: b200_colsum_workspace_bytes(rows, cols); dx may alias dy. */
+int32_t b200_gelu_bwd_bias(const void* dy, const void* x, void* dx, float* dbias, int64_t rows, int32_t cols,
+                           int32_t dtype, void* ws, int64_t ws_bytes, void* stream);
 /* out[cols] fp32 = column sums of x[rows][cols] (bias gradients; deterministic two-stage) */
 int64_t b200_colsum_workspace_bytes(int64_t rows, int32_t cols);
 int32_t b200_colsum(const void* x, float* out, int64_t rows, int32_t cols, int32_t dtype, void* ws, int64_t ws_bytes,

@@ -175,6 +175,8 @@ _STATUS = {}
 _CHECK_IDS = os.environ.get("B200_CHECK_IDS") is not None
 _M64 = 0xFFFFFFFFFFFFFFFF
 _FLASH = os.environ.get("B200_NO_FLASH_ATTENTION") is None
+_CAPTURING = [False]
+_CAPTURE_PK = {}
 
 
 def _cast_into(src, dst):
@@ -188,6 +190,19 @@ def _operand(ws, dtype):
     if len(ws) == 1 and dtype == torch.float32:
         return ws[0].detach()
     key = tuple(id(w) for w in ws) + (dtype,)
+    if _CAPTURING[0]:
+        # inside a graph capture the cast is recorded (the weights change between replays) into a buffer owned by
+        # the graph, once per operand: the backward graph of the step reads the forward graph's copies
+        out = _CAPTURE_PK.get(key)
+        if out is None:
+            rows = sum(w.shape[0] for w in ws)
+            out = torch.empty((rows,) + tuple(ws[0].shape[1:]), dtype=dtype, device=ws[0].device)
+            r = 0
+            for w in ws:
+                _cast_into(w.detach(), out[r:r + w.shape[0]])
+                r += w.shape[0]
+            _CAPTURE_PK[key] = out
+        return out
     sig = tuple((w.data_ptr(), w._version) for w in ws)
     e = _PK.get(key)
     if e is not None and e[0] == sig:
@@ -232,7 +247,9 @@ def _site(call, site):
     return ((call * 64 + site) << 34) & _M64
 
 
-def _encoder_fwd(model, ids, type_ids, mask, save, training):
+def _encoder_fwd(model, ids, type_ids, mask, save, training, call=None):
+    """call=None: eager (the call index is folded into the Philox offsets passed by value); call=0 under graph
+    capture (a device-resident counter registered with b200_dropout_counter supplies the call index at replay)."""
     c = model.config
     dt = F.act_dtype()
     N, S = ids.shape
@@ -240,15 +257,16 @@ def _encoder_fwd(model, ids, type_ids, mask, save, training):
     p_h = float(c.hidden_dropout_prob) if training else 0.0
     p_a = float(c.attention_probs_dropout_prob) if training else 0.0
     seed = torch.cuda.initial_seed() & _M64
-    call = _CALLS[0]
-    _CALLS[0] += 1
+    if call is None:
+        call = _CALLS[0]
+        _CALLS[0] += 1
     e = model.bert.embeddings
     status = _status(ids.device)
     s0, h, m0, r0 = ops.embed_ln_fwd(ids, type_ids, e.word_embeddings.weight.detach(),
                                      e.position_embeddings.weight.detach(), e.token_type_embeddings.weight.detach(),
                                      e.LayerNorm.weight.detach(), e.LayerNorm.bias.detach(), e.LayerNorm.eps, p_h, seed,
                                      _site(call, 0), dt, status)
-    if _CHECK_IDS and int(status.item()) != 0:
+    if _CHECK_IDS and not _CAPTURING[0] and int(status.item()) != 0:
         status.zero_()
         raise IndexError("b200net BertEmbeddings: input id out of range")
     st = _EncoderState()
@@ -288,8 +306,9 @@ def _encoder_fwd(model, ids, type_ids, mask, save, training):
     return cls, st
 
 
-def _encoder_bwd(model, st, dcls, emit):
-    """Reverse walk over the saved activations; emit(param, grad) is called as soon as a gradient is enqueued."""
+def _encoder_bwd(model, st, dcls, emit, release=True):
+    """Reverse walk over the saved activations; emit(param, grad) is called as soon as a gradient is enqueued.
+    release=False keeps the saved activations referenced (a captured graph replays over them)."""
     c = model.config
     N, S, dt = st.N, st.S, st.dtype
     H, heads, FF = c.hidden_size, c.num_attention_heads, c.intermediate_size
@@ -301,7 +320,8 @@ def _encoder_bwd(model, st, dcls, emit):
         L = layers[li]
         a, o = L.attention, L.output
         h_in, qkv, probs, ctx, s1, m1, r1, h1, pre, act, s2, m2, r2 = st.layers[li]
-        st.layers[li] = None
+        if release:
+            st.layers[li] = None
         # BertOutput: LayerNorm(dropout(dense(act)) + h1)
         dres2, df2, dg, db, dbias = ops.ln_bwd(dh_a, dh_b, s2, m2, r2, o.LayerNorm.weight.detach(), p_h, seed,
                                                _site(call, 3 + 3 * li))
@@ -310,8 +330,8 @@ def _encoder_bwd(model, st, dcls, emit):
         emit(o.dense.bias, dbias)
         emit(o.dense.weight, ops.dense_bwd_weight(df2, act))
         dact = ops.dense_bwd_input(df2, _operand((o.dense.weight,), dt), FF)
-        dpre = ops.gelu_bwd(dact, pre, out=dact)
-        emit(L.intermediate.dense.bias, ops.colsum_any(dpre))
+        dpre, db1 = ops.gelu_bwd_bias(dact, pre, out=dact)
+        emit(L.intermediate.dense.bias, db1)
         emit(L.intermediate.dense.weight, ops.dense_bwd_weight(dpre, h1))
         dh1_b = ops.dense_bwd_input(dpre, _operand((L.intermediate.dense.weight,), dt), H)
         # BertSelfOutput: LayerNorm(dropout(dense(ctx)) + h_in)
@@ -344,6 +364,150 @@ def _encoder_bwd(model, st, dcls, emit):
     emit(e.word_embeddings.weight, dword)
     emit(e.position_embeddings.weight, dpos)
     emit(e.token_type_embeddings.weight, dtyp)
+
+
+# ------------------------------------------------------------------ CUDA-graph replay of the encoder
+# One training step is ~520 kernel launches (~12 ms of Python / ctypes enqueue work against ~12 ms of GPU work).
+# After GRAPH_WARMUP eager calls with the same (model, batch shape, mode, precision, trainable set) the encoder's
+# forward and backward are captured once and replayed; the reference's loop body
+# (pytorch_on_language_distr.py:257-275) is unchanged.  Dropout stays fresh per step through the device-resident
+# call counter (b200_dropout_counter).  B200_CUDA_GRAPHS=0 disables it; DDP keeps the eager path (per-parameter
+# hand-off of gradients to the communication stream).
+GRAPH_WARMUP = 3
+GRAPH_CACHE = 4
+_BG = {}
+_BG_SEEN = {}
+F._GRAPH_CACHES.extend([_BG, _BG_SEEN])
+
+
+class _BertGraph(object):
+    __slots__ = ("fwd", "bwd", "ids", "tt", "mask", "cls", "dcls", "grads", "ctr", "state", "ptrs", "keep", "uses")
+
+
+def _graph_key(model, ids, tt, mask, params):
+    needs = tuple(p.requires_grad for p in params) if torch.is_grad_enabled() else ()
+    # forward-only graphs read operands cast outside the graph: valid for the captured weight versions only
+    wver = -1 if any(needs) else sum(p._version for p in params)
+    return (id(model), tuple(ids.shape), ids.device.index, F.get_precision(), model.training, tt is not None,
+            mask is not None, needs, wver)
+
+
+def _param_ptrs(params):
+    return tuple(p.data_ptr() for p in params)
+
+
+def _capture(model, ids, tt, mask, params, key):
+    needs = key[7]
+    save = any(needs)
+    rec = _BertGraph()
+    rec.ids = ids.clone()
+    rec.tt = tt.clone() if tt is not None else None
+    rec.mask = mask.clone() if mask is not None else None
+    rec.ctr = torch.zeros(1, dtype=torch.int64, device=ids.device)
+    rec.ptrs = _param_ptrs(params)
+    rec.uses = 0
+    pool = torch.cuda.graph_pool_handle()
+    _CAPTURE_PK.clear()
+    _CAPTURING[0] = save          # forward-only graphs use the eager operand cache (validity is part of the key)
+    ops.NO_WORKSPACE_GROWTH[0] = True
+    check(lib.b200_dropout_counter(rec.ctr.data_ptr()), "dropout_counter")
+    try:
+        torch.cuda.synchronize()
+        rec.fwd = torch.cuda.CUDAGraph()
+        with torch.no_grad():
+            with torch.cuda.graph(rec.fwd, pool=pool):
+                rec.cls, rec.state = _encoder_fwd(model, rec.ids, rec.tt, rec.mask, save, model.training, call=0)
+        rec.bwd, rec.grads, rec.dcls = None, None, None
+        if save:
+            rec.dcls = torch.zeros_like(rec.cls)
+            grads = {}
+
+            def emit(p, g):
+                if p.requires_grad:
+                    grads[id(p)] = g
+
+            rec.bwd = torch.cuda.CUDAGraph()
+            with torch.no_grad():
+                with torch.cuda.graph(rec.bwd, pool=pool):
+                    _encoder_bwd(model, rec.state, rec.dcls, emit, release=False)
+            rec.grads = [grads.get(id(p)) for p in params]
+        rec.keep = (dict(ops._WS), list(_CAPTURE_PK.values()), [e[1] for e in _PK.values()])
+    finally:
+        check(lib.b200_dropout_counter(None), "dropout_counter")
+        _CAPTURING[0] = False
+        ops.NO_WORKSPACE_GROWTH[0] = False
+        _CAPTURE_PK.clear()
+    return rec
+
+
+class _GraphedEncoder(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, rec, ids, tt, mask, *params):
+        rec.ids.copy_(ids)
+        if tt is not None:
+            rec.tt.copy_(tt)
+        if mask is not None:
+            rec.mask.copy_(mask)
+        rec.ctr.fill_(_CALLS[0])
+        _CALLS[0] += 1
+        rec.fwd.replay()
+        ctx.rec = rec
+        ctx.saved_params = params
+        return rec.cls.clone()
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dcls):
+        rec = ctx.rec
+        if rec.bwd is None:
+            raise RuntimeError("b200net: this encoder graph was captured without a backward pass")
+        rec.dcls.copy_(dcls)
+        rec.bwd.replay()
+        # gradients live in graph-owned memory that the next replay overwrites; with zero_grad -> backward -> step
+        # they are consumed before that.  A parameter that still holds a .grad gets a private copy.
+        out = [None if g is None else (g if p.grad is None else g.clone())
+               for p, g in zip(ctx.saved_params, rec.grads)]
+        return (None, None, None, None) + tuple(out)
+
+
+def bert_encoder(model, ids, tt, mask):
+    """[N,S] ids -> final hidden state of the first token [N][hidden] fp32 (embeddings + every encoder layer)."""
+    params = _encoder_params(model)
+    if not (F._GRAPHS_ON and F._GRAD_SINK is None and not torch.cuda.is_current_stream_capturing()):
+        return _BertEncoderFn.apply(model, torch.is_grad_enabled(), ids, tt, mask, *params)
+    key = _graph_key(model, ids, tt, mask, params)
+    rec = _BG.get(key)
+    if rec is not None and rec != "failed":
+        if rec.ptrs == _param_ptrs(params):
+            rec.uses += 1
+            return _GraphedEncoder.apply(rec, ids, tt, mask, *params)
+        del _BG[key]
+        _BG_SEEN[key] = 0
+        rec = None
+    if rec is None:
+        seen = _BG_SEEN.get(key, 0)
+        if seen >= GRAPH_WARMUP:
+            try:
+                if len(_BG) >= GRAPH_CACHE:
+                    victim = min((k for k in _BG if _BG[k] != "failed"), key=lambda k: _BG[k].uses, default=None)
+                    if victim is not None:
+                        del _BG[victim]
+                rec = _capture(model, ids, tt, mask, params, key)
+                _BG[key] = rec
+                rec.uses = 1
+                return _GraphedEncoder.apply(rec, ids, tt, mask, *params)
+            except Exception as e:                    # capture is an optimisation: never fatal
+                if "workspace would have to grow" in str(e):
+                    _BG_SEEN[key] = 0                 # the eager calls so far never ran the backward: try again later
+                else:
+                    warnings.warn("b200net: CUDA-graph capture of the BERT encoder failed (%s); staying on the "
+                                  "eager path" % e)
+                    _BG[key] = "failed"
+        else:
+            if len(_BG_SEEN) > 64:
+                _BG_SEEN.clear()
+            _BG_SEEN[key] = seen + 1
+    return _BertEncoderFn.apply(model, torch.is_grad_enabled(), ids, tt, mask, *params)
 
 
 class _BertEncoderFn(torch.autograd.Function):
@@ -447,8 +611,7 @@ class BertForSequenceClassification(nn.Module):
             raise NotImplementedError("b200net BERT: sequence length must be a multiple of 4 (pad the batch)")
         tt = token_type_ids.long().contiguous() if token_type_ids is not None else None
         mask = attention_mask.long().contiguous() if attention_mask is not None else None
-        params = _encoder_params(self)
-        cls_rows = _BertEncoderFn.apply(self, torch.is_grad_enabled(), ids, tt, mask, *params)
+        cls_rows = bert_encoder(self, ids, tt, mask)
         pool = self.bert.pooler.dense
         pooled = F.tanh(F.linear(cls_rows, pool.weight, pool.bias))
         pooled = F.dropout(pooled, self.dropout.p, self.training)

@@ -35,8 +35,9 @@ template <typename T>
 __global__ void __launch_bounds__(ATT_THREADS)
 attention_fwd_kernel(const T* __restrict__ qkv, const long long* __restrict__ mask, T* __restrict__ probs,
                      T* __restrict__ ctx, int S, int heads, float scale, float p, float inv_keep, uint64_t seed,
-                     uint64_t offset) {
+                     uint64_t offset, const unsigned long long* __restrict__ ctr) {
   extern __shared__ float smem[];
+  if (ctr != nullptr) offset += *ctr << 40;
   const int Sp = (S + 3) / 4 * 4 + 4;                          // padded row of the score tile
   float (*Qs)[ATT_D + 1] = reinterpret_cast<float (*)[ATT_D + 1]>(smem);
   float (*KVs)[ATT_D + 1] = reinterpret_cast<float (*)[ATT_D + 1]>(smem + ATT_QT * (ATT_D + 1));
@@ -133,8 +134,9 @@ template <typename T>
 __global__ void __launch_bounds__(ATT_THREADS)
 attention_bwd_q_kernel(const T* __restrict__ qkv, const T* __restrict__ probs, const T* __restrict__ dctx,
                        T* __restrict__ ds_out, T* __restrict__ dqkv, int S, int heads, float scale, float p,
-                       float inv_keep, uint64_t seed, uint64_t offset) {
+                       float inv_keep, uint64_t seed, uint64_t offset, const unsigned long long* __restrict__ ctr) {
   extern __shared__ float smem[];
+  if (ctr != nullptr) offset += *ctr << 40;
   const int Sp = (S + 3) / 4 * 4 + 4;
   float (*dOs)[ATT_D + 1] = reinterpret_cast<float (*)[ATT_D + 1]>(smem);
   float (*KVs)[ATT_D + 1] = reinterpret_cast<float (*)[ATT_D + 1]>(smem + ATT_QT * (ATT_D + 1));
@@ -230,8 +232,9 @@ template <typename T>
 __global__ void __launch_bounds__(ATT_THREADS)
 attention_bwd_kv_kernel(const T* __restrict__ qkv, const T* __restrict__ probs, const T* __restrict__ ds_in,
                         const T* __restrict__ dctx, T* __restrict__ dqkv, int S, int heads, float scale, float p,
-                        float inv_keep, uint64_t seed, uint64_t offset) {
+                        float inv_keep, uint64_t seed, uint64_t offset, const unsigned long long* __restrict__ ctr) {
   __shared__ float Qs[ATT_KQ][ATT_D + 1];
+  if (ctr != nullptr) offset += *ctr << 40;
   __shared__ float dOs[ATT_KQ][ATT_D + 1];
   __shared__ float Pt[ATT_KQ][ATT_QT + 1];    // [query in chunk][key in tile]
   __shared__ float dSt[ATT_KQ][ATT_QT + 1];
@@ -294,23 +297,32 @@ template <typename T>
 static int32_t attention_fwd_t(const T* qkv, const long long* mask, T* probs, T* ctx, int N, int S, int heads,
                                float p, uint64_t seed, uint64_t offset, cudaStream_t st) {
   const size_t smem = att_smem_bytes(S);
-  cudaFuncSetAttribute(attention_fwd_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  static size_t attr_smem = 0;   // not a stream operation: raise the limit once per size, outside any capture replay
+  if (smem > attr_smem) {
+    cudaFuncSetAttribute(attention_fwd_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    attr_smem = smem;
+  }
   dim3 grid((S + ATT_QT - 1) / ATT_QT, heads, N);
   attention_fwd_kernel<T><<<grid, ATT_THREADS, smem, st>>>(qkv, mask, probs, ctx, S, heads, 0.125f, p,
-                                                          p > 0.f ? 1.f / (1.f - p) : 1.f, seed, offset);
+                                                          p > 0.f ? 1.f / (1.f - p) : 1.f, seed, offset,
+                                                          dropout_ctr());
   return check_launch("attention_fwd");
 }
 template <typename T>
 static int32_t attention_bwd_t(const T* qkv, const T* probs, const T* dctx, T* ds, T* dqkv, int N, int S, int heads,
                                float p, uint64_t seed, uint64_t offset, cudaStream_t st) {
   const size_t smem = att_smem_bytes(S);
-  cudaFuncSetAttribute(attention_bwd_q_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  static size_t attr_smem = 0;
+  if (smem > attr_smem) {
+    cudaFuncSetAttribute(attention_bwd_q_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    attr_smem = smem;
+  }
   dim3 grid((S + ATT_QT - 1) / ATT_QT, heads, N);
   const float ik = p > 0.f ? 1.f / (1.f - p) : 1.f;
   attention_bwd_q_kernel<T><<<grid, ATT_THREADS, smem, st>>>(qkv, probs, dctx, ds, dqkv, S, heads, 0.125f, p, ik,
-                                                            seed, offset);
+                                                            seed, offset, dropout_ctr());
   attention_bwd_kv_kernel<T><<<grid, ATT_THREADS, 0, st>>>(qkv, probs, ds, dctx, dqkv, S, heads, 0.125f, p, ik, seed,
-                                                          offset);
+                                                          offset, dropout_ctr());
   return check_launch("attention_bwd", 2);
 }
 

@@ -46,6 +46,7 @@ struct AttParams {
   __nv_bfloat16* ctx;             // forward output / backward input [N*S][heads*64]
   const __nv_bfloat16* dctx;
   __nv_bfloat16* dqkv;
+  const unsigned long long* ctr;  // optional device-resident call counter added to the Philox offset (<< 40)
   uint32_t* keep_bits;            // [N][heads][S][S/32] dropout keep mask (bit j of word w = key 32w+j); p > 0 only
 };
 
@@ -250,6 +251,7 @@ att_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__
   const uint32_t trow = tmem_base + (static_cast<uint32_t>(warp * 32) << 16);
   const long long pbase_head = ((long long)n * P.heads + h) * S;   // * S + key gives the flat probability index
   const bool drop = P.p > 0.f;
+  const uint64_t rng_offset = P.offset + (P.ctr != nullptr ? *P.ctr << 40 : 0ull);
   float rmax = 0.f, rsum = 0.f;
   if (MODE == ATT_FWD) {
     rmax = -3.0e38f;
@@ -278,7 +280,7 @@ att_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__
 #pragma unroll
         for (int g = 0; g < 8; ++g) {
           float mk[4];
-          dropout_scale4(P.seed, P.offset, pbase + ch * 32 + g * 4, P.p, 1.f, mk);
+          dropout_scale4(P.seed, rng_offset, pbase + ch * 32 + g * 4, P.p, 1.f, mk);
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
             v[g * 4 + e] *= mk[e];
@@ -373,8 +375,12 @@ template <int MODE>
 static int32_t att_tc_launch(const CUtensorMap& tq, const CUtensorMap& tdo, const AttParams& P, int N,
                              cudaStream_t st) {
   const int smem = att_tc_smem_bytes<MODE>(P.S);
-  cudaError_t e = cudaFuncSetAttribute(att_tc_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-  if (e != cudaSuccess) return fail(B200_CUDA_ERROR, "attention: smem attribute: %s", cudaGetErrorString(e));
+  static int attr_smem = 0;      // raise the limit once per size (not a stream operation: keep it out of captures)
+  if (smem > attr_smem) {
+    cudaError_t e = cudaFuncSetAttribute(att_tc_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return fail(B200_CUDA_ERROR, "attention: smem attribute: %s", cudaGetErrorString(e));
+    attr_smem = smem;
+  }
   att_tc_kernel<MODE><<<dim3(P.S / ATC_ROWS, P.heads, N), ATC_ROWS, smem, st>>>(tq, tdo, P);
   return check_launch("attention_flash");
 }
@@ -403,6 +409,7 @@ int32_t b200_attention_flash_fwd(const void* qkv, const int64_t* mask, float* ls
   P.S = S; P.heads = heads; P.scale = 0.125f; P.c = 0.125f * 1.4426950408889634f;
   P.p = p_drop; P.inv_keep = p_drop > 0.f ? 1.f / (1.f - p_drop) : 1.f; P.seed = seed; P.offset = offset;
   P.mask = (const long long*)mask; P.lse = lse; P.ctx = (__nv_bfloat16*)ctx; P.keep_bits = keep_bits;
+  P.ctr = dropout_ctr();
   return att_tc_launch<ATT_FWD>(tq, tq, P, N, as_stream(stream));
 }
 

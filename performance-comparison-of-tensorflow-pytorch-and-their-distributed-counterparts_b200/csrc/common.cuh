@@ -30,6 +30,13 @@ inline int32_t check_launch(const char* what, int kernels = 1) {
   return B200_OK;
 }
 inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
+// Optional device-resident dropout call counter of the calling thread (b200_dropout_counter): when set, every
+// dropout site adds (*ctr) << 40 to its Philox offset at EXECUTION time, so a captured CUDA graph draws a fresh
+// mask at every replay.
+inline const unsigned long long*& dropout_ctr() {
+  static thread_local const unsigned long long* p = nullptr;
+  return p;
+}
 
 inline int num_sms() {
   static int n = 0;

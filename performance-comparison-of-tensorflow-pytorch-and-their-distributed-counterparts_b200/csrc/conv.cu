@@ -131,6 +131,9 @@ static inline WgradPlan wgrad_plan(const b200_conv_desc* d, const ConvGeom& g) {
   w.pb_total = w.box.tiles_w * w.box.tiles_h * w.box.tiles_n;
   const long long ctas = (long long)((g.RSC + w.bn_tile - 1) / w.bn_tile) * ((d->K + 127) / 128);
   long long s = (2LL * num_sms() + ctas - 1) / ctas;
+  // a flat problem whose output tiles already fill one wave (the 768 x 3072 Linears of BERT: 144 tiles) runs unsplit:
+  // the kernel then writes the gradient in place and the slab reduction disappears
+  if (is_flat(d) && ctas * 100 >= 85LL * num_sms() && ctas <= num_sms()) s = 1;
   if (s > w.pb_total) s = w.pb_total;
   if (s > 1024) s = 1024;
   const long long slab = (long long)d->K * g.ldw * 4;
@@ -298,9 +301,11 @@ static int32_t implicit_wgrad(const b200_conv_desc* d, const ConvGeom& g, const 
   P.ntaps = d->R * d->S;
   for (int r = 0; r < d->R; ++r)
     for (int s2 = 0; s2 < d->S; ++s2) P.taps[r * d->S + s2] = ConvTap{s2 - d->pad, r - d->pad, (r * d->S + s2) * d->C};
-  P.out = ws; P.ldo = g.ldw; P.split_stride = (long long)d->K * g.ldw;
+  // unsplit 1x1: the packed [K][C] slab IS the OIHW gradient, so the kernel writes dw directly
+  const bool direct = wp.nsplits == 1 && d->R * d->S == 1 && g.ldw == d->C && (reinterpret_cast<uintptr_t>(dw) & 15) == 0;
+  P.out = direct ? (void*)dw : ws; P.ldo = g.ldw; P.split_stride = (long long)d->K * g.ldw;
   P.ncols = g.RSC; P.cdim = d->C; P.out_fp32 = 1; P.accumulate = 0;
-  P.vec_ok = (reinterpret_cast<uintptr_t>(ws) & 15) == 0;   // ldw % 8 == 0 and column tiles start at multiples of 256
+  P.vec_ok = (reinterpret_cast<uintptr_t>(P.out) & 15) == 0;   // ldw % 8 == 0 and column tiles start at multiples of 256
   P.nsplits = wp.nsplits; P.pb_total = wp.pb_total; P.pb_per_split = wp.pb_per; P.x_mul = d->stride;
   P.kr = wp.box.bw * wp.box.bh * wp.box.bn;
   P.mrows = d->K;
@@ -321,6 +326,7 @@ static int32_t implicit_wgrad(const b200_conv_desc* d, const ConvGeom& g, const 
   rc = launch_conv_mode<MODE_WGRAD>(wp.bn_tile, ta, tb, ta, P, st);
   timing_end(e0, e1, 2.0 * g.M * d->K * g.RSC, st);
   if (rc) return fail(B200_CUDA_ERROR, "conv_wgrad: launch failed (%d)", rc);
+  if (direct) return B200_OK;
   return launch_reduce_wgrad((const float*)ws, wp.nsplits, P.split_stride, d->K, d->C, d->R * d->S, g.ldw, dw, st);
 }
 

@@ -331,12 +331,17 @@ _GRAPH_SEEN = {}  # key -> number of eager calls so far
 _CAPTURING = [False]
 
 
+_GRAPH_CACHES = []   # other modules' graph caches (bert.py registers its own), cleared together with ours
+
+
 def set_cuda_graphs(on):
     global _GRAPHS_ON
     _GRAPHS_ON = bool(on)
     if not on:
         _GRAPHS.clear()
         _GRAPH_SEEN.clear()
+        for c in _GRAPH_CACHES:
+            c.clear()
 
 
 class _GraphRecord(object):

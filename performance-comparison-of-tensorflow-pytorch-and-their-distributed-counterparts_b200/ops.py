@@ -487,6 +487,18 @@ def gelu_bwd(dy, x, out=None):
     return dx
 
 
+def gelu_bwd_bias(dy, x, out=None):
+    """(dx, dbias) = (dy * gelu'(x), column sums of dx) in one pass over [rows][cols]"""
+    rows, cols = x.shape
+    dx = torch.empty_like(x) if out is None else out
+    db = torch.empty((cols,), dtype=torch.float32, device=x.device)
+    n = int(lib.b200_colsum_workspace_bytes(rows, cols))
+    ws = workspace(n, x.device)
+    check(lib.b200_gelu_bwd_bias(dy.data_ptr(), x.data_ptr(), dx.data_ptr(), db.data_ptr(), rows, cols, _dt(x),
+                                 ws.data_ptr(), n, _stream()), "gelu_bwd_bias")
+    return dx, db
+
+
 def colsum_any(x):
     """fp32 column sums of a [rows][cols] matrix in either dtype (bias gradients)."""
     rows, cols = x.shape

@@ -145,6 +145,9 @@ def test_gelu_colsum_tanh(prec):
     yd.backward(dy.double())
     assert _rel(ops.gelu_fwd(x), yd) < TOL[prec]
     assert _rel(ops.gelu_bwd(dy, x), xd.grad) < TOL[prec]
+    dx, db = ops.gelu_bwd_bias(dy, x)
+    assert torch.equal(dx, ops.gelu_bwd(dy, x))
+    assert _rel(db, dx.double().sum(0)) < 1e-5
     for rows, cols in ((200, 3072), (8192, 768), (3, 2304), (1000, 8)):
         m = _rand((rows, cols), dt, 3)
         assert _rel(ops.colsum_any(m), m.double().sum(0)) < 1e-5
@@ -439,3 +442,32 @@ def test_bert_full_size_properties():
     changed = sum(int(not torch.equal(a, p.detach())) for a, p in zip(before, model.parameters()))
     # position rows >= S and unused vocabulary rows get a zero gradient but Adam still leaves them alone; every tensor moves
     assert changed == len(before)
+
+
+def test_bert_graph_replay_matches_eager():
+    """After GRAPH_WARMUP eager calls the encoder forward/backward replay as CUDA graphs inside the unchanged loop
+    body; with dropout on, the device-resident call counter must give the replayed steps the same masks the eager
+    path draws (same seed, same call index), so the loss curves coincide (embedding-gradient atomics aside)."""
+    import b200net
+    from b200net import bert
+    from oracle import bert_oracle as B
+    ref = B.build_reference_model(num_layers=2)
+    curves = {}
+    for graphs in (False, True):
+        b200net.set_cuda_graphs(False)          # drop any cached graphs
+        b200net.set_cuda_graphs(graphs)
+        try:
+            torch.manual_seed(11)
+            bert._CALLS[0] = 0
+            b200net.functional._DROPOUT_CALLS[0] = 0
+            model = _our_model(ref, dropout=0.1)
+            r = B.run_case(model, 4, 128, 8, make_opt=_our_optimizer, clip=b200net.utils.clip_grad_norm_,
+                           device=_dev())
+            curves[graphs] = r["losses"] + [float(r["eval_logits"].abs().sum())]
+            if graphs:
+                recs = [v for v in bert._BG.values() if v != "failed"]
+                assert any(v.bwd is not None and v.uses >= 4 for v in recs), "training graph was not used"
+        finally:
+            b200net.set_cuda_graphs(True)
+    for a, b in zip(curves[True], curves[False]):
+        assert abs(a - b) <= 1e-4 * max(1.0, abs(b)), (curves[True], curves[False])
