@@ -371,8 +371,8 @@ def _encoder_bwd(model, st, dcls, emit, release=True):
 # After GRAPH_WARMUP eager calls with the same (model, batch shape, mode, precision, trainable set) the encoder's
 # forward and backward are captured once and replayed; the reference's loop body
 # (pytorch_on_language_distr.py:257-275) is unchanged.  Dropout stays fresh per step through the device-resident
-# call counter (b200_dropout_counter).  B200_CUDA_GRAPHS=0 disables it; DDP keeps the eager path (per-parameter
-# hand-off of gradients to the communication stream).
+# call counter (b200_dropout_counter).  B200_CUDA_GRAPHS=0 disables it.  Under DistributedDataParallel the copies
+# into the gradient buckets are part of the backward graph and the all-reduces are launched after the replay.
 GRAPH_WARMUP = 3
 GRAPH_CACHE = 4
 _BG = {}
@@ -381,7 +381,8 @@ F._GRAPH_CACHES.extend([_BG, _BG_SEEN])
 
 
 class _BertGraph(object):
-    __slots__ = ("fwd", "bwd", "ids", "tt", "mask", "cls", "dcls", "grads", "ctr", "state", "ptrs", "keep", "uses")
+    __slots__ = ("fwd", "bwd", "ids", "tt", "mask", "cls", "dcls", "grads", "ctr", "state", "ptrs", "keep", "uses",
+                 "ddp", "order")
 
 
 def _graph_key(model, ids, tt, mask, params):
@@ -389,7 +390,7 @@ def _graph_key(model, ids, tt, mask, params):
     # forward-only graphs read operands cast outside the graph: valid for the captured weight versions only
     wver = -1 if any(needs) else sum(p._version for p in params)
     return (id(model), tuple(ids.shape), ids.device.index, F.get_precision(), model.training, tt is not None,
-            mask is not None, needs, wver)
+            mask is not None, needs, wver, id(F.grad_sink_owner()))
 
 
 def _param_ptrs(params):
@@ -417,14 +418,15 @@ def _capture(model, ids, tt, mask, params, key):
         with torch.no_grad():
             with torch.cuda.graph(rec.fwd, pool=pool):
                 rec.cls, rec.state = _encoder_fwd(model, rec.ids, rec.tt, rec.mask, save, model.training, call=0)
-        rec.bwd, rec.grads, rec.dcls = None, None, None
+        rec.bwd, rec.grads, rec.dcls, rec.ddp, rec.order = None, None, None, None, None
         if save:
             rec.dcls = torch.zeros_like(rec.cls)
             grads = {}
+            rec.ddp, rec.order = F.grad_sink_owner(), []
 
             def emit(p, g):
                 if p.requires_grad:
-                    grads[id(p)] = g
+                    grads[id(p)] = g if rec.ddp is None else rec.ddp._sink_capture(p, g, rec.order)
 
             rec.bwd = torch.cuda.CUDAGraph()
             with torch.no_grad():
@@ -463,6 +465,9 @@ class _GraphedEncoder(torch.autograd.Function):
             raise RuntimeError("b200net: this encoder graph was captured without a backward pass")
         rec.dcls.copy_(dcls)
         rec.bwd.replay()
+        if rec.ddp is not None:
+            rec.ddp._replayed(rec.order)      # buckets are complete: launch their all-reduces in the fixed order
+            return (None, None, None, None) + tuple(rec.grads)
         # gradients live in graph-owned memory that the next replay overwrites; with zero_grad -> backward -> step
         # they are consumed before that.  A parameter that still holds a .grad gets a private copy.
         out = [None if g is None else (g if p.grad is None else g.clone())
@@ -473,7 +478,9 @@ class _GraphedEncoder(torch.autograd.Function):
 def bert_encoder(model, ids, tt, mask):
     """[N,S] ids -> final hidden state of the first token [N][hidden] fp32 (embeddings + every encoder layer)."""
     params = _encoder_params(model)
-    if not (F._GRAPHS_ON and F._GRAD_SINK is None and not torch.cuda.is_current_stream_capturing()):
+    owner = F.grad_sink_owner()
+    if not (F._GRAPHS_ON and not torch.cuda.is_current_stream_capturing()
+            and (F._GRAD_SINK is None or (owner is not None and owner.graph_ok()))):
         return _BertEncoderFn.apply(model, torch.is_grad_enabled(), ids, tt, mask, *params)
     key = _graph_key(model, ids, tt, mask, params)
     rec = _BG.get(key)

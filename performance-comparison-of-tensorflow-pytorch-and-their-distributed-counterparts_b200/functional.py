@@ -48,6 +48,12 @@ def set_grad_sink(fn):
     _GRAD_SINK = fn
 
 
+def grad_sink_owner():
+    """The DistributedDataParallel wrapper behind the current sink when it can take part in graph replay."""
+    owner = getattr(_GRAD_SINK, "__self__", None)
+    return owner if hasattr(owner, "_sink_capture") else None
+
+
 # ------------------------------------------------------------------ packed-weight cache
 # key: id(param) -> (data_ptr, version, dtype, packed).  Our optimizers bump the parameter version after the raw
 # in-place update (torch.autograd.graph.increment_version), stock optimizers do it through ATen.
@@ -321,8 +327,8 @@ class _ResNetBackbone(torch.autograd.Function):
 # (model, input shape, mode, precision, set of trainable parameters) the forward and the backward are each captured
 # into a CUDA graph once and replayed from then on: the reference's loop
 # (pytorch_training_inference_on_image.ipynb:664-673, :855-861) is unchanged, only what happens inside
-# model.forward / loss.backward differs.  B200_CUDA_GRAPHS=0 disables it; DDP (per-parameter gradient hand-off to the
-# communication stream) keeps the eager path.
+# model.forward / loss.backward differs.  B200_CUDA_GRAPHS=0 disables it.  Under DistributedDataParallel the copies
+# into the gradient buckets are recorded in the backward graph and the all-reduces start right after the replay.
 GRAPH_WARMUP = 3
 GRAPH_CACHE = 6
 _GRAPHS_ON = os.environ.get("B200_CUDA_GRAPHS", "1") != "0"
@@ -345,7 +351,7 @@ def set_cuda_graphs(on):
 
 
 class _GraphRecord(object):
-    __slots__ = ("fwd", "bwd", "x", "feat", "dfeat", "grads", "dx", "state", "ptrs", "ws", "uses")
+    __slots__ = ("fwd", "bwd", "x", "feat", "dfeat", "grads", "dx", "state", "ptrs", "ws", "uses", "ddp", "order")
 
 
 def _graph_key(model, x, params, needs_x):
@@ -354,7 +360,8 @@ def _graph_key(model, x, params, needs_x):
     # forward-only graphs (inference, frozen backbone) use weights packed OUTSIDE the graph, so they are only valid
     # for the weight versions they were captured with
     wver = -1 if (any(needs) or needs_x) else sum(p._version for p in params)
-    return (id(model), tuple(x.shape), x.device.index, _PRECISION, bn_flags, needs, bool(needs_x), wver)
+    return (id(model), tuple(x.shape), x.device.index, _PRECISION, bn_flags, needs, bool(needs_x), wver,
+            id(grad_sink_owner()))
 
 
 def _tensor_ptrs(model):
@@ -381,13 +388,15 @@ def _capture(model, x, params, key):
         with torch.no_grad():
             with torch.cuda.graph(rec.fwd, pool=pool):
                 rec.feat, rec.state = _backbone_fwd(model, rec.x, save, needs_x)
-        rec.bwd = None
+        rec.bwd, rec.ddp, rec.order = None, None, None
         if save:
             rec.dfeat = torch.zeros_like(rec.feat)
             rec.bwd = torch.cuda.CUDAGraph()
+            rec.ddp, rec.order = grad_sink_owner(), []
+            sink = None if rec.ddp is None else (lambda p, g: rec.ddp._sink_capture(p, g, rec.order))
             with torch.no_grad():
                 with torch.cuda.graph(rec.bwd, pool=pool):
-                    rec.dx, rec.grads = _backbone_bwd(rec.state, rec.dfeat, params, list(needs), needs_x, None)
+                    rec.dx, rec.grads = _backbone_bwd(rec.state, rec.dfeat, params, list(needs), needs_x, sink)
         rec.ws = (dict(ops._WS), [e[3] for e in _PACKED.values()])   # raw pointers captured: keep the memory alive
     finally:
         _CAPTURING[0] = False
@@ -413,6 +422,9 @@ class _GraphedBackbone(torch.autograd.Function):
             raise RuntimeError("b200net: this backbone graph was captured without a backward pass")
         rec.dfeat.copy_(dfeat)
         rec.bwd.replay()
+        if rec.ddp is not None:
+            rec.ddp._replayed(rec.order)      # buckets are complete: launch their all-reduces in the fixed order
+            return (None, rec.dx.clone() if rec.dx is not None else None) + tuple(rec.grads)
         # The gradients live in graph-owned memory that the next replay overwrites.  With the usual
         # zero_grad() -> backward() -> step() cycle they are consumed before that, so they are handed out as they
         # are; a parameter that still holds a .grad (gradient accumulation) gets a private copy instead, because
@@ -425,7 +437,9 @@ class _GraphedBackbone(torch.autograd.Function):
 def resnet_backbone(model, x):
     """[N,3,H,W] fp32 NCHW -> [N,2048] fp32 features (everything up to and including avgpool + flatten)."""
     params = _backbone_params(model)
-    if not (_GRAPHS_ON and _GRAD_SINK is None and x.is_cuda and not torch.cuda.is_current_stream_capturing()):
+    owner = grad_sink_owner()
+    if not (_GRAPHS_ON and x.is_cuda and not torch.cuda.is_current_stream_capturing()
+            and (_GRAD_SINK is None or (owner is not None and owner.graph_ok()))):
         return _ResNetBackbone.apply(model, torch.is_grad_enabled(), x, *params)
     needs_x = x.requires_grad and torch.is_grad_enabled()
     key = _graph_key(model, x, params, needs_x)

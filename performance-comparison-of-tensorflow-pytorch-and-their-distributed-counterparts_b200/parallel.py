@@ -8,6 +8,10 @@ construction, buffers (BatchNorm running statistics) are re-broadcast before eve
 (`broadcast_buffers=True`), gradients of parameters that require grad are averaged across ranks in buckets laid out
 in REVERSE registration order (1 MiB first bucket, then `bucket_cap_mb`), BatchNorm batch statistics stay per rank.
 
+CUDA graphs: the fused backbone / encoder nodes still replay their captured forward and backward graphs under this
+wrapper (the copies into the bucket slices are part of the backward graph); the buckets are then all-reduced right
+after the replay, in the same fixed order.  The eager path keeps the per-layer overlap described below.
+
 B200 design: gradients LIVE in the flat fp32 buckets (`param.grad` is a view of its bucket slice, so there is no
 unpack and the optimizer reads reduced values in place); a bucket is all-reduced (ncclAvg over NVLink/NVSwitch) on a
 dedicated communication stream as soon as its last gradient is written, overlapping the rest of backward.  The fused
@@ -193,6 +197,29 @@ class DistributedDataParallel(_nn.Module):
                 view.copy_(grad)
         self._mark_ready(p)
         return view
+
+    # ---- CUDA-graph mode of the fused nodes (functional.resnet_backbone, bert.bert_encoder): the pack into the
+    # bucket slice is recorded inside the backward graph; after every replay the node reports the parameters in the
+    # recorded order, which launches the buckets' all-reduces in the usual fixed order on the communication stream.
+    def _sink_capture(self, p, grad, order):
+        if id(p) not in self._where:
+            return grad
+        view = self.grad_view(p)
+        if grad.data_ptr() != view.data_ptr():
+            check(lib.b200_bucket_pack(1, ptr_array([grad.data_ptr()]), i64_array([grad.numel()]), view.data_ptr(),
+                                       1.0, torch.cuda.current_stream().cuda_stream), "bucket_pack")
+        order.append(p)
+        return view
+
+    def _replayed(self, order):
+        for p in order:
+            self._mark_ready(p)
+
+    def graph_ok(self):
+        """Fused nodes may replay graphs under this wrapper: CUDA, gradient sync on, no stale .grad tensors (an
+        accumulating step has to take the eager path, whose sink leaves accumulation to autograd)."""
+        return (self.on_cuda and self.require_backward_grad_sync
+                and all(q.grad is None for b in self.buckets for q in b.params))
 
     def _post_acc_hook(self, p):
         view = self.grad_view(p)

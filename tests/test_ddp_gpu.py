@@ -94,3 +94,101 @@ def test_ddp_world2_nccl():
     results = mgr.dict()
     mp.spawn(_worker, args=(world, port, results), nprocs=world, join=True)
     assert dict(results) == {0: "ok", 1: "ok"}
+
+
+def _bert_worker(rank, world, port, results):
+    """The IMDB model under DDP (the commented constructor at pytorch_on_language_distr.py:220-221, config C5):
+    gradients of the fused encoder node reach the buckets through the gradient sink, the head's through autograd
+    hooks; the all-reduced result must be the mean of the ranks' local gradients."""
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    try:
+        import b200net
+        from b200net import bert
+        from oracle import bert_oracle as B
+        b200net.set_precision("bf16")
+        torch.manual_seed(42)
+        cfg = bert.BertConfig(num_labels=2, num_hidden_layers=2, hidden_dropout_prob=0.0,
+                              attention_probs_dropout_prob=0.0)
+        src = bert.BertForSequenceClassification(cfg)
+
+        def make():
+            m = bert.BertForSequenceClassification(cfg)
+            m.load_state_dict(src.state_dict())
+            return m.to(dev).train()
+
+        ids, mask, labels = B.make_batch(4, 128, 70 + rank, dev)
+        local = make()
+        local(ids, token_type_ids=None, attention_mask=mask, labels=labels)[0].backward()
+        torch.cuda.synchronize()
+        expect = {}
+        for n, p in local.named_parameters():
+            g = p.grad.clone()
+            dist.all_reduce(g, op=dist.ReduceOp.SUM)
+            expect[n] = g / world
+        model = make()
+        ddp = b200net.parallel.DistributedDataParallel(model, device_ids=[rank], output_device=rank)
+        opt = bert.AdamW(ddp.parameters(), lr=2e-5, eps=1e-8)
+        for step in range(2):
+            opt.zero_grad()
+            ddp(ids, token_type_ids=None, attention_mask=mask, labels=labels)[0].backward()
+            torch.cuda.synchronize()
+            if step == 0:
+                for n, p in model.named_parameters():
+                    e = expect[n]
+                    # the word-embedding scatter uses fp32 atomics: summation order differs between runs
+                    tol = 1e-4 if "word_embeddings" in n else 1e-5
+                    err = ((p.grad - e).abs().max() / e.abs().max().clamp_min(1e-20)).item()
+                    assert err <= tol, (n, err)
+                    assert p.grad.data_ptr() == ddp.grad_view(p).data_ptr(), n
+            b200net.utils.clip_grad_norm_(model.parameters(), 1.0)
+            opt.step()
+        torch.cuda.synchronize()
+        for n, p in model.named_parameters():
+            ref = p.detach().clone()
+            dist.broadcast(ref, 0)
+            assert torch.equal(ref, p.detach()), n
+
+        # CUDA-graph replay under DDP: the bucket packs are part of the backward graph, the all-reduces follow the
+        # replay.  Eight steps with graphs on and off from the same weights must end in the same parameters, equal
+        # on both ranks.
+        def train(graphs):
+            b200net.set_cuda_graphs(False)
+            b200net.set_cuda_graphs(graphs)
+            m = make()
+            d = b200net.parallel.DistributedDataParallel(m, device_ids=[rank], output_device=rank)
+            o = bert.AdamW(d.parameters(), lr=1e-3, eps=1e-8)
+            for _ in range(8):
+                o.zero_grad()
+                d(ids, token_type_ids=None, attention_mask=mask, labels=labels)[0].backward()
+                b200net.utils.clip_grad_norm_(m.parameters(), 1.0)
+                o.step()
+            torch.cuda.synchronize()
+            if graphs:
+                recs = [v for v in bert._BG.values() if v != "failed"]
+                assert any(v.ddp is d and v.uses >= 3 for v in recs), "graph replay was not used under DDP"
+            return m
+        m_eager, m_graph = train(False), train(True)
+        b200net.set_cuda_graphs(True)
+        for (n, a), (_, b) in zip(m_graph.named_parameters(), m_eager.named_parameters()):
+            ref = a.detach().clone()
+            dist.broadcast(ref, 0)
+            assert torch.equal(ref, a.detach()), n
+            err = ((a - b).abs().max() / b.abs().max().clamp_min(1e-6)).item()
+            assert err < 2e-3, (n, err)
+        results[rank] = "ok"
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_ddp_world2_nccl_bert():
+    world = 2
+    port = _free_port()
+    mgr = mp.Manager()
+    results = mgr.dict()
+    mp.spawn(_bert_worker, args=(world, port, results), nprocs=world, join=True)
+    assert dict(results) == {0: "ok", 1: "ok"}
