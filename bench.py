@@ -31,6 +31,11 @@ UNIT = "img/s"
 PER_GPU_BATCH = 256
 HW = 160
 GFLOP_PER_IMG_TRAIN = 12.398     # BASELINE.md section 3 / SURVEY 8(d): fwd + dgrad + wgrad, no stem dgrad
+# DRAM bytes per launch of the tcgen05 conv kernel from the committed `ncu --set full` captures (dram__bytes_read.sum
+# + dram__bytes_write.sum, mean over the captured launches): profiles/r01h_ncu_full_conv_summary.txt (ResNet step) and
+# profiles/r01m_bert_ncu_full_summary.txt (BERT step)
+CONV_TRAFFIC_BYTES_PER_LAUNCH = 45.5e6
+BERT_GEMM_TRAFFIC_BYTES_PER_LAUNCH = 36.8e6
 CPU_SAMPLE_BATCH = 32            # configs[0] batch: the reference's own CPU-runnable case
 WORKLOAD = ("resnet50 train step (Mode A: all layers trainable, SGD 0.001, NLL), batch %d/GPU, 3x%dx%d "
             "(BASELINE.json configs[1]; DDP = configs[2] when n_gpus > 1)")
@@ -223,7 +228,9 @@ def bert_leg(dev, rank, world, distributed, steps, warmup, timed, with_roofline)
         achieved = fl.value / (tms.value * 1e-3) / 1e12
         out["roofline"] = {"bound": "tensor", "kernel": "conv_sm100_kernel as flat 1x1 (the encoder's Linear layers: "
                            "fprop / dgrad / wgrad)", "achieved": achieved, "peak": pk["tflops"], "unit": "TFLOP/s",
-                           "frac": achieved / pk["tflops"], "peak_source": pk["src"] + " sustained bf16", "traffic": None,
+                           "frac": achieved / pk["tflops"], "peak_source": pk["src"] + " sustained bf16",
+                           "traffic": BERT_GEMM_TRAFFIC_BYTES_PER_LAUNCH,
+                           "traffic_source": "profiles/r01m_bert_ncu_full_summary.txt (bytes per launch, ncu --set full)",
                            "launches_per_step": n.value // prof_steps, "kernel_ms_per_step": tms.value / prof_steps,
                            "gemm_tflop_per_step": fl.value / prof_steps / 1e12}
     del net, model, optimizer
@@ -405,7 +412,8 @@ def main():
         achieved = algo_flops / (ms.value * 1e-3) / 1e12
         roof = {"bound": "tensor", "kernel": "conv_sm100_kernel (tcgen05 implicit-GEMM conv fprop/dgrad/wgrad family)",
                 "achieved": achieved, "peak": pk["tflops"], "unit": "TFLOP/s", "frac": achieved / pk["tflops"],
-                "peak_source": pk["src"] + " sustained bf16", "traffic": None,
+                "peak_source": pk["src"] + " sustained bf16", "traffic": CONV_TRAFFIC_BYTES_PER_LAUNCH,
+                "traffic_source": "profiles/r01h_ncu_full_conv_summary.txt (bytes per launch, ncu --set full)",
                 "launches_per_step": n.value // prof_steps, "kernel_ms_per_step": ms.value / prof_steps,
                 "executed_gemm_tflop_per_step": fl.value / prof_steps / 1e12}
 
