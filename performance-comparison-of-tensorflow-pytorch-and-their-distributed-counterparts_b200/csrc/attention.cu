@@ -304,7 +304,7 @@ static int32_t attention_fwd_t(const T* qkv, const long long* mask, T* probs, T*
   }
   dim3 grid((S + ATT_QT - 1) / ATT_QT, heads, N);
   attention_fwd_kernel<T><<<grid, ATT_THREADS, smem, st>>>(qkv, mask, probs, ctx, S, heads, 0.125f, p,
-                                                          p > 0.f ? 1.f / (1.f - p) : 1.f, seed, offset,
+                                                          dropout_inv_keep(p), seed, offset,
                                                           dropout_ctr());
   return check_launch("attention_fwd");
 }
@@ -318,7 +318,7 @@ static int32_t attention_bwd_t(const T* qkv, const T* probs, const T* dctx, T* d
     attr_smem = smem;
   }
   dim3 grid((S + ATT_QT - 1) / ATT_QT, heads, N);
-  const float ik = p > 0.f ? 1.f / (1.f - p) : 1.f;
+  const float ik = dropout_inv_keep(p);
   attention_bwd_q_kernel<T><<<grid, ATT_THREADS, smem, st>>>(qkv, probs, dctx, ds, dqkv, S, heads, 0.125f, p, ik,
                                                             seed, offset, dropout_ctr());
   attention_bwd_kv_kernel<T><<<grid, ATT_THREADS, 0, st>>>(qkv, probs, ds, dctx, dqkv, S, heads, 0.125f, p, ik, seed,

@@ -1,7 +1,8 @@
 // Fused multi-head attention on tcgen05 for sm_100a (bf16 operands, fp32 accumulation in TMEM), for the
 // BertSelfAttention modules of the IMDB model (pytorch_on_language_distr.py:258-261): S in {128, 256}, head dim 64.
 //
-// One CTA (128 threads = 128 TMEM lanes = 128 rows) per (sequence, head, 128-row tile).  All three kernels share one
+// One CTA (128 TMEM lanes = 128 rows, 256 threads: warps w and w+4 share a lane quarter and split the columns) per
+// (sequence, head, 128-row tile).  All three kernels share one
 // skeleton:
 //   1. TMA loads the [rows][64] operand tiles of this head straight out of the fused-QKV activation matrix
 //      (128-byte rows, 128B swizzle) -- no head split / transpose pass ever runs;
@@ -30,6 +31,7 @@ namespace b200 {
 enum { ATT_FWD = 0, ATT_BWD_Q = 1, ATT_BWD_KV = 2 };
 constexpr int ATC_D = 64;
 constexpr int ATC_ROWS = 128;
+constexpr int ATC_THREADS = 256;           // two threads per row: each owns half of the row's score columns
 constexpr int ATC_TILE = ATC_ROWS * 128;   // bytes of one [128 rows][64 bf16] tile
 constexpr float ATC_MASKED = -1.0e30f;     // finite: a fully masked row degrades to uniform weights like the additive
                                            // finfo.min mask of the reference implementation
@@ -57,7 +59,7 @@ __host__ __device__ constexpr int att_tc_smem_bytes(int S) {
   if (MODE == ATT_FWD) bytes = a2 + S * 128;                                              // P | V   (Q,K under P)
   if (MODE == ATT_BWD_Q) bytes = (a2 > 2 * ATC_TILE + S * 128 ? a2 : 2 * ATC_TILE + S * 128) + S * 128;  // dS | K
   if (MODE == ATT_BWD_KV) bytes = 2 * a2 + 2 * S * 128;                                    // PdT dST | Q dO
-  return bytes + 2 * S * 4 + (MODE == ATT_BWD_KV ? S * 16 : 0) + 64 + 1024;
+  return bytes + 2 * S * 4 + (MODE == ATT_BWD_KV ? S * 16 : 0) + 4 * ATC_ROWS * 4 + 64 + 1024;
 }
 
 __device__ __forceinline__ void att_store_chunk32(uint8_t* tile_base, int row, int chunk32, const float (&v)[32]) {
@@ -75,27 +77,24 @@ __device__ __forceinline__ void att_store_chunk32(uint8_t* tile_base, int row, i
   }
 }
 
-// store 64 fp32 accumulator columns of this thread's row as bf16 (128 contiguous bytes in global memory)
-__device__ __forceinline__ void att_store_row64(__nv_bfloat16* dst, uint32_t taddr, float mul) {
+// store 32 fp32 accumulator columns of this thread's row as bf16 (64 contiguous bytes in global memory)
+__device__ __forceinline__ void att_store_row32(__nv_bfloat16* dst, uint32_t taddr, float mul) {
+  uint32_t r[32];
+  tmem_ld_32x32b_x32(taddr, r);
+  tmem_ld_wait();
 #pragma unroll
-  for (int h = 0; h < 2; ++h) {
-    uint32_t r[32];
-    tmem_ld_32x32b_x32(taddr + h * 32, r);
-    tmem_ld_wait();
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      uint4 u;
-      u.x = pack_bf16x2(__uint_as_float(r[8 * j + 0]) * mul, __uint_as_float(r[8 * j + 1]) * mul);
-      u.y = pack_bf16x2(__uint_as_float(r[8 * j + 2]) * mul, __uint_as_float(r[8 * j + 3]) * mul);
-      u.z = pack_bf16x2(__uint_as_float(r[8 * j + 4]) * mul, __uint_as_float(r[8 * j + 5]) * mul);
-      u.w = pack_bf16x2(__uint_as_float(r[8 * j + 6]) * mul, __uint_as_float(r[8 * j + 7]) * mul);
-      reinterpret_cast<uint4*>(dst)[h * 4 + j] = u;
-    }
+  for (int j = 0; j < 4; ++j) {
+    uint4 u;
+    u.x = pack_bf16x2(__uint_as_float(r[8 * j + 0]) * mul, __uint_as_float(r[8 * j + 1]) * mul);
+    u.y = pack_bf16x2(__uint_as_float(r[8 * j + 2]) * mul, __uint_as_float(r[8 * j + 3]) * mul);
+    u.z = pack_bf16x2(__uint_as_float(r[8 * j + 4]) * mul, __uint_as_float(r[8 * j + 5]) * mul);
+    u.w = pack_bf16x2(__uint_as_float(r[8 * j + 6]) * mul, __uint_as_float(r[8 * j + 7]) * mul);
+    reinterpret_cast<uint4*>(dst)[j] = u;
   }
 }
 
 template <int MODE>
-__global__ void __launch_bounds__(ATC_ROWS, 1)
+__global__ void __launch_bounds__(ATC_THREADS, 1)
 att_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO,
               const __grid_constant__ AttParams P) {
   extern __shared__ uint8_t smem_raw[];
@@ -106,6 +105,8 @@ att_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__
   const int a2 = ngroups * ATC_TILE;
   const int r0 = blockIdx.x * ATC_ROWS, h = blockIdx.y, n = blockIdx.z;
   const int tid = threadIdx.x, warp = tid >> 5;
+  const int lrow = tid & (ATC_ROWS - 1);      // row of the tile this thread works on (= its TMEM lane)
+  const int half = tid >> 7;                  // which half of the row's score columns it owns
   const int row_base = n * S;
 
   // shared-memory map (see att_tc_smem_bytes)
@@ -134,7 +135,9 @@ att_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__
   float* vecA = reinterpret_cast<float*>(tail);         // fwd / bwd_q: key bias [S]; bwd_kv: lse [S]
   float* vecB = vecA + S;                               // bwd_kv: D [S]
   uint32_t* bitsT = reinterpret_cast<uint32_t*>(vecB + S);  // bwd_kv: keep words [S queries][4] of this key tile
-  uint64_t* bars = reinterpret_cast<uint64_t*>(bitsT + (MODE == ATT_BWD_KV ? S * 4 : 0));   // loads, MMA 1, MMA 2
+  float* xmax = reinterpret_cast<float*>(bitsT + (MODE == ATT_BWD_KV ? S * 4 : 0));   // [2][128] row-max exchange
+  float* xsum = xmax + 2 * ATC_ROWS;                                                  // [2][128] row-sum exchange
+  uint64_t* bars = reinterpret_cast<uint64_t*>(xsum + 2 * ATC_ROWS);   // loads, MMA 1, MMA 2
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3);
 
   const uint32_t tmem_cols = MODE == ATT_FWD ? (uint32_t)S : (uint32_t)(2 * S);
@@ -187,19 +190,19 @@ att_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__
 
   // per-column vectors -> shared memory; per-row scalars -> registers (overlaps the TMA loads)
   const long long vrow = ((long long)n * P.heads + h) * S;     // base of this head's [S] vectors
-  const int row = r0 + tid;                                    // this thread's row within the sequence
+  const int row = r0 + lrow;                                   // this thread's row within the sequence
   float row_lse = 0.f, row_D = 0.f, row_bias = 0.f;
   if (MODE == ATT_BWD_KV) {
-    for (int i = tid; i < S; i += ATC_ROWS) {
+    for (int i = tid; i < S; i += ATC_THREADS) {
       vecA[i] = P.lse[vrow + i];
       vecB[i] = P.dvec[vrow + i];
     }
     row_bias = (P.mask != nullptr && P.mask[(long long)n * S + row] == 0) ? ATC_MASKED : 0.f;
     if (P.p > 0.f)
-      for (int i = tid; i < S * 4; i += ATC_ROWS)
+      for (int i = tid; i < S * 4; i += ATC_THREADS)
         bitsT[i] = P.keep_bits[(vrow + (i >> 2)) * (S / 32) + (r0 >> 5) + (i & 3)];
   } else {
-    for (int i = tid; i < S; i += ATC_ROWS)
+    for (int i = tid; i < S; i += ATC_THREADS)
       vecA[i] = (P.mask != nullptr && P.mask[(long long)n * S + i] == 0) ? ATC_MASKED : 0.f;
     if (MODE == ATT_BWD_Q) {
       row_lse = P.lse[vrow + row];
@@ -216,7 +219,7 @@ att_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__
           row_D += fa.x * fb.x + fa.y * fb.y;
         }
       }
-      P.dvec[vrow + row] = row_D;
+      if (half == 0) P.dvec[vrow + row] = row_D;
     }
   }
   __syncthreads();
@@ -248,22 +251,26 @@ att_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__
   tc_fence_after();
 
   // ---------------------------------------------------------------- row pass
-  const uint32_t trow = tmem_base + (static_cast<uint32_t>(warp * 32) << 16);
+  const uint32_t trow = tmem_base + (static_cast<uint32_t>((warp & 3) * 32) << 16);
+  const int nch = S / 32, ch0 = half * (nch / 2), ch1 = ch0 + nch / 2;   // this thread's 32-column chunks
   const long long pbase_head = ((long long)n * P.heads + h) * S;   // * S + key gives the flat probability index
   const bool drop = P.p > 0.f;
   const uint64_t rng_offset = P.offset + (P.ctr != nullptr ? *P.ctr << 40 : 0ull);
   float rmax = 0.f, rsum = 0.f;
   if (MODE == ATT_FWD) {
     rmax = -3.0e38f;
-    for (int ch = 0; ch < S / 32; ++ch) {
+    for (int ch = ch0; ch < ch1; ++ch) {
       uint32_t r[32];
       tmem_ld_32x32b_x32(trow + ch * 32, r);
       tmem_ld_wait();
 #pragma unroll
       for (int j = 0; j < 32; ++j) rmax = fmaxf(rmax, fmaf(__uint_as_float(r[j]), P.c, vecA[ch * 32 + j]));
     }
+    xmax[half * ATC_ROWS + lrow] = rmax;
+    __syncthreads();
+    rmax = fmaxf(xmax[lrow], xmax[ATC_ROWS + lrow]);
     const long long pbase = (pbase_head + row) * S;
-    for (int ch = 0; ch < S / 32; ++ch) {
+    for (int ch = ch0; ch < ch1; ++ch) {
       uint32_t r[32];
       tmem_ld_32x32b_x32(trow + ch * 32, r);
       tmem_ld_wait();
@@ -277,22 +284,18 @@ att_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__
       }
       if (drop) {
         uint32_t word = 0u;
+        const uint32_t thresh = dropout_thresh16(P.p);
 #pragma unroll
-        for (int g = 0; g < 8; ++g) {
-          float mk[4];
-          dropout_scale4(P.seed, rng_offset, pbase + ch * 32 + g * 4, P.p, 1.f, mk);
+        for (int g = 0; g < 4; ++g) word |= dropout_keep8(P.seed, rng_offset, pbase + ch * 32 + g * 8, thresh) << (g * 8);
 #pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            v[g * 4 + e] *= mk[e];
-            word |= (mk[e] != 0.f ? 1u : 0u) << (g * 4 + e);
-          }
-        }
+        for (int j = 0; j < 32; ++j) v[j] = ((word >> j) & 1u) ? v[j] : 0.f;
         P.keep_bits[(vrow + row) * (S / 32) + ch] = word;   // the backward kernels read the mask instead of Philox
       }
-      att_store_chunk32(smA2a + (ch >> 1) * ATC_TILE, tid, ch & 1, v);
+      att_store_chunk32(smA2a + (ch >> 1) * ATC_TILE, lrow, ch & 1, v);
     }
+    xsum[half * ATC_ROWS + lrow] = rsum;      // combined after the barrier that precedes the second MMA
   } else if (MODE == ATT_BWD_Q) {
-    for (int ch = 0; ch < S / 32; ++ch) {
+    for (int ch = ch0; ch < ch1; ++ch) {
       uint32_t r[32], d[32];
       tmem_ld_32x32b_x32(trow + ch * 32, r);
       tmem_ld_32x32b_x32(trow + S + ch * 32, d);
@@ -305,11 +308,11 @@ att_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__
         const float pv = exp2f(fmaf(__uint_as_float(r[j]), P.c, vecA[ch * 32 + j]) - row_lse);
         v[j] = pv * (__uint_as_float(d[j]) * keep - row_D);
       }
-      att_store_chunk32(smA2a + (ch >> 1) * ATC_TILE, tid, ch & 1, v);
+      att_store_chunk32(smA2a + (ch >> 1) * ATC_TILE, lrow, ch & 1, v);
     }
   } else {
     // rows are keys, columns are queries: bit `lane` of keep word [q][warp] is this key's mask in query row q
-    for (int ch = 0; ch < S / 32; ++ch) {
+    for (int ch = ch0; ch < ch1; ++ch) {
       uint32_t r[32], d[32];
       tmem_ld_32x32b_x32(trow + ch * 32, r);
       tmem_ld_32x32b_x32(trow + S + ch * 32, d);
@@ -319,13 +322,13 @@ att_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__
       for (int j = 0; j < 32; ++j) {
         const int q = ch * 32 + j;
         float keep = 1.f;
-        if (drop) keep = ((bitsT[q * 4 + warp] >> (tid & 31)) & 1u) ? P.inv_keep : 0.f;
+        if (drop) keep = ((bitsT[q * 4 + (warp & 3)] >> (tid & 31)) & 1u) ? P.inv_keep : 0.f;
         const float pv = exp2f(fmaf(__uint_as_float(r[j]), P.c, row_bias) - vecA[q]);
         pd[j] = pv * keep;
         ds[j] = pv * (__uint_as_float(d[j]) * keep - vecB[q]);
       }
-      att_store_chunk32(smA2a + (ch >> 1) * ATC_TILE, tid, ch & 1, pd);
-      att_store_chunk32(smA2b + (ch >> 1) * ATC_TILE, tid, ch & 1, ds);
+      att_store_chunk32(smA2a + (ch >> 1) * ATC_TILE, lrow, ch & 1, pd);
+      att_store_chunk32(smA2b + (ch >> 1) * ATC_TILE, lrow, ch & 1, ds);
     }
   }
   fence_proxy_async_smem();
@@ -357,14 +360,16 @@ att_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__
 
   // ---------------------------------------------------------------- epilogue
   const long long grow = (long long)row_base + row;
+  const int c32 = half * 32;                 // each of the row's two threads stores 32 of the 64 output columns
   if (MODE == ATT_FWD) {
-    att_store_row64(P.ctx + grow * HD + cq, trow, P.inv_keep / rsum);
-    P.lse[vrow + row] = rmax + log2f(rsum);
+    rsum = xsum[lrow] + xsum[ATC_ROWS + lrow];
+    att_store_row32(P.ctx + grow * HD + cq + c32, trow + c32, P.inv_keep / rsum);
+    if (half == 0) P.lse[vrow + row] = rmax + log2f(rsum);
   } else if (MODE == ATT_BWD_Q) {
-    att_store_row64(P.dqkv + grow * 3 * HD + cq, trow, P.scale);
+    att_store_row32(P.dqkv + grow * 3 * HD + cq + c32, trow + c32, P.scale);
   } else {
-    att_store_row64(P.dqkv + grow * 3 * HD + cv, trow, 1.f);
-    att_store_row64(P.dqkv + grow * 3 * HD + ck, trow + ATC_D, P.scale);
+    att_store_row32(P.dqkv + grow * 3 * HD + cv + c32, trow + c32, 1.f);
+    att_store_row32(P.dqkv + grow * 3 * HD + ck + c32, trow + ATC_D + c32, P.scale);
   }
   tc_fence_before();
   __syncthreads();
@@ -381,7 +386,7 @@ static int32_t att_tc_launch(const CUtensorMap& tq, const CUtensorMap& tdo, cons
     if (e != cudaSuccess) return fail(B200_CUDA_ERROR, "attention: smem attribute: %s", cudaGetErrorString(e));
     attr_smem = smem;
   }
-  att_tc_kernel<MODE><<<dim3(P.S / ATC_ROWS, P.heads, N), ATC_ROWS, smem, st>>>(tq, tdo, P);
+  att_tc_kernel<MODE><<<dim3(P.S / ATC_ROWS, P.heads, N), ATC_THREADS, smem, st>>>(tq, tdo, P);
   return check_launch("attention_flash");
 }
 
@@ -407,7 +412,7 @@ int32_t b200_attention_flash_fwd(const void* qkv, const int64_t* mask, float* ls
   if (rc) return fail(B200_CUDA_ERROR, "attention_flash_fwd: tensor map failed (%d)", rc);
   AttParams P{};
   P.S = S; P.heads = heads; P.scale = 0.125f; P.c = 0.125f * 1.4426950408889634f;
-  P.p = p_drop; P.inv_keep = p_drop > 0.f ? 1.f / (1.f - p_drop) : 1.f; P.seed = seed; P.offset = offset;
+  P.p = p_drop; P.inv_keep = dropout_inv_keep(p_drop); P.seed = seed; P.offset = offset;
   P.mask = (const long long*)mask; P.lse = lse; P.ctx = (__nv_bfloat16*)ctx; P.keep_bits = keep_bits;
   P.ctr = dropout_ctr();
   return att_tc_launch<ATT_FWD>(tq, tq, P, N, as_stream(stream));
@@ -427,7 +432,7 @@ int32_t b200_attention_flash_bwd(const void* qkv, const int64_t* mask, const flo
   if (rc) return fail(B200_CUDA_ERROR, "attention_flash_bwd: tensor map failed (%d)", rc);
   AttParams P{};
   P.S = S; P.heads = heads; P.scale = 0.125f; P.c = 0.125f * 1.4426950408889634f;
-  P.p = p_drop; P.inv_keep = p_drop > 0.f ? 1.f / (1.f - p_drop) : 1.f;
+  P.p = p_drop; P.inv_keep = dropout_inv_keep(p_drop);
   P.keep_bits = const_cast<uint32_t*>(keep_bits);
   P.mask = (const long long*)mask; P.lse = const_cast<float*>(lse); P.dvec = dvec;
   P.ctx = (__nv_bfloat16*)const_cast<void*>(ctx); P.dctx = (const __nv_bfloat16*)dctx; P.dqkv = (__nv_bfloat16*)dqkv;

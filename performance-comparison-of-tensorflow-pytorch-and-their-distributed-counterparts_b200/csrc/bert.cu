@@ -11,20 +11,35 @@
 
 namespace b200 {
 
-// multipliers (0 or 1/(1-p)) for W consecutive elements starting at flat index `base` (base % 4 == 0)
+// multipliers (0 or inv_keep) for W consecutive elements starting at flat index `base` (base % W == 0)
 template <int W>
 __device__ __forceinline__ void dropout_scale_vec(uint64_t seed, uint64_t offset, long long base, float p,
                                                   float inv_keep, float (&m)[W]) {
+  if (W == 8) {
+    const uint32_t bits = dropout_keep8(seed, offset, base, dropout_thresh16(p));
 #pragma unroll
-  for (int g = 0; g < W / 4; ++g) {
-    uint32_t r[4];
-    philox4x32_10(seed, offset + (uint64_t)(base / 4 + g), r);
+    for (int e = 0; e < W; ++e) m[e] = ((bits >> e) & 1u) ? inv_keep : 0.f;
+  } else {
+    float t[4];
+    dropout_scale4(seed, offset, base, p, inv_keep, t);
 #pragma unroll
-    for (int e = 0; e < 4; ++e) m[4 * g + e] = philox_uniform(r[e]) >= p ? inv_keep : 0.f;
+    for (int e = 0; e < 4; ++e) m[e] = t[e];
   }
 }
 
 template <typename T> __device__ __forceinline__ float round_to(float v) { return to_f(from_f<T>(v)); }
+
+// raw 16-byte vectors (kept packed while they wait in registers as the prefetch of the next row)
+__device__ __forceinline__ void unpack_vec(const float4& v, float (&f)[4]) { f[0] = v.x; f[1] = v.y; f[2] = v.z; f[3] = v.w; }
+__device__ __forceinline__ void unpack_vec(const uint4& v, float (&f)[8]) {
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 t = __bfloat1622float2(h[i]);
+    f[2 * i] = t.x;
+    f[2 * i + 1] = t.y;
+  }
+}
 
 // row statistics of v[NV][W] held by one warp: mean and 1/sqrt(var + eps) (two-pass, in registers)
 template <int NV, int W>
@@ -57,6 +72,12 @@ ln_fwd_kernel(const T* __restrict__ x, const T* __restrict__ res, T* sum_out, T*
               uint64_t offset, const unsigned long long* __restrict__ ctr) {
   constexpr int W = VecTraits<T>::W;
   constexpr int H = NV * 32 * W;
+  __shared__ __align__(16) float sg[H], sb[H];   // scalar __ldg of gamma/beta was 48 load instructions per lane and row
+  for (int i = threadIdx.x; i < H; i += blockDim.x) {
+    sg[i] = gamma[i];
+    sb[i] = beta[i];
+  }
+  __syncthreads();
   if (ctr != nullptr) offset += *ctr << 40;
   const int lane = threadIdx.x & 31;
   const long long warp = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
@@ -94,7 +115,14 @@ ln_fwd_kernel(const T* __restrict__ x, const T* __restrict__ res, T* sum_out, T*
       const int col = (lane + 32 * i) * W;
       float o_[W];
 #pragma unroll
-      for (int e = 0; e < W; ++e) o_[e] = (v[i][e] - mean) * rstd * __ldg(gamma + col + e) + __ldg(beta + col + e);
+      for (int q = 0; q < W / 4; ++q) {
+        const float4 gq = *reinterpret_cast<const float4*>(sg + col + 4 * q);
+        const float4 bq = *reinterpret_cast<const float4*>(sb + col + 4 * q);
+        o_[4 * q + 0] = (v[i][4 * q + 0] - mean) * rstd * gq.x + bq.x;
+        o_[4 * q + 1] = (v[i][4 * q + 1] - mean) * rstd * gq.y + bq.y;
+        o_[4 * q + 2] = (v[i][4 * q + 2] - mean) * rstd * gq.z + bq.z;
+        o_[4 * q + 3] = (v[i][4 * q + 3] - mean) * rstd * gq.w + bq.w;
+      }
       store_vec(y + row * H + col, o_);
     }
   }
@@ -173,7 +201,7 @@ embed_ln_fwd_kernel(const long long* __restrict__ ids, const long long* __restri
 // keeps only its own vector's three column accumulators, so the kernel stays at ~60 registers and ~24 warps per SM.
 // The two row sums cross warps through shared memory and one named barrier per row (slots alternate between rows).
 template <typename T, int TPR, int G>
-__global__ void __launch_bounds__(TPR * G)
+__global__ void __launch_bounds__(TPR * G, (TPR * G <= 384 ? 2 : 1))
 ln_bwd_kernel(const T* __restrict__ dy_a, const T* __restrict__ dy_b, const T* __restrict__ s,
               const float* __restrict__ mean_in, const float* __restrict__ rstd_in, const float* __restrict__ gamma,
               T* __restrict__ dres, T* __restrict__ dx, float* __restrict__ partials, long long rows, float p,
@@ -193,19 +221,42 @@ ln_bwd_kernel(const T* __restrict__ dy_a, const T* __restrict__ dy_b, const T* _
     gm[e] = gamma[col + e];
     ag[e] = ab[e] = ad[e] = 0.f;
   }
+  // the next row's three vectors (and its statistics) are fetched before this row's reduction barrier, so the
+  // dependent load -> reduce -> store chain of one row overlaps the memory latency of the next
+  using V = typename VecTraits<T>::V;
+  const long long stride = (long long)gridDim.x * G;
+  long long row = (long long)blockIdx.x * G + grp;
+  V na = V(), nb = V(), ns = V();
+  float nmean = 0.f, nrstd = 0.f;
+  if (row < rows) {
+    const long long o = row * H + col;
+    na = *reinterpret_cast<const V*>(dy_a + o);
+    if (dy_b != nullptr) nb = *reinterpret_cast<const V*>(dy_b + o);
+    ns = *reinterpret_cast<const V*>(s + o);
+    nmean = mean_in[row];
+    nrstd = rstd_in[row];
+  }
   int it = 0;
-  for (long long row = (long long)blockIdx.x * G + grp; row < rows; row += (long long)gridDim.x * G, ++it) {
-    const float mean = mean_in[row], rstd = rstd_in[row];
+  for (; row < rows; row += stride, ++it) {
+    const float mean = nmean, rstd = nrstd;
     const long long o = row * H + col;
     float d[W], xh[W];
-    load_vec(dy_a + o, d);
+    unpack_vec(na, d);
     if (dy_b != nullptr) {
       float tb[W];
-      load_vec(dy_b + o, tb);
+      unpack_vec(nb, tb);
 #pragma unroll
       for (int e = 0; e < W; ++e) d[e] += tb[e];
     }
-    load_vec(s + o, xh);
+    unpack_vec(ns, xh);
+    if (row + stride < rows) {
+      const long long o2 = (row + stride) * H + col;
+      na = *reinterpret_cast<const V*>(dy_a + o2);
+      if (dy_b != nullptr) nb = *reinterpret_cast<const V*>(dy_b + o2);
+      ns = *reinterpret_cast<const V*>(s + o2);
+      nmean = mean_in[row + stride];
+      nrstd = rstd_in[row + stride];
+    }
     if (drop_after && p > 0.f) {
       float m[W];
       dropout_scale_vec<W>(seed, offset, o, p, inv_keep, m);
@@ -515,7 +566,7 @@ static inline int ew_grid(long long n, int threads) {
   const long long cap = (long long)num_sms() * 8;
   return (int)(want < cap ? (want < 1 ? 1 : want) : cap);
 }
-constexpr int LN_BWD_BLOCKS_PER_SM = 3;
+constexpr int LN_BWD_BLOCKS_PER_SM = 2;
 static inline int ln_bwd_grid(long long rows) { return row_grid(rows, 2, LN_BWD_BLOCKS_PER_SM); }
 static inline int ln_nv(int H, int W) { return (H % (32 * W) == 0) ? H / (32 * W) : 0; }
 
@@ -539,7 +590,7 @@ static int32_t ln_fwd_t(const T* x, const T* res, T* sum_out, T* y, float* mean,
                         const float* beta, float eps, long long rows, int H, float p, uint64_t seed, uint64_t offset,
                         cudaStream_t st) {
   const int nv = ln_nv(H, VecTraits<T>::W);
-  const float ik = p > 0.f ? 1.f / (1.f - p) : 1.f;
+  const float ik = dropout_inv_keep(p);
   const int grid = row_grid(rows, 8, 8);
   B200_LN_DISPATCH_NV(nv, (ln_fwd_kernel<T, NV><<<grid, 256, 0, st>>>(x, res, sum_out, y, mean, rstd, gamma, beta, eps,
                                                                     rows, p, ik, seed, offset, dropout_ctr())));
@@ -552,7 +603,7 @@ static int32_t embed_fwd_t(const long long* ids, const long long* tt, const floa
                            const float* beta, float eps, long long rows, int S, int H, int vocab, float p,
                            uint64_t seed, uint64_t offset, int* status, cudaStream_t st) {
   const int nv = ln_nv(H, VecTraits<T>::W);
-  const float ik = p > 0.f ? 1.f / (1.f - p) : 1.f;
+  const float ik = dropout_inv_keep(p);
   const int grid = row_grid(rows, 8, 8);
   B200_LN_DISPATCH_NV(nv, (embed_ln_fwd_kernel<T, NV><<<grid, 256, 0, st>>>(ids, tt, word, pos, type, sum_out, y, mean,
                                                                           rstd, gamma, beta, eps, rows, S, vocab, p,
@@ -567,7 +618,7 @@ static int32_t ln_bwd_t(const T* dy_a, const T* dy_b, const T* s, const float* m
                         cudaStream_t st) {
   constexpr int W = VecTraits<T>::W;
   const int tpr = (H % (32 * W) == 0) ? H / W : 0;
-  const float ik = p > 0.f ? 1.f / (1.f - p) : 1.f;
+  const float ik = dropout_inv_keep(p);
   const int grid = ln_bwd_grid(rows);
 #define B200_LN_BWD_CASE(TPR_, G_)                                                                              \
   case TPR_:                                                                                                     \
@@ -591,7 +642,7 @@ static int32_t ln_bwd_t(const T* dy_a, const T* dy_b, const T* s, const float* m
 
 static inline int colsum_chunks(long long rows, int cols, int W) {
   const int cblocks = (cols + 32 * W - 1) / (32 * W);
-  long long chunks = (2LL * num_sms() + cblocks - 1) / cblocks;
+  long long chunks = (8LL * num_sms() + cblocks - 1) / cblocks;   // ~8 blocks per SM: enough loads in flight
   if (chunks > (rows + 63) / 64) chunks = (rows + 63) / 64;
   return (int)(chunks < 1 ? 1 : chunks);
 }
@@ -614,9 +665,7 @@ static int32_t colsum_t(const T* x, float* out, long long rows, int cols, float*
                         cudaStream_t st) {
   constexpr int W = VecTraits<T>::W;
   const int cblocks = (cols + 32 * W - 1) / (32 * W);
-  int chunks = (2 * num_sms() + cblocks - 1) / cblocks;
-  if (chunks > (rows + 63) / 64) chunks = (int)((rows + 63) / 64);
-  if (chunks < 1) chunks = 1;
+  const int chunks = colsum_chunks(rows, cols, W);
   if ((long long)chunks * cols > ws_floats) return fail(B200_WORKSPACE_TOO_SMALL, "colsum: workspace too small");
   const long long rpc = (rows + chunks - 1) / chunks;
   colsum_partial_kernel<T><<<dim3(cblocks, chunks), 256, 0, st>>>(x, ws, rows, cols, rpc);
@@ -769,7 +818,7 @@ int32_t b200_gelu_bwd_bias(const void* dy, const void* x, void* dx, float* dbias
 
 int64_t b200_colsum_workspace_bytes(int64_t rows, int32_t cols) {
   (void)rows;
-  return (int64_t)(2 * num_sms() + 8) * cols * (int64_t)sizeof(float);
+  return (int64_t)(8 * num_sms() + 8) * cols * (int64_t)sizeof(float);
 }
 
 int32_t b200_colsum(const void* x, float* out, int64_t rows, int32_t cols, int32_t dtype, void* ws, int64_t ws_bytes,

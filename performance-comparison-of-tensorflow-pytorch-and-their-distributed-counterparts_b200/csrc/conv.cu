@@ -134,6 +134,17 @@ static inline WgradPlan wgrad_plan(const b200_conv_desc* d, const ConvGeom& g) {
   // a flat problem whose output tiles already fill one wave (the 768 x 3072 Linears of BERT: 144 tiles) runs unsplit:
   // the kernel then writes the gradient in place and the slab reduction disappears
   if (is_flat(d) && ctas * 100 >= 85LL * num_sms() && ctas <= num_sms()) s = 1;
+  else if (is_flat(d) && g.M >= 4096) {
+    // big flat problems (BERT's 2304x768 and 768x768 gradients: 108 / 36 tiles): pick the split count whose
+    // rounds-per-split ratio ceil(ctas*s / SMs) / s is smallest (108 tiles: 4 splits = 2.92 waves instead of 3 = 2.19)
+    long long best = 1;
+    double best_cost = 1e30;
+    for (long long c = 1; c <= 16; ++c) {
+      const double cost = (double)((ctas * c + num_sms() - 1) / num_sms()) / (double)c + 0.01 * (double)c;
+      if (cost < best_cost - 1e-9) { best_cost = cost; best = c; }
+    }
+    s = best;
+  }
   if (s > w.pb_total) s = w.pb_total;
   if (s > 1024) s = 1024;
   const long long slab = (long long)d->K * g.ldw * 4;

@@ -28,13 +28,37 @@ __device__ __forceinline__ void philox4x32_10(uint64_t seed, uint64_t ctr, uint3
 // uniform in [0,1) from the top 24 bits
 __device__ __forceinline__ float philox_uniform(uint32_t r) { return (float)(r >> 8) * (1.0f / 16777216.0f); }
 
-// dropout multipliers (0 or 1/(1-p)) for the four consecutive elements starting at flat index `base` (base % 4 == 0)
+// ---------------------------------------------------------------- dropout masks (BERT sites)
+// One Philox call serves EIGHT consecutive elements: each 32-bit word is split into two 16-bit uniforms, compared
+// against thresh = round(p * 65536) (p is honoured to 1.5e-5; the scale is 65536 / (65536 - thresh), so the mask
+// stays exactly unbiased).  Halving the generator work matters: the LayerNorm and attention kernels were
+// instruction-bound on Philox, not bandwidth-bound (profiles/r01m_bert_ncu_full_summary.txt).
+__host__ __device__ __forceinline__ uint32_t dropout_thresh16(float p) {
+  const float t = p * 65536.f + 0.5f;
+  return t <= 0.f ? 0u : (t >= 65535.f ? 65535u : (uint32_t)t);
+}
+inline float dropout_inv_keep(float p) {
+  return p > 0.f ? 65536.f / (65536.f - (float)dropout_thresh16(p)) : 1.f;
+}
+// bit e of the result = element base+e is kept (base % 8 == 0)
+__device__ __forceinline__ uint32_t dropout_keep8(uint64_t seed, uint64_t offset, long long base, uint32_t thresh) {
+  uint32_t r[4];
+  philox4x32_10(seed, offset + (uint64_t)(base >> 3), r);
+  uint32_t bits = 0u;
+#pragma unroll
+  for (int w = 0; w < 4; ++w) {
+    bits |= ((r[w] & 0xFFFFu) >= thresh ? 1u : 0u) << (2 * w);
+    bits |= ((r[w] >> 16) >= thresh ? 1u : 0u) << (2 * w + 1);
+  }
+  return bits;
+}
+// multipliers (0 or inv_keep) for the four consecutive elements starting at `base` (base % 4 == 0): the matching
+// half of the eight-element group
 __device__ __forceinline__ void dropout_scale4(uint64_t seed, uint64_t offset, long long base, float p,
                                                float inv_keep, float (&m)[4]) {
-  uint32_t r[4];
-  philox4x32_10(seed, offset + (uint64_t)(base / 4), r);
+  const uint32_t bits = dropout_keep8(seed, offset, base & ~7LL, dropout_thresh16(p)) >> (base & 4);
 #pragma unroll
-  for (int e = 0; e < 4; ++e) m[e] = philox_uniform(r[e]) >= p ? inv_keep : 0.f;
+  for (int e = 0; e < 4; ++e) m[e] = ((bits >> e) & 1u) ? inv_keep : 0.f;
 }
 
 }  // namespace b200
