@@ -130,13 +130,19 @@ static inline WgradPlan wgrad_plan(const b200_conv_desc* d, const ConvGeom& g) {
   w.box = choose_pixel_box(w.Wq, w.Hq, w.Nq, w.bn_tile == 256 ? 64 : 128, 16, d->stride);
   w.pb_total = w.box.tiles_w * w.box.tiles_h * w.box.tiles_n;
   const long long ctas = (long long)((g.RSC + w.bn_tile - 1) / w.bn_tile) * ((d->K + 127) / 128);
-  long long s = (2LL * num_sms() + ctas - 1) / ctas;
-  // a flat problem whose output tiles already fill one wave (the 768 x 3072 Linears of BERT: 144 tiles) runs unsplit:
-  // the kernel then writes the gradient in place and the slab reduction disappears
-  if (is_flat(d) && ctas * 100 >= 85LL * num_sms() && ctas <= num_sms()) s = 1;
-  else if (is_flat(d) && g.M >= 4096) {
-    // big flat problems (BERT's 2304x768 and 768x768 gradients: 108 / 36 tiles): pick the split count whose
-    // rounds-per-split ratio ceil(ctas*s / SMs) / s is smallest (108 tiles: 4 splits = 2.92 waves instead of 3 = 2.19)
+  long long s = (2LL * num_sms() + ctas - 1) / ctas;   // two waves of work items: measured best for the conv layers
+  // Linear layers (a true [tokens][features] matrix: N = H = 1, thousands of rows; BERT) are tuned separately --
+  // measured on the 768/2304/3072-wide layers at 8192 tokens.  The same rules applied to ResNet's 1x1 convolutions
+  // cost 1.7 ms per step (A/B: 14.08 vs 15.83 ms), so they stay on the two-wave rule.
+  static const bool old_splits = getenv("B200_WGRAD_OLD_SPLITS") != nullptr;
+  const bool linear = is_flat(d) && d->N == 1 && d->H == 1 && g.M >= 4096 && !old_splits;
+  if (linear && ctas * 100 >= 85LL * num_sms() && ctas <= num_sms()) {
+    // the output tiles already fill one wave (768 x 3072: 144 tiles): run unsplit, the kernel then writes the
+    // gradient in place and the slab reduction disappears
+    s = 1;
+  } else if (linear) {
+    // 2304x768 / 768x768 gradients (108 / 36 tiles): the split count with the smallest rounds-per-split ratio
+    // ceil(ctas*s / SMs) / s (108 tiles: 4 splits = 2.92 waves instead of 3 splits = 2.19 waves)
     long long best = 1;
     double best_cost = 1e30;
     for (long long c = 1; c <= 16; ++c) {
@@ -186,6 +192,13 @@ static inline void timing_end(cudaEvent_t e0, cudaEvent_t e1, double flops, cuda
   launch_counter() += 1;
 }
 
+// Column-tile width of fprop / dgrad: as wide as the output allows.  (Measured on BERT's 768-column Linears, which
+// fill only 1.3 waves with 256-wide tiles: 128-wide tiles = 2.6 waves of half the work are 25-30 % SLOWER, e.g. FFN2
+// forward 39.5 -> 50.9 us -- the kernel is bound by operand traffic from L2 per MMA, which narrower tiles raise.)
+static inline int pick_bn(const b200_conv_desc*, const ConvGeom&, int cols) {
+  return cols > 128 ? 256 : (cols > 64 ? 128 : 64);
+}
+
 // fprop (mode 0) and dgrad (mode 1) of one pixel grid / tap set
 static inline PixelBox fprop_box(const b200_conv_desc* d, const ConvGeom& g) {
   const bool flat = is_flat(d);
@@ -213,7 +226,7 @@ static int32_t implicit_fprop(const b200_conv_desc* d, const ConvGeom& g, const 
   int rc = flat ? make_tmap_bf16_nhwc(&ta, x, 1, 1, (int)g.M, d->C, b.bw, b.bh, b.bn, 1)
                 : make_tmap_bf16_nhwc(&ta, x, d->N, d->H, d->W, d->C, b.bw, b.bh, b.bn, d->stride);
   if (rc) return fail(B200_CUDA_ERROR, "conv_fprop: activation tensor map failed (%d)", rc);
-  const int bn = d->K > 128 ? 256 : (d->K > 64 ? 128 : 64);
+  const int bn = pick_bn(d, g, d->K);
   rc = make_tmap_bf16_2d(&tb, w, g.RSC, d->K, g.ldw, 64, bn);
   if (rc) return fail(B200_CUDA_ERROR, "conv_fprop: weight tensor map failed (%d)", rc);
   const long long tiles = (long long)b.tiles_w * b.tiles_h * b.tiles_n;
@@ -244,7 +257,7 @@ static int32_t implicit_dgrad(const b200_conv_desc* d, const ConvGeom& g, const 
   CUtensorMap tb;
   int rc = make_tmap_bf16_2d(&tb, w, g.RSC, d->K, g.ldw, 64, 64);
   if (rc) return fail(B200_CUDA_ERROR, "conv_dgrad: weight tensor map failed (%d)", rc);
-  const int bn = d->C > 128 ? 256 : (d->C > 64 ? 128 : 64);
+  const int bn = pick_bn(d, g, d->C);
   const int classes = d->stride == 1 ? 1 : 4;
   for (int cls = 0; cls < classes; ++cls) {
     const int ph = d->stride == 1 ? 0 : cls / 2, pw = d->stride == 1 ? 0 : cls % 2;
@@ -504,7 +517,7 @@ extern "C" int64_t b200_conv_fprop_bnstats_rows(const b200_conv_desc* d) {
   if (off || !implicit_ok(d)) return 0;
   const ConvGeom g = geom(d);
   const PixelBox b = fprop_box(d, g);
-  const int bn = d->K > 128 ? 256 : (d->K > 64 ? 128 : 64);
+  const int bn = pick_bn(d, g, d->K);
   const int n_tiles = (d->K + bn - 1) / bn;
   const long long total = (long long)b.tiles_w * b.tiles_h * b.tiles_n * n_tiles;
   if (total > 0x7fffffffLL) return 0;
