@@ -224,6 +224,10 @@ int32_t b200_bucket_pack(int32_t n, const float* const* srcs, const int64_t* siz
                          void* stream);
 int32_t b200_bucket_unpack(int32_t n, float* const* dsts, const int64_t* sizes, const float* flat, float scale,
                            void* stream);
+/* dst_i = src_i * scale for n independent tensor pairs, 48 pairs per launch: how the captured backward graphs move
+ * a whole segment's gradients into their (non-adjacent) bucket slices with a handful of launches */
+int32_t b200_multi_tensor_copy(int32_t n, float* const* dsts, const float* const* srcs, const int64_t* sizes,
+                               float scale, void* stream);
 
 /* ------------------------------------------------------------------ BERT-base encoder (IMDB fine-tuning step)
  * model = BertForSequenceClassification.from_pretrained("bert-base-uncased", num_labels=2, ...)

@@ -83,6 +83,7 @@ SIGNATURES = {
     "b200_multi_tensor_zero": (I32, [I32, _PP, _PI64, P]),
     "b200_bucket_pack": (I32, [I32, _PP, _PI64, P, F, P]),
     "b200_bucket_unpack": (I32, [I32, _PP, _PI64, P, F, P]),
+    "b200_multi_tensor_copy": (I32, [I32, _PP, _PP, _PI64, F, P]),
     "b200_dropout_counter": (I32, [P]),
     "b200_embed_ln_fwd": (I32, [P, P, P, P, P, P, P, F, I32, I32, I32, I32, I32, F, U64, U64, P, P, P, P, P, I32, P]),
     "b200_embed_bwd": (I32, [P, P, P, I32, I32, I32, I32, I32, P, P, P, P, I64, I32, P]),

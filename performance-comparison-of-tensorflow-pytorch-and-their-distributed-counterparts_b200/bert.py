@@ -306,7 +306,7 @@ def _encoder_fwd(model, ids, type_ids, mask, save, training, call=None):
     return cls, st
 
 
-def _encoder_bwd(model, st, dcls, emit, release=True):
+def _encoder_bwd(model, st, dcls, emit, release=True, cut=None, cut_every=0):
     """Reverse walk over the saved activations; emit(param, grad) is called as soon as a gradient is enqueued.
     release=False keeps the saved activations referenced (a captured graph replays over them)."""
     c = model.config
@@ -317,6 +317,8 @@ def _encoder_bwd(model, st, dcls, emit, release=True):
     dh_b = None
     layers = model.bert.encoder.layer
     for li in range(len(layers) - 1, -1, -1):
+        if cut is not None and cut_every and li != len(layers) - 1 and (len(layers) - 1 - li) % cut_every == 0:
+            cut()         # graph capture under DDP: a new segment starts here
         L = layers[li]
         a, o = L.attention, L.output
         h_in, qkv, probs, ctx, s1, m1, r1, h1, pre, act, s2, m2, r2 = st.layers[li]
@@ -382,7 +384,7 @@ F._GRAPH_CACHES.extend([_BG, _BG_SEEN])
 
 class _BertGraph(object):
     __slots__ = ("fwd", "bwd", "ids", "tt", "mask", "cls", "dcls", "grads", "ctr", "state", "ptrs", "keep", "uses",
-                 "ddp", "order")
+                 "ddp", "order", "segments")
 
 
 def _graph_key(model, ids, tt, mask, params):
@@ -418,20 +420,36 @@ def _capture(model, ids, tt, mask, params, key):
         with torch.no_grad():
             with torch.cuda.graph(rec.fwd, pool=pool):
                 rec.cls, rec.state = _encoder_fwd(model, rec.ids, rec.tt, rec.mask, save, model.training, call=0)
-        rec.bwd, rec.grads, rec.dcls, rec.ddp, rec.order = None, None, None, None, None
+        rec.bwd, rec.grads, rec.dcls, rec.ddp, rec.order, rec.segments = None, None, None, None, None, None
         if save:
             rec.dcls = torch.zeros_like(rec.cls)
             grads = {}
             rec.ddp, rec.order = F.grad_sink_owner(), []
+            pending = []
 
             def emit(p, g):
                 if p.requires_grad:
-                    grads[id(p)] = g if rec.ddp is None else rec.ddp._sink_capture(p, g, rec.order)
+                    grads[id(p)] = g if rec.ddp is None else rec.ddp._sink_capture(p, g, rec.order, pending)
 
-            rec.bwd = torch.cuda.CUDAGraph()
-            with torch.no_grad():
-                with torch.cuda.graph(rec.bwd, pool=pool):
-                    _encoder_bwd(model, rec.state, rec.dcls, emit, release=False)
+            if rec.ddp is None:
+                rec.bwd = torch.cuda.CUDAGraph()
+                with torch.no_grad():
+                    with torch.cuda.graph(rec.bwd, pool=pool):
+                        _encoder_bwd(model, rec.state, rec.dcls, emit, release=False)
+            else:
+                # DDP: one graph per three encoder layers; the buckets a segment completed are all-reduced while the
+                # next segment runs
+                def cut():
+                    rec.ddp.flush_pending(pending)      # this segment's gradients -> bucket slices, one launch per 48
+                    sc.cut(lambda: len(rec.order))
+
+                with torch.no_grad():
+                    with F._SegmentedCapture(pool) as sc:
+                        _encoder_bwd(model, rec.state, rec.dcls, emit, release=False, cut=cut, cut_every=3)
+                        rec.ddp.flush_pending(pending)
+                bounds = [0] + list(sc.marks) + [len(rec.order)]
+                rec.segments = [(g, rec.order[bounds[i]:bounds[i + 1]]) for i, g in enumerate(sc.graphs)]
+                rec.bwd = sc.graphs[0]
             rec.grads = [grads.get(id(p)) for p in params]
         rec.keep = (dict(ops._WS), list(_CAPTURE_PK.values()), [e[1] for e in _PK.values()])
     finally:
@@ -464,10 +482,12 @@ class _GraphedEncoder(torch.autograd.Function):
         if rec.bwd is None:
             raise RuntimeError("b200net: this encoder graph was captured without a backward pass")
         rec.dcls.copy_(dcls)
-        rec.bwd.replay()
         if rec.ddp is not None:
-            rec.ddp._replayed(rec.order)      # buckets are complete: launch their all-reduces in the fixed order
+            for g, ready in rec.segments:
+                g.replay()
+                rec.ddp._replayed(ready)      # completed buckets start their all-reduce while the next segment runs
             return (None, None, None, None) + tuple(rec.grads)
+        rec.bwd.replay()
         # gradients live in graph-owned memory that the next replay overwrites; with zero_grad -> backward -> step
         # they are consumed before that.  A parameter that still holds a .grad gets a private copy.
         out = [None if g is None else (g if p.grad is None else g.clone())

@@ -288,6 +288,20 @@ extern "C" int32_t b200_bucket_unpack(int32_t n, float* const* dsts, const int64
   return check_launch("bucket_unpack", nlaunch);
 }
 
+extern "C" int32_t b200_multi_tensor_copy(int32_t n, float* const* dsts, const float* const* srcs,
+                                          const int64_t* sizes, float scale, void* stream) {
+  if (n <= 0 || !dsts || !srcs || !sizes) return fail(B200_INVALID_ARG, "multi_tensor_copy: bad arguments");
+  cudaStream_t st = as_stream(stream);
+  int nlaunch = 0;
+  MT_FOREACH_CHUNK(n, {
+    for (int i = 0; i < cnt; ++i) {
+      t.a[i] = dsts[lo + i]; t.b[i] = (void*)srcs[lo + i]; t.c[i] = t.d[i] = nullptr; t.n[i] = sizes[lo + i];
+    }
+    mt_copy_scale_kernel<<<dim3(mt_blocks(sizes, lo, hi, 2 * num_sms()), cnt), MT_THREADS, 0, st>>>(t, scale);
+  })
+  return check_launch("multi_tensor_copy", nlaunch);
+}
+
 namespace b200 {
 long long& launch_counter() {
   static long long n = 0;

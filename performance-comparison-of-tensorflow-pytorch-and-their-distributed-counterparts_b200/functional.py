@@ -233,7 +233,7 @@ def _backbone_fwd(model, x, save, x_needs_grad):
     return feat, st
 
 
-def _backbone_bwd(st, dfeat, params, param_needs, x_needs_grad, sink):
+def _backbone_bwd(st, dfeat, params, param_needs, x_needs_grad, sink, cut=None, cut_after=()):
     """Reverse walk: BN backward (mask from the saved byte mask) -> wgrad -> dgrad; the block-input gradient is the
     residual gradient with conv1's dgrad accumulated in the GEMM epilogue.  Returns (dx or None, [grad per param])."""
     dfeat = dfeat.contiguous().float()
@@ -272,7 +272,9 @@ def _backbone_bwd(st, dfeat, params, param_needs, x_needs_grad, sink):
         return ops.conv_dgrad(dy, wp, u.x.shape, K, R, S, stride, pad, out=out, accumulate=accumulate)
 
     dcur = ops.avgpool_bwd(dfeat, st.final_shape, st.dtype)
-    for (u1, u2, u3, ud) in reversed(st.blocks):
+    for bi, (u1, u2, u3, ud) in enumerate(reversed(st.blocks)):
+        if cut is not None and bi in cut_after:
+            cut()         # graph capture under DDP: a new segment starts here (see _SegmentedCapture)
         dy3, g = unit_backward(u3, dcur, want_dres=True)
         dz2 = dgrad(u3, dy3)
         dy2, _ = unit_backward(u2, dz2, want_dres=False)
@@ -350,8 +352,49 @@ def set_cuda_graphs(on):
             c.clear()
 
 
+class _SegmentedCapture(object):
+    """Captures one launch sequence into SEVERAL CUDA graphs (one private pool), split wherever the sequence calls
+    cut().  Under DistributedDataParallel the backward is replayed segment by segment and the gradient buckets that
+    a segment completed are all-reduced on the communication stream while the next segment runs."""
+
+    def __init__(self, pool):
+        self.pool, self.graphs, self.cur, self.marks = pool, [], None, []
+        self.stream = torch.cuda.Stream()
+
+    def __enter__(self):
+        torch.cuda.synchronize()
+        self.stream.wait_stream(torch.cuda.current_stream())
+        self._ctx = torch.cuda.stream(self.stream)
+        self._ctx.__enter__()
+        self._begin()
+        return self
+
+    def _begin(self):
+        self.cur = torch.cuda.CUDAGraph()
+        self.cur.capture_begin(pool=self.pool)
+
+    def cut(self, mark=None):
+        self.cur.capture_end()
+        self.graphs.append(self.cur)
+        self.marks.append(mark() if mark is not None else None)
+        self._begin()
+
+    def __exit__(self, et, ev, tb):
+        try:
+            if self.cur is not None:
+                self.cur.capture_end()
+                if et is None:
+                    self.graphs.append(self.cur)
+                self.cur = None
+        finally:
+            self._ctx.__exit__(et, ev, tb)
+            torch.cuda.current_stream().wait_stream(self.stream)
+        return False
+
+
 class _GraphRecord(object):
-    __slots__ = ("fwd", "bwd", "x", "feat", "dfeat", "grads", "dx", "state", "ptrs", "ws", "uses", "ddp", "order")
+    __slots__ = ("fwd", "bwd", "x", "feat", "dfeat", "grads", "dx", "state", "ptrs", "ws", "uses", "ddp", "order",
+                 "segments")
 
 
 def _graph_key(model, x, params, needs_x):
@@ -388,15 +431,37 @@ def _capture(model, x, params, key):
         with torch.no_grad():
             with torch.cuda.graph(rec.fwd, pool=pool):
                 rec.feat, rec.state = _backbone_fwd(model, rec.x, save, needs_x)
-        rec.bwd, rec.ddp, rec.order = None, None, None
+        rec.bwd, rec.ddp, rec.order, rec.segments = None, None, None, None
         if save:
             rec.dfeat = torch.zeros_like(rec.feat)
-            rec.bwd = torch.cuda.CUDAGraph()
             rec.ddp, rec.order = grad_sink_owner(), []
-            sink = None if rec.ddp is None else (lambda p, g: rec.ddp._sink_capture(p, g, rec.order))
-            with torch.no_grad():
-                with torch.cuda.graph(rec.bwd, pool=pool):
-                    rec.dx, rec.grads = _backbone_bwd(rec.state, rec.dfeat, params, list(needs), needs_x, sink)
+            if rec.ddp is None:
+                rec.bwd = torch.cuda.CUDAGraph()
+                with torch.no_grad():
+                    with torch.cuda.graph(rec.bwd, pool=pool):
+                        rec.dx, rec.grads = _backbone_bwd(rec.state, rec.dfeat, params, list(needs), needs_x, None)
+            else:
+                # DDP: one graph per stage group (layer4 | layer3 | the rest).  layer4 + layer3 hold 87 % of the
+                # parameters and finish first, so their buckets travel while layer2 / layer1 / stem (most of the
+                # backward's time at this resolution) are still running.
+                pending = []
+                sink = lambda p, g: rec.ddp._sink_capture(p, g, rec.order, pending)   # noqa: E731
+                n4 = len(getattr(model, "layer4", ()))
+                n3 = len(getattr(model, "layer3", ()))
+                cuts = tuple(c for c in (n4, n4 + n3) if 0 < c < len(rec.state.blocks))
+
+                def cut():
+                    rec.ddp.flush_pending(pending)      # this segment's gradients -> bucket slices, one launch per 48
+                    sc.cut(lambda: len(rec.order))
+
+                with torch.no_grad():
+                    with _SegmentedCapture(pool) as sc:
+                        rec.dx, rec.grads = _backbone_bwd(rec.state, rec.dfeat, params, list(needs), needs_x, sink,
+                                                          cut=cut, cut_after=cuts)
+                        rec.ddp.flush_pending(pending)
+                bounds = [0] + list(sc.marks) + [len(rec.order)]
+                rec.segments = [(g, rec.order[bounds[i]:bounds[i + 1]]) for i, g in enumerate(sc.graphs)]
+                rec.bwd = sc.graphs[0]
         rec.ws = (dict(ops._WS), [e[3] for e in _PACKED.values()])   # raw pointers captured: keep the memory alive
     finally:
         _CAPTURING[0] = False
@@ -421,10 +486,12 @@ class _GraphedBackbone(torch.autograd.Function):
         if rec.bwd is None:
             raise RuntimeError("b200net: this backbone graph was captured without a backward pass")
         rec.dfeat.copy_(dfeat)
-        rec.bwd.replay()
         if rec.ddp is not None:
-            rec.ddp._replayed(rec.order)      # buckets are complete: launch their all-reduces in the fixed order
+            for g, ready in rec.segments:
+                g.replay()
+                rec.ddp._replayed(ready)      # completed buckets start their all-reduce while the next segment runs
             return (None, rec.dx.clone() if rec.dx is not None else None) + tuple(rec.grads)
+        rec.bwd.replay()
         # The gradients live in graph-owned memory that the next replay overwrites.  With the usual
         # zero_grad() -> backward() -> step() cycle they are consumed before that, so they are handed out as they
         # are; a parameter that still holds a .grad (gradient accumulation) gets a private copy instead, because
