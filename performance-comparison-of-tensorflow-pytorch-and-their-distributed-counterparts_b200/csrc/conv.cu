@@ -161,6 +161,20 @@ static inline WgradPlan wgrad_plan(const b200_conv_desc* d, const ConvGeom& g) {
   return w;
 }
 
+// CTA pairs (tcgen05 cta_group::2) for 256-wide fprop / dgrad tiles: each CTA of a cluster loads half of the B tile and
+// the leader issues one M = 256 MMA for both (conv_sm100_kernel<..., CG = 2>, validated by tools/umma2sm_probe.cu and
+// tests/test_kernels_gpu.py::test_cta_pair_kernels).  OPT-IN (B200_2SM=1): measured on BERT's Linears it is not
+// faster than the single-CTA kernel (fprop 31.0 -> 35.2 us, dgrad 34.6 -> 33.6 us at 8192 x 768 x 2304/3072) -- those
+// GEMMs already run at 1.0-1.15 PFLOP/s against a measured sustained cuBLAS peak of 1.38, so B-operand traffic per SM
+// was not the limiter it looked like.  Not combined with the fused BatchNorm statistics (their per-CTA partial rows
+// assume the single-CTA tile walk).
+static inline int pair_items(int bn, long long pixel_tiles, int n_tiles, bool stats) {
+  static const bool on = getenv("B200_2SM") != nullptr;
+  if (!on || bn != 256 || stats || pixel_tiles < 2) return 0;
+  const long long items = ((pixel_tiles + 1) / 2) * n_tiles;
+  return items > 0x3fffffffLL ? 0 : (int)items;
+}
+
 template <int MODE>
 static int launch_conv_mode(int bn, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to,
                             const ConvParams& P, cudaStream_t st) {
@@ -169,6 +183,7 @@ static int launch_conv_mode(int bn, const CUtensorMap& ta, const CUtensorMap& tb
     if (bn == 256) return launch_conv_cfg<256, 4, MODE>(ta, tb, to, P, ctas, st);
     return launch_conv_cfg<128, 3, MODE>(ta, tb, to, P, ctas, st);
   } else {
+    if (bn == 256 && P.total_pairs > 0) return launch_conv_cfg<256, 5, MODE, 2>(ta, tb, to, P, ctas, st);   // CTA pairs
     if (bn == 256) return launch_conv_cfg<256, 4, MODE>(ta, tb, to, P, ctas, st);
     if (bn == 128) return launch_conv_cfg<128, 6, MODE>(ta, tb, to, P, ctas, st);
     return launch_conv_cfg<64, 7, MODE>(ta, tb, to, P, ctas, st);
@@ -227,10 +242,11 @@ static int32_t implicit_fprop(const b200_conv_desc* d, const ConvGeom& g, const 
                 : make_tmap_bf16_nhwc(&ta, x, d->N, d->H, d->W, d->C, b.bw, b.bh, b.bn, d->stride);
   if (rc) return fail(B200_CUDA_ERROR, "conv_fprop: activation tensor map failed (%d)", rc);
   const int bn = pick_bn(d, g, d->K);
-  rc = make_tmap_bf16_2d(&tb, w, g.RSC, d->K, g.ldw, 64, bn);
-  if (rc) return fail(B200_CUDA_ERROR, "conv_fprop: weight tensor map failed (%d)", rc);
   const long long tiles = (long long)b.tiles_w * b.tiles_h * b.tiles_n;
   P.n_tiles = (d->K + bn - 1) / bn;
+  P.total_pairs = pair_items(bn, tiles, P.n_tiles, stats != nullptr);
+  rc = make_tmap_bf16_2d(&tb, w, g.RSC, d->K, g.ldw, 64, P.total_pairs > 0 ? bn / 2 : bn);   // a pair CTA loads half
+  if (rc) return fail(B200_CUDA_ERROR, "conv_fprop: weight tensor map failed (%d)", rc);
   P.m_tiles = 1;
   if (tiles * P.n_tiles > 0x7fffffffLL) return fail(B200_UNSUPPORTED, "conv_fprop: too many tiles");
   P.total_tiles = (int)(tiles * P.n_tiles);
@@ -299,6 +315,7 @@ static int32_t implicit_dgrad(const b200_conv_desc* d, const ConvGeom& g, const 
     P.m_tiles = 1;
     if (tiles * P.n_tiles > 0x7fffffffLL) return fail(B200_UNSUPPORTED, "conv_dgrad: too many tiles");
     P.total_tiles = (int)(tiles * P.n_tiles);
+    P.total_pairs = pair_items(bn, tiles, P.n_tiles, false);
     CUtensorMap to;
     static const bool no_tma_store = getenv("B200_NO_TMA_STORE") != nullptr;
     // strided (parity-class) outputs keep the per-thread store path; accumulation uses the TMA reduce-add

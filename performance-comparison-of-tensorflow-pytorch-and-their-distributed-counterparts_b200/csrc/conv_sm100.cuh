@@ -54,6 +54,7 @@ struct ConvParams {
   // persistent tile walk: tile = n_tile + n_tiles * (pixel tile | m_tile + m_tiles * (tap*nsplits + split))
   int n_tiles, m_tiles, total_tiles;
   int n_inner;                       // wgrad: column tiles per tap (n_tiles = n_inner * tap groups)
+  int total_pairs;                   // CTA-pair kernels (CG = 2): ceil(pixel tiles / 2) * n_tiles work items per pair
   int tma_store;                     // fprop/dgrad: bf16 output written by TMA from a swizzled smem staging tile
   const float* ep_scale;             // fprop + tma_store (eval-mode BatchNorm folded into the epilogue):
   const float* ep_shift;             //   out = act(acc * ep_scale[col] + ep_shift[col]), act = ReLU when ep_relu
@@ -66,10 +67,10 @@ struct ConvParams {
 // wgrad stage geometry: 128-column tiles use 128-pixel k-blocks, 256-column tiles 64-pixel k-blocks (same bytes)
 #define CONV_WGRAD_KR(BN_) ((BN_) == 256 ? 64 : 128)
 
-template <int BN, int STAGES, int MODE>
+template <int BN, int STAGES, int MODE, int CG = 1>
 constexpr int conv_smem_bytes() {
   constexpr int a = MODE == MODE_WGRAD ? 2 * CONV_WGRAD_KR(BN) * 128 : GEMM_BM * 128;
-  constexpr int b = MODE == MODE_WGRAD ? (BN / 64) * CONV_WGRAD_KR(BN) * 128 : BN * 128;
+  constexpr int b = MODE == MODE_WGRAD ? (BN / 64) * CONV_WGRAD_KR(BN) * 128 : BN * 128 / CG;
   return STAGES * (a + b) + (MODE == MODE_WGRAD ? 0 : CONV_STAGING_BYTES + CONV_STATS_RED_BYTES) + 1024 + 256;
 }
 
@@ -117,12 +118,19 @@ __device__ __forceinline__ ConvTile conv_decode_tile(const ConvParams& P, int ti
   return t;
 }
 
-template <int BN, int STAGES, int MODE>
+// CG = 2 (fprop / dgrad, BN = 256): the CTA PAIR of a cluster shares one M = 256 MMA (tcgen05 cta_group::2).  Each
+// CTA keeps its own pixel tile (A, accumulator, epilogue) but loads only HALF of the B tile -- the leader's MMA reads
+// both halves -- so a k-block costs 16 + 16 KB of L2->SM traffic per CTA instead of 16 + 32 KB: the 128x256 tile was
+// operand-traffic bound.  TMA completions of both CTAs are counted on the leader's `full` barrier, tcgen05.commit is
+// multicast to both CTAs' `empty` / `tmem_full` barriers, and both CTAs' epilogue warps release the accumulator on
+// the leader's `tmem_empty` barrier.
+template <int BN, int STAGES, int MODE, int CG = 1>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                   const __grid_constant__ CUtensorMap tmO, const __grid_constant__ ConvParams P) {
   constexpr int A_BYTES = MODE == MODE_WGRAD ? 2 * CONV_WGRAD_KR(BN) * 128 : GEMM_BM * 128;
-  constexpr int B_BYTES = MODE == MODE_WGRAD ? (BN / 64) * CONV_WGRAD_KR(BN) * 128 : BN * 128;
+  constexpr int B_BYTES = MODE == MODE_WGRAD ? (BN / 64) * CONV_WGRAD_KR(BN) * 128 : BN * 128 / CG;
+  static_assert(CG == 1 || (CG == 2 && MODE != MODE_WGRAD && BN == 256), "CTA pairs: fprop / dgrad with 256-wide tiles");
   constexpr int STG_BYTES = MODE == MODE_WGRAD ? 0 : CONV_STAGING_BYTES + CONV_STATS_RED_BYTES;
   constexpr uint32_t TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;   // two accumulators
   static_assert(2 * BN <= 512, "two accumulators must fit TMEM");
@@ -142,6 +150,16 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  // persistent walk: CTA b takes tiles b, b + grid, ...; a CTA pair takes pair items c, c + clusters, ... where item
+  // w = (column tile w % n_tiles, pixel-tile pair w / n_tiles) and rank r of the pair owns pixel tile 2*pair + r
+  const int rank = CG == 2 ? (int)cluster_ctarank() : 0;
+  const int walk_id = CG == 2 ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int walk_n = CG == 2 ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+  const int walk_total = CG == 2 ? P.total_pairs : P.total_tiles;
+  auto tile_of = [&](int w) -> int {
+    if (CG == 1) return w;
+    return (w % P.n_tiles) + P.n_tiles * (2 * (w / P.n_tiles) + rank);
+  };
   const uint32_t box_bytes = static_cast<uint32_t>(P.bw * P.bh * P.bn) * 128u;
 
   if (threadIdx.x == 0) {
@@ -156,16 +174,23 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 #pragma unroll
     for (int b = 0; b < 2; ++b) {
       mbar_init(&tmem_full[b], 1);
-      mbar_init(&tmem_empty[b], 4);   // one arrive per epilogue warp
+      mbar_init(&tmem_empty[b], 4 * CG);   // one arrive per epilogue warp (of both CTAs of a pair)
     }
     mbar_fence_init();
   }
+  if (CG == 2) cluster_sync_all();      // both CTAs' barriers exist before anything remote touches them
   if (warp == 1) {
-    tmem_alloc(tmem_slot, TMEM_COLS);
-    tmem_relinquish();
+    if (CG == 2) {
+      tmem_alloc_2sm(tmem_slot, TMEM_COLS);
+      tmem_relinquish_2sm();
+    } else {
+      tmem_alloc(tmem_slot, TMEM_COLS);
+      tmem_relinquish();
+    }
   }
   tc_fence_before();
-  __syncthreads();
+  if (CG == 2) cluster_sync_all();
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -174,7 +199,8 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     if (lane == 0) {
       int stage = 0;          // ring position and phase run continuously across tiles
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < P.total_tiles; tile += gridDim.x) {
+      for (int w = walk_id; w < walk_total; w += walk_n) {
+        const int tile = tile_of(w);
         const ConvTile T = conv_decode_tile<BN, MODE>(P, tile);
         if (MODE != MODE_WGRAD) {
           // taps x 64-channel chunks, no per-k-block division; stage index / phase carried incrementally
@@ -185,6 +211,19 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
               mbar_wait(&empty[stage], phase ^ 1);
               uint8_t* a = smA + stage * A_BYTES;
               uint8_t* b = smB + stage * B_BYTES;
+              if (CG == 2) {
+                // bytes of BOTH CTAs land on the leader's barrier; each CTA brings its pixel box and its half of B
+                if (rank == 0) mbar_expect_tx(&full[stage], 2 * (box_bytes + B_BYTES));
+                tma_load_4d_2sm(a, &tmA, &full[stage], cc * 64, aw, ah, T.i0);
+                if (MODE == MODE_FPROP) {
+                  tma_load_2d_2sm(b, &tmB, &full[stage], bcol + cc * 64, T.n0 + rank * (BN / 2));  // {64 c, BN/2 cout}
+                } else {
+#pragma unroll
+                  for (int h = 0; h < BN / 128; ++h)
+                    tma_load_2d_2sm(b + h * 8192, &tmB, &full[stage], bcol + T.n0 + (rank * (BN / 128) + h) * 64,
+                                    cc * 64);
+                }
+              } else {
               mbar_expect_tx(&full[stage], box_bytes + B_BYTES);
               tma_load_4d(a, &tmA, &full[stage], cc * 64, aw, ah, T.i0);
               if (MODE == MODE_FPROP) {
@@ -193,6 +232,7 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 #pragma unroll
                 for (int h = 0; h < BN / 64; ++h)
                   tma_load_2d(b + h * 8192, &tmB, &full[stage], bcol + T.n0 + h * 64, cc * 64);  // {64 cin, 64 k}
+              }
               }
               if (++stage == STAGES) { stage = 0; phase ^= 1; }
             }
@@ -253,12 +293,13 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     __syncwarp();
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer
-    if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc_bf16(GEMM_BM, BN, MODE == MODE_WGRAD, MODE != MODE_FPROP);
+    if (lane == 0 && rank == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(GEMM_BM * CG, BN, MODE == MODE_WGRAD, MODE != MODE_FPROP);
       int stage = 0;
       uint32_t phase = 0;
       uint32_t it = 0;   // local tile counter
-      for (int tile = blockIdx.x; tile < P.total_tiles; tile += gridDim.x, ++it) {
+      for (int w = walk_id; w < walk_total; w += walk_n, ++it) {
+        const int tile = tile_of(w);
         const ConvTile T = conv_decode_tile<BN, MODE>(P, tile);
         const uint32_t buf = it & 1, use = it >> 1;
         mbar_wait(&tmem_empty[buf], (use & 1) ^ 1);   // epilogue has drained this accumulator
@@ -278,7 +319,8 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
               const uint64_t adesc = umma_smem_desc(a_addr + k * 32, 16, 1024);
               const uint64_t bdesc = MODE == MODE_FPROP ? umma_smem_desc(b_addr + k * 32, 16, 1024)
                                                         : umma_smem_desc(b_addr + k * 2048, 8192, 1024);
-              umma_f16(d_tmem, adesc, bdesc, idesc, (!first || k > 0) ? 1u : 0u);
+              if (CG == 2) umma_f16_2sm(d_tmem, adesc, bdesc, idesc, (!first || k > 0) ? 1u : 0u);
+              else umma_f16(d_tmem, adesc, bdesc, idesc, (!first || k > 0) ? 1u : 0u);
             }
           } else {
             const int ksteps = P.kr >> 4;
@@ -289,9 +331,11 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             }
           }
           first = false;
-          umma_commit(&empty[s]);
+          if (CG == 2) umma_commit_2sm(&empty[s]);
+          else umma_commit(&empty[s]);
         }
-        umma_commit(&tmem_full[buf]);
+        if (CG == 2) umma_commit_2sm(&tmem_full[buf]);
+        else umma_commit(&tmem_full[buf]);
       }
     }
     __syncwarp();
@@ -306,7 +350,8 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     float st_acc[BN / 64][4];
 #pragma unroll
     for (int g = 0; g < BN / 64; ++g) { st_acc[g][0] = 0.f; st_acc[g][1] = 0.f; st_acc[g][2] = 0.f; st_acc[g][3] = 0.f; }
-    for (int tile = blockIdx.x; tile < P.total_tiles; tile += gridDim.x, ++it) {
+    for (int w = walk_id; w < walk_total; w += walk_n, ++it) {
+      const int tile = tile_of(w);
       const ConvTile T = conv_decode_tile<BN, MODE>(P, tile);
       const uint32_t buf = it & 1, use = it >> 1;
       const bool have_work = T.kb_end > T.kb_begin;
@@ -414,7 +459,10 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         }
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&tmem_empty[buf]);
+        if (lane == 0) {
+          if (CG == 2) mbar_arrive_leader(&tmem_empty[buf]);
+          else mbar_arrive(&tmem_empty[buf]);
+        }
         continue;
       }
 #pragma unroll 1
@@ -486,7 +534,10 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       // this warp has finished reading the accumulator: hand it back to the MMA issuer
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&tmem_empty[buf]);
+      if (lane == 0) {
+        if (CG == 2) mbar_arrive_leader(&tmem_empty[buf]);
+        else mbar_arrive(&tmem_empty[buf]);
+      }
     }
     if (MODE != MODE_WGRAD && P.tma_store && warp == 2 && lane == 0) tma_store_wait<0>();  // smem must outlive the stores
     if (MODE == MODE_FPROP && P.tma_store && P.stats != nullptr) {
@@ -518,10 +569,12 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   }
 
   tc_fence_before();
-  __syncthreads();
+  if (CG == 2) cluster_sync_all();     // the peer may still be reading this CTA's shared memory / signalling its barriers
+  else __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, TMEM_COLS);
+    if (CG == 2) tmem_dealloc_2sm(tmem_base, TMEM_COLS);
+    else tmem_dealloc(tmem_base, TMEM_COLS);
   }
 }
 
@@ -578,11 +631,11 @@ inline int conv_stats_grid(int total_tiles, int n_tiles, int num_ctas) {
   return g < n_tiles ? n_tiles : g;
 }
 
-template <int BN, int STAGES, int MODE>
+template <int BN, int STAGES, int MODE, int CG = 1>
 inline int launch_conv_cfg(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, const ConvParams& P,
                            int num_ctas, cudaStream_t st) {
-  auto kern = conv_sm100_kernel<BN, STAGES, MODE>;
-  constexpr int smem = conv_smem_bytes<BN, STAGES, MODE>();
+  auto kern = conv_sm100_kernel<BN, STAGES, MODE, CG>;
+  constexpr int smem = conv_smem_bytes<BN, STAGES, MODE, CG>();
   static bool attr_done = false;
   if (!attr_done) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
@@ -591,6 +644,25 @@ inline int launch_conv_cfg(const CUtensorMap& ta, const CUtensorMap& tb, const C
   }
   int grid = P.total_tiles < num_ctas ? P.total_tiles : num_ctas;
   if (MODE == MODE_FPROP && P.stats != nullptr) grid = conv_stats_grid(P.total_tiles, P.n_tiles, num_ctas);
+  if (CG == 2) {
+    // one cluster (CTA pair) per two SMs, persistent over the pair items
+    int clusters = P.total_pairs < num_ctas / 2 ? P.total_pairs : num_ctas / 2;
+    if (clusters < 1) clusters = 1;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(2 * clusters);
+    cfg.blockDim = dim3(GEMM_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    cudaError_t e2 = cudaLaunchKernelEx(&cfg, kern, ta, tb, to, P);
+    return e2 == cudaSuccess ? 0 : 400 + static_cast<int>(e2);
+  }
   kern<<<grid, GEMM_THREADS, smem, st>>>(ta, tb, to, P);
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? 0 : 400 + static_cast<int>(e);
