@@ -312,6 +312,26 @@ int32_t b200_gather_rows(const void* x, float* out, int32_t N, int64_t row_strid
 int32_t b200_scatter_rows(const float* d, void* out, int32_t N, int64_t row_stride, int32_t H, int32_t dtype,
                           void* stream);
 
+/* ------------------------------------------------------------------ VGG16 path
+ * models.vgg16(pretrained=True) + classifier[6] head (pytorch_training_inference_on_image.ipynb:1968-2041,
+ * another_neural_net.py:244-258).  The 13 conv3x3+bias+ReLU layers are b200_conv_fprop_affine (scale = 1,
+ * shift = bias, relu = 1) / b200_conv_dgrad / b200_conv_wgrad, the classifier's Linears the same kernel as flat
+ * 1x1 problems; these are the remaining layers.  NHWC, `dtype` storage. */
+/* MaxPool2d(kernel_size=2, stride=2) (floor mode): y [N,H/2,W/2,C]; argmax (optional) = window position 0..3 */
+int32_t b200_maxpool2x2_fwd(const void* x, void* y, uint8_t* argmax, int32_t N, int32_t H, int32_t W, int32_t C,
+                            int32_t dtype, void* stream);
+int32_t b200_maxpool2x2_bwd(const void* dy, const uint8_t* argmax, void* dx, int32_t N, int32_t H, int32_t W,
+                            int32_t C, int32_t dtype, void* stream);
+/* AdaptiveAvgPool2d((OH, OW)): windows [floor(i*H/OH), ceil((i+1)*H/OH)) as in ATen */
+int32_t b200_adaptive_avgpool_fwd(const void* x, void* y, int32_t N, int32_t H, int32_t W, int32_t C, int32_t OH,
+                                  int32_t OW, int32_t dtype, void* stream);
+int32_t b200_adaptive_avgpool_bwd(const void* dy, void* dx, int32_t N, int32_t H, int32_t W, int32_t C, int32_t OH,
+                                  int32_t OW, int32_t dtype, void* stream);
+/* Dropout on an activation buffer: y = x * keep / (1 - p), mask from Philox (seed, offset, index); applying the
+ * same call to the output gradient is the backward.  n % 8 == 0. */
+int32_t b200_dropout_act(const void* x, void* y, int64_t n, float p_drop, uint64_t seed, uint64_t offset,
+                         int32_t dtype, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -100,6 +100,11 @@ SIGNATURES = {
     "b200_attention_flash_supported": (I32, [I32, I32]),
     "b200_attention_flash_fwd": (I32, [P, P, P, P, P, I32, I32, I32, I32, F, U64, U64, P]),
     "b200_attention_flash_bwd": (I32, [P, P, P, P, P, P, P, P, I32, I32, I32, I32, F, P]),
+    "b200_maxpool2x2_fwd": (I32, [P, P, P, I32, I32, I32, I32, I32, P]),
+    "b200_maxpool2x2_bwd": (I32, [P, P, P, I32, I32, I32, I32, I32, P]),
+    "b200_adaptive_avgpool_fwd": (I32, [P, P, I32, I32, I32, I32, I32, I32, I32, P]),
+    "b200_adaptive_avgpool_bwd": (I32, [P, P, I32, I32, I32, I32, I32, I32, I32, P]),
+    "b200_dropout_act": (I32, [P, P, I64, F, U64, U64, I32, P]),
     "b200_tanh_fwd_f32": (I32, [P, P, I64, P]),
     "b200_tanh_bwd_f32": (I32, [P, P, P, I64, P]),
     "b200_gather_rows": (I32, [P, P, I32, I64, I32, I32, P]),

@@ -113,3 +113,6 @@ def resnet50(pretrained: bool = False, progress: bool = True, weights=None, **kw
                            "no network; build with pretrained=False and load_state_dict() a local file" %
                            os.path.join(torch.hub.get_dir(), "checkpoints"))
     return model
+
+
+from .vgg import VGG, vgg16  # noqa: E402,F401  (models.vgg16, another_neural_net.py:244)

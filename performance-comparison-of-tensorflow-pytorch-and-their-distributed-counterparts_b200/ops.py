@@ -598,13 +598,13 @@ def _ones(n, device):
     return t
 
 
-def dense_fwd(x, wp, bias, w_f32=None):
+def dense_fwd(x, wp, bias, relu=False):
     """wp: packed [out][in] operand in x.dtype (for fp32 this is the parameter itself)."""
     M, K = x.shape
     N = wp.shape[0]
     if x.dtype == torch.float32:
-        return gemm_f32(x, wp, M, N, K, K, K, False, False, bias=bias)
-    y = conv_fprop_affine(x.view(1, 1, M, K), wp, N, 1, 1, 1, 0, _ones(N, x.device), bias, False)
+        return gemm_f32(x, wp, M, N, K, K, K, False, False, bias=bias, relu=relu)
+    y = conv_fprop_affine(x.view(1, 1, M, K), wp, N, 1, 1, 1, 0, _ones(N, x.device), bias, relu)
     if y is None:
         raise RuntimeError("b200net dense_fwd: shape [%d,%d]x[%d] is not on the tensor-core path" % (M, K, N))
     return y.view(M, N)
@@ -626,3 +626,44 @@ def dense_bwd_weight(dy, x):
     if dy.dtype == torch.float32:
         return gemm_f32(dy, x, N, K, M, N, K, True, True)
     return conv_wgrad(x.view(1, 1, M, K), dy.view(1, 1, M, N), N, 1, 1, 1, 0).view(N, K)
+
+
+# ------------------------------------------------------------------ VGG16 extras
+def maxpool2_fwd(x, want_index):
+    N, H, W, C = x.shape
+    y = torch.empty((N, H // 2, W // 2, C), dtype=x.dtype, device=x.device)
+    idx = torch.empty((N, H // 2, W // 2, C), dtype=torch.uint8, device=x.device) if want_index else None
+    check(lib.b200_maxpool2x2_fwd(x.data_ptr(), y.data_ptr(), _p(idx), N, H, W, C, _dt(x), _stream()), "maxpool2x2_fwd")
+    return y, idx
+
+
+def maxpool2_bwd(dy, idx, x_shape):
+    N, H, W, C = x_shape
+    dx = torch.empty((N, H, W, C), dtype=dy.dtype, device=dy.device)
+    check(lib.b200_maxpool2x2_bwd(dy.data_ptr(), idx.data_ptr(), dx.data_ptr(), N, H, W, C, _dt(dy), _stream()),
+          "maxpool2x2_bwd")
+    return dx
+
+
+def adaptive_avgpool_fwd(x, oh, ow):
+    N, H, W, C = x.shape
+    y = torch.empty((N, oh, ow, C), dtype=x.dtype, device=x.device)
+    check(lib.b200_adaptive_avgpool_fwd(x.data_ptr(), y.data_ptr(), N, H, W, C, oh, ow, _dt(x), _stream()),
+          "adaptive_avgpool_fwd")
+    return y
+
+
+def adaptive_avgpool_bwd(dy, x_shape):
+    N, H, W, C = x_shape
+    dx = torch.empty((N, H, W, C), dtype=dy.dtype, device=dy.device)
+    check(lib.b200_adaptive_avgpool_bwd(dy.data_ptr(), dx.data_ptr(), N, H, W, C, dy.shape[1], dy.shape[2], _dt(dy),
+                                        _stream()), "adaptive_avgpool_bwd")
+    return dx
+
+
+def dropout_act(x, p, seed, offset, out=None):
+    """y = dropout(x) with the Philox mask of (seed, offset); the same call on a gradient is the backward."""
+    y = torch.empty_like(x) if out is None else out
+    check(lib.b200_dropout_act(x.data_ptr(), y.data_ptr(), x.numel(), float(p), seed, offset, _dt(x), _stream()),
+          "dropout_act")
+    return y
