@@ -238,6 +238,57 @@ def bert_leg(dev, rank, world, distributed, steps, warmup, timed, with_roofline)
     return out
 
 
+# ------------------------------------------------------------------ VGG16 leg
+VGG_BATCH, VGG_HW = 64, 224          # another_neural_net.py:64 batch size, :229/:240 CenterCrop(224)
+VGG_GFLOP_PER_IMG_FWD = 30.95        # torchvision vgg16 at 224x224: 15.47 GMAC forward
+
+
+def vgg_leg(dev, rank, world, steps, warmup, timed):
+    """The reference's VGG16 recipe (another_neural_net.py:244-300): pretrained part frozen, classifier[6] replaced,
+    optim.Adam(model.parameters()), train-mode forward (dropout in the 4096-wide layers) + backward through the head;
+    then the eval-mode forward at batch 256.  Every rank runs its own replica on its own data (no collective)."""
+    import torch
+    import b200net
+    from oracle import torch_oracle as O     # synthetic batch generator + head definition only
+    torch.manual_seed(O.SEED_WEIGHTS)
+    model = b200net.models.vgg16(pretrained=False)
+    for param in model.parameters():
+        param.requires_grad = False
+    model.classifier[6] = O.make_vgg_head()
+    model.to(dev).train()
+    criterion = b200net.nn.NLLLoss()
+    optimizer = b200net.optim.Adam(model.parameters())
+    x, y = O.make_batch(VGG_BATCH, VGG_HW, 3000 + rank, dev)
+
+    def step():
+        optimizer.zero_grad()
+        logps = model.forward(x)
+        loss = criterion(logps, y)
+        loss.backward()
+        optimizer.step()
+        return loss
+
+    for _ in range(max(warmup, 3)):
+        step()
+    ms = timed(step, steps)
+    model.eval()
+    with torch.no_grad():
+        xi = torch.rand(256, 3, VGG_HW, VGG_HW, device=dev)
+        for _ in range(3):
+            model(xi)
+        ms_inf = timed(lambda: model(xi).argmax(1), 5)
+    pk = peaks()
+    train_ips = world * VGG_BATCH * steps / (ms * 1e-3)
+    inf_ips = world * 256 * 5 / (ms_inf * 1e-3)
+    del model, optimizer, xi
+    torch.cuda.empty_cache()
+    return {"workload": "vgg16 reference recipe (frozen pretrained part, Adam on classifier[6]), batch %d/GPU, 3x%dx%d; "
+                        "eval forward at batch 256" % (VGG_BATCH, VGG_HW, VGG_HW),
+            "train_img_s": train_ips, "train_ms_per_step": ms / steps, "infer_img_s": inf_ips,
+            "infer_ms_per_batch": ms_inf / 5,
+            "infer_tensor_util": VGG_GFLOP_PER_IMG_FWD * 1e9 * inf_ips / world / 1e12 / pk["tflops"]}
+
+
 def run_bert_reference(args, rank):
     if rank != 0:
         return
@@ -267,6 +318,7 @@ def main():
     ap.add_argument("--workload", default="resnet", choices=["resnet", "bert"],
                     help="resnet = the headline line (BASELINE.json metric); bert = a full line for configs[4]")
     ap.add_argument("--no-bert", action="store_true", help="skip the BERT leg of the default line")
+    ap.add_argument("--no-vgg", action="store_true", help="skip the VGG16 leg of the default line")
     ap.add_argument("--local_rank", type=int, default=0)     # torch.distributed.launch compatibility
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -447,6 +499,9 @@ def main():
         del x_dev
         torch.cuda.empty_cache()
         bert_out = bert_leg(dev, rank, world, distributed, 10, 3, timed, with_roofline=False)
+    vgg_out = None
+    if args.precision == "bf16" and not args.no_vgg:
+        vgg_out = vgg_leg(dev, rank, world, 10, 3, timed)
 
     if rank == 0:
         ips = world * B * args.steps / (total_ms * 1e-3)
@@ -476,6 +531,8 @@ def main():
             out["infer"] = infer
         if bert_out:
             out["bert"] = bert_out
+        if vgg_out:
+            out["vgg16"] = vgg_out
         if world == 1 and not args.no_cpu_baseline:
             cips, cms, cores = cpu_reference_run(steps=5, warmup=2)
             out["cpu_baseline"] = {"value": cips, "unit": UNIT, "cores": cores, "kind": "port",
