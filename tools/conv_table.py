@@ -1,6 +1,7 @@
 """Per-layer-class timing of the bf16 conv kernels (fprop / dgrad / wgrad) against their rooflines.
-Classes = SURVEY.md 8(a') at N images of 160x160.  CUDA events, 3 warm-up + 10 timed, inputs > L2 rotate is not
-needed here: every class at N=256 moves more than the 126 MB L2 or is tensor-bound.  usage: conv_table.py [N] [filter]"""
+Classes = SURVEY.md 8(a') at N images of 160x160 (ResNet-50), or with a third argument `vgg` the twelve 64+-channel
+3x3 layers of VGG16 at 224x224.  CUDA events, 3 warm-up + 10 timed, inputs > L2 rotate is not
+needed here: every class at N=256 moves more than the 126 MB L2 or is tensor-bound.  usage: conv_table.py [N] [filter] [vgg]"""
 import json, os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
@@ -18,6 +19,11 @@ CLASSES = [  # name, H, C, K, R, stride, pad, count
     ("p", 10, 256, 256, 3, 1, 1, 5), ("q", 10, 1024, 512, 1, 1, 0, 1), ("r", 10, 512, 512, 3, 2, 1, 1),
     ("s", 5, 512, 2048, 1, 1, 0, 3), ("t", 10, 1024, 2048, 1, 2, 0, 1), ("u", 5, 2048, 512, 1, 1, 0, 2),
     ("v", 5, 512, 512, 3, 1, 1, 2),
+]
+VGG_CLASSES = [
+    ("A", 224, 64, 64, 3, 1, 1, 1), ("B", 112, 64, 128, 3, 1, 1, 1), ("C", 112, 128, 128, 3, 1, 1, 1),
+    ("D", 56, 128, 256, 3, 1, 1, 1), ("E", 56, 256, 256, 3, 1, 1, 2), ("F", 28, 256, 512, 3, 1, 1, 1),
+    ("G", 28, 512, 512, 3, 1, 1, 2), ("H", 14, 512, 512, 3, 1, 1, 3),
 ]
 
 
@@ -37,11 +43,14 @@ def timeit(fn, iters=10):
 def main():
     N = int(sys.argv[1]) if len(sys.argv) > 1 else 256
     filt = sys.argv[2] if len(sys.argv) > 2 else ""
+    classes = VGG_CLASSES if (len(sys.argv) > 3 and sys.argv[3] == "vgg") else CLASSES
+    if filt == "-":
+        filt = ""
     dev = torch.device("cuda:0")
     peak, hbm = PK["bf16_tflops"] * 1e12, PK["hbm_gbs"] * 1e9
     tot = {"fprop": [0, 0], "dgrad": [0, 0], "wgrad": [0, 0]}
     print("%-3s %-26s %9s | %8s %8s %5s | %8s %8s %5s | %8s %8s %5s" % ("cls", "shape", "MFLOP/img", "fprop us", "roof us", "frac", "dgrad us", "roof us", "frac", "wgrad us", "roof us", "frac"))
-    for name, H, C, K, R, st, pad, cnt in CLASSES:
+    for name, H, C, K, R, st, pad, cnt in classes:
         if filt and name not in filt:
             continue
         Ho = (H + 2 * pad - R) // st + 1
