@@ -102,3 +102,18 @@ def test_precision_switch():
     with pytest.raises(ValueError):
         b200net.set_precision("fp8")
     b200net.set_precision(prev)
+
+
+def test_torch_save_roundtrip_bert_and_vgg():
+    """torch.save(model, path) / torch.load(path) (...on_image.ipynb:700,852) for the other two model families."""
+    import b200net
+    from b200net import bert
+    for m in (bert.BertForSequenceClassification(bert.BertConfig(num_hidden_layers=1)),
+              b200net.models.vgg16(pretrained=False)):
+        buf = io.BytesIO()
+        torch.save(m, buf)
+        buf.seek(0)
+        m2 = torch.load(buf, weights_only=False)
+        assert repr(m2) == repr(m)
+        a, b = next(iter(m.parameters())), next(iter(m2.parameters()))
+        assert torch.equal(a, b)
