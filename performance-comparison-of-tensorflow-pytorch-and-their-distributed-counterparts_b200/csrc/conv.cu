@@ -168,9 +168,25 @@ static inline WgradPlan wgrad_plan(const b200_conv_desc* d, const ConvGeom& g) {
 // GEMMs already run at 1.0-1.15 PFLOP/s against a measured sustained cuBLAS peak of 1.38, so B-operand traffic per SM
 // was not the limiter it looked like.  Not combined with the fused BatchNorm statistics (their per-CTA partial rows
 // assume the single-CTA tile walk).
-static inline int pair_items(int bn, long long pixel_tiles, int n_tiles, bool stats) {
-  static const bool on = getenv("B200_2SM") != nullptr;
-  if (!on || bn != 256 || stats || pixel_tiles < 2) return 0;
+// Two-pixel-tile work items for 256-wide fprop / dgrad tiles; both variants are built, parity-tested
+// (tests/test_kernels_gpu.py::test_two_tile_kernel_variants) and OFF by default because neither beat the single-tile
+// kernel when measured (tools/bert_kernel_bench.py, tools/conv_table.py vgg):
+//   mode 3 (B200_DUAL_MIN_KB=<k-blocks>): one CTA computes both tiles -- a 256 x 256 output tile, B loaded once for
+//           two MMAs.  Only the deepest reductions gain (512->512 3x3 dgrad 164 -> 158 us); 12-k-block Linears lose
+//           20-40 % (QKV forward 30.7 -> 39.2 us) because the epilogue no longer overlaps the next main loop.
+//   mode 2 (B200_2SM=1): CTA pairs, tcgen05 cta_group::2 -- see conv_sm100.cuh; fprop 31.0 -> 35.2 us.
+// The deep layers already run at 0.85-0.88 of the nominal roofline (~1.3 PFLOP/s, the chip's sustained limit), so
+// operand traffic per SM was not the limiter the first ncu reading suggested; what is left is per-tile latency on
+// shallow reductions.
+static inline int pair_mode_for(int kblocks) {
+  static const bool two_sm = getenv("B200_2SM") != nullptr;
+  static const int dual_min = getenv("B200_DUAL_MIN_KB") ? atoi(getenv("B200_DUAL_MIN_KB")) : 0;
+  if (two_sm) return 2;
+  if (dual_min > 0 && kblocks >= dual_min) return 3;
+  return 0;
+}
+static inline int pair_items(int bn, long long pixel_tiles, int n_tiles, bool stats, int mode) {
+  if (mode == 0 || bn != 256 || stats || pixel_tiles < 2) return 0;
   const long long items = ((pixel_tiles + 1) / 2) * n_tiles;
   return items > 0x3fffffffLL ? 0 : (int)items;
 }
@@ -183,6 +199,7 @@ static int launch_conv_mode(int bn, const CUtensorMap& ta, const CUtensorMap& tb
     if (bn == 256) return launch_conv_cfg<256, 4, MODE>(ta, tb, to, P, ctas, st);
     return launch_conv_cfg<128, 3, MODE>(ta, tb, to, P, ctas, st);
   } else {
+    if (bn == 256 && P.total_pairs > 0 && P.pair_mode == 3) return launch_conv_cfg<256, 3, MODE, 3>(ta, tb, to, P, ctas, st);
     if (bn == 256 && P.total_pairs > 0) return launch_conv_cfg<256, 5, MODE, 2>(ta, tb, to, P, ctas, st);   // CTA pairs
     if (bn == 256) return launch_conv_cfg<256, 4, MODE>(ta, tb, to, P, ctas, st);
     if (bn == 128) return launch_conv_cfg<128, 6, MODE>(ta, tb, to, P, ctas, st);
@@ -244,8 +261,9 @@ static int32_t implicit_fprop(const b200_conv_desc* d, const ConvGeom& g, const 
   const int bn = pick_bn(d, g, d->K);
   const long long tiles = (long long)b.tiles_w * b.tiles_h * b.tiles_n;
   P.n_tiles = (d->K + bn - 1) / bn;
-  P.total_pairs = pair_items(bn, tiles, P.n_tiles, stats != nullptr);
-  rc = make_tmap_bf16_2d(&tb, w, g.RSC, d->K, g.ldw, 64, P.total_pairs > 0 ? bn / 2 : bn);   // a pair CTA loads half
+  P.pair_mode = pair_mode_for(d->R * d->S * (d->C / 64));
+  P.total_pairs = pair_items(bn, tiles, P.n_tiles, stats != nullptr, P.pair_mode);
+  rc = make_tmap_bf16_2d(&tb, w, g.RSC, d->K, g.ldw, 64, (P.total_pairs > 0 && P.pair_mode == 2) ? bn / 2 : bn);
   if (rc) return fail(B200_CUDA_ERROR, "conv_fprop: weight tensor map failed (%d)", rc);
   P.m_tiles = 1;
   if (tiles * P.n_tiles > 0x7fffffffLL) return fail(B200_UNSUPPORTED, "conv_fprop: too many tiles");
@@ -315,7 +333,8 @@ static int32_t implicit_dgrad(const b200_conv_desc* d, const ConvGeom& g, const 
     P.m_tiles = 1;
     if (tiles * P.n_tiles > 0x7fffffffLL) return fail(B200_UNSUPPORTED, "conv_dgrad: too many tiles");
     P.total_tiles = (int)(tiles * P.n_tiles);
-    P.total_pairs = pair_items(bn, tiles, P.n_tiles, false);
+    P.pair_mode = pair_mode_for(P.ntaps * P.cchunks);
+    P.total_pairs = pair_items(bn, tiles, P.n_tiles, false, P.pair_mode);
     CUtensorMap to;
     static const bool no_tma_store = getenv("B200_NO_TMA_STORE") != nullptr;
     // strided (parity-class) outputs keep the per-thread store path; accumulation uses the TMA reduce-add

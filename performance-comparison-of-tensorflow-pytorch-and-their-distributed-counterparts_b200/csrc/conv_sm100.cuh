@@ -54,7 +54,8 @@ struct ConvParams {
   // persistent tile walk: tile = n_tile + n_tiles * (pixel tile | m_tile + m_tiles * (tap*nsplits + split))
   int n_tiles, m_tiles, total_tiles;
   int n_inner;                       // wgrad: column tiles per tap (n_tiles = n_inner * tap groups)
-  int total_pairs;                   // CTA-pair kernels (CG = 2): ceil(pixel tiles / 2) * n_tiles work items per pair
+  int total_pairs;                   // CG = 2 / 3 kernels: ceil(pixel tiles / 2) * n_tiles work items (two pixel tiles each)
+  int pair_mode;                     // 2 = CTA pair (cta_group::2), 3 = both pixel tiles in one CTA
   int tma_store;                     // fprop/dgrad: bf16 output written by TMA from a swizzled smem staging tile
   const float* ep_scale;             // fprop + tma_store (eval-mode BatchNorm folded into the epilogue):
   const float* ep_shift;             //   out = act(acc * ep_scale[col] + ep_shift[col]), act = ReLU when ep_relu
@@ -69,8 +70,8 @@ struct ConvParams {
 
 template <int BN, int STAGES, int MODE, int CG = 1>
 constexpr int conv_smem_bytes() {
-  constexpr int a = MODE == MODE_WGRAD ? 2 * CONV_WGRAD_KR(BN) * 128 : GEMM_BM * 128;
-  constexpr int b = MODE == MODE_WGRAD ? (BN / 64) * CONV_WGRAD_KR(BN) * 128 : BN * 128 / CG;
+  constexpr int a = MODE == MODE_WGRAD ? 2 * CONV_WGRAD_KR(BN) * 128 : GEMM_BM * 128 * (CG == 3 ? 2 : 1);
+  constexpr int b = MODE == MODE_WGRAD ? (BN / 64) * CONV_WGRAD_KR(BN) * 128 : BN * 128 / (CG == 2 ? 2 : 1);
   return STAGES * (a + b) + (MODE == MODE_WGRAD ? 0 : CONV_STAGING_BYTES + CONV_STATS_RED_BYTES) + 1024 + 256;
 }
 
@@ -124,13 +125,19 @@ __device__ __forceinline__ ConvTile conv_decode_tile(const ConvParams& P, int ti
 // operand-traffic bound.  TMA completions of both CTAs are counted on the leader's `full` barrier, tcgen05.commit is
 // multicast to both CTAs' `empty` / `tmem_full` barriers, and both CTAs' epilogue warps release the accumulator on
 // the leader's `tmem_empty` barrier.
+//
+// CG = 3 (fprop / dgrad, BN = 256): ONE CTA works on both pixel tiles of a pair item -- a 256 x 256 output tile as two
+// M = 128 MMAs per k-step that share the B tile.  A k-block then brings 2 x 16 + 32 KB for twice the MMA work
+// (32 KB per 128x256x64 unit instead of 48): the single-tile kernel is bound by L2 -> SM operand traffic
+// (~115 GB/s per SM: 0.43 us per 48 KB k-block against 0.28 us of MMA time).  The two accumulators fill TMEM, so the
+// epilogue of an item no longer overlaps the next item's main loop: worth it when the reduction is deep.
 template <int BN, int STAGES, int MODE, int CG = 1>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                   const __grid_constant__ CUtensorMap tmO, const __grid_constant__ ConvParams P) {
-  constexpr int A_BYTES = MODE == MODE_WGRAD ? 2 * CONV_WGRAD_KR(BN) * 128 : GEMM_BM * 128;
-  constexpr int B_BYTES = MODE == MODE_WGRAD ? (BN / 64) * CONV_WGRAD_KR(BN) * 128 : BN * 128 / CG;
-  static_assert(CG == 1 || (CG == 2 && MODE != MODE_WGRAD && BN == 256), "CTA pairs: fprop / dgrad with 256-wide tiles");
+  constexpr int A_BYTES = MODE == MODE_WGRAD ? 2 * CONV_WGRAD_KR(BN) * 128 : GEMM_BM * 128 * (CG == 3 ? 2 : 1);
+  constexpr int B_BYTES = MODE == MODE_WGRAD ? (BN / 64) * CONV_WGRAD_KR(BN) * 128 : BN * 128 / (CG == 2 ? 2 : 1);
+  static_assert(CG == 1 || (MODE != MODE_WGRAD && BN == 256), "CG 2 / 3: fprop / dgrad with 256-wide tiles");
   constexpr int STG_BYTES = MODE == MODE_WGRAD ? 0 : CONV_STAGING_BYTES + CONV_STATS_RED_BYTES;
   constexpr uint32_t TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;   // two accumulators
   static_assert(2 * BN <= 512, "two accumulators must fit TMEM");
@@ -155,10 +162,10 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   const int rank = CG == 2 ? (int)cluster_ctarank() : 0;
   const int walk_id = CG == 2 ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
   const int walk_n = CG == 2 ? (int)(gridDim.x >> 1) : (int)gridDim.x;
-  const int walk_total = CG == 2 ? P.total_pairs : P.total_tiles;
-  auto tile_of = [&](int w) -> int {
+  const int walk_total = CG != 1 ? P.total_pairs : P.total_tiles;
+  auto tile_of = [&](int w, int r) -> int {
     if (CG == 1) return w;
-    return (w % P.n_tiles) + P.n_tiles * (2 * (w / P.n_tiles) + rank);
+    return (w % P.n_tiles) + P.n_tiles * (2 * (w / P.n_tiles) + r);
   };
   const uint32_t box_bytes = static_cast<uint32_t>(P.bw * P.bh * P.bn) * 128u;
 
@@ -174,7 +181,7 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 #pragma unroll
     for (int b = 0; b < 2; ++b) {
       mbar_init(&tmem_full[b], 1);
-      mbar_init(&tmem_empty[b], 4 * CG);   // one arrive per epilogue warp (of both CTAs of a pair)
+      mbar_init(&tmem_empty[b], CG == 2 ? 8 : 4);   // one arrive per epilogue warp (of both CTAs of a pair)
     }
     mbar_fence_init();
   }
@@ -200,9 +207,10 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       int stage = 0;          // ring position and phase run continuously across tiles
       uint32_t phase = 0;
       for (int w = walk_id; w < walk_total; w += walk_n) {
-        const int tile = tile_of(w);
+        const int tile = tile_of(w, rank);
         const ConvTile T = conv_decode_tile<BN, MODE>(P, tile);
         if (MODE != MODE_WGRAD) {
+          const ConvTile T1 = conv_decode_tile<BN, MODE>(P, tile_of(w, 1));   // CG == 3: the item's second pixel tile
           // taps x 64-channel chunks, no per-k-block division; stage index / phase carried incrementally
           for (int t = 0; t < P.ntaps; ++t) {
             const int aw = T.q0 * P.a_mul + P.taps[t].dw, ah = T.p0 * P.a_mul + P.taps[t].dh;
@@ -211,7 +219,19 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
               mbar_wait(&empty[stage], phase ^ 1);
               uint8_t* a = smA + stage * A_BYTES;
               uint8_t* b = smB + stage * B_BYTES;
-              if (CG == 2) {
+              if (CG == 3) {
+                mbar_expect_tx(&full[stage], 2 * box_bytes + B_BYTES);
+                tma_load_4d(a, &tmA, &full[stage], cc * 64, aw, ah, T.i0);
+                tma_load_4d(a + GEMM_BM * 128, &tmA, &full[stage], cc * 64, T1.q0 * P.a_mul + P.taps[t].dw,
+                            T1.p0 * P.a_mul + P.taps[t].dh, T1.i0);
+                if (MODE == MODE_FPROP) {
+                  tma_load_2d(b, &tmB, &full[stage], bcol + cc * 64, T.n0);
+                } else {
+#pragma unroll
+                  for (int h = 0; h < BN / 64; ++h)
+                    tma_load_2d(b + h * 8192, &tmB, &full[stage], bcol + T.n0 + h * 64, cc * 64);
+                }
+              } else if (CG == 2) {
                 // bytes of BOTH CTAs land on the leader's barrier; each CTA brings its pixel box and its half of B
                 if (rank == 0) mbar_expect_tx(&full[stage], 2 * (box_bytes + B_BYTES));
                 tma_load_4d_2sm(a, &tmA, &full[stage], cc * 64, aw, ah, T.i0);
@@ -294,15 +314,16 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer
     if (lane == 0 && rank == 0) {
-      constexpr uint32_t idesc = umma_idesc_bf16(GEMM_BM * CG, BN, MODE == MODE_WGRAD, MODE != MODE_FPROP);
+      constexpr uint32_t idesc = umma_idesc_bf16(GEMM_BM * (CG == 2 ? 2 : 1), BN, MODE == MODE_WGRAD, MODE != MODE_FPROP);
       int stage = 0;
       uint32_t phase = 0;
       uint32_t it = 0;   // local tile counter
       for (int w = walk_id; w < walk_total; w += walk_n, ++it) {
-        const int tile = tile_of(w);
+        const int tile = tile_of(w, rank);
         const ConvTile T = conv_decode_tile<BN, MODE>(P, tile);
-        const uint32_t buf = it & 1, use = it >> 1;
+        const uint32_t buf = CG == 3 ? 0u : (it & 1), use = CG == 3 ? it : (it >> 1);
         mbar_wait(&tmem_empty[buf], (use & 1) ^ 1);   // epilogue has drained this accumulator
+        if (CG == 3) mbar_wait(&tmem_empty[1], (use & 1) ^ 1);   // ... and the second one: an item uses both
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + buf * BN;
         bool first = true;
@@ -321,6 +342,9 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                                                         : umma_smem_desc(b_addr + k * 2048, 8192, 1024);
               if (CG == 2) umma_f16_2sm(d_tmem, adesc, bdesc, idesc, (!first || k > 0) ? 1u : 0u);
               else umma_f16(d_tmem, adesc, bdesc, idesc, (!first || k > 0) ? 1u : 0u);
+              if (CG == 3)   // second pixel tile of the item: same B, its own A rows and accumulator
+                umma_f16(d_tmem + BN, umma_smem_desc(a_addr + GEMM_BM * 128 + k * 32, 16, 1024), bdesc, idesc,
+                         (!first || k > 0) ? 1u : 0u);
             }
           } else {
             const int ksteps = P.kr >> 4;
@@ -336,6 +360,7 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         }
         if (CG == 2) umma_commit_2sm(&tmem_full[buf]);
         else umma_commit(&tmem_full[buf]);
+        if (CG == 3) umma_commit(&tmem_full[1]);
       }
     }
     __syncwarp();
@@ -350,10 +375,11 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     float st_acc[BN / 64][4];
 #pragma unroll
     for (int g = 0; g < BN / 64; ++g) { st_acc[g][0] = 0.f; st_acc[g][1] = 0.f; st_acc[g][2] = 0.f; st_acc[g][3] = 0.f; }
-    for (int w = walk_id; w < walk_total; w += walk_n, ++it) {
-      const int tile = tile_of(w);
+    for (int w = walk_id; w < walk_total; w += walk_n, ++it)
+    for (int half = 0; half < (CG == 3 ? 2 : 1); ++half) {      // CG == 3: the item's two pixel tiles, one after the other
+      const int tile = tile_of(w, CG == 3 ? half : rank);
       const ConvTile T = conv_decode_tile<BN, MODE>(P, tile);
-      const uint32_t buf = it & 1, use = it >> 1;
+      const uint32_t buf = CG == 3 ? (uint32_t)half : (it & 1), use = CG == 3 ? it : (it >> 1);
       const bool have_work = T.kb_end > T.kb_begin;
       mbar_wait(&tmem_full[buf], use & 1);
       tc_fence_after();
@@ -643,6 +669,7 @@ inline int launch_conv_cfg(const CUtensorMap& ta, const CUtensorMap& tb, const C
     attr_done = true;
   }
   int grid = P.total_tiles < num_ctas ? P.total_tiles : num_ctas;
+  if (CG == 3) grid = P.total_pairs < num_ctas ? P.total_pairs : num_ctas;
   if (MODE == MODE_FPROP && P.stats != nullptr) grid = conv_stats_grid(P.total_tiles, P.n_tiles, num_ctas);
   if (CG == 2) {
     // one cluster (CTA pair) per two SMs, persistent over the pair items

@@ -384,16 +384,18 @@ def test_clip_grad_norm():
     assert abs(n3.item() - 1.0) < 1e-3
 
 
-def test_cta_pair_kernels():
-    """The opt-in CTA-pair (tcgen05 cta_group::2) variant of the fprop / dgrad kernel: the environment switch is read
-    once per process, so the conv / Linear parity tests are re-run in a child process with B200_2SM=1."""
+@pytest.mark.parametrize("env", [{"B200_2SM": "1"}, {"B200_DUAL_MIN_KB": "1"}])
+def test_two_tile_kernel_variants(env):
+    """The two-pixel-tile variants of the fprop / dgrad kernel -- CTA pairs (tcgen05 cta_group::2, opt-in) and the
+    256 x 256 single-CTA tile (chosen by reduction depth; forced for every shape here).  The switches are read once
+    per process, so the conv / Linear parity tests are re-run in a child process."""
     import os
     import subprocess
     import sys
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    env = dict(os.environ, B200_2SM="1")
     r = subprocess.run([sys.executable, "-m", "pytest", "-x", "-q", "-p", "no:cacheprovider",
                         os.path.join(root, "tests", "test_kernels_gpu.py"), os.path.join(root, "tests", "test_bert_gpu.py"),
-                        "-k", "conv or dense"], env=env, cwd=root, capture_output=True, text=True, timeout=600)
+                        "-k", "conv or dense"], env=dict(os.environ, **env), cwd=root, capture_output=True, text=True,
+                       timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
     assert " passed" in r.stdout
