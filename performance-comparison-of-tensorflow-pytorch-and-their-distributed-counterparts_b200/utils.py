@@ -30,3 +30,54 @@ def clip_grad_norm_(parameters, max_norm, norm_type=2.0):
     check(lib.b200_multi_tensor_clip_scale(len(grads), ptrs, sizes, norm_sq.data_ptr(), float(max_norm), st),
           "clip_scale")
     return norm_sq.sqrt().reshape(())
+
+
+class DevicePrefetcher(object):
+    """Wraps any iterable of (inputs, labels) host batches -- the reference's `trainloader`
+    (pytorch_training_inference_on_image.ipynb:664, another_neural_net.py:123) -- and hands out the same batches
+    already on the device: batch i+1 is copied host->device on a side stream while step i computes, so the loop's
+    own `inputs.to(device), labels.to(device)` become no-ops and the copy no longer sits in front of every step
+    (78 MB per 256-image batch: ~1.5 ms of a 14 ms step).  Pinned host tensors make the copies truly asynchronous;
+    pageable ones still work.
+
+        trainloader = b200net.utils.DevicePrefetcher(trainloader, device)
+        for inputs, labels in trainloader:          # unchanged loop
+            inputs, labels = inputs.to(device), labels.to(device)
+    """
+
+    def __init__(self, loader, device):
+        self.loader = loader
+        self.device = torch.device(device)
+        self.stream = torch.cuda.Stream(device=self.device)
+
+    def __len__(self):
+        return len(self.loader)
+
+    def _to_device(self, item):
+        if isinstance(item, torch.Tensor):
+            return item.to(self.device, non_blocking=True)
+        if isinstance(item, (list, tuple)):
+            return type(item)(self._to_device(t) for t in item)
+        return item
+
+    def __iter__(self):
+        it = iter(self.loader)
+        cur = torch.cuda.current_stream(self.device)
+
+        def fetch():
+            try:
+                batch = next(it)
+            except StopIteration:
+                return None
+            with torch.cuda.stream(self.stream):
+                return self._to_device(batch)
+
+        nxt = fetch()
+        while nxt is not None:
+            cur.wait_stream(self.stream)
+            batch = nxt
+            for t in (batch if isinstance(batch, (list, tuple)) else [batch]):
+                if isinstance(t, torch.Tensor):
+                    t.record_stream(cur)
+            nxt = fetch()
+            yield batch
