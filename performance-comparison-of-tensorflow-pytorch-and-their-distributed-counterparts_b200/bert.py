@@ -384,7 +384,7 @@ F._GRAPH_CACHES.extend([_BG, _BG_SEEN])
 
 class _BertGraph(object):
     __slots__ = ("fwd", "bwd", "ids", "tt", "mask", "cls", "dcls", "grads", "ctr", "state", "ptrs", "keep", "uses",
-                 "ddp", "order", "segments")
+                 "ddp", "order", "segments", "gen", "live")
 
 
 def _graph_key(model, ids, tt, mask, params):
@@ -409,6 +409,7 @@ def _capture(model, ids, tt, mask, params, key):
     rec.ctr = torch.zeros(1, dtype=torch.int64, device=ids.device)
     rec.ptrs = _param_ptrs(params)
     rec.uses = 0
+    rec.gen, rec.live = 0, None
     pool = torch.cuda.graph_pool_handle()
     _CAPTURE_PK.clear()
     _CAPTURING[0] = save          # forward-only graphs use the eager operand cache (validity is part of the key)
@@ -471,6 +472,7 @@ class _GraphedEncoder(torch.autograd.Function):
         rec.ctr.fill_(_CALLS[0])
         _CALLS[0] += 1
         rec.fwd.replay()
+        F.graph_replay_begin(rec, ctx)
         ctx.rec = rec
         ctx.saved_params = params
         return rec.cls.clone()
@@ -481,6 +483,7 @@ class _GraphedEncoder(torch.autograd.Function):
         rec = ctx.rec
         if rec.bwd is None:
             raise RuntimeError("b200net: this encoder graph was captured without a backward pass")
+        F.graph_replay_check(rec, ctx)
         rec.dcls.copy_(dcls)
         if rec.ddp is not None:
             for g, ready in rec.segments:
@@ -506,6 +509,8 @@ def bert_encoder(model, ids, tt, mask):
     rec = _BG.get(key)
     if rec is not None and rec != "failed":
         if rec.ptrs == _param_ptrs(params):
+            if F.graph_record_busy(rec):   # an earlier replayed forward still waits for its backward
+                return _BertEncoderFn.apply(model, torch.is_grad_enabled(), ids, tt, mask, *params)
             rec.uses += 1
             return _GraphedEncoder.apply(rec, ids, tt, mask, *params)
         del _BG[key]

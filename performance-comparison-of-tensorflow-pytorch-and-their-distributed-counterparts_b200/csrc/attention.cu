@@ -297,11 +297,8 @@ template <typename T>
 static int32_t attention_fwd_t(const T* qkv, const long long* mask, T* probs, T* ctx, int N, int S, int heads,
                                float p, uint64_t seed, uint64_t offset, cudaStream_t st) {
   const size_t smem = att_smem_bytes(S);
-  static size_t attr_smem = 0;   // not a stream operation: raise the limit once per size, outside any capture replay
-  if (smem > attr_smem) {
-    cudaFuncSetAttribute(attention_fwd_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    attr_smem = smem;
-  }
+  static int attr_state[B200_MAX_DEVICES] = {0};   // per device; raised once per size, outside any capture replay
+  ensure_dyn_smem(attention_fwd_kernel<T>, (int)smem, attr_state);
   dim3 grid((S + ATT_QT - 1) / ATT_QT, heads, N);
   attention_fwd_kernel<T><<<grid, ATT_THREADS, smem, st>>>(qkv, mask, probs, ctx, S, heads, 0.125f, p,
                                                           dropout_inv_keep(p), seed, offset,
@@ -312,11 +309,8 @@ template <typename T>
 static int32_t attention_bwd_t(const T* qkv, const T* probs, const T* dctx, T* ds, T* dqkv, int N, int S, int heads,
                                float p, uint64_t seed, uint64_t offset, cudaStream_t st) {
   const size_t smem = att_smem_bytes(S);
-  static size_t attr_smem = 0;
-  if (smem > attr_smem) {
-    cudaFuncSetAttribute(attention_bwd_q_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    attr_smem = smem;
-  }
+  static int attr_state[B200_MAX_DEVICES] = {0};
+  ensure_dyn_smem(attention_bwd_q_kernel<T>, (int)smem, attr_state);
   dim3 grid((S + ATT_QT - 1) / ATT_QT, heads, N);
   const float ik = dropout_inv_keep(p);
   attention_bwd_q_kernel<T><<<grid, ATT_THREADS, smem, st>>>(qkv, probs, dctx, ds, dqkv, S, heads, 0.125f, p, ik,

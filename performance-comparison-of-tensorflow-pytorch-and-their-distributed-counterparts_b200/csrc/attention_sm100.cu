@@ -380,12 +380,9 @@ template <int MODE>
 static int32_t att_tc_launch(const CUtensorMap& tq, const CUtensorMap& tdo, const AttParams& P, int N,
                              cudaStream_t st) {
   const int smem = att_tc_smem_bytes<MODE>(P.S);
-  static int attr_smem = 0;      // raise the limit once per size (not a stream operation: keep it out of captures)
-  if (smem > attr_smem) {
-    cudaError_t e = cudaFuncSetAttribute(att_tc_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    if (e != cudaSuccess) return fail(B200_CUDA_ERROR, "attention: smem attribute: %s", cudaGetErrorString(e));
-    attr_smem = smem;
-  }
+  static int attr_state[B200_MAX_DEVICES] = {0};   // per device, raised once per size (not a stream operation)
+  if (cudaError_t e = ensure_dyn_smem(att_tc_kernel<MODE>, smem, attr_state))
+    return fail(B200_CUDA_ERROR, "attention: smem attribute: %s", cudaGetErrorString(e));
   att_tc_kernel<MODE><<<dim3(P.S / ATC_ROWS, P.heads, N), ATC_THREADS, smem, st>>>(tq, tdo, P);
   return check_launch("attention_flash");
 }

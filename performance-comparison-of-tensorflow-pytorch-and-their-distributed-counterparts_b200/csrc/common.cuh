@@ -6,6 +6,7 @@
 #include <stdio.h>
 #include <stdarg.h>
 #include "../../include/b200net.h"
+#include "device_state.cuh"
 
 namespace b200 {
 
@@ -36,17 +37,6 @@ inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStream_t>(s
 inline const unsigned long long*& dropout_ctr() {
   static thread_local const unsigned long long* p = nullptr;
   return p;
-}
-
-inline int num_sms() {
-  static int n = 0;
-  if (!n) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
-    if (n <= 0) n = 148;
-  }
-  return n;
 }
 
 template <typename T> struct VecTraits;

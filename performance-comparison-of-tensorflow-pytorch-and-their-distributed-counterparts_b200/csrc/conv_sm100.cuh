@@ -662,12 +662,8 @@ inline int launch_conv_cfg(const CUtensorMap& ta, const CUtensorMap& tb, const C
                            int num_ctas, cudaStream_t st) {
   auto kern = conv_sm100_kernel<BN, STAGES, MODE, CG>;
   constexpr int smem = conv_smem_bytes<BN, STAGES, MODE, CG>();
-  static bool attr_done = false;
-  if (!attr_done) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    if (e != cudaSuccess) return 300 + static_cast<int>(e);
-    attr_done = true;
-  }
+  static int attr_state[B200_MAX_DEVICES] = {0};
+  if (cudaError_t e = ensure_dyn_smem(kern, smem, attr_state)) return 300 + static_cast<int>(e);
   int grid = P.total_tiles < num_ctas ? P.total_tiles : num_ctas;
   if (CG == 3) grid = P.total_pairs < num_ctas ? P.total_pairs : num_ctas;
   if (MODE == MODE_FPROP && P.stats != nullptr) grid = conv_stats_grid(P.total_tiles, P.n_tiles, num_ctas);

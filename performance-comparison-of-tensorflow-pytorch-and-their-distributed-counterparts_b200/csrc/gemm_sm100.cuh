@@ -10,6 +10,7 @@
 // This is what lets fprop / dgrad / wgrad of a convolution share one mainloop without any transposed copies.
 #pragma once
 #include "sm100_ptx.cuh"
+#include "device_state.cuh"
 
 namespace b200 {
 
@@ -274,12 +275,8 @@ inline int launch_gemm_cfg(const GemmProblem& p, cudaStream_t st) {
   splits = (num_kb + kb_per - 1) / kb_per;  // every split gets at least one k-block
   auto kern = gemm_sm100_kernel<BN, STAGES, A_MN, B_MN>;
   constexpr int smem = gemm_smem_bytes<BN, STAGES>();
-  static bool attr_done = false;
-  if (!attr_done) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    if (e != cudaSuccess) return 300 + static_cast<int>(e);
-    attr_done = true;
-  }
+  static int attr_state[B200_MAX_DEVICES] = {0};
+  if (cudaError_t e = ensure_dyn_smem(kern, smem, attr_state)) return 300 + static_cast<int>(e);
   dim3 grid((p.N + BN - 1) / BN, (p.M + GEMM_BM - 1) / GEMM_BM, splits);
   kern<<<grid, GEMM_THREADS, smem, st>>>(ta, tb, p.out, p.M, p.N, num_kb, kb_per);
   cudaError_t e = cudaGetLastError();

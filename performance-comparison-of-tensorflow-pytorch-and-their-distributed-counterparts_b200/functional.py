@@ -10,6 +10,7 @@ Two granularities:
     stand-alone modules in nn.py and by the classifier head.
 """
 import os
+import weakref
 
 import torch
 from torch.autograd.function import once_differentiable
@@ -394,7 +395,39 @@ class _SegmentedCapture(object):
 
 class _GraphRecord(object):
     __slots__ = ("fwd", "bwd", "x", "feat", "dfeat", "grads", "dx", "state", "ptrs", "ws", "uses", "ddp", "order",
-                 "segments")
+                 "segments", "gen", "live")
+
+
+class _ReplayToken(object):
+    """Lives exactly as long as the autograd node of one replayed forward (it hangs off the node's ctx)."""
+    __slots__ = ("__weakref__",)
+
+
+def graph_record_busy(rec):
+    """A graph record holds ONE set of saved activations.  While a forward replayed from it still waits for its
+    backward (its autograd node is alive), a second forward must not replay the same record -- it would overwrite
+    what the first backward reads (two micro-batches whose losses are summed, a siamese use, forward twice then
+    backward).  Such calls take the eager node, which keeps its state per call."""
+    live = getattr(rec, "live", None)
+    return live is not None and live() is not None
+
+
+def graph_replay_begin(rec, ctx):
+    """Forward side of the guard: stamps the record's generation into ctx and registers the node as pending."""
+    rec.gen = (getattr(rec, "gen", 0) or 0) + 1
+    ctx.gen = rec.gen
+    if rec.bwd is not None:
+        ctx.token = _ReplayToken()
+        rec.live = weakref.ref(ctx.token)
+
+
+def graph_replay_check(rec, ctx):
+    """Backward side: the saved state must still be the one this node's forward produced."""
+    if getattr(ctx, "gen", None) != getattr(rec, "gen", None):
+        raise RuntimeError("b200net: the CUDA-graph record of this forward was replayed again before its backward ran; "
+                           "its saved activations are gone (set B200_CUDA_GRAPHS=0 for this usage)")
+    rec.live = None
+    ctx.token = None
 
 
 _BN_MODULES = {}   # id(model) -> (structure signature, [BatchNorm2d modules])
@@ -444,6 +477,7 @@ def _capture(model, x, params, key):
     rec.x = x.detach().clone()
     rec.ptrs = _tensor_ptrs(model, params)
     rec.uses = 0
+    rec.gen, rec.live = 0, None
     pool = torch.cuda.graph_pool_handle()
     _CAPTURE_PACKED.clear()
     # training graphs re-pack the weights on every replay (they change every step); forward-only graphs read the
@@ -500,6 +534,7 @@ class _GraphedBackbone(torch.autograd.Function):
     def forward(ctx, rec, x, *params):
         rec.x.copy_(x)
         rec.fwd.replay()
+        graph_replay_begin(rec, ctx)
         ctx.rec = rec
         ctx.saved_params = params
         return rec.feat.clone()
@@ -510,6 +545,7 @@ class _GraphedBackbone(torch.autograd.Function):
         rec = ctx.rec
         if rec.bwd is None:
             raise RuntimeError("b200net: this backbone graph was captured without a backward pass")
+        graph_replay_check(rec, ctx)
         rec.dfeat.copy_(dfeat)
         if rec.ddp is not None:
             for g, ready in rec.segments:
@@ -538,6 +574,8 @@ def resnet_backbone(model, x):
     rec = _GRAPHS.get(key)
     if rec is not None and rec != "failed":
         if rec.ptrs == _tensor_ptrs(model, params):
+            if graph_record_busy(rec):     # an earlier replayed forward still waits for its backward
+                return _ResNetBackbone.apply(model, torch.is_grad_enabled(), x, *params)
             rec.uses += 1
             return _GraphedBackbone.apply(rec, x, *params)
         del _GRAPHS[key]          # parameters were re-allocated (model.to(), new tensors): recapture

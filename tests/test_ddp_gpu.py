@@ -192,3 +192,26 @@ def test_ddp_world2_nccl_bert():
     results = mgr.dict()
     mp.spawn(_bert_worker, args=(world, port, results), nprocs=world, join=True)
     assert dict(results) == {0: "ok", 1: "ok"}
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_second_device_in_one_process():
+    """Kernel attributes (the dynamic shared-memory opt-in of the tcgen05 kernels) and the SM count are cached per
+    DEVICE: a process that drives cuda:1 after cuda:0 must get the same results on both."""
+    import b200net
+    from b200net import ops
+    outs = []
+    for d in (0, 1):
+        with torch.cuda.device(d):
+            dev = torch.device("cuda", d)
+            g = torch.Generator().manual_seed(5)
+            x = torch.randn(4, 20, 20, 128, generator=g).to(torch.bfloat16).to(dev)
+            w = (torch.randn(128, 128, 3, 3, generator=g) / 34.0).to(dev)
+            wp = ops.pack_weight(w, torch.bfloat16)
+            y = ops.conv_fprop(x, wp, 128, 3, 3, 1, 1)
+            dx = ops.conv_dgrad(y, wp, x.shape, 128, 3, 3, 1, 1)
+            dw = ops.conv_wgrad(x, y, 128, 3, 3, 1, 1)
+            torch.cuda.synchronize(dev)
+            outs.append((y.cpu(), dx.cpu(), dw.cpu()))
+    for a, b in zip(outs[0], outs[1]):
+        assert torch.equal(a, b)

@@ -152,6 +152,60 @@ def test_conv_fprop_dgrad_wgrad(prec, case):
     assert _rel(dw, wd.grad) < (1e-4 if prec == "fp32" else 5e-3)
 
 
+# Shapes of the BENCHMARKED configuration (bench.py: N=256 at 160 px, bf16): every case has several times more output
+# tiles than the B200 has SMs, so each persistent CTA walks many tiles, both TMEM accumulators wrap around several
+# times, the smem ring's phase bits flip repeatedly, and the per-CTA BatchNorm statistics accumulate over many tiles.
+# (The small cases above never give a CTA a second tile.)  fp64 cuDNN/ATen on the GPU is the checker.
+BIG_CONV_CASES = [
+    # N, H, C, K, R, stride, pad     tiles (fprop, 128-pixel boxes x column tiles)
+    (64, 40, 64, 256, 1, 1, 0),      # c: 800 x 1
+    (64, 40, 64, 64, 3, 1, 1),       # b: 800 x 1
+    (128, 40, 128, 128, 3, 2, 1),    # f: 400 x 1, dgrad = four parity classes
+    (256, 10, 256, 1024, 1, 1, 0),   # m at the benchmark batch: 200 x 4
+    (1024, 5, 512, 512, 3, 1, 1),    # v: 205 x 2, 125-row boxes (ragged M tile)
+    (96, 20, 256, 512, 1, 2, 0),     # h: 1x1 stride-2 downsample
+]
+
+
+@pytest.mark.parametrize("case", BIG_CONV_CASES)
+def test_conv_bf16_multi_tile_persistent_walk(case):
+    from b200net import ops
+    N, H, C, K, R, stride, pad = case
+    dt = torch.bfloat16
+    x = _rand((N, C, H, H), dt, 11)
+    w = _rand((K, C, R, R), torch.float32, 12, scale=1.0 / math.sqrt(C * R * R))
+    xd = x.double().requires_grad_(True)
+    wd = w.to(dt).double().requires_grad_(True)
+    yref = TF.conv2d(xd, wd, stride=stride, padding=pad)
+    dy = _rand(tuple(yref.shape), dt, 13)
+    yref.backward(dy.double())
+    xh, dyh = _nhwc(x, dt), _nhwc(dy, dt)
+    wp = ops.pack_weight(w, dt)
+    tol = TOL["bf16"]
+
+    y, part = ops.conv_fprop_bnstats(xh, wp, K, R, R, stride, pad)
+    assert part is not None, "benchmark shapes must be on the fused-statistics path"
+    ntiles = ((N * yref.shape[2] * yref.shape[3]) // 128) * ((K + 255) // 256)
+    assert ntiles >= 148, ntiles
+    assert _rel(y.permute(0, 3, 1, 2), yref) < tol
+    assert torch.equal(y, ops.conv_fprop(xh, wp, K, R, R, stride, pad))
+    yd = y.double().reshape(-1, K)
+    assert _rel(part[:, 0].double().sum(0), yd.sum(0)) < 1e-5
+    assert _rel(part[:, 1].double().sum(0), (yd * yd).sum(0)) < 1e-5
+
+    dx = ops.conv_dgrad(dyh, wp, xh.shape, K, R, R, stride, pad)
+    assert _rel(dx.permute(0, 3, 1, 2), xd.grad) < tol
+    base = _rand(tuple(xh.shape), dt, 14)
+    acc = base.clone()
+    ops.conv_dgrad(dyh, wp, xh.shape, K, R, R, stride, pad, out=acc, accumulate=True)
+    assert _rel(acc.permute(0, 3, 1, 2), xd.grad + base.double().permute(0, 3, 1, 2)) < tol
+
+    dw = ops.conv_wgrad(xh, dyh, K, R, R, stride, pad)
+    assert _rel(dw, wd.grad) < 5e-3
+    # deterministic: a second launch gives the same bits (ordered split-K reduction, no atomics)
+    assert torch.equal(dw, ops.conv_wgrad(xh, dyh, K, R, R, stride, pad))
+
+
 @pytest.mark.parametrize("case", [c for c in CONV_CASES if c[2] % 64 == 0 and c[3] % 64 == 0])
 def test_conv_fprop_fused_bn_statistics(case):
     """The fprop epilogue also emits per-pixel-tile column sums / sums of squares of the bf16 output: they must add up

@@ -128,10 +128,24 @@ def test_fp32_parity_c1_config_batch32_160px():
         print("C1 eval logits: ours vs fp32 %.3e, tolerance %.3e" % (_relmax(got["eval_logps"], exp["eval_logps"]), tole))
         assert _relmax(got["eval_logps"], exp["eval_logps"]) <= tole
         assert torch.equal(got["eval_top"], exp["eval_top"])
-        sd64 = ref64.state_dict()
-        for k in ("conv1.weight", "layer1.0.conv2.weight", "layer2.0.downsample.0.weight", "layer4.2.conv3.weight",
-                  "layer3.4.bn2.weight", "fc.0.weight", "fc.3.bias", "layer4.1.bn3.running_var"):
-            assert _relmax_w(ours.state_dict()[k], ref.state_dict()[k]) <= O.arbitrated_tol(ref.state_dict()[k], sd64[k], 1e-3), k
+        # EVERY state_dict tensor after the step, with the effective (arbitrated) tolerance printed so the log shows
+        # how far above the north-star 1e-3 the fp64 arbiter had to lift it and on which tensors
+        sd64, sdo, sdr = ref64.state_dict(), ours.state_dict(), ref.state_dict()
+        rows = []
+        for k, v in sdr.items():
+            if not v.dtype.is_floating_point:
+                assert torch.equal(sdo[k].cpu(), v), k
+                continue
+            tol = O.arbitrated_tol(v, sd64[k], 1e-3)
+            rows.append((tol, _relmax_w(sdo[k], v), k))
+        lifted = [r for r in rows if r[0] > 1e-3]
+        print("C1 after-step tensors: %d compared, %d at the plain 1e-3, %d lifted by the fp64 arbiter (max %.3e)"
+              % (len(rows), len(rows) - len(lifted), len(lifted), max(r[0] for r in rows)))
+        for tol, err, k in sorted(lifted, reverse=True)[:15]:
+            print("  tol %.3e  ours-vs-fp32 %.3e  %s" % (tol, err, k))
+        for tol, err, k in rows:
+            assert err <= tol, (k, err, tol)
+        assert max(r[0] for r in rows) < 0.5, "arbitrated tolerance ballooned"
     finally:
         b200net.set_precision("bf16")
 
@@ -148,6 +162,104 @@ def test_bf16_first_steps_within_1e2_of_fp32_oracle():
     exp = O.run_case(ref, "A", n=32, hw=128, steps=3)
     for a, b in zip(got["losses"], exp["losses"]):
         assert abs(a - b) <= 1e-2 * abs(b), (got["losses"], exp["losses"])
+
+
+def _cos(a, b):
+    a, b = a.double().reshape(-1).cpu(), b.double().reshape(-1).cpu()
+    return (torch.dot(a, b) / (a.norm() * b.norm()).clamp_min(1e-300)).item()
+
+
+def test_bf16_benchmark_config_step_n256_160px():
+    """The configuration bench.py times (BASELINE.json configs[1]): N=256, 3x160x160, bf16 tensor-core mode, one
+    Mode-A step of the reference loop.  Every convolution launches several waves of tiles per CTA here.  Checked
+    against the CPU oracle (stock torch fp32): loss within 1e-2; log-probabilities within 1e-2 or, where bf16 storage
+    of 53 layers of activations itself moves them further, within 1.5x the deviation of STOCK torch running the same
+    module under bf16 autocast on the GPU (the witness SURVEY 8(d) C2 names; both figures are printed, max and RMS);
+    and every parameter gradient against the exact-arithmetic arbiter (the same torchvision module in float64, run by stock torch on the GPU):
+    cosine >= 0.999, or -- for the BatchNorm shifts/scales of the residual branches, whose gradient is a sum of
+    nearly cancelling terms that stock fp32 itself does not resolve -- at least as close as 10x what stock fp32
+    loses.  The per-tensor figures are printed."""
+    import b200net
+    b200net.set_precision("bf16")
+    torch.set_num_threads(O.cpu_threads())
+    n, hw = 256, 160
+    ref = O.build_reference_model(dropout=False)
+    ours = _ours_from(ref)
+    got = _run_ours(ours, "A", n=n, hw=hw, steps=1)
+    g_ours = {k: p.grad.detach().double().cpu() for k, p in ours.named_parameters()}
+    exp = O.run_case(ref, "A", n=n, hw=hw, steps=1)
+    g32 = {k: p.grad.detach().double() for k, p in ref.named_parameters()}
+    ref64 = O.build_reference_model(dropout=False).double().to(DEV)
+    e64 = O.run_case(ref64, "A", n=n, hw=hw, steps=1)
+    g64 = {k: p.grad.detach().double().cpu() for k, p in ref64.named_parameters()}
+    del ref64
+    torch.cuda.empty_cache()
+    # stock bf16 witness: the oracle module itself, forward under autocast on the GPU (train-mode BatchNorm)
+    wit = O.build_reference_model(dropout=False).to(DEV).train()
+    xw, _ = O.make_batch(n, hw, O.SEED_DATA, DEV)
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+        lw = wit(xw).float().cpu()
+    del wit, xw
+    torch.cuda.empty_cache()
+    lerr = abs(got["losses"][0] - exp["losses"][0]) / abs(exp["losses"][0])
+    perr, werr = _relmax(got["logps"][0], exp["logps"][0]), _relmax(lw, exp["logps"][0])
+    rms = lambda a, b: ((a.double() - b.double()).pow(2).mean().sqrt() / b.double().abs().max()).item()
+    print("N=256 bf16 step: loss ours %.6f oracle fp32 %.6f fp64 %.6f (rel %.2e); log-probs vs fp32 oracle: ours max "
+          "%.2e rms %.2e, stock bf16 autocast max %.2e rms %.2e"
+          % (got["losses"][0], exp["losses"][0], e64["losses"][0], lerr, perr, rms(got["logps"][0], exp["logps"][0]),
+             werr, rms(lw, exp["logps"][0])))
+    assert lerr <= 1e-2
+    assert perr <= max(1e-2, 1.5 * werr), (perr, werr)
+    assert rms(got["logps"][0], exp["logps"][0]) <= max(1e-2, 1.5 * rms(lw, exp["logps"][0]))
+    worst = []
+    for k, g in g64.items():
+        c_ours, c_32 = _cos(g_ours[k], g), _cos(g32[k], g)
+        worst.append((c_ours, c_32, k))
+    worst.sort()
+    for c_ours, c_32, k in worst[:12]:
+        print("grad cosine vs fp64: ours %.6f  stock fp32 %.6f  %s" % (c_ours, c_32, k))
+    n_ok = sum(1 for c, _, _ in worst if c >= 0.999)
+    print("%d of %d gradient tensors at cosine >= 0.999" % (n_ok, len(worst)))
+    for c_ours, c_32, k in worst:
+        assert c_ours >= min(0.999, 1.0 - 10.0 * (1.0 - c_32)) - 1e-12, (k, c_ours, c_32)
+    # every convolution weight (the tensors the tcgen05 kernels produce) must meet the plain bound
+    for c_ours, c_32, k in worst:
+        if k.endswith("conv1.weight") or k.endswith("conv2.weight") or k.endswith("conv3.weight") or "downsample.0" in k:
+            assert c_ours >= 0.999, (k, c_ours)
+
+
+def test_bf16_eval_n1024_argmax_vs_oracle():
+    """BASELINE.json configs[3]: eval-mode inference at batch 1024, bf16, against the fp32 CPU oracle.  bf16 cannot
+    promise bit-exact argmax on near-ties, so the test states what it does promise: log-probabilities within
+    2e-2 of their scale, and a prediction may differ from the oracle's ONLY where the oracle's own top-2 margin is
+    below twice that error bound.  The flip count is printed (bench.py reports it as infer.argmax_flips)."""
+    import b200net
+    b200net.set_precision("bf16")
+    torch.set_num_threads(O.cpu_threads())
+    ref = O.build_reference_model(dropout=False)
+    O.run_case(ref, "A", n=32, hw=160, steps=3)          # non-trivial weights and BN running statistics
+    ours = _ours_from(ref)
+    ref.eval()
+    ours.eval()
+    x, _ = O.make_batch(1024, 160, 77)
+    with torch.no_grad():
+        lo = ref(x).double()
+        lg = ours(x.to(DEV)).double().cpu()
+    scale = lo.abs().max().item()
+    err = (lg - lo).abs().max().item()
+    srt = lo.sort(dim=1, descending=True).values
+    margin = srt[:, 0] - srt[:, 1]
+    flips = lo.argmax(1) != lg.argmax(1)
+    bound = 2.0 * 2e-2 * scale
+    print("N=1024 bf16 eval: max |dlogp| %.3e (scale %.3f), argmax flips %d of 1024, largest oracle margin among "
+          "flipped rows %.3e (bound %.3e), median margin %.3e"
+          % (err, scale, int(flips.sum()), margin[flips].max().item() if flips.any() else 0.0, bound,
+             margin.median().item()))
+    assert err <= 2e-2 * scale
+    assert (not flips.any()) or margin[flips].max().item() < bound
+    # per row: a flip needs the two candidates' errors to bridge the oracle's margin
+    row_err = (lg - lo).abs().max(1).values
+    assert bool((margin[flips] <= 2.0 * row_err[flips]).all())
 
 
 def test_bf16_loss_curve_100_steps():
@@ -261,6 +373,56 @@ def test_cuda_graph_replay_equals_eager():
             for a, b in zip(oe, og):
                 assert torch.equal(a, b)
             assert all(torch.equal(og[0], o) for o in og)
+    finally:
+        b200net.set_cuda_graphs(True)
+
+
+def test_graph_record_is_not_replayed_while_a_backward_is_pending():
+    """A graph record holds one set of saved activations.  Two forwards followed by the backward of the FIRST (two
+    micro-batches whose losses are combined, a siamese use) must still give the first batch's gradients: the second
+    forward takes the eager node while the first replay waits for its backward."""
+    import b200net
+    from b200net import functional as F
+    ref = O.build_reference_model(dropout=False)
+    crit = nn.NLLLoss()
+    x1, y1 = O.make_batch(8, 64, 21, DEV)
+    x2, y2 = O.make_batch(8, 64, 22, DEV)
+
+    def grads_of(m, first, second):
+        m.zero_grad(set_to_none=True)
+        out1 = m(first[0])
+        out2 = m(second[0]) if second is not None else None
+        crit(out1, first[1]).backward()
+        g1 = [p.grad.clone() for p in m.parameters()]
+        if out2 is not None:
+            m.zero_grad(set_to_none=True)
+            crit(out2, second[1]).backward()
+            return g1, [p.grad.clone() for p in m.parameters()]
+        return g1, None
+
+    try:
+        b200net.set_cuda_graphs(False)
+        m = _ours_from(ref).train()
+        e1, _ = grads_of(m, (x1, y1), None)
+        e2, _ = grads_of(m, (x2, y2), None)
+        b200net.set_cuda_graphs(True)
+        m = _ours_from(ref).train()
+        for p in m.parameters():
+            p.requires_grad = True
+        for _ in range(F.GRAPH_WARMUP + 2):          # warm-up calls, capture, one replay
+            m.zero_grad(set_to_none=True)
+            crit(m(x1), y1).backward()
+        assert any(r != "failed" and r.bwd is not None and r.uses >= 2 for r in F._GRAPHS.values())
+        g1, g2 = grads_of(m, (x1, y1), (x2, y2))
+        for a, b in zip(g1, e1):
+            assert torch.equal(a, b)
+        for a, b in zip(g2, e2):
+            assert torch.equal(a, b)
+        # and the record is free again afterwards
+        m.zero_grad(set_to_none=True)
+        crit(m(x1), y1).backward()
+        for p, b in zip(m.parameters(), e1):
+            assert torch.equal(p.grad, b)
     finally:
         b200net.set_cuda_graphs(True)
 
