@@ -54,6 +54,7 @@ class DistributedDataParallel(_nn.Module):
         self.device_ids = device_ids
         self.output_device = output_device
         self.broadcast_buffers = broadcast_buffers
+        self.find_unused_parameters = bool(find_unused_parameters)
         self.process_group = process_group if process_group is not None else dist.group.WORLD
         self.world_size = dist.get_world_size(self.process_group)
         self.require_backward_grad_sync = True
@@ -251,12 +252,22 @@ class DistributedDataParallel(_nn.Module):
         self._mark_ready(p)
 
     def _finalize(self):
-        # parameters that produced no gradient this iteration (unused) still have to take part in the collective
-        for b in self.buckets:
-            if not b.launched:
-                for p, off in zip(b.params, b.offsets):
-                    if id(p) not in self._ready:
-                        b.flat[off:off + p.numel()].zero_()
+        # Parameters that produced no gradient in this backward.  Under no_sync() nothing is reduced and their
+        # bucket slices may hold gradients accumulated by earlier micro-steps (p.grad is a view of the slice): leave
+        # them alone.  With synchronisation on, torch's DDP raises unless find_unused_parameters=True; with it, the
+        # unused parameters take part in the collective as zeros -- unless they still carry an accumulated gradient.
+        unused = [(b, p, off) for b in self.buckets if not b.launched
+                  for p, off in zip(b.params, b.offsets) if id(p) not in self._ready]
+        if unused and self.require_backward_grad_sync:
+            if not self.find_unused_parameters:
+                self._reset()
+                raise RuntimeError(
+                    "DistributedDataParallel: %d parameter(s) that require grad received no gradient in this backward "
+                    "pass. Pass find_unused_parameters=True to the constructor if parts of the module are "
+                    "legitimately unused (same rule as torch.nn.parallel.DistributedDataParallel)." % len(unused))
+            for b, p, off in unused:
+                if p.grad is None:
+                    b.flat[off:off + p.numel()].zero_()
         while self._next_to_launch < len(self.buckets):
             self._launch(self.buckets[self._next_to_launch])
             self._next_to_launch += 1

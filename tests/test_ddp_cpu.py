@@ -50,7 +50,7 @@ def _worker(rank, world, port, results):
         ref = Net()
         torch.manual_seed(1234)                        # what rank 0 holds
         rank0 = Net()
-        ddp = DDP(ours, device_ids=None, output_device=None, bucket_cap_mb=1)
+        ddp = DDP(ours, device_ids=None, output_device=None, bucket_cap_mb=1, find_unused_parameters=True)
         # (1) construction broadcast: every rank now holds rank 0's parameters and buffers
         for (k, v), (_, v0) in zip(ours.state_dict().items(), rank0.state_dict().items()):
             assert torch.equal(v, v0), k
@@ -108,6 +108,38 @@ def _worker(rank, world, port, results):
         others = [torch.zeros_like(g_local) for _ in range(world)]
         dist.all_gather(others, g_local)
         assert not torch.allclose(others[0], others[1])
+        # (7) gradient accumulation under no_sync when a parameter is used in the first micro-step only: the second
+        # backward must not wipe what the first one left in that parameter's bucket slice
+        class Two(nn.Module):
+            def __init__(self):
+                super().__init__()
+                self.a = nn.Linear(6, 6)
+                self.b = nn.Linear(6, 6)
+
+            def forward(self, x, use_b):
+                return self.b(self.a(x)) if use_b else self.a(x)
+
+        torch.manual_seed(7)
+        two = Two()
+        d2 = DDP(two, device_ids=None, output_device=None, find_unused_parameters=True)
+        xs = torch.randn(4, 6, generator=torch.Generator().manual_seed(50 + rank))
+        d2.zero_grad()
+        with d2.no_sync():
+            d2(xs, True).sum().backward()
+            gb = two.b.weight.grad.clone()
+            assert float(gb.abs().sum()) > 0
+            d2(xs, False).sum().backward()
+            assert torch.equal(two.b.weight.grad, gb), "no_sync micro-step wiped an accumulated gradient"
+        # (8) without find_unused_parameters an unused parameter is an error, as in torch's DDP
+        torch.manual_seed(7)
+        three = Two()
+        d3 = DDP(three, device_ids=None, output_device=None)
+        raised = False
+        try:
+            d3(xs, False).sum().backward()
+        except RuntimeError as e:
+            raised = "find_unused_parameters" in str(e)
+        assert raised
         results[rank] = "ok"
     finally:
         dist.destroy_process_group()
