@@ -156,16 +156,22 @@ int32_t b200_bn_eval_coeffs(const float* gamma, const float* beta, const float* 
  * mask (optional, may be NULL): receives the ReLU mask of the STORED output, one byte per 16-byte vector of y
  * (bit e = element e of the vector is > 0; b200_bn_mask_bytes gives the size, 0 = not available for this C). */
 int64_t b200_bn_mask_bytes(int64_t rows, int32_t C, int32_t dtype);
+/* reverse != 0: the kernel walks the tensor from its last element to its first.  A bandwidth kernel that starts
+ * where its producer finished finds that end of the tensor still in the 126 MB L2 (the result does not depend on
+ * the direction); callers alternate the direction along a producer -> consumer chain. */
 int32_t b200_bn_apply(const void* x, const void* residual, void* y, uint8_t* mask, int64_t rows, int32_t C,
-                      int32_t dtype, const float* scale, const float* shift, int32_t relu, void* stream);
+                      int32_t dtype, const float* scale, const float* shift, int32_t relu, int32_t reverse,
+                      void* stream);
 /* Backward of y = act(bn(x) (+res)).  g = dz * [y > 0] when relu, else g = dz.  The sign of y comes from `mask`
  * (as written by b200_bn_apply) when it is given, otherwise from z = the saved output.
  *   dgamma = sum g*xhat, dbeta = sum g, dx = gamma*invstd*(g - dbeta/n - xhat*dgamma/n);
- *   dres (optional, may be NULL) receives g (gradient of the residual branch). */
+ *   dres (optional, may be NULL) receives g (gradient of the residual branch).
+ *   walk: bit 0 = the reduction pass, bit 1 = the dx pass walks the tensors from the last row to the first (see
+ *   b200_bn_apply; results are independent of it). */
 int32_t b200_bn_backward(const void* dz, const void* z, const uint8_t* mask, const void* x, void* dx, void* dres,
                          int64_t rows, int32_t C, int32_t dtype, const float* gamma, const float* save_mean,
                          const float* save_invstd, int32_t relu, float* dgamma, float* dbeta, void* ws,
-                         int64_t ws_bytes, void* stream);
+                         int64_t ws_bytes, int32_t walk, void* stream);
 /* standalone ReLU backward / elementwise add used between blocks: y = a + b ; y = dz*[z>0] */
 int32_t b200_add(const void* a, const void* b, void* y, int64_t n, int32_t dtype, void* stream);
 int32_t b200_relu_bwd(const void* dz, const void* z, void* dx, int64_t n, int32_t dtype, void* stream);

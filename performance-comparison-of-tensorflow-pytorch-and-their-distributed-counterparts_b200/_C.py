@@ -59,8 +59,8 @@ SIGNATURES = {
     "b200_bn_train_stats_noalloc": (I32, [P, I64, I32, I32, P, P, P, P, F, F, P, P, P, P, P]),
     "b200_bn_eval_coeffs": (I32, [P, P, P, P, F, P, P, I32, P]),
     "b200_bn_mask_bytes": (I64, [I64, I32, I32]),
-    "b200_bn_apply": (I32, [P, P, P, P, I64, I32, I32, P, P, I32, P]),
-    "b200_bn_backward": (I32, [P, P, P, P, P, P, I64, I32, I32, P, P, P, I32, P, P, P, I64, P]),
+    "b200_bn_apply": (I32, [P, P, P, P, I64, I32, I32, P, P, I32, I32, P]),
+    "b200_bn_backward": (I32, [P, P, P, P, P, P, I64, I32, I32, P, P, P, I32, P, P, P, I64, I32, P]),
     "b200_add": (I32, [P, P, P, I64, I32, P]),
     "b200_relu_bwd": (I32, [P, P, P, I64, I32, P]),
     "b200_maxpool3x3s2_fwd": (I32, [P, P, P, I32, I32, I32, I32, I32, P]),

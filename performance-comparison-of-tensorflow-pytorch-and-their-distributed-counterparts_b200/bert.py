@@ -17,6 +17,7 @@ Nothing goes through ATen's matmul, layer_norm, softmax or embedding.
 """
 import math
 import os
+import weakref
 import warnings
 
 import torch
@@ -205,7 +206,8 @@ def _operand(ws, dtype):
         return out
     sig = tuple((w.data_ptr(), w._version) for w in ws)
     e = _PK.get(key)
-    if e is not None and e[0] == sig:
+    # id() values are recycled across models: the entry also remembers which parameter objects it was built from
+    if e is not None and e[0] == sig and all(r() is w for r, w in zip(e[2], ws)):
         return e[1]
     rows = sum(w.shape[0] for w in ws)
     out = torch.empty((rows,) + tuple(ws[0].shape[1:]), dtype=dtype, device=ws[0].device)
@@ -213,7 +215,7 @@ def _operand(ws, dtype):
     for w in ws:
         _cast_into(w.detach(), out[r:r + w.shape[0]])
         r += w.shape[0]
-    _PK[key] = (sig, out)
+    _PK[key] = (sig, out, tuple(weakref.ref(w, lambda _r, k=key: _PK.pop(k, None)) for w in ws))
     return out
 
 
@@ -611,12 +613,27 @@ class BertForSequenceClassification(nn.Module):
 
     @classmethod
     def from_pretrained(cls, name_or_path, num_labels=2, **kw):
-        """A local directory holding `pytorch_model.bin` is loaded; a hub name cannot be fetched on an offline box,
-        so it yields the architecture with transformers' random initialisation (and says so)."""
+        """A local directory holding `pytorch_model.bin` or `model.safetensors` (the two files Hugging Face
+        checkpoints ship) is loaded; a directory that exists but holds neither is an error.  A hub name cannot be
+        fetched on an offline box, so it yields the architecture with transformers' random initialisation (and says
+        so)."""
         model = cls(BertConfig(num_labels=num_labels, **kw))
-        ckpt = os.path.join(str(name_or_path), "pytorch_model.bin")
+        path = str(name_or_path)
+        ckpt, st_file = os.path.join(path, "pytorch_model.bin"), os.path.join(path, "model.safetensors")
+        sd = None
         if os.path.isfile(ckpt):
             sd = torch.load(ckpt, map_location="cpu")
+        elif os.path.isfile(st_file):
+            from safetensors.torch import load_file
+            sd = load_file(st_file, device="cpu")
+        elif os.path.isdir(path):
+            raise OSError("b200net from_pretrained: %r holds neither pytorch_model.bin nor model.safetensors" % path)
+        if sd is not None:
+            # checkpoints of the bare encoder (BertModel / BertForPreTraining) store keys without / with other prefixes
+            if not any(k.startswith("bert.") for k in sd):
+                sd = {"bert." + k: v for k, v in sd.items()}
+            sd = {k.replace("LayerNorm.gamma", "LayerNorm.weight").replace("LayerNorm.beta", "LayerNorm.bias"): v
+                  for k, v in sd.items()}
             missing, unexpected = model.load_state_dict(sd, strict=False)
             head = [k for k in missing if not k.startswith("classifier.")]
             if head:
@@ -663,7 +680,12 @@ from . import optim as _optim  # noqa: E402
 class AdamW(_optim.AdamW):
     """`transformers.AdamW(model.parameters(), lr=2e-5, eps=1e-8)` (pytorch_on_language_distr.py:167-170): the
     transformers signature and defaults (eps=1e-6, weight_decay=0.0, correct_bias=True) over the multi-tensor
-    Adam kernel."""
+    Adam kernel, with the PUBLISHED transformers update rule: p -= lr*sqrt(1-b2^t)/(1-b1^t) * m / (sqrt(v) + eps)
+    (eps is added before the bias correction of v; torch.optim.AdamW adds it after, an effective eps that is
+    sqrt(1-b2^t) ~ 0.03x smaller at step 1).  One deviation remains and only matters when weight_decay != 0 (the
+    reference uses the default 0.0): transformers applies p -= lr*wd*p AFTER the Adam update, this kernel -- like
+    torch -- before it; the two differ by O(lr^2 * wd)."""
+    _eps_before_bias_correction = True
 
     def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-6, weight_decay=0.0, correct_bias=True):
         if not correct_bias:

@@ -46,14 +46,17 @@ template <typename T, int MODE>
 __global__ void __launch_bounds__(BN_THREADS)
 bn_partial_vec_kernel(const T* __restrict__ x, const T* __restrict__ dz, const T* __restrict__ z,
                       const uint8_t* __restrict__ mask, const float* __restrict__ mean, long long rows, int C, int cx,
-                      long long rows_per_block, float* __restrict__ part) {
+                      long long rows_per_block, float* __restrict__ part, int reverse) {
   constexpr int VEC = VecTraits<T>::W;
   constexpr int U = 4;  // rows in flight per thread (raw 16-byte registers, converted only when consumed)
   __shared__ float red[BN_THREADS][2 * VEC + 1];
   const int nvec = C / VEC;
   const int ry = BN_THREADS / cx;
   const int tx = threadIdx.x % cx, ty = threadIdx.x / cx;
-  const long long r0 = blockIdx.x * rows_per_block;
+  // reverse: the first blocks to be scheduled take the LAST rows (what the producer kernel touched most recently
+  // and L2 still holds); the partial row a block writes follows its rows, so the result does not depend on it
+  const int blk = reverse ? (int)(gridDim.x - 1 - blockIdx.x) : (int)blockIdx.x;
+  const long long r0 = blk * rows_per_block;
   long long r1 = r0 + rows_per_block;
   if (r1 > rows) r1 = rows;
   for (int base = 0; base < nvec; base += cx) {
@@ -116,8 +119,8 @@ bn_partial_vec_kernel(const T* __restrict__ x, const T* __restrict__ dz, const T
       for (int e = 0; e < VEC; ++e) {
         float a = 0.f, b = 0.f;
         for (int yy = 0; yy < ry; ++yy) { a += red[yy * cx + tx][e]; b += red[yy * cx + tx][VEC + e]; }
-        part[((long long)blockIdx.x * 2 + 0) * C + cv * VEC + e] = a;
-        part[((long long)blockIdx.x * 2 + 1) * C + cv * VEC + e] = b;
+        part[((long long)blk * 2 + 0) * C + cv * VEC + e] = a;
+        part[((long long)blk * 2 + 1) * C + cv * VEC + e] = b;
       }
     }
     __syncthreads();
@@ -255,33 +258,37 @@ template <typename T, int VEC, bool FIXEDC>
 __global__ void __launch_bounds__(BN_THREADS)
 bn_apply_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __restrict__ y, uint8_t* __restrict__ mask,
                 long long nvec_total, int nvec, const float* __restrict__ scale, const float* __restrict__ shift,
-                int relu) {
+                int relu, int reverse) {
   const long long stride = (long long)gridDim.x * blockDim.x;
   long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  // reverse: element index = last - i (the walk starts where the producer kernel finished, i.e. at what L2 still
+  // holds); the channel of an index changes from i % nvec to nvec-1 - i % nvec, still fixed per thread
+  const long long last = nvec_total - 1;
+#define B200_IDX(v) (reverse ? last - (v) : (v))
   float sc[VEC], sh[VEC];
   if (FIXEDC) {
-    const int c = (int)(i % nvec) * VEC;
+    const int c = (int)(B200_IDX(i) % nvec) * VEC;
 #pragma unroll
     for (int e = 0; e < VEC; ++e) { sc[e] = scale[c + e]; sh[e] = shift[c + e]; }
   }
   if constexpr (FIXEDC && VEC > 1) {
     // streaming loop, two 16-byte vectors (plus residuals) in flight per thread
     for (; i < nvec_total; i += 2 * stride) {
-      const long long i1 = i + stride;
-      const bool has1 = i1 < nvec_total;
+      const bool has1 = i + stride < nvec_total;
+      const long long e0 = B200_IDX(i), e1 = has1 ? B200_IDX(i + stride) : 0;
       float x0[VEC], x1[VEC], r0[VEC], r1[VEC];
-      load_vec(x + i * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(x0));
-      if (has1) load_vec(x + i1 * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(x1));
+      load_vec(x + e0 * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(x0));
+      if (has1) load_vec(x + e1 * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(x1));
       if (res) {
-        load_vec(res + i * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(r0));
-        if (has1) load_vec(res + i1 * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(r1));
+        load_vec(res + e0 * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(r0));
+        if (has1) load_vec(res + e1 * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(r1));
       }
 #pragma unroll
       for (int half = 0; half < 2; ++half) {
         if (half == 1 && !has1) break;
         float (&xv)[VEC] = half ? x1 : x0;
         float (&rv)[VEC] = half ? r1 : r0;
-        const long long ii = half ? i1 : i;
+        const long long ii = half ? e1 : e0;
         uint32_t m = 0;
 #pragma unroll
         for (int e = 0; e < VEC; ++e) {
@@ -301,12 +308,13 @@ bn_apply_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __restric
     return;
   }
   for (; i < nvec_total; i += stride) {
+    const long long ei = B200_IDX(i);
     if (!FIXEDC) {
-      const int c = (int)(i % nvec) * VEC;
+      const int c = (int)(ei % nvec) * VEC;
 #pragma unroll
       for (int e = 0; e < VEC; ++e) { sc[e] = scale[c + e]; sh[e] = shift[c + e]; }
     }
-    const long long off = i * VEC;
+    const long long off = ei * VEC;
     float xv[VEC], rv[VEC];
     if constexpr (VEC == 1) { xv[0] = to_f(x[off]); if (res) rv[0] = to_f(res[off]); }
     else {
@@ -328,10 +336,11 @@ bn_apply_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __restric
         // the bit must describe the STORED value (after rounding to T), which is what "z > 0" meant before
 #pragma unroll
         for (int e = 0; e < VEC; ++e) m |= (to_f(from_f<T>(xv[e])) > 0.f ? 1u : 0u) << e;
-        mask[i] = (uint8_t)m;
+        mask[ei] = (uint8_t)m;
       }
     }
   }
+#undef B200_IDX
 }
 
 enum { DM_NONE = 0, DM_Z = 1, DM_MASK = 2 };
@@ -339,31 +348,33 @@ template <typename T, int VEC, bool FIXEDC, int DMODE>
 __global__ void __launch_bounds__(BN_THREADS)
 bn_bwd_dx_kernel(const T* __restrict__ dz, const T* __restrict__ z, const uint8_t* __restrict__ mask,
                  const T* __restrict__ x, T* __restrict__ dx, T* __restrict__ dres, long long nvec_total, int nvec,
-                 int C, const float* __restrict__ mean, const float* __restrict__ coef) {
+                 int C, const float* __restrict__ mean, const float* __restrict__ coef, int reverse) {
   const long long stride = (long long)gridDim.x * blockDim.x;
   long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const long long last = nvec_total - 1;      // reverse walk: see bn_apply_kernel
+#define B200_IDX(v) (reverse ? last - (v) : (v))
   float cA[VEC], cB[VEC], cC[VEC], mu[VEC];
   if (FIXEDC) {
-    const int c = (int)(i % nvec) * VEC;
+    const int c = (int)(B200_IDX(i) % nvec) * VEC;
 #pragma unroll
     for (int e = 0; e < VEC; ++e) { cA[e] = coef[c + e]; cB[e] = coef[C + c + e]; cC[e] = coef[2 * C + c + e]; mu[e] = mean[c + e]; }
   }
   if constexpr (FIXEDC && VEC > 1) {
     // streaming loop, two vectors of each input in flight per thread
     for (; i < nvec_total; i += 2 * stride) {
-      const long long i1 = i + stride;
-      const bool has1 = i1 < nvec_total;
+      const bool has1 = i + stride < nvec_total;
+      const long long e0 = B200_IDX(i), e1 = has1 ? B200_IDX(i + stride) : 0;
       float g0[VEC], g1[VEC], x0[VEC], x1[VEC], z0[VEC], z1[VEC];
       uint32_t m0 = 0xffffffffu, m1 = 0xffffffffu;
-      load_vec(dz + i * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(g0));
-      load_vec(x + i * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(x0));
-      if (DMODE == DM_Z) load_vec(z + i * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(z0));
-      if (DMODE == DM_MASK) m0 = mask[i];
+      load_vec(dz + e0 * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(g0));
+      load_vec(x + e0 * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(x0));
+      if (DMODE == DM_Z) load_vec(z + e0 * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(z0));
+      if (DMODE == DM_MASK) m0 = mask[e0];
       if (has1) {
-        load_vec(dz + i1 * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(g1));
-        load_vec(x + i1 * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(x1));
-        if (DMODE == DM_Z) load_vec(z + i1 * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(z1));
-        if (DMODE == DM_MASK) m1 = mask[i1];
+        load_vec(dz + e1 * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(g1));
+        load_vec(x + e1 * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(x1));
+        if (DMODE == DM_Z) load_vec(z + e1 * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(z1));
+        if (DMODE == DM_MASK) m1 = mask[e1];
       }
 #pragma unroll
       for (int half = 0; half < 2; ++half) {
@@ -372,7 +383,7 @@ bn_bwd_dx_kernel(const T* __restrict__ dz, const T* __restrict__ z, const uint8_
         float (&xv)[VEC] = half ? x1 : x0;
         float (&zv)[VEC] = half ? z1 : z0;
         const uint32_t m = half ? m1 : m0;
-        const long long ii = half ? i1 : i;
+        const long long ii = half ? e1 : e0;
 #pragma unroll
         for (int e = 0; e < VEC; ++e) {
           bool on = true;
@@ -389,12 +400,13 @@ bn_bwd_dx_kernel(const T* __restrict__ dz, const T* __restrict__ z, const uint8_
     return;
   }
   for (; i < nvec_total; i += stride) {
+    const long long ei = B200_IDX(i);
     if (!FIXEDC) {
-      const int c = (int)(i % nvec) * VEC;
+      const int c = (int)(ei % nvec) * VEC;
 #pragma unroll
       for (int e = 0; e < VEC; ++e) { cA[e] = coef[c + e]; cB[e] = coef[C + c + e]; cC[e] = coef[2 * C + c + e]; mu[e] = mean[c + e]; }
     }
-    const long long off = i * VEC;
+    const long long off = ei * VEC;
     float gv[VEC], zv[VEC], xv[VEC];
     uint32_t m = 0xffffffffu;
     if constexpr (VEC == 1) {
@@ -404,7 +416,7 @@ bn_bwd_dx_kernel(const T* __restrict__ dz, const T* __restrict__ z, const uint8_
       load_vec(dz + off, reinterpret_cast<float(&)[VecTraits<T>::W]>(gv));
       load_vec(x + off, reinterpret_cast<float(&)[VecTraits<T>::W]>(xv));
       if (DMODE == DM_Z) load_vec(z + off, reinterpret_cast<float(&)[VecTraits<T>::W]>(zv));
-      if (DMODE == DM_MASK) m = mask[i];
+      if (DMODE == DM_MASK) m = mask[ei];
     }
 #pragma unroll
     for (int e = 0; e < VEC; ++e) {
@@ -421,6 +433,7 @@ bn_bwd_dx_kernel(const T* __restrict__ dz, const T* __restrict__ z, const uint8_
       if (dres) store_vec(dres + off, reinterpret_cast<float(&)[VecTraits<T>::W]>(gv));
     }
   }
+#undef B200_IDX
 }
 
 template <typename T>
@@ -482,17 +495,17 @@ static BnPlan bn_plan(long long rows, int C) {
 
 template <typename T>
 static void launch_bn_partial(const BnPlan& p, int mode, const T* x, const T* dz, const T* z, const uint8_t* mask,
-                              const float* mean, long long rows, int C, float* part, cudaStream_t st) {
+                              const float* mean, long long rows, int C, float* part, cudaStream_t st, int reverse = 0) {
   if (p.vec == 1) {
     if (mode == PM_FWD) bn_partial_scalar_kernel<T, PM_FWD><<<p.nblk, BN_THREADS, 0, st>>>(x, dz, z, mean, rows, C, p.cx, p.rows_per_block, part);
     else if (mode == PM_BWD) bn_partial_scalar_kernel<T, PM_BWD><<<p.nblk, BN_THREADS, 0, st>>>(x, dz, z, mean, rows, C, p.cx, p.rows_per_block, part);
     else bn_partial_scalar_kernel<T, PM_BWD_Z><<<p.nblk, BN_THREADS, 0, st>>>(x, dz, z, mean, rows, C, p.cx, p.rows_per_block, part);
     return;
   }
-  if (mode == PM_FWD) bn_partial_vec_kernel<T, PM_FWD><<<p.nblk, BN_THREADS, 0, st>>>(x, dz, z, mask, mean, rows, C, p.cx, p.rows_per_block, part);
-  else if (mode == PM_BWD) bn_partial_vec_kernel<T, PM_BWD><<<p.nblk, BN_THREADS, 0, st>>>(x, dz, z, mask, mean, rows, C, p.cx, p.rows_per_block, part);
-  else if (mode == PM_BWD_Z) bn_partial_vec_kernel<T, PM_BWD_Z><<<p.nblk, BN_THREADS, 0, st>>>(x, dz, z, mask, mean, rows, C, p.cx, p.rows_per_block, part);
-  else bn_partial_vec_kernel<T, PM_BWD_MASK><<<p.nblk, BN_THREADS, 0, st>>>(x, dz, z, mask, mean, rows, C, p.cx, p.rows_per_block, part);
+  if (mode == PM_FWD) bn_partial_vec_kernel<T, PM_FWD><<<p.nblk, BN_THREADS, 0, st>>>(x, dz, z, mask, mean, rows, C, p.cx, p.rows_per_block, part, reverse);
+  else if (mode == PM_BWD) bn_partial_vec_kernel<T, PM_BWD><<<p.nblk, BN_THREADS, 0, st>>>(x, dz, z, mask, mean, rows, C, p.cx, p.rows_per_block, part, reverse);
+  else if (mode == PM_BWD_Z) bn_partial_vec_kernel<T, PM_BWD_Z><<<p.nblk, BN_THREADS, 0, st>>>(x, dz, z, mask, mean, rows, C, p.cx, p.rows_per_block, part, reverse);
+  else bn_partial_vec_kernel<T, PM_BWD_MASK><<<p.nblk, BN_THREADS, 0, st>>>(x, dz, z, mask, mean, rows, C, p.cx, p.rows_per_block, part, reverse);
 }
 
 template <typename T>
@@ -507,17 +520,17 @@ static int32_t bn_stats_impl(const T* x, long long rows, int C, const float* gam
 
 template <typename T>
 static int32_t bn_apply_impl(const T* x, const T* res, T* y, uint8_t* mask, long long rows, int C, const float* scale,
-                             const float* shift, int relu, cudaStream_t st) {
+                             const float* shift, int relu, int reverse, cudaStream_t st) {
   const bool aligned = ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y) | reinterpret_cast<uintptr_t>(res)) & 15) == 0;
   if (C % VecTraits<T>::W == 0 && aligned) {
     constexpr int V = VecTraits<T>::W;
     bool fixed;
     const int grid = ew_grid_fixed(rows * (C / V), C / V, &fixed);
-    if (fixed) bn_apply_kernel<T, V, true><<<grid, BN_THREADS, 0, st>>>(x, res, y, mask, rows * (C / V), C / V, scale, shift, relu);
-    else bn_apply_kernel<T, V, false><<<grid, BN_THREADS, 0, st>>>(x, res, y, mask, rows * (C / V), C / V, scale, shift, relu);
+    if (fixed) bn_apply_kernel<T, V, true><<<grid, BN_THREADS, 0, st>>>(x, res, y, mask, rows * (C / V), C / V, scale, shift, relu, reverse);
+    else bn_apply_kernel<T, V, false><<<grid, BN_THREADS, 0, st>>>(x, res, y, mask, rows * (C / V), C / V, scale, shift, relu, reverse);
   } else {
     if (mask) return fail(B200_UNSUPPORTED, "bn_apply: the ReLU mask needs C %% %d == 0 and 16-byte aligned tensors", VecTraits<T>::W);
-    bn_apply_kernel<T, 1, false><<<ew_grid(rows * C), BN_THREADS, 0, st>>>(x, res, y, nullptr, rows * C, C, scale, shift, relu);
+    bn_apply_kernel<T, 1, false><<<ew_grid(rows * C), BN_THREADS, 0, st>>>(x, res, y, nullptr, rows * C, C, scale, shift, relu, reverse);
   }
   return check_launch("bn_apply");
 }
@@ -525,7 +538,8 @@ static int32_t bn_apply_impl(const T* x, const T* res, T* y, uint8_t* mask, long
 template <typename T>
 static int32_t bn_bwd_impl(const T* dz, const T* z, const uint8_t* mask, const T* x, T* dx, T* dres, long long rows,
                            int C, const float* gamma, const float* mean, const float* invstd, int relu, float* dgamma,
-                           float* dbeta, float* ws, cudaStream_t st) {
+                           float* dbeta, float* ws, int walk, cudaStream_t st) {
+  const int rev_reduce = walk & 1, reverse = (walk >> 1) & 1;   // walk direction of the reduction pass / the dx pass
   const BnPlan p = bn_plan<T>(rows, C);
   float* part = ws;
   float* coef = ws + (size_t)BN_MAX_BLOCKS * 2 * C;
@@ -535,21 +549,21 @@ static int32_t bn_bwd_impl(const T* dz, const T* z, const uint8_t* mask, const T
     return fail(B200_UNSUPPORTED, "bn_backward: the ReLU mask needs C %% %d == 0 and 16-byte aligned tensors", VecTraits<T>::W);
   if (p.vec != 1 && !aligned) return fail(B200_INVALID_ARG, "bn_backward: tensors must be 16-byte aligned");
   const int pmode = !relu ? PM_BWD : (mask ? PM_BWD_MASK : PM_BWD_Z);
-  launch_bn_partial<T>(p, pmode, x, dz, z, mask, mean, rows, C, part, st);
+  launch_bn_partial<T>(p, pmode, x, dz, z, mask, mean, rows, C, part, st, rev_reduce);
   bn_finalize_bwd_kernel<<<(C + FIN_CX - 1) / FIN_CX, dim3(FIN_CX, FIN_RY), 0, st>>>(part, p.nblk, C, (double)rows, gamma, invstd, dgamma, dbeta, coef);
   if (p.vec != 1) {
     constexpr int V = VecTraits<T>::W;
     bool fixed;
     const int grid = ew_grid_fixed(rows * (C / V), C / V, &fixed);
     const long long nv = rows * (C / V);
-#define B200_DX(FX, DM) bn_bwd_dx_kernel<T, V, FX, DM><<<grid, BN_THREADS, 0, st>>>(dz, z, mask, x, dx, dres, nv, C / V, C, mean, coef)
+#define B200_DX(FX, DM) bn_bwd_dx_kernel<T, V, FX, DM><<<grid, BN_THREADS, 0, st>>>(dz, z, mask, x, dx, dres, nv, C / V, C, mean, coef, reverse)
     if (!relu) { if (fixed) B200_DX(true, DM_NONE); else B200_DX(false, DM_NONE); }
     else if (mask) { if (fixed) B200_DX(true, DM_MASK); else B200_DX(false, DM_MASK); }
     else { if (fixed) B200_DX(true, DM_Z); else B200_DX(false, DM_Z); }
 #undef B200_DX
   } else {
-    if (!relu) bn_bwd_dx_kernel<T, 1, false, DM_NONE><<<ew_grid(rows * C), BN_THREADS, 0, st>>>(dz, z, nullptr, x, dx, dres, rows * C, C, C, mean, coef);
-    else bn_bwd_dx_kernel<T, 1, false, DM_Z><<<ew_grid(rows * C), BN_THREADS, 0, st>>>(dz, z, nullptr, x, dx, dres, rows * C, C, C, mean, coef);
+    if (!relu) bn_bwd_dx_kernel<T, 1, false, DM_NONE><<<ew_grid(rows * C), BN_THREADS, 0, st>>>(dz, z, nullptr, x, dx, dres, rows * C, C, C, mean, coef, reverse);
+    else bn_bwd_dx_kernel<T, 1, false, DM_Z><<<ew_grid(rows * C), BN_THREADS, 0, st>>>(dz, z, nullptr, x, dx, dres, rows * C, C, C, mean, coef, reverse);
   }
   return check_launch("bn_backward", 3);
 }
@@ -616,27 +630,28 @@ extern "C" int32_t b200_bn_eval_coeffs(const float* gamma, const float* beta, co
 }
 
 extern "C" int32_t b200_bn_apply(const void* x, const void* residual, void* y, uint8_t* mask, int64_t rows, int32_t C,
-                                 int32_t dtype, const float* scale, const float* shift, int32_t relu, void* stream) {
+                                 int32_t dtype, const float* scale, const float* shift, int32_t relu, int32_t reverse,
+                                 void* stream) {
   if (!x || !y || !scale || !shift || rows <= 0 || C <= 0) return fail(B200_INVALID_ARG, "bn_apply: bad arguments");
   cudaStream_t st = as_stream(stream);
-  if (dtype == B200_F32) return bn_apply_impl<float>((const float*)x, (const float*)residual, (float*)y, mask, rows, C, scale, shift, relu, st);
+  if (dtype == B200_F32) return bn_apply_impl<float>((const float*)x, (const float*)residual, (float*)y, mask, rows, C, scale, shift, relu, reverse != 0, st);
   if (dtype == B200_BF16)
-    return bn_apply_impl<__nv_bfloat16>((const __nv_bfloat16*)x, (const __nv_bfloat16*)residual, (__nv_bfloat16*)y, mask, rows, C, scale, shift, relu, st);
+    return bn_apply_impl<__nv_bfloat16>((const __nv_bfloat16*)x, (const __nv_bfloat16*)residual, (__nv_bfloat16*)y, mask, rows, C, scale, shift, relu, reverse != 0, st);
   return fail(B200_INVALID_ARG, "bn_apply: bad dtype");
 }
 
 extern "C" int32_t b200_bn_backward(const void* dz, const void* z, const uint8_t* mask, const void* x, void* dx,
                                     void* dres, int64_t rows, int32_t C, int32_t dtype, const float* gamma,
                                     const float* save_mean, const float* save_invstd, int32_t relu, float* dgamma,
-                                    float* dbeta, void* ws, int64_t ws_bytes, void* stream) {
+                                    float* dbeta, void* ws, int64_t ws_bytes, int32_t walk, void* stream) {
   if (!dz || !x || !dx || !save_mean || !save_invstd || rows <= 0 || C <= 0 || (relu && !z && !mask))
     return fail(B200_INVALID_ARG, "bn_backward: bad arguments");
   if (!ws || ws_bytes < b200_bn_workspace_bytes(rows, C)) return fail(B200_WORKSPACE_TOO_SMALL, "bn_backward: workspace too small");
   cudaStream_t st = as_stream(stream);
   if (dtype == B200_F32)
-    return bn_bwd_impl<float>((const float*)dz, (const float*)z, mask, (const float*)x, (float*)dx, (float*)dres, rows, C, gamma, save_mean, save_invstd, relu, dgamma, dbeta, (float*)ws, st);
+    return bn_bwd_impl<float>((const float*)dz, (const float*)z, mask, (const float*)x, (float*)dx, (float*)dres, rows, C, gamma, save_mean, save_invstd, relu, dgamma, dbeta, (float*)ws, walk, st);
   if (dtype == B200_BF16)
-    return bn_bwd_impl<__nv_bfloat16>((const __nv_bfloat16*)dz, (const __nv_bfloat16*)z, mask, (const __nv_bfloat16*)x, (__nv_bfloat16*)dx, (__nv_bfloat16*)dres, rows, C, gamma, save_mean, save_invstd, relu, dgamma, dbeta, (float*)ws, st);
+    return bn_bwd_impl<__nv_bfloat16>((const __nv_bfloat16*)dz, (const __nv_bfloat16*)z, mask, (const __nv_bfloat16*)x, (__nv_bfloat16*)dx, (__nv_bfloat16*)dres, rows, C, gamma, save_mean, save_invstd, relu, dgamma, dbeta, (float*)ws, walk, st);
   return fail(B200_INVALID_ARG, "bn_backward: bad dtype");
 }
 

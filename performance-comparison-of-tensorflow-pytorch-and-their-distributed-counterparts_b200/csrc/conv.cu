@@ -7,6 +7,7 @@
 #include "common.cuh"
 #include "gemm_sm100.cuh"
 #include "conv_sm100.cuh"
+#include "wgrad_sm100.cuh"
 #include <vector>
 #include <stdlib.h>
 #include <utility>
@@ -390,6 +391,102 @@ static int32_t implicit_wgrad(const b200_conv_desc* d, const ConvGeom& g, const 
   return launch_reduce_wgrad((const float*)ws, wp.nsplits, P.split_stride, d->K, d->C, d->R * d->S, g.ldw, dw, st);
 }
 
+// ------------------------------------------------------------------------------------------------ wgrad, 2nd generation
+// (wgrad_sm100.cuh: 256 x 256 tiles, split-K over a thread-block cluster reduced through distributed shared memory)
+struct WgradPlan2 {
+  PixelBox box;
+  int Wq, Hq, Nq, tm, n_tiles, m_tiles, pb_total, pb_per, cluster, groups;
+  bool direct;
+};
+static inline bool wgrad_v2_ok(const b200_conv_desc* d, const ConvGeom& g) {
+  static const int force = getenv("B200_WGRAD_GEN") ? atoi(getenv("B200_WGRAD_GEN")) : 0;   // 1 / 2: force a generation
+  // true matrices (BERT's Linear layers: thousands of rows, N = H = 1) keep the first-generation kernel and its
+  // measured split rules
+  const bool linear = is_flat(d) && d->N == 1 && d->H == 1;
+  if (linear) return false;
+  if (force) return force == 2;
+  // Measured per layer class at N = 256 (tools/conv_table.py, graph replay): the 256-wide tiles win on every 3x3 and
+  // stride-2 layer (1.2-1.5x), on the big 1x1 layers (K*C >= 2^19) and on the narrow-output ones (K <= 128, where the
+  // first generation re-reads X for nothing); the mid-size 1x1 layers (64->256, 128->512, 512->256, 256<->1024) are
+  // 5-15 % faster on the 128-wide tiles, whose epilogue overlaps the next tile's main loop.
+  return d->R * d->S > 1 || d->stride > 1 || (long long)d->K * d->C >= (1LL << 19) || d->K <= 128;
+}
+static inline WgradPlan2 wgrad_plan2(const b200_conv_desc* d, const ConvGeom& g, const float* dw) {
+  WgradPlan2 w;
+  if (is_flat(d)) { w.Wq = (int)g.M; w.Hq = 1; w.Nq = 1; }
+  else { w.Wq = g.Wo; w.Hq = g.Ho; w.Nq = d->N; }
+  w.tm = d->K > 128 ? 256 : 128;
+  w.n_tiles = (g.RSC + WG_TN - 1) / WG_TN;
+  w.m_tiles = (d->K + w.tm - 1) / w.tm;
+  w.box = choose_pixel_box(w.Wq, w.Hq, w.Nq, WG_KR, 16, d->stride);
+  w.pb_total = w.box.tiles_w * w.box.tiles_h * w.box.tiles_n;
+  const int tiles = w.n_tiles * w.m_tiles;
+  // Splits: one wave of CTAs (one per SM).  A cluster reduces its ranks' accumulators through distributed shared
+  // memory; measured, that pays for PAIRS only (DSMEM moves ~20 B/clk per SM, so a rank that gathers a 1/8 slice from
+  // eight peers takes longer than writing its slab to L2; clusters of 4 / 8 also strand SMs of a GPC), so the
+  // default is pairs of CTAs and one fp32 slab per pair.  B200_WGRAD_CLUSTER=1/2/4/8 overrides.
+  static const int force_cs = getenv("B200_WGRAD_CLUSTER") ? atoi(getenv("B200_WGRAD_CLUSTER")) : 0;
+  int s_want = num_sms() / tiles;
+  if (s_want > w.pb_total / 2) s_want = w.pb_total / 2;     // at least two k-blocks per CTA
+  if (s_want < 1) s_want = 1;
+  int cs = force_cs > 0 ? force_cs : 2;
+  while (cs > 1 && cs > s_want) cs >>= 1;
+  w.cluster = cs;
+  w.groups = s_want / cs > 0 ? s_want / cs : 1;
+  const int S = w.cluster * w.groups;
+  w.pb_per = (w.pb_total + S - 1) / S;
+  w.direct = w.groups == 1 && (reinterpret_cast<uintptr_t>(dw) & 15) == 0 && (d->R * d->S > 1 || g.ldw == d->C);
+  return w;
+}
+
+static int32_t implicit_wgrad_v2(const b200_conv_desc* d, const ConvGeom& g, const void* x, const void* dy, float* dw,
+                                 void* ws, cudaStream_t st) {
+  const WgradPlan2 wp = wgrad_plan2(d, g, dw);
+  const bool flat = is_flat(d);
+  WgradParams P{};
+  P.bw = wp.box.bw; P.bh = wp.box.bh; P.bn = wp.box.bn; P.tiles_w = wp.box.tiles_w; P.tiles_h = wp.box.tiles_h;
+  P.kr = wp.box.bw * wp.box.bh * wp.box.bn;
+  P.x_mul = d->stride;
+  for (int r = 0; r < d->R; ++r)
+    for (int s2 = 0; s2 < d->S; ++s2) P.taps[r * d->S + s2] = ConvTap{s2 - d->pad, r - d->pad, (r * d->S + s2) * d->C};
+  P.cdim = d->C; P.ncols = g.RSC; P.mrows = d->K; P.n_tiles = wp.n_tiles; P.tm = wp.tm;
+  P.pb_total = wp.pb_total; P.pb_per_split = wp.pb_per; P.cluster = wp.cluster;
+  P.direct = wp.direct ? 1 : 0;
+  P.rs = d->R * d->S;
+  P.out = wp.direct ? dw : reinterpret_cast<float*>(ws);
+  P.ldo = g.ldw; P.group_stride = (long long)d->K * g.ldw;
+  if (!wp.direct && ((reinterpret_cast<uintptr_t>(ws) & 15) != 0)) return fail(B200_INVALID_ARG, "conv_wgrad: misaligned workspace");
+  CUtensorMap ta, tb;
+  int rc = flat ? make_tmap_bf16_nhwc(&ta, dy, 1, 1, (int)g.M, d->K, P.bw, P.bh, P.bn, 1)
+                : make_tmap_bf16_nhwc(&ta, dy, d->N, g.Ho, g.Wo, d->K, P.bw, P.bh, P.bn, 1);
+  if (rc) return fail(B200_CUDA_ERROR, "conv_wgrad: gradient tensor map failed (%d)", rc);
+  rc = flat ? make_tmap_bf16_nhwc(&tb, x, 1, 1, (int)g.M, d->C, P.bw, P.bh, P.bn, 1)
+            : make_tmap_bf16_nhwc(&tb, x, d->N, d->H, d->W, d->C, P.bw, P.bh, P.bn, d->stride);
+  if (rc) return fail(B200_CUDA_ERROR, "conv_wgrad: activation tensor map failed (%d)", rc);
+  static int attr_state[B200_MAX_DEVICES] = {0};
+  if (cudaError_t e = ensure_dyn_smem(wgrad_sm100_kernel, WG_SMEM_BYTES, attr_state))
+    return fail(B200_CUDA_ERROR, "conv_wgrad: shared-memory attribute: %s", cudaGetErrorString(e));
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(wp.cluster * wp.groups, wp.n_tiles * wp.m_tiles, 1);
+  cfg.blockDim = dim3(WG_THREADS);
+  cfg.dynamicSmemBytes = WG_SMEM_BYTES;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = wp.cluster;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  timing_begin(e0, e1, st);
+  cudaError_t le = cudaLaunchKernelEx(&cfg, wgrad_sm100_kernel, ta, tb, P);
+  timing_end(e0, e1, 2.0 * g.M * d->K * g.RSC, st);
+  if (le != cudaSuccess) return fail(B200_CUDA_ERROR, "conv_wgrad: launch failed (%s)", cudaGetErrorString(le));
+  if (wp.direct) return B200_OK;
+  return launch_reduce_wgrad((const float*)ws, wp.groups, P.group_stride, d->K, d->C, d->R * d->S, g.ldw, dw, st);
+}
+
 }  // namespace b200
 
 using namespace b200;
@@ -401,7 +498,13 @@ extern "C" int64_t b200_conv_workspace_bytes(const b200_conv_desc* d, int32_t wh
   const ConvGeom g = geom(d);
   if (implicit_ok(d)) {
     if (which == B200_CONV_FPROP || which == B200_CONV_DGRAD) return 0;
-    if (which == B200_CONV_WGRAD) return (int64_t)align_up((size_t)wgrad_plan(d, g).nsplits * d->K * g.ldw * 4, 256);
+    if (which == B200_CONV_WGRAD) {
+      // upper bound over both generations of the kernel (the second one needs one slab per cluster group, and none
+      // when a single cluster covers the reduction)
+      size_t need = (size_t)wgrad_plan(d, g).nsplits * d->K * g.ldw * 4;
+      if (wgrad_v2_ok(d, g)) need = (size_t)wgrad_plan2(d, g, nullptr).groups * d->K * g.ldw * 4;
+      return (int64_t)align_up(need, 256);
+    }
     return -1;
   }
   size_t col = g.direct ? 0 : align_up((size_t)g.M * g.ldw * g.esz, 256);
@@ -477,7 +580,7 @@ extern "C" int32_t b200_conv_wgrad(const b200_conv_desc* d, const void* x, const
   cudaStream_t st = as_stream(stream);
   if (ws_bytes < b200_conv_workspace_bytes(d, B200_CONV_WGRAD) || !ws)
     return fail(B200_WORKSPACE_TOO_SMALL, "conv_wgrad: workspace too small");
-  if (implicit_ok(d)) return implicit_wgrad(d, g, x, dy, dw, ws, st);
+  if (implicit_ok(d)) return wgrad_v2_ok(d, g) ? implicit_wgrad_v2(d, g, x, dy, dw, ws, st) : implicit_wgrad(d, g, x, dy, dw, ws, st);
   const size_t col_bytes = g.direct ? 0 : align_up((size_t)g.M * g.ldw * g.esz, 256);
   const void* Bm = x;
   long long ldb = d->C;

@@ -73,10 +73,13 @@ def packed_weight(w, dtype, cpad=None, ld=None):
             _CAPTURE_PACKED[(key, dtype, cpad, ld)] = cached
         return cached
     e = _PACKED.get(key)
-    if e is not None and e[0] == w.data_ptr() and e[1] == w._version and e[2] == dtype and e[4] == (cpad, ld):
+    # id() values are recycled: a parameter of a NEW model can land on the id (and storage address, and version
+    # count) of a dead one, so the entry also remembers which object it was made for
+    if (e is not None and e[5]() is w and e[0] == w.data_ptr() and e[1] == w._version and e[2] == dtype
+            and e[4] == (cpad, ld)):
         return e[3]
     p = ops.pack_weight(w, dtype, cpad) if ld is None else ops.pack_weight_ld(w, dtype, cpad, ld)
-    _PACKED[key] = (w.data_ptr(), w._version, dtype, p, (cpad, ld))
+    _PACKED[key] = (w.data_ptr(), w._version, dtype, p, (cpad, ld), weakref.ref(w, lambda _r, k=key: _PACKED.pop(k, None)))
     return p
 
 
@@ -133,6 +136,12 @@ class _Unit(object):
     __slots__ = ("conv", "bn", "x", "y", "z", "mask", "mean", "invstd", "relu", "geom", "staged")
 
 
+# L2-aware walk order (B200_L2_WALK=1; OFF by default): a bandwidth kernel that starts where its producer finished
+# should find that end of the tensor still in the 126 MB L2 -- the BatchNorm apply walks last -> first after a
+# convolution that walked first -> last, the backward reduction pass walks against the dgrad that produced its input,
+# the dx pass against the reduction pass.  Measured on the N=256 step: 13.90 ms with, 13.93 ms without -- no gain (the
+# tensors that matter are several times larger than L2), so the kernels keep the option but nothing uses it.
+_L2_WALK = os.environ.get("B200_L2_WALK") is not None
 _FOLD_EVAL_BN = os.environ.get("B200_NO_FOLD_EVAL_BN") is None
 _FOLD_EVAL_RESIDUAL = os.environ.get("B200_FOLD_EVAL_RESIDUAL") is not None
 
@@ -168,8 +177,8 @@ def _unit_forward(conv, bn, x, relu, residual, save, stage=False):
     scale, shift, mean, invstd = _bn_coeffs(bn, y, bump_nbt=False, partials=partials)
     if not save:
         # y is dead after the apply -> write in place
-        return ops.bn_apply(y, scale, shift, relu, residual, out=y), None
-    z, mask = ops.bn_apply(y, scale, shift, relu, residual, want_mask=True)
+        return ops.bn_apply(y, scale, shift, relu, residual, out=y, reverse=_L2_WALK), None
+    z, mask = ops.bn_apply(y, scale, shift, relu, residual, want_mask=True, reverse=_L2_WALK)
     u = _Unit()
     u.conv, u.bn, u.x, u.y, u.z, u.mean, u.invstd, u.relu = conv, bn, x, y, z, mean, invstd, relu
     u.mask = mask
@@ -234,11 +243,44 @@ def _backbone_fwd(model, x, save, x_needs_grad):
     return feat, st
 
 
+_SIDE_STREAMS = {}
+_WGRAD_OVERLAP = os.environ.get("B200_WGRAD_OVERLAP") is not None
+
+
+def _side_stream(device):
+    key = device.index if device.index is not None else torch.cuda.current_device()
+    s = _SIDE_STREAMS.get(key)
+    if s is None:
+        s = torch.cuda.Stream(device=device)
+        _SIDE_STREAMS[key] = s
+    return s
+
+
 def _backbone_bwd(st, dfeat, params, param_needs, x_needs_grad, sink, cut=None, cut_after=()):
     """Reverse walk: BN backward (mask from the saved byte mask) -> wgrad -> dgrad; the block-input gradient is the
-    residual gradient with conv1's dgrad accumulated in the GEMM epilogue.  Returns (dx or None, [grad per param])."""
+    residual gradient with conv1's dgrad accumulated in the GEMM epilogue.  Returns (dx or None, [grad per param]).
+
+    B200_WGRAD_OVERLAP=1 (OFF by default): weight gradients are off the critical path (nothing in the backward reads
+    them), so they can run on a SIDE STREAM -- wgrad(u) starts as soon as dy_u exists and overlaps the dgrad ->
+    BatchNorm-backward chain of the main stream; both streams are joined before the function returns (and before every
+    graph-segment cut), and inside a CUDA-graph capture the fork / join become parallel branches of the graph.
+    Measured at N=256: 13.87 ms with, 13.85 ms without.  Every kernel of this step already runs against the same
+    shared limits (L2 slice throughput for the GEMM operands, HBM for the BatchNorm passes, one ~200 KB-smem CTA per
+    SM for both convolution kernels), so running two of them at once only interleaves them.  Kept as an option."""
     dfeat = dfeat.contiguous().float()
     grads = {}  # id(param) -> grad
+    capturing = torch.cuda.is_current_stream_capturing()
+    overlap = _WGRAD_OVERLAP and dfeat.is_cuda and (sink is None or capturing)
+    main = torch.cuda.current_stream() if overlap else None
+    side = _side_stream(dfeat.device) if overlap else None
+    keep = []        # tensors the side stream reads: kept alive until the streams are joined
+    forked = [False]
+
+    def join():
+        if overlap and forked[0]:
+            main.wait_stream(side)
+            forked[0] = False
+            del keep[:]
 
     def emit(p, g):
         grads[id(p)] = sink(p, g) if sink is not None else g
@@ -248,7 +290,8 @@ def _backbone_bwd(st, dfeat, params, param_needs, x_needs_grad, sink, cut=None, 
             raise RuntimeError("b200net: backward through BatchNorm in eval mode is not supported on this path")
         need_bn = u.bn.weight is not None and (u.bn.weight.requires_grad or u.bn.bias.requires_grad)
         dy, dres, dgamma, dbeta = ops.bn_backward(dz, u.z if u.relu else None, u.y, u.bn.weight, u.mean, u.invstd,
-                                                  u.relu, want_dres=want_dres, want_param_grads=need_bn, mask=u.mask)
+                                                  u.relu, want_dres=want_dres, want_param_grads=need_bn, mask=u.mask,
+                                                  walk=1 if _L2_WALK else 0)
         if need_bn:
             if u.bn.bias.requires_grad:
                 emit(u.bn.bias, dbeta)
@@ -256,14 +299,25 @@ def _backbone_bwd(st, dfeat, params, param_needs, x_needs_grad, sink, cut=None, 
                 emit(u.bn.weight, dgamma)
         K, R, S, stride, pad = u.geom
         if u.conv.weight.requires_grad:
-            dw = ops.conv_wgrad(u.x, dy, K, R, S, stride, pad)
-            if u.staged is not None:                   # staged stem: [K][R*S*cp (+pad)] -> OIHW
-                r0, s0, _, _, cp0, _ = u.staged
-                dw = dw.reshape(K, -1)[:, :r0 * s0 * cp0].reshape(K, r0, s0, cp0)
-                dw = dw[..., :u.conv.in_channels].permute(0, 3, 1, 2).contiguous()
-            elif dw.shape[1] != u.conv.in_channels:    # channel-padded stem: drop the zero channel
-                dw = dw[:, :u.conv.in_channels].contiguous()
-            emit(u.conv.weight, dw)
+            def wgrad():
+                dw = ops.conv_wgrad(u.x, dy, K, R, S, stride, pad)
+                if u.staged is not None:                   # staged stem: [K][R*S*cp (+pad)] -> OIHW
+                    r0, s0, _, _, cp0, _ = u.staged
+                    dw = dw.reshape(K, -1)[:, :r0 * s0 * cp0].reshape(K, r0, s0, cp0)
+                    dw = dw[..., :u.conv.in_channels].permute(0, 3, 1, 2).contiguous()
+                elif dw.shape[1] != u.conv.in_channels:    # channel-padded stem: drop the zero channel
+                    dw = dw[:, :u.conv.in_channels].contiguous()
+                emit(u.conv.weight, dw)
+            if overlap:
+                ev = torch.cuda.Event()
+                ev.record(main)                            # dy is complete here
+                side.wait_event(ev)
+                keep.append(dy)
+                forked[0] = True
+                with torch.cuda.stream(side), ops.side_workspace():
+                    wgrad()
+            else:
+                wgrad()
         return dy, dres
 
     def dgrad(u, dy, out=None, accumulate=False):
@@ -275,6 +329,7 @@ def _backbone_bwd(st, dfeat, params, param_needs, x_needs_grad, sink, cut=None, 
     dcur = ops.avgpool_bwd(dfeat, st.final_shape, st.dtype)
     for bi, (u1, u2, u3, ud) in enumerate(reversed(st.blocks)):
         if cut is not None and bi in cut_after:
+            join()
             cut()         # graph capture under DDP: a new segment starts here (see _SegmentedCapture)
         dy3, g = unit_backward(u3, dcur, want_dres=True)
         dz2 = dgrad(u3, dy3)
@@ -295,6 +350,7 @@ def _backbone_bwd(st, dfeat, params, param_needs, x_needs_grad, sink, cut=None, 
     dx = None
     if x_needs_grad:
         dx = ops.to_nchw(dgrad(u0, dy0))[:, :u0.conv.in_channels].contiguous()
+    join()
     return dx, [grads.get(id(p)) if need else None for p, need in zip(params, param_needs)]
 
 

@@ -31,10 +31,23 @@ def _stream():
 # ------------------------------------------------------------------ workspace (one growing buffer per device)
 _WS = {}
 NO_WORKSPACE_GROWTH = [False]   # set while a CUDA graph is being captured
+WORKSPACE_SLOT = [0]            # 0 = the main stream's buffer; 1 = the side stream's (kernels that overlap with the
+                                # main stream -- the weight gradients -- must not share scratch with it)
+
+
+class side_workspace(object):
+    """Context: scratch requests inside it come from the side stream's own buffer."""
+
+    def __enter__(self):
+        self.prev = WORKSPACE_SLOT[0]
+        WORKSPACE_SLOT[0] = 1
+
+    def __exit__(self, *a):
+        WORKSPACE_SLOT[0] = self.prev
 
 
 def workspace(nbytes, device):
-    key = device.index if device.index is not None else torch.cuda.current_device()
+    key = (device.index if device.index is not None else torch.cuda.current_device(), WORKSPACE_SLOT[0])
     buf = _WS.get(key)
     if buf is None or buf.numel() < nbytes:
         if NO_WORKSPACE_GROWTH[0]:
@@ -245,7 +258,7 @@ def bn_eval_coeffs(gamma, beta, running_mean, running_var, eps):
     return st[0], st[1]
 
 
-def bn_apply(x, scale, shift, relu, residual=None, out=None, want_mask=False):
+def bn_apply(x, scale, shift, relu, residual=None, out=None, want_mask=False, reverse=False):
     """y = act(x*scale + shift (+residual)).  With want_mask the ReLU mask of the stored output is returned too
     (one byte per 16-byte vector; None when C does not allow it) -- the backward kernels then never re-read y."""
     C = x.shape[-1]
@@ -258,11 +271,11 @@ def bn_apply(x, scale, shift, relu, residual=None, out=None, want_mask=False):
             mask = torch.empty(nb, dtype=torch.uint8, device=x.device)
     check(lib.b200_bn_apply(x.data_ptr(), residual.data_ptr() if residual is not None else None, y.data_ptr(),
                             mask.data_ptr() if mask is not None else None, rows, C, _dt(x), scale.data_ptr(),
-                            shift.data_ptr(), 1 if relu else 0, _stream()), "bn_apply")
+                            shift.data_ptr(), 1 if relu else 0, 1 if reverse else 0, _stream()), "bn_apply")
     return (y, mask) if want_mask else y
 
 
-def bn_backward(dz, z, x, gamma, mean, invstd, relu, want_dres=False, want_param_grads=True, mask=None):
+def bn_backward(dz, z, x, gamma, mean, invstd, relu, want_dres=False, want_param_grads=True, mask=None, walk=0):
     C = x.shape[-1]
     rows = x.numel() // C
     dx = torch.empty_like(x)
@@ -275,7 +288,7 @@ def bn_backward(dz, z, x, gamma, mean, invstd, relu, want_dres=False, want_param
         dres.data_ptr() if dres is not None else None, rows, C, _dt(x),
         gamma.data_ptr() if gamma is not None else None, mean.data_ptr(), invstd.data_ptr(), 1 if relu else 0,
         pg[0].data_ptr() if pg is not None else None, pg[1].data_ptr() if pg is not None else None,
-        ws.data_ptr(), n, _stream()), "bn_backward")
+        ws.data_ptr(), n, int(walk), _stream()), "bn_backward")
     if pg is None:
         return dx, dres, None, None
     return dx, dres, pg[0], pg[1]

@@ -86,6 +86,10 @@ class SGD(Optimizer):
 
 class Adam(Optimizer):
     _decoupled = False
+    # transformers.AdamW divides by (sqrt(v) + eps) with the step size lr*sqrt(bc2)/bc1; torch divides by
+    # (sqrt(v)/sqrt(bc2) + eps) with lr/bc1.  The two coincide when torch's rule is given eps/sqrt(bc2) at that step,
+    # which is how bert.AdamW selects the published transformers rule on the same kernel.
+    _eps_before_bias_correction = False
 
     def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0, amsgrad=False):
         if amsgrad:
@@ -115,12 +119,15 @@ class Adam(Optimizer):
                 by_step.setdefault(int(st["step"]), []).append((p, g, st))
             b1, b2 = group["betas"]
             for step, sel in by_step.items():
+                eps = float(group["eps"])
+                if self._eps_before_bias_correction:
+                    eps = eps / (1.0 - float(b2) ** step) ** 0.5
                 check(lib.b200_multi_tensor_adam(
                     len(sel), ptr_array([p.data_ptr() for p, _, _ in sel]), ptr_array([g.data_ptr() for _, g, _ in sel]),
                     ptr_array([s["exp_avg"].data_ptr() for _, _, s in sel]),
                     ptr_array([s["exp_avg_sq"].data_ptr() for _, _, s in sel]),
                     i64_array([p.numel() for p, _, _ in sel]), float(group["lr"]), float(b1), float(b2),
-                    float(group["eps"]), float(group["weight_decay"]), 1 if self._decoupled else 0, step, 1.0,
+                    eps, float(group["weight_decay"]), 1 if self._decoupled else 0, step, 1.0,
                     _stream()), "multi_tensor_adam")
             _bump(ps)
         return loss

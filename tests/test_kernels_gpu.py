@@ -422,6 +422,37 @@ def test_optimizers_match_torch(name, kw):
         assert _rel(p, q) < 1e-5
 
 
+def test_transformers_adamw_rule():
+    """bert.AdamW follows the update rule transformers.AdamW published (the class the reference imports at
+    pytorch_on_language_distr.py:151; transformers 5.x no longer ships it): eps is added to sqrt(v) BEFORE the bias
+    correction.  Checked against a float64 restatement of that rule; torch.optim.AdamW differs measurably at these
+    settings, which the last assertion shows."""
+    from b200net import bert
+    lr, b1, b2, eps = 1e-3, 0.9, 0.999, 1e-3          # large eps so the two rules separate clearly
+    ours = [torch.nn.Parameter(t.clone().to(_dev())) for t in _param_set(81)]
+    ref = [t.clone().double().to(_dev()) for t in _param_set(81)]
+    m = [torch.zeros_like(t) for t in ref]
+    v = [torch.zeros_like(t) for t in ref]
+    stock = [torch.nn.Parameter(t.clone().double().to(_dev())) for t in _param_set(81)]
+    o1 = bert.AdamW(ours, lr=lr, eps=eps)
+    o2 = torch.optim.AdamW(stock, lr=lr, eps=eps, weight_decay=0.0)
+    for step in range(1, 5):
+        grads = _param_set(200 + step)
+        for i, g in enumerate(grads):
+            gd = g.double().to(_dev())
+            ours[i].grad = g.to(_dev())
+            stock[i].grad = gd
+            m[i].mul_(b1).add_(gd, alpha=1 - b1)
+            v[i].mul_(b2).addcmul_(gd, gd, value=1 - b2)
+            step_size = lr * math.sqrt(1 - b2 ** step) / (1 - b1 ** step)
+            ref[i].addcdiv_(m[i], v[i].sqrt().add_(eps), value=-step_size)
+        o1.step()
+        o2.step()
+    for p, q in zip(ours, ref):
+        assert _rel(p, q) < 1e-5
+    assert max(_rel(p, q) for p, q in zip(stock, ref)) > 1e-4
+
+
 def test_clip_grad_norm():
     import b200net
     ours = [torch.nn.Parameter(t.clone().to(_dev())) for t in _param_set(71)]

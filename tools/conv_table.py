@@ -27,11 +27,34 @@ VGG_CLASSES = [
 ]
 
 
+GRAPH = os.environ.get("CONV_TABLE_EAGER") is None
+
+
 def timeit(fn, iters=10):
+    """us per call.  By default the `iters` calls are captured into one CUDA graph and the graph is replayed (that is
+    how the training step runs them, and it keeps host launch overhead -- tensor-map encodes, ctypes -- out of the
+    number); CONV_TABLE_EAGER=1 times eager launches instead."""
     for _ in range(3):
         fn()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if GRAPH:
+        ops.NO_WORKSPACE_GROWTH[0] = True
+        try:
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                for _ in range(iters):
+                    fn()
+        finally:
+            ops.NO_WORKSPACE_GROWTH[0] = False
+        g.replay()
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(3):
+            g.replay()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / (3 * iters) * 1e3
     e0.record()
     for _ in range(iters):
         fn()
