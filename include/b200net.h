@@ -59,6 +59,18 @@ int32_t b200_pack_weight(const float* w_oihw, void* w_krsc, int32_t K, int32_t C
  * and weight gradient share the staged matrix). */
 int32_t b200_im2col(const void* x, void* col, int32_t N, int32_t H, int32_t W, int32_t C, int32_t R, int32_t S,
                     int32_t stride, int32_t pad, int32_t ld, int32_t dtype, void* stream);
+/* Row-pair window staging for the stem (Conv2d(3, 64, kernel_size=7, stride=2, padding=3): the first line of the
+ * stored repr, pytorch_training_inference_on_image.ipynb:455), bf16 mode.  x is the channel-padded image
+ * [N][H][W][4] bf16 (b200_nchw_to_nhwc with Cpad = 4); out is [N][Ho + R' - 1][Wo][64] bf16 with R' = (R+1)/2:
+ * out[n][j][q][r2*32 + s*4 + c] = x[n][2j + r2 - pad][2q + s - pad][c] (zero outside the image), s = 0..7.
+ * The stem then runs as an R' x 1 stride-1 convolution over 64 channels on the implicit tcgen05 path (desc
+ * {N, Ho+R'-1, Wo, 64, K, R', 1, 1, 0}) with the weights packed by b200_stem_pack_weight into [K][R'*64]
+ * (column j*64 + r2*32 + s*4 + c = w[k][c][2j+r2][s]); forward and weight gradient share the staged tensor,
+ * which is a quarter of a full im2col matrix.  Stride 2, S <= 8, at most 4 channels. */
+int32_t b200_stem_stage(const void* x_nhwc4, void* out, int32_t N, int32_t H, int32_t W, int32_t R, int32_t S,
+                        int32_t pad, void* stream);
+int32_t b200_stem_pack_weight(const float* w_oihw, void* w_packed, int32_t K, int32_t Cw, int32_t R, int32_t S,
+                              void* stream);
 /* dtype cast of a flat buffer (fp32 <-> bf16) */
 int32_t b200_cast(const void* x, void* y, int64_t n, int32_t in_dtype, int32_t out_dtype, void* stream);
 

@@ -111,7 +111,7 @@ static int32_t gemm_bf16_run(const void* A, const void* B, void* C, int M, int N
 // 3-channel stem.  Other shapes keep the staged (im2col) path above.
 static inline bool implicit_ok(const b200_conv_desc* d) {
   static const bool disabled = getenv("B200_NO_IMPLICIT_CONV") != nullptr;
-  return !disabled && d->dtype == B200_BF16 && d->C % 64 == 0 && d->K % 64 == 0 && d->R <= 3 && d->S <= 3 &&
+  return !disabled && d->dtype == B200_BF16 && d->C % 64 == 0 && d->K % 64 == 0 && d->R * d->S <= CONV_MAX_TAPS &&
          (d->stride == 1 || d->stride == 2) && d->pad < d->R && d->pad < d->S;
 }
 static inline bool is_flat(const b200_conv_desc* d) { return d->R == 1 && d->S == 1 && d->stride == 1 && d->pad == 0; }

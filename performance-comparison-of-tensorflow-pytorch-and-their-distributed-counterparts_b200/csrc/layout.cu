@@ -124,6 +124,51 @@ im2col_px8_kernel(const uint2* __restrict__ x, uint2* __restrict__ col, int N, i
   }
 }
 
+// Row-pair window staging for a stride-2 convolution over a 4-channel (8-byte pixel) image -- the ResNet stem,
+// 7x7 / 2 over the channel-padded RGB batch.  out[n][j][q][r2*32 + s*4 + c] = x[n][2j + r2 - pad][2q + s - pad][c]
+// (s = 0..7, zero outside the image): one 128-byte row holds, for output column q, the 8-pixel windows of the two
+// input rows of row pair j.  The convolution then is an R' = ceil(R/2) x 1, stride-1 convolution over 64 "channels"
+// on the implicit tcgen05 path (filter-row pair j' is a coordinate shift along j), and the staged tensor is
+// (Ho + R' - 1) * Wo * 128 bytes per image -- a quarter of a full im2col matrix, small enough to stay in L2 between
+// the four taps.  One thread moves 16 bytes (two pixels).
+__global__ void __launch_bounds__(256)
+stem_stage_kernel(const uint2* __restrict__ x, uint4* __restrict__ out, int N, int H, int W, int pad, int Hs, int Wo) {
+  const long long total = (long long)N * Hs * Wo * 8;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int t = (int)(i & 7);            // 16-byte chunk of the row: r2 = t >> 2, pixels 2*(t&3), 2*(t&3)+1
+    long long rest = i >> 3;
+    const int q = (int)(rest % Wo);
+    rest /= Wo;
+    const int j = (int)(rest % Hs);
+    const int n = (int)(rest / Hs);
+    const int h = 2 * j + (t >> 2) - pad;
+    const int w = 2 * q + 2 * (t & 3) - pad;
+    uint2 a = make_uint2(0u, 0u), b = make_uint2(0u, 0u);
+    if (h >= 0 && h < H) {
+      const uint2* row = x + ((long long)n * H + h) * W;
+      if (w >= 0 && w < W) a = row[w];
+      if (w + 1 >= 0 && w + 1 < W) b = row[w + 1];
+    }
+    out[i] = make_uint4(a.x, a.y, b.x, b.y);
+  }
+}
+// OIHW fp32 stem filter [K][Cw <= 4][R][S <= 8] -> [K][R' * 64] bf16 in the column order of stem_stage_kernel:
+// column j*64 + r2*32 + s*4 + c holds w[k][c][2j + r2][s] (zero where r >= R, s >= S or c >= Cw).
+__global__ void stem_pack_weight_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ out, int K, int Cw, int R,
+                                        int S, int ld) {
+  const long long total = (long long)K * ld;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int k = (int)(i / ld), col = (int)(i - (long long)k * ld);
+    const int j = col >> 6, r2 = (col >> 5) & 1, s = (col >> 2) & 7, c = col & 3;
+    const int r = 2 * j + r2;
+    float v = 0.f;
+    if (r < R && s < S && c < Cw) v = w[(((long long)k * Cw + c) * R + r) * S + s];
+    out[i] = __float2bfloat16_rn(v);
+  }
+}
+
 template <typename T>
 __global__ void im2col_pad_kernel(T* __restrict__ col, long long M, int used, int ld) {
   const int padw = ld - used;
@@ -318,6 +363,29 @@ extern "C" int32_t b200_cast(const void* x, void* y, int64_t n, int32_t in_dtype
 }
 
 /* explicit staging of a convolution's A operand: col[m][(r*S+s)*C + c], row stride ld >= R*S*C, zero-filled tail */
+extern "C" int32_t b200_stem_stage(const void* x, void* out, int32_t N, int32_t H, int32_t W, int32_t R, int32_t S,
+                                   int32_t pad, void* stream) {
+  if (!x || !out || N <= 0 || H <= 0 || W <= 0 || R <= 0 || S <= 0 || S > 8 || pad < 0)
+    return fail(B200_INVALID_ARG, "stem_stage: bad arguments (8-byte pixels, stride 2, S <= 8)");
+  if ((reinterpret_cast<uintptr_t>(x) & 7) || (reinterpret_cast<uintptr_t>(out) & 15))
+    return fail(B200_INVALID_ARG, "stem_stage: misaligned buffers");
+  const int Ho = (H + 2 * pad - R) / 2 + 1, Wo = (W + 2 * pad - S) / 2 + 1;
+  if (Ho <= 0 || Wo <= 0) return fail(B200_INVALID_ARG, "stem_stage: filter larger than input");
+  const int Hs = Ho + (R + 1) / 2 - 1;
+  const long long total = (long long)N * Hs * Wo * 8;
+  stem_stage_kernel<<<grid_for(total, 256, 16), 256, 0, as_stream(stream)>>>((const uint2*)x, (uint4*)out, N, H, W, pad, Hs, Wo);
+  return check_launch("stem_stage");
+}
+
+extern "C" int32_t b200_stem_pack_weight(const float* w_oihw, void* out, int32_t K, int32_t Cw, int32_t R, int32_t S,
+                                         void* stream) {
+  if (!w_oihw || !out || K <= 0 || Cw <= 0 || Cw > 4 || R <= 0 || S <= 0 || S > 8)
+    return fail(B200_INVALID_ARG, "stem_pack_weight: bad arguments (at most 4 channels, S <= 8)");
+  const int ld = ((R + 1) / 2) * 64;
+  stem_pack_weight_kernel<<<grid_for((long long)K * ld), 256, 0, as_stream(stream)>>>(w_oihw, (__nv_bfloat16*)out, K, Cw, R, S, ld);
+  return check_launch("stem_pack_weight");
+}
+
 extern "C" int32_t b200_im2col(const void* x, void* col, int32_t N, int32_t H, int32_t W, int32_t C, int32_t R,
                                int32_t S, int32_t stride, int32_t pad, int32_t ld, int32_t dtype, void* stream) {
   if (!x || !col || N <= 0 || H <= 0 || W <= 0 || C <= 0 || R <= 0 || S <= 0 || stride <= 0 || pad < 0 || ld < R * S * C)

@@ -62,6 +62,12 @@ _PACKED = {}
 _CAPTURE_PACKED = {}   # packed buffers of the graph being captured (one pack per weight per graph)
 
 
+def _pack(w, dtype, cpad, ld):
+    if cpad == "stem":                  # row-pair window order of the staged stride-2 stem
+        return ops.stem_pack_weight(w)
+    return ops.pack_weight(w, dtype, cpad) if ld is None else ops.pack_weight_ld(w, dtype, cpad, ld)
+
+
 def packed_weight(w, dtype, cpad=None, ld=None):
     key = id(w)
     if _CAPTURING[0]:
@@ -69,7 +75,7 @@ def packed_weight(w, dtype, cpad=None, ld=None):
         # leak into the eager cache (the buffer belongs to the graph's memory pool)
         cached = _CAPTURE_PACKED.get((key, dtype, cpad, ld))
         if cached is None:
-            cached = ops.pack_weight(w, dtype, cpad) if ld is None else ops.pack_weight_ld(w, dtype, cpad, ld)
+            cached = _pack(w, dtype, cpad, ld)
             _CAPTURE_PACKED[(key, dtype, cpad, ld)] = cached
         return cached
     e = _PACKED.get(key)
@@ -78,7 +84,7 @@ def packed_weight(w, dtype, cpad=None, ld=None):
     if (e is not None and e[5]() is w and e[0] == w.data_ptr() and e[1] == w._version and e[2] == dtype
             and e[4] == (cpad, ld)):
         return e[3]
-    p = ops.pack_weight(w, dtype, cpad) if ld is None else ops.pack_weight_ld(w, dtype, cpad, ld)
+    p = _pack(w, dtype, cpad, ld)
     _PACKED[key] = (w.data_ptr(), w._version, dtype, p, (cpad, ld), weakref.ref(w, lambda _r, k=key: _PACKED.pop(k, None)))
     return p
 
@@ -142,6 +148,7 @@ class _Unit(object):
 # the dx pass against the reduction pass.  Measured on the N=256 step: 13.90 ms with, 13.93 ms without -- no gain (the
 # tensors that matter are several times larger than L2), so the kernels keep the option but nothing uses it.
 _L2_WALK = os.environ.get("B200_L2_WALK") is not None
+_STEM_PAIRS = os.environ.get("B200_STEM_IM2COL") is None
 _FOLD_EVAL_BN = os.environ.get("B200_NO_FOLD_EVAL_BN") is None
 _FOLD_EVAL_RESIDUAL = os.environ.get("B200_FOLD_EVAL_RESIDUAL") is not None
 
@@ -149,10 +156,19 @@ _FOLD_EVAL_RESIDUAL = os.environ.get("B200_FOLD_EVAL_RESIDUAL") is not None
 def _unit_forward(conv, bn, x, relu, residual, save, stage=False):
     K, R, S, stride, pad = _conv_geom(conv)
     staged = None
-    if stage:
-        # Stem (3 -> 64, 7x7/2) in bf16 mode: the channel-padded image is staged ONCE as an im2col matrix with 256
-        # columns and the convolution becomes a 1x1 convolution over 256 "channels" on the implicit tcgen05 path
-        # (persistent kernel, TMA-store epilogue, fused BN statistics); the weight gradient reuses the staged matrix.
+    if stage and stride == 2 and S <= 8 and x.shape[-1] == 4 and _STEM_PAIRS:
+        # Stem (3 -> 64, 7x7/2) in bf16 mode: the channel-padded image is staged ONCE as a row-pair window tensor
+        # [N][Ho+3][Wo][64] (128 bytes per output column: the 8-pixel windows of two input rows; a quarter of an
+        # im2col matrix) and the convolution becomes a 4x1 stride-1 convolution over 64 "channels" on the implicit
+        # tcgen05 path -- filter-row pairs are TMA coordinate shifts, the four taps re-read the staged tensor from L2;
+        # fused BN statistics as everywhere; the weight gradient reuses the staged tensor.
+        wp = packed_weight(conv.weight, x.dtype, "stem")
+        staged = ("pairs", R, S)
+        x = ops.stem_stage(x, R, S, pad)
+        R, S, stride, pad = (R + 1) // 2, 1, 1, 0
+    elif stage:
+        # other narrow-input first layers: the image is staged as an im2col matrix (columns padded to a multiple of
+        # 64) and the convolution becomes a 1x1 convolution over those columns
         cp = x.shape[-1]
         ld = (R * S * cp + 63) // 64 * 64
         wp = packed_weight(conv.weight, x.dtype, cp, ld)
@@ -301,7 +317,12 @@ def _backbone_bwd(st, dfeat, params, param_needs, x_needs_grad, sink, cut=None, 
         if u.conv.weight.requires_grad:
             def wgrad():
                 dw = ops.conv_wgrad(u.x, dy, K, R, S, stride, pad)
-                if u.staged is not None:                   # staged stem: [K][R*S*cp (+pad)] -> OIHW
+                if u.staged is not None and u.staged[0] == "pairs":
+                    # row-pair staged stem: dw is [K][64 = (r2, s, c)][R' = j][1]; filter row r = 2j + r2
+                    _, r0, s0 = u.staged
+                    dw = dw.reshape(K, 2, 8, 4, dw.shape[2]).permute(0, 3, 4, 1, 2).reshape(K, 4, 2 * dw.shape[2], 8)
+                    dw = dw[:, :u.conv.in_channels, :r0, :s0].contiguous()
+                elif u.staged is not None:                 # im2col-staged first layer: [K][R*S*cp (+pad)] -> OIHW
                     r0, s0, _, _, cp0, _ = u.staged
                     dw = dw.reshape(K, -1)[:, :r0 * s0 * cp0].reshape(K, r0, s0, cp0)
                     dw = dw[..., :u.conv.in_channels].permute(0, 3, 1, 2).contiguous()

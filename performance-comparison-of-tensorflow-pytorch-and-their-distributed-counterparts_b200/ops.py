@@ -109,6 +109,27 @@ def im2col(x, R, S, stride, pad, ld):
     return col
 
 
+def stem_stage(x4, R, S, pad):
+    """[N,H,W,4] bf16 -> [N, Ho + R' - 1, Wo, 64] row-pair window tensor of a stride-2 stem (see b200_stem_stage)."""
+    N, H, W, C = x4.shape
+    assert C == 4 and x4.dtype == torch.bfloat16
+    Ho, Wo = (H + 2 * pad - R) // 2 + 1, (W + 2 * pad - S) // 2 + 1
+    out = torch.empty((N, Ho + (R + 1) // 2 - 1, Wo, 64), dtype=torch.bfloat16, device=x4.device)
+    check(lib.b200_stem_stage(x4.data_ptr(), out.data_ptr(), N, H, W, R, S, pad, _stream()), "stem_stage")
+    return out
+
+
+def stem_pack_weight(w):
+    """OIHW fp32 stem filter -> [K][R'*64] bf16 in the staged column order."""
+    K, Cw, R, S = w.shape
+    out = torch.empty((K, ((R + 1) // 2) * 64), dtype=torch.bfloat16, device=w.device)
+    wd = w.detach()
+    if wd.dtype != torch.float32 or not wd.is_contiguous():
+        wd = wd.float().contiguous()
+    check(lib.b200_stem_pack_weight(wd.data_ptr(), out.data_ptr(), K, Cw, R, S, _stream()), "stem_pack_weight")
+    return out
+
+
 def pack_weight_ld(w, dtype, cpad, ld):
     """pack_weight with an explicit row stride (the stem's staged-1x1 form needs ld = 256)."""
     K, Cw, R, S = w.shape

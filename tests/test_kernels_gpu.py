@@ -206,6 +206,34 @@ def test_conv_bf16_multi_tile_persistent_walk(case):
     assert torch.equal(dw, ops.conv_wgrad(xh, dyh, K, R, R, stride, pad))
 
 
+@pytest.mark.parametrize("N,H,W", [(2, 40, 40), (3, 37, 42), (1, 224, 224)])
+def test_stem_row_pair_staging(N, H, W):
+    """The stem (Conv2d(3, 64, 7, stride 2, padding 3), pytorch_training_inference_on_image.ipynb:455) in bf16 mode:
+    channel-padded image -> row-pair window tensor -> 4x1 stride-1 convolution over 64 channels on the implicit
+    tcgen05 path, forward and weight gradient, against float64 conv2d (odd sizes included)."""
+    from b200net import ops
+    K = 64
+    x = torch.rand(N, 3, H, W, generator=torch.Generator().manual_seed(5)).to(_dev())
+    w = _rand((K, 3, 7, 7), torch.float32, 6, scale=1.0 / math.sqrt(147))
+    xq = x.to(torch.bfloat16)
+    xd = xq.double()
+    wd = w.to(torch.bfloat16).double().requires_grad_(True)
+    yref = TF.conv2d(xd, wd, stride=2, padding=3)
+    dy = _rand(tuple(yref.shape), torch.bfloat16, 7)
+    yref.backward(dy.double())
+    x4 = ops.to_nhwc(x, torch.bfloat16, 4)
+    st = ops.stem_stage(x4, 7, 7, 3)
+    Ho, Wo = yref.shape[2], yref.shape[3]
+    assert st.shape == (N, Ho + 3, Wo, 64)
+    wp = ops.stem_pack_weight(w)
+    y, part = ops.conv_fprop_bnstats(st, wp, K, 4, 1, 1, 0)
+    assert y.shape == (N, Ho, Wo, K) and part is not None
+    assert _rel(y.permute(0, 3, 1, 2), yref) < TOL["bf16"]
+    dw = ops.conv_wgrad(st, _nhwc(dy, torch.bfloat16), K, 4, 1, 1, 0)          # [K][64 = (r2, s, c)][4 = j][1]
+    dw = dw.reshape(K, 2, 8, 4, 4).permute(0, 3, 4, 1, 2).reshape(K, 4, 8, 8)[:, :3, :7, :7]
+    assert _rel(dw, wd.grad) < 5e-3
+
+
 @pytest.mark.parametrize("case", [c for c in CONV_CASES if c[2] % 64 == 0 and c[3] % 64 == 0])
 def test_conv_fprop_fused_bn_statistics(case):
     """The fprop epilogue also emits per-pixel-tile column sums / sums of squares of the bf16 output: they must add up
