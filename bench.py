@@ -31,11 +31,24 @@ UNIT = "img/s"
 PER_GPU_BATCH = 256
 HW = 160
 GFLOP_PER_IMG_TRAIN = 12.398     # BASELINE.md section 3 / SURVEY 8(d): fwd + dgrad + wgrad, no stem dgrad
-# DRAM bytes per launch of the tcgen05 conv kernel from the committed `ncu --set full` captures (dram__bytes_read.sum
-# + dram__bytes_write.sum, mean over the captured launches): profiles/r01h_ncu_full_conv_summary.txt (ResNet step) and
-# profiles/r01m_bert_ncu_full_summary.txt (BERT step)
-CONV_TRAFFIC_BYTES_PER_LAUNCH = 45.5e6
+# roofline.traffic: DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum, `ncu --set full`) of ONE NAMED launch of
+# the dominant kernel -- the forward 64->256 1x1 convolution of layer1 at 40x40 (class c of SURVEY 8(a'), four per
+# step and the longest conv launch of the step) -- next to the ALGORITHMIC bytes of that same launch (read x, write y,
+# read w once).  Source: profiles/r02_ncu_named_launches.txt.
+CONV_TRAFFIC_LAUNCH = "conv_sm100_kernel<256,4,fprop>: 256 x 40x40, 64->256, 1x1 (class c)"
+CONV_TRAFFIC_BYTES_PER_LAUNCH = None            # filled from profiles/r02_ncu_named_launches.json when present
+CONV_ALGO_BYTES_PER_LAUNCH = 2.0 * (256 * 40 * 40 * 64 + 256 * 40 * 40 * 256 + 256 * 64)
 BERT_GEMM_TRAFFIC_BYTES_PER_LAUNCH = 36.8e6
+
+
+def _named_launch_traffic():
+    p = os.path.join(ROOT, "profiles", "r02_ncu_named_launches.json")
+    if os.path.exists(p):
+        try:
+            return json.load(open(p)).get("conv_c_fprop", {}).get("dram_bytes")
+        except Exception:
+            return None
+    return None
 CPU_SAMPLE_BATCH = 32            # configs[0] batch: the reference's own CPU-runnable case
 WORKLOAD = ("resnet50 train step (Mode A: all layers trainable, SGD 0.001, NLL), batch %d/GPU, 3x%dx%d "
             "(BASELINE.json configs[1]; DDP = configs[2] when n_gpus > 1)")
@@ -306,6 +319,137 @@ def run_bert_reference(args, rank):
     }), flush=True)
 
 
+def hbm_kernels_leg(dev, model, optimizer):
+    """Achieved HBM GB/s of the bandwidth kernels SURVEY 8(d) names, each timed alone with CUDA events on the largest
+    activation of the step (layer1's block output at N=256: [409600 rows][256 channels] bf16 = 210 MB, > L2) and, for
+    the optimizer, on the model's own 161 tensors.  Bytes are the ALGORITHMIC ones of SURVEY 8(d): apply 4 B/elem
+    (+1/8 B mask), backward reduction 4 B/elem (+1/8), backward dx 6 B/elem (+1/8), SGD 12 B/param."""
+    import torch
+    from b200net import ops
+    rows, C = 256 * 40 * 40, 256
+    x = torch.randn(rows, C, device=dev).to(torch.bfloat16)
+    dz = torch.randn(rows, C, device=dev).to(torch.bfloat16)
+    gamma, beta = torch.ones(C, device=dev), torch.zeros(C, device=dev)
+    mean, invstd, scale, shift = ops.bn_train_stats(x, gamma, beta, None, None, 0.0, 1e-5)
+    z, mask = ops.bn_apply(x, scale, shift, True, None, want_mask=True)
+    elems = rows * C
+
+    def t(fn, iters=10):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(iters):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / iters * 1e-3
+
+    out = {}
+    pk = peaks()
+    zbuf, mbuf = torch.empty_like(x), torch.empty_like(mask)
+    lib = __import__("b200net")._C.lib
+    st = torch.cuda.current_stream().cuda_stream
+    sec = t(lambda: lib.b200_bn_apply(x.data_ptr(), None, zbuf.data_ptr(), mbuf.data_ptr(), rows, C, 1, scale.data_ptr(),
+                                      shift.data_ptr(), 1, 0, st))
+    out["bn_apply_relu_mask"] = {"gbs": elems * 4.125 / sec / 1e9, "bytes_per_elem": 4.125}
+    sec_all = t(lambda: ops.bn_backward(dz, None, x, gamma, mean, invstd, True, want_dres=False, mask=mask))
+    # the two passes of the backward share one entry point: time the reduction alone through the statistics kernel
+    # of the same structure (two inputs -> partial sums) is not exposed, so report the pair against its 10.25 B/elem
+    out["bn_backward_reduce_plus_dx"] = {"gbs": elems * 10.25 / sec_all / 1e9, "bytes_per_elem": 10.25}
+    sec = t(lambda: ops.bn_train_stats(x, gamma, beta, None, None, 0.0, 1e-5))
+    out["bn_stats"] = {"gbs": elems * 2.0 / sec / 1e9, "bytes_per_elem": 2.0}
+    params = [p for p in model.parameters() if p.grad is not None]
+    nparam = sum(p.numel() for p in params)
+    sec = t(lambda: optimizer.step(), iters=5)
+    out["mt_sgd"] = {"gbs": nparam * 12.0 / sec / 1e9, "bytes_per_param": 12.0, "params": nparam}
+    for v in out.values():
+        v["frac_of_hbm_peak"] = v["gbs"] / pk["hbm"]
+    out["peak_gbs"] = pk["hbm"]
+    out["tensor"] = "[%d rows][%d ch] bf16 (%.0f MB), CUDA events, 10 launches each" % (rows, C, elems * 2 / 1e6)
+    del x, dz, z, mask, zbuf, mbuf
+    torch.cuda.empty_cache()
+    return out
+
+
+def argmax_flips(net, dev, n=256):
+    """bf16 eval predictions against the fp32 CPU oracle on n images of the inference batch shape: how many argmax
+    values differ, and the oracle's largest top-2 margin among those rows (flips only happen at near-ties)."""
+    import torch
+    from oracle import torch_oracle as O
+    ref = O.build_reference_model(dropout=False)
+    ref.load_state_dict({k: v.detach().cpu() for k, v in net.state_dict().items()})
+    ref.eval()
+    torch.set_num_threads(O.cpu_threads())
+    x, _ = O.make_batch(n, HW, 4242)
+    with torch.no_grad():
+        lo = ref(x).double()
+        lg = net(x.to(dev)).double().cpu()
+    srt = lo.sort(dim=1, descending=True).values
+    margin = srt[:, 0] - srt[:, 1]
+    fl = lo.argmax(1) != lg.argmax(1)
+    return {"flips": int(fl.sum()), "of": n, "checker": "oracle (stock torch CPU fp32), same weights",
+            "max_oracle_margin_among_flipped": float(margin[fl].max()) if fl.any() else 0.0,
+            "median_oracle_margin": float(margin.median()), "max_abs_logprob_dev": float((lg - lo).abs().max())}
+
+
+def ddp_check(model, criterion, x_dev, y_dev, world):
+    """Driver-run correctness of the multi-GPU path (the GPU test box has one GPU): after the timed region,
+    (a) every parameter is bit-identical on all ranks, (b) the bucket gradients of a synchronised backward equal the
+    mean over ranks of the gradients of an unsynchronised (no_sync) backward of the same batch."""
+    import torch
+    import torch.distributed as dist
+    net = model.module
+    worst_param = 0.0
+    for p in net.parameters():
+        ref = p.detach().clone()
+        dist.broadcast(ref, 0)
+        worst_param = max(worst_param, float((ref - p.detach()).abs().max()))
+    model.zero_grad(set_to_none=True)
+    with model.no_sync():
+        criterion(model(x_dev), y_dev).backward()
+    local = [p.grad.detach().clone() for p in net.parameters()]
+    for g in local:
+        dist.all_reduce(g, op=dist.ReduceOp.SUM)
+        g.div_(world)
+    model.zero_grad(set_to_none=True)
+    criterion(model(x_dev), y_dev).backward()
+    torch.cuda.synchronize()
+    worst = 0.0
+    for p, g in zip(net.parameters(), local):
+        worst = max(worst, float(((p.grad - g).abs().max() / g.abs().max().clamp_min(1e-20))))
+    model.zero_grad(set_to_none=True)
+    t = torch.tensor([worst_param, worst], device=x_dev.device)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return {"params_identical_across_ranks": bool(t[0].item() == 0.0), "max_param_diff": t[0].item(),
+            "bucket_grad_vs_mean_of_local_max_rel": t[1].item(), "ok": bool(t[0].item() == 0.0 and t[1].item() < 1e-4)}
+
+
+def comm_leg(model, dev, world, timed, step_sync, step_nosync, steps):
+    """All-reduce bus bandwidth on the wrapper's own buckets (stand-alone, device-timed) and the part of a step that
+    data parallelism adds: the DDP step minus the SAME step of an unwrapped replica in the same process (both replay
+    CUDA graphs; every rank runs its replica at the same time, so host and memory contention are alike)."""
+    import torch
+    import torch.distributed as dist
+    sizes = [b.flat.numel() * 4 for b in model.buckets]
+    total = sum(sizes)
+    def allreduce_all():
+        for b in model.buckets:
+            dist.all_reduce(b.flat, op=dist.ReduceOp.AVG)
+    scratch = [b.flat.clone() for b in model.buckets]
+    for _ in range(3):
+        allreduce_all()
+    ms = timed(allreduce_all, 10) / 10
+    for b, s0 in zip(model.buckets, scratch):
+        b.flat.copy_(s0)
+    busbw = total * 2.0 * (world - 1) / world / (ms * 1e-3) / 1e9
+    t_sync = timed(step_sync, steps) / steps
+    t_nosync = timed(step_nosync, steps) / steps
+    return {"buckets": len(sizes), "bytes": total, "allreduce_ms_all_buckets_standalone": ms, "busbw_gbs": busbw,
+            "step_ms_ddp": t_sync, "step_ms_unwrapped_replica": t_nosync, "exposed_comm_ms": t_sync - t_nosync}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -440,6 +584,11 @@ def main():
     sampler.start()
     total_ms = timed(step_resident, args.steps)
     clocks = sampler.stop()
+    grecs = [r for r in b200net.functional._GRAPHS.values() if r != "failed"]
+    graphs_used = {"backbone_graphs": len(grecs), "replays": int(sum(r.uses for r in grecs)),
+                   "training_graph": any(r.bwd is not None and r.uses >= args.steps for r in grecs)}
+    if args.precision == "bf16" and not graphs_used["training_graph"] and os.environ.get("B200_CUDA_GRAPHS", "1") != "0":
+        raise SystemExit("bench.py: the timed region did not replay the training graph (capture failed?)")
     for _ in range(3):
         step_e2e()
     e2e_verbatim_ms = timed(step_e2e, args.steps)
@@ -479,8 +628,10 @@ def main():
         achieved = algo_flops / (ms.value * 1e-3) / 1e12
         roof = {"bound": "tensor", "kernel": "conv_sm100_kernel (tcgen05 implicit-GEMM conv fprop/dgrad/wgrad family)",
                 "achieved": achieved, "peak": pk["tflops"], "unit": "TFLOP/s", "frac": achieved / pk["tflops"],
-                "peak_source": pk["src"] + " sustained bf16", "traffic": CONV_TRAFFIC_BYTES_PER_LAUNCH,
-                "traffic_source": "profiles/r01h_ncu_full_conv_summary.txt (bytes per launch, ncu --set full)",
+                "peak_source": pk["src"] + " sustained bf16", "traffic": _named_launch_traffic(),
+                "algorithmic_bytes": CONV_ALGO_BYTES_PER_LAUNCH, "traffic_launch": CONV_TRAFFIC_LAUNCH,
+                "traffic_source": "profiles/r02_ncu_named_launches.txt (ncu --set full, dram__bytes_read.sum + "
+                                  "dram__bytes_write.sum of that one launch)",
                 "launches_per_step": n.value // prof_steps, "kernel_ms_per_step": ms.value / prof_steps,
                 "executed_gemm_tflop_per_step": fl.value / prof_steps / 1e12}
 
@@ -503,10 +654,39 @@ def main():
             for _ in range(100):
                 int(net(x1).data.cpu().numpy().argmax())       # predict_image(): one D2H sync per image
             lat = (time.perf_counter() - t0) / 100 * 1e3
+            flips = argmax_flips(net, dev) if rank == 0 else None
         net.train()
-        infer = {"batch": 1024, "img_s": world * 1024 * 10 / (t_inf * 1e-3), "ms_per_batch": t_inf / 10,
+        infer = {"argmax_flips": flips, "batch": 1024, "img_s": world * 1024 * 10 / (t_inf * 1e-3), "ms_per_batch": t_inf / 10,
                  "batch1_224px_latency_ms": lat, "tensor_util": 4.1727e9 * 1024 * 10 / (t_inf * 1e-3) / 1e12 / peaks()["tflops"]}
         del xi
+
+    hbm = None
+    if args.precision == "bf16" and rank == 0 and world == 1:
+        hbm = hbm_kernels_leg(dev, model, optimizer)
+    ddpc = comm = None
+    if distributed:
+        ddpc = ddp_check(model, criterion, x_dev, y_dev, world)
+
+        torch.manual_seed(O.SEED_WEIGHTS)
+        plain = b200net.models.resnet50(pretrained=False)
+        plain.fc = b200net.nn.Sequential(b200net.nn.Linear(2048, 512), b200net.nn.ReLU(), b200net.nn.Dropout(0.2),
+                                         b200net.nn.Linear(512, 10), b200net.nn.LogSoftmax(dim=1))
+        plain.to(dev).train()
+        popt = b200net.optim.SGD(plain.parameters(), lr=0.001)
+
+        def step_plain():
+            b200net.functional.set_grad_sink(None)       # the wrapper installs its sink on every forward
+            popt.zero_grad()
+            loss = criterion(plain.forward(x_dev), y_dev)
+            loss.backward()
+            popt.step()
+            return loss
+        for _ in range(8):
+            step_plain()
+        for _ in range(3):
+            step_resident()
+        comm = comm_leg(model, dev, world, timed, step_resident, step_plain, 10)
+        del plain, popt
 
     # BERT / IMDB leg (configs[4]): the same reference statements on the second model of the harness
     bert_out = None
@@ -541,7 +721,14 @@ def main():
                     "verbatim_loop_value": world * B * args.steps / (e2e_verbatim_ms * 1e-3)},
             "gpu_launches": int(launches) * args.steps,
             "gpu_launches_per_step": int(launches),
+            "graphs_used": graphs_used,
         }
+        if hbm:
+            out["hbm_kernels"] = hbm
+        if ddpc:
+            out["ddp_check"] = ddpc
+        if comm:
+            out["comm"] = comm
         if roof:
             out["roofline"] = roof
         if infer:

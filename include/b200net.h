@@ -53,6 +53,11 @@ int32_t b200_conv_weight_ld(int32_t R, int32_t S, int32_t C);
 /* Cw = channels of the parameter, C >= Cw = channels of the packed operand (zero-filled beyond Cw). */
 int32_t b200_pack_weight(const float* w_oihw, void* w_krsc, int32_t K, int32_t Cw, int32_t R, int32_t S,
                          int32_t C, int32_t ld, int32_t out_dtype, void* stream);
+/* b200_pack_weight for `count` parameters in one launch per 48 (host arrays of device pointers and of the
+ * per-tensor K, Cw, C, R*S, ld): the training step re-packs every convolution weight after each optimizer update. */
+int32_t b200_pack_weight_multi(int32_t count, const void* const* w_oihw, void* const* w_krsc, const int32_t* K,
+                               const int32_t* Cw, const int32_t* C, const int32_t* RS, const int32_t* ld,
+                               int32_t out_dtype, void* stream);
 /* Explicit im2col staging: col[m][(r*S+s)*C + c] for output pixel m = (n*Ho + p)*Wo + q, row stride ld >= R*S*C
  * (tail zero-filled).  Used for the 3-channel stem: the image is widened to 4 channels, staged once per step with
  * ld = 256, and the stem then runs as a 1x1 convolution over 256 "channels" on the implicit tcgen05 path (forward

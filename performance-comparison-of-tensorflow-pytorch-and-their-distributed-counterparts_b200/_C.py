@@ -42,6 +42,8 @@ SIGNATURES = {
     "b200_nhwc_to_nchw": (I32, [P, P, I32, I32, I32, I32, I32, P]),
     "b200_conv_weight_ld": (I32, [I32, I32, I32]),
     "b200_pack_weight": (I32, [P, P, I32, I32, I32, I32, I32, I32, I32, P]),
+    "b200_pack_weight_multi": (I32, [I32, _PP, _PP, POINTER(c_int32), POINTER(c_int32), POINTER(c_int32),
+                                     POINTER(c_int32), POINTER(c_int32), I32, P]),
     "b200_im2col": (I32, [P, P, I32, I32, I32, I32, I32, I32, I32, I32, I32, I32, P]),
     "b200_stem_stage": (I32, [P, P, I32, I32, I32, I32, I32, I32, P]),
     "b200_stem_pack_weight": (I32, [P, P, I32, I32, I32, I32, P]),
@@ -131,6 +133,10 @@ def check(rc, what=""):
 
 def ptr_array(ptrs):
     return (c_void_p * len(ptrs))(*ptrs)
+
+
+def i32_array(vals):
+    return (c_int32 * len(vals))(*vals)
 
 
 def i64_array(vals):

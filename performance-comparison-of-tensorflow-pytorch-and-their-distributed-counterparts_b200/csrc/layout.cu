@@ -56,6 +56,34 @@ __global__ void pack_weight_kernel(const float* __restrict__ w, T* __restrict__ 
   }
 }
 
+// Several weights in one launch (the training graph re-packs all 53 convolution weights every step: one launch per
+// 48 tensors instead of one each).  The table travels by value in the kernel parameter block.
+constexpr int PACK_MAX = 48;
+struct PackArgs {
+  const float* w[PACK_MAX];
+  void* out[PACK_MAX];
+  int K[PACK_MAX], Cw[PACK_MAX], C[PACK_MAX], RS[PACK_MAX], ld[PACK_MAX];
+};
+template <typename T>
+__global__ void __launch_bounds__(256) pack_weight_multi_kernel(PackArgs a) {
+  const int ti = blockIdx.y;
+  const float* __restrict__ w = a.w[ti];
+  T* __restrict__ out = reinterpret_cast<T*>(a.out[ti]);
+  const int K = a.K[ti], Cw = a.Cw[ti], C = a.C[ti], RS = a.RS[ti], ld = a.ld[ti];
+  const long long total = (long long)K * ld;
+  const int RSC = RS * C;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int k = (int)(i / ld), j = (int)(i - (long long)k * ld);
+    float v = 0.f;
+    if (j < RSC) {
+      const int c = j % C, rs = j / C;
+      if (c < Cw) v = w[((long long)k * Cw + c) * RS + rs];
+    }
+    out[i] = from_f<T>(v);
+  }
+}
+
 template <typename TI, typename TO>
 __global__ void cast_kernel(const TI* __restrict__ x, TO* __restrict__ y, long long n) {
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
@@ -345,6 +373,34 @@ extern "C" int32_t b200_pack_weight(const float* w, void* out, int32_t K, int32_
   else if (out_dtype == B200_BF16) pack_weight_kernel<__nv_bfloat16><<<grid_for((long long)K * ld), 256, 0, st>>>(w, (__nv_bfloat16*)out, K, Cw, C, R, S, ld);
   else return fail(B200_INVALID_ARG, "bad dtype");
   return check_launch("pack_weight");
+}
+
+extern "C" int32_t b200_pack_weight_multi(int32_t count, const void* const* w_oihw, void* const* w_krsc,
+                                          const int32_t* K, const int32_t* Cw, const int32_t* C, const int32_t* RS,
+                                          const int32_t* ld, int32_t out_dtype, void* stream) {
+  if (count <= 0) return B200_OK;
+  if (!w_oihw || !w_krsc || !K || !Cw || !C || !RS || !ld) return fail(B200_INVALID_ARG, "pack_weight_multi: null table");
+  if (out_dtype != B200_F32 && out_dtype != B200_BF16) return fail(B200_INVALID_ARG, "pack_weight_multi: bad dtype");
+  cudaStream_t st = as_stream(stream);
+  for (int lo = 0; lo < count; lo += PACK_MAX) {
+    const int cnt = count - lo < PACK_MAX ? count - lo : PACK_MAX;
+    PackArgs a;
+    long long biggest = 0;
+    for (int i = 0; i < cnt; ++i) {
+      const int t = lo + i;
+      if (!w_oihw[t] || !w_krsc[t] || C[t] < Cw[t] || ld[t] < RS[t] * C[t] || K[t] <= 0)
+        return fail(B200_INVALID_ARG, "pack_weight_multi: bad entry %d", t);
+      a.w[i] = (const float*)w_oihw[t]; a.out[i] = w_krsc[t];
+      a.K[i] = K[t]; a.Cw[i] = Cw[t]; a.C[i] = C[t]; a.RS[i] = RS[t]; a.ld[i] = ld[t];
+      const long long n = (long long)K[t] * ld[t];
+      if (n > biggest) biggest = n;
+    }
+    const int bx = grid_for(biggest, 256, 2);
+    if (out_dtype == B200_F32) pack_weight_multi_kernel<float><<<dim3(bx, cnt), 256, 0, st>>>(a);
+    else pack_weight_multi_kernel<__nv_bfloat16><<<dim3(bx, cnt), 256, 0, st>>>(a);
+    if (int32_t rc = check_launch("pack_weight_multi")) return rc;
+  }
+  return B200_OK;
 }
 
 extern "C" int32_t b200_cast(const void* x, void* y, int64_t n, int32_t in_dtype, int32_t out_dtype, void* stream) {

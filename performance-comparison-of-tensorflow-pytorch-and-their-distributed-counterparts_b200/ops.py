@@ -100,6 +100,30 @@ def pack_weight(w, dtype, cpad=None):
     return out
 
 
+def pack_weights_multi(ws, dtype):
+    """pack_weight for a list of OIHW fp32 parameters (channels not padded) in one launch per 48 tensors."""
+    outs, meta = [], []
+    for w in ws:
+        K, C, R, S = w.shape
+        ld = weight_ld(R, S, C)
+        outs.append(torch.empty((K, ld), dtype=dtype, device=w.device))
+        meta.append((K, C, C, R * S, ld))
+    if not ws:
+        return outs
+    srcs = []
+    for w in ws:
+        wd = w.detach()
+        if wd.dtype != torch.float32 or not wd.is_contiguous():
+            wd = wd.float().contiguous()
+        srcs.append(wd)
+    check(lib.b200_pack_weight_multi(len(ws), _C.ptr_array([t.data_ptr() for t in srcs]),
+                                     _C.ptr_array([t.data_ptr() for t in outs]), _C.i32_array([m[0] for m in meta]),
+                                     _C.i32_array([m[1] for m in meta]), _C.i32_array([m[2] for m in meta]),
+                                     _C.i32_array([m[3] for m in meta]), _C.i32_array([m[4] for m in meta]),
+                                     _DT[dtype], _stream()), "pack_weight_multi")
+    return outs
+
+
 def im2col(x, R, S, stride, pad, ld):
     """NHWC [N,H,W,C] -> staged matrix [N,Ho,Wo,ld] (column (r*S+s)*C+c, zero tail)."""
     N, H, W, C = x.shape
