@@ -76,6 +76,17 @@ int32_t b200_stem_stage(const void* x_nhwc4, void* out, int32_t N, int32_t H, in
                         int32_t pad, void* stream);
 int32_t b200_stem_pack_weight(const float* w_oihw, void* w_packed, int32_t K, int32_t Cw, int32_t R, int32_t S,
                               void* stream);
+/* Input pipeline: the reference's per-image transform
+ * transforms.Compose([transforms.Resize((224,224)), transforms.ToTensor()])
+ * (pytorch_training_inference_on_image.ipynb:325-326, :847-848; another_neural_net.py:38-46) for a batch of DECODED
+ * images.  image_ptrs / heights / widths / row_strides are DEVICE arrays of N entries: uint8 HWC (RGB) pixel
+ * pointers, sizes and row strides in bytes -- images of one batch may differ in size.  Bilinear resize to Ho x Wo
+ * with PIL's antialiasing (antialias != 0; 0 = plain bilinear, torch's tensor default), rounded to a byte as PIL
+ * does, then x/255 into out_layout 0: [N][Ho][Wo][4] bf16 (the stem's 8-byte pixels; the model accepts this tensor
+ * directly) or 1: [N][3][Ho][Wo] fp32 (what ToTensor() returns).  JPEG entropy decoding stays on the host. */
+int32_t b200_preprocess_u8(const void* const* image_ptrs, const int32_t* heights, const int32_t* widths,
+                           const int64_t* row_strides, int32_t N, int32_t Ho, int32_t Wo, void* out,
+                           int32_t out_layout, int32_t antialias, void* stream);
 /* dtype cast of a flat buffer (fp32 <-> bf16) */
 int32_t b200_cast(const void* x, void* y, int64_t n, int32_t in_dtype, int32_t out_dtype, void* stream);
 

@@ -47,6 +47,7 @@ SIGNATURES = {
     "b200_im2col": (I32, [P, P, I32, I32, I32, I32, I32, I32, I32, I32, I32, I32, P]),
     "b200_stem_stage": (I32, [P, P, I32, I32, I32, I32, I32, I32, P]),
     "b200_stem_pack_weight": (I32, [P, P, I32, I32, I32, I32, P]),
+    "b200_preprocess_u8": (I32, [P, P, P, P, I32, I32, I32, P, I32, I32, P]),
     "b200_cast": (I32, [P, P, I64, I32, I32, P]),
     "b200_conv_workspace_bytes": (I64, [POINTER(ConvDesc), I32]),
     "b200_conv_fprop": (I32, [POINTER(ConvDesc), P, P, P, P, I64, P]),

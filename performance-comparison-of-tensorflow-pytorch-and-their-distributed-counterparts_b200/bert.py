@@ -617,8 +617,19 @@ class BertForSequenceClassification(nn.Module):
         checkpoints ship) is loaded; a directory that exists but holds neither is an error.  A hub name cannot be
         fetched on an offline box, so it yields the architecture with transformers' random initialisation (and says
         so)."""
-        model = cls(BertConfig(num_labels=num_labels, **kw))
         path = str(name_or_path)
+        cfg_file = os.path.join(path, "config.json")
+        cfg_kw = {}
+        if os.path.isfile(cfg_file):              # the checkpoint's own architecture (layers, widths, vocabulary)
+            import json
+            known = ("vocab_size hidden_size num_hidden_layers num_attention_heads intermediate_size hidden_act "
+                     "hidden_dropout_prob attention_probs_dropout_prob max_position_embeddings type_vocab_size "
+                     "initializer_range layer_norm_eps pad_token_id classifier_dropout").split()
+            with open(cfg_file) as fh:
+                raw = json.load(fh)
+            cfg_kw = {k: raw[k] for k in known if k in raw}
+        cfg_kw.update(kw)
+        model = cls(BertConfig(num_labels=num_labels, **cfg_kw))
         ckpt, st_file = os.path.join(path, "pytorch_model.bin"), os.path.join(path, "model.safetensors")
         sd = None
         if os.path.isfile(ckpt):

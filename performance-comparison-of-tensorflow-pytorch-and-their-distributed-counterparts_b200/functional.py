@@ -261,11 +261,13 @@ def _under(fc, m, model):
 
 class _BackboneState(object):
     """What the backbone's backward needs from its forward."""
-    __slots__ = ("unit0", "blocks", "pool_idx", "stem_shape", "final_shape", "dtype")
+    __slots__ = ("unit0", "blocks", "pool_idx", "stem_shape", "final_shape", "dtype", "pool")
 
 
-def _backbone_fwd(model, x, save, x_needs_grad):
-    """Stem -> layer1..4 -> avgpool on NHWC activations.  Returns (features [N,2048] fp32, state or None)."""
+def _backbone_fwd(model, x, save, x_needs_grad, pool=True):
+    """Stem -> layer1..4 -> avgpool on NHWC activations.  Returns (features [N,2048] fp32, state or None).
+    pool=False returns the layer4 map itself as NCHW fp32 [N,2048,h,w] (the `include_top=False` + Flatten + Dense
+    head of resnet.py:17-23 has no average pool)."""
     dtype = act_dtype()
     # num_batches_tracked += 1 for every BatchNorm in train mode: one multi-tensor launch instead of 53
     nbt = [m.num_batches_tracked for m in model.modules()
@@ -276,7 +278,10 @@ def _backbone_fwd(model, x, save, x_needs_grad):
     cp = _stem_cpad(model.conv1, dtype)
     if dtype == torch.bfloat16:
         prepack_weights(_backbone_convs(model), dtype)
-    xh = ops.to_nhwc(x, dtype, cp)
+    if x.dtype == torch.bfloat16 and x.dim() == 4 and x.shape[-1] == 4 and cp == 4:
+        xh = x.contiguous()               # already the stem's layout (b200net.utils.GpuPreprocess): nothing to convert
+    else:
+        xh = ops.to_nhwc(x, dtype, cp)
     z, u0 = _unit_forward(model.conv1, model.bn1, xh, True, None, save, stage=cp is not None and not x_needs_grad)
     stem_shape = z.shape
     cur, pool_idx = ops.maxpool_fwd(z, save)
@@ -292,10 +297,11 @@ def _backbone_fwd(model, x, save, x_needs_grad):
                 res = cur
             cur, u3 = _unit_forward(blk.conv3, blk.bn3, z2, True, res, save)
             blocks.append((u1, u2, u3, ud))
-    feat = ops.avgpool_fwd(cur)
+    feat = ops.avgpool_fwd(cur) if pool else ops.to_nchw(cur)
     if not save:
         return feat, None
     st = _BackboneState()
+    st.pool = pool
     st.unit0, st.blocks, st.pool_idx, st.stem_shape, st.final_shape, st.dtype = u0, blocks, pool_idx, stem_shape, \
         cur.shape, dtype
     return feat, st
@@ -389,7 +395,7 @@ def _backbone_bwd(st, dfeat, params, param_needs, x_needs_grad, sink, cut=None, 
         wp = packed_weight(u.conv.weight, dy.dtype, cin if cin != u.conv.in_channels else None)
         return ops.conv_dgrad(dy, wp, u.x.shape, K, R, S, stride, pad, out=out, accumulate=accumulate)
 
-    dcur = ops.avgpool_bwd(dfeat, st.final_shape, st.dtype)
+    dcur = ops.avgpool_bwd(dfeat, st.final_shape, st.dtype) if st.pool else ops.to_nhwc(dfeat, st.dtype)
     for bi, (u1, u2, u3, ud) in enumerate(reversed(st.blocks)):
         if cut is not None and bi in cut_after:
             join()
@@ -423,10 +429,13 @@ class _ResNetBackbone(torch.autograd.Function):
     @staticmethod
     def forward(ctx, model, grad_on, x, *params):
         # forward() itself always runs with grad mode off and needs_input_grad ignores torch.no_grad(), so the
-        # caller's grad mode comes in explicitly
+        # caller's grad mode comes in explicitly.  grad_on may carry the pool flag as (grad_on, pool).
+        pool = True
+        if isinstance(grad_on, tuple):
+            grad_on, pool = grad_on
         nig = ctx.needs_input_grad[2:]
         save = grad_on and any(nig)
-        feat, st = _backbone_fwd(model, x, save, grad_on and nig[0])
+        feat, st = _backbone_fwd(model, x, save, grad_on and nig[0], pool)
         if save:
             ctx.state = st
             ctx.params = params
@@ -565,14 +574,14 @@ def _bn_modules(model):
     return e[1]
 
 
-def _graph_key(model, x, params, needs_x):
+def _graph_key(model, x, params, needs_x, pool=True):
     bn_flags = tuple(m.training for m in _bn_modules(model))
     needs = tuple(p.requires_grad for p in params) if torch.is_grad_enabled() else ()
     # forward-only graphs (inference, frozen backbone) use weights packed OUTSIDE the graph, so they are only valid
     # for the weight versions they were captured with
     wver = -1 if (any(needs) or needs_x) else sum(p._version for p in params)
     return (id(model), tuple(x.shape), x.device.index, _PRECISION, bn_flags, needs, bool(needs_x), wver,
-            id(grad_sink_owner()))
+            id(grad_sink_owner()), bool(pool))
 
 
 def _tensor_ptrs(model, params=None):
@@ -608,7 +617,7 @@ def _capture(model, x, params, key):
         rec.fwd = torch.cuda.CUDAGraph()
         with torch.no_grad():
             with torch.cuda.graph(rec.fwd, pool=pool):
-                rec.feat, rec.state = _backbone_fwd(model, rec.x, save, needs_x)
+                rec.feat, rec.state = _backbone_fwd(model, rec.x, save, needs_x, key[9])
         rec.bwd, rec.ddp, rec.order, rec.segments = None, None, None, None
         if save:
             rec.dfeat = torch.zeros_like(rec.feat)
@@ -681,20 +690,21 @@ class _GraphedBackbone(torch.autograd.Function):
         return (None, rec.dx.clone() if rec.dx is not None else None) + tuple(out)
 
 
-def resnet_backbone(model, x):
-    """[N,3,H,W] fp32 NCHW -> [N,2048] fp32 features (everything up to and including avgpool + flatten)."""
+def resnet_backbone(model, x, pool=True):
+    """[N,3,H,W] fp32 NCHW -> [N,2048] fp32 features (everything up to and including avgpool + flatten); with
+    pool=False the layer4 map [N,2048,h,w] fp32 instead."""
     params = _backbone_params(model)
     owner = grad_sink_owner()
     if not (_GRAPHS_ON and x.is_cuda and not torch.cuda.is_current_stream_capturing()
             and (_GRAD_SINK is None or (owner is not None and owner.graph_ok()))):
-        return _ResNetBackbone.apply(model, torch.is_grad_enabled(), x, *params)
+        return _ResNetBackbone.apply(model, (torch.is_grad_enabled(), pool), x, *params)
     needs_x = x.requires_grad and torch.is_grad_enabled()
-    key = _graph_key(model, x, params, needs_x)
+    key = _graph_key(model, x, params, needs_x, pool)
     rec = _GRAPHS.get(key)
     if rec is not None and rec != "failed":
         if rec.ptrs == _tensor_ptrs(model, params):
             if graph_record_busy(rec):     # an earlier replayed forward still waits for its backward
-                return _ResNetBackbone.apply(model, torch.is_grad_enabled(), x, *params)
+                return _ResNetBackbone.apply(model, (torch.is_grad_enabled(), pool), x, *params)
             rec.uses += 1
             return _GraphedBackbone.apply(rec, x, *params)
         del _GRAPHS[key]          # parameters were re-allocated (model.to(), new tensors): recapture
@@ -721,7 +731,7 @@ def resnet_backbone(model, x):
             if len(_GRAPH_SEEN) > 256:               # variable-size inference: do not grow without bound
                 _GRAPH_SEEN.clear()
             _GRAPH_SEEN[key] = seen + 1
-    return _ResNetBackbone.apply(model, torch.is_grad_enabled(), x, *params)
+    return _ResNetBackbone.apply(model, (torch.is_grad_enabled(), pool), x, *params)
 
 
 # ------------------------------------------------------------------ classifier head (fp32, [rows][features])

@@ -88,11 +88,25 @@ class ResNet(_nn.Module):
         """[N,3,H,W] -> [N,2048]: the whole backbone as one fused autograd node."""
         return F.resnet_backbone(self, x)
 
+    def _pools_to_1x1(self):
+        p = self.avgpool
+        if not isinstance(p, _nn.AdaptiveAvgPool2d):
+            return False
+        size = p.output_size if isinstance(p.output_size, (tuple, list)) else (p.output_size, p.output_size)
+        return tuple(size) == (1, 1)
+
     def forward(self, x):
         if not x.is_cuda:
             raise RuntimeError("b200net.models.ResNet runs on CUDA tensors only (no CPU fallback); "
                                "call model.to('cuda') and inputs.to('cuda') as the reference loop does")
-        feat = self.features(x)
+        if self._pools_to_1x1():
+            feat = self.features(x)
+        else:
+            # `model.avgpool = nn.Identity()`: the Keras recipe of the reference, ResNet50(include_top=False) ->
+            # Flatten -> Dense(n_classes, softmax) on the whole 5x5x2048 map (resnet.py:17-23), written against the
+            # torchvision graph.  The fused node hands out the layer4 map; torchvision's forward then applies
+            # whatever the user put in `avgpool`, flattens, and calls `fc`.
+            feat = torch.flatten(self.avgpool(F.resnet_backbone(self, x, pool=False)), 1)
         return nn.run_head(self.fc, feat)
 
 

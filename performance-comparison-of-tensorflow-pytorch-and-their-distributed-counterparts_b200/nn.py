@@ -83,6 +83,8 @@ def run_head(fc, feat):
             x = F.dropout(x, m.p, m.training)
         elif isinstance(m, _nn.LogSoftmax) and x.dim() == 2 and m.dim in (1, -1):
             x = F.log_softmax(x, 1)
+        elif isinstance(m, _nn.Flatten):
+            x = x.flatten(m.start_dim, m.end_dim)
         elif isinstance(m, _nn.Sequential):
             x = run_head(m, x)
         else:

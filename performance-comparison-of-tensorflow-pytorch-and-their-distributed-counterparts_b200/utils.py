@@ -81,3 +81,54 @@ class DevicePrefetcher(object):
                     t.record_stream(cur)
             nxt = fetch()
             yield batch
+
+
+class GpuPreprocess(object):
+    """The reference's image transform on the GPU -- `transforms.Compose([transforms.Resize(size),
+    transforms.ToTensor()])` (pytorch_training_inference_on_image.ipynb:325-326, :847-848) -- for a batch of decoded
+    uint8 HWC images (numpy arrays, PIL images or uint8 tensors; sizes may differ within a batch).
+
+        prep = b200net.utils.GpuPreprocess((160, 160), device)
+        inputs = prep(images)                    # -> model-ready batch; model(inputs) as usual
+        inputs = prep(images, layout="nchw")     # -> [N,3,H,W] fp32, exactly what ToTensor() would have produced
+
+    The default output is the stem's own input layout ([N,H,W,4] bf16, 8-byte pixels), which `model.forward` accepts
+    directly in bf16 mode: the host -> device copy moves the 3-byte source pixels instead of 12-byte resized floats
+    and the model's first layout kernel disappears.  JPEG decoding stays with PIL on the host."""
+
+    def __init__(self, size, device="cuda", antialias=True):
+        self.size = (size, size) if isinstance(size, int) else tuple(size)
+        self.device = torch.device(device)
+        self.antialias = bool(antialias)
+
+    def __call__(self, images, layout="packed"):
+        import numpy as np
+        from ._C import lib, check
+        ts = []
+        for im in images:
+            if not isinstance(im, torch.Tensor):
+                im = torch.from_numpy(np.ascontiguousarray(np.asarray(im)))
+            if im.dtype != torch.uint8 or im.dim() != 3 or im.shape[2] != 3:
+                raise ValueError("GpuPreprocess: images must be uint8 [H, W, 3] (RGB)")
+            ts.append(im.contiguous().to(self.device, non_blocking=True))
+        n = len(ts)
+        ptrs = torch.tensor([t.data_ptr() for t in ts], dtype=torch.int64).to(self.device, non_blocking=True)
+        hs = torch.tensor([t.shape[0] for t in ts], dtype=torch.int32).to(self.device, non_blocking=True)
+        ws = torch.tensor([t.shape[1] for t in ts], dtype=torch.int32).to(self.device, non_blocking=True)
+        rs = torch.tensor([t.shape[1] * 3 for t in ts], dtype=torch.int64).to(self.device, non_blocking=True)
+        ho, wo = self.size
+        if layout == "packed":
+            out = torch.empty((n, ho, wo, 4), dtype=torch.bfloat16, device=self.device)
+            code = 0
+        elif layout == "nchw":
+            out = torch.empty((n, 3, ho, wo), dtype=torch.float32, device=self.device)
+            code = 1
+        else:
+            raise ValueError("layout must be 'packed' or 'nchw'")
+        with torch.cuda.device(self.device):
+            check(lib.b200_preprocess_u8(ptrs.data_ptr(), hs.data_ptr(), ws.data_ptr(), rs.data_ptr(), n, ho, wo,
+                                         out.data_ptr(), code, 1 if self.antialias else 0,
+                                         torch.cuda.current_stream().cuda_stream), "preprocess_u8")
+        for t in ts:                       # the kernel reads them on the current stream
+            t.record_stream(torch.cuda.current_stream())
+        return out

@@ -452,6 +452,50 @@ def test_graph_record_is_not_replayed_while_a_backward_is_pending():
         b200net.set_cuda_graphs(True)
 
 
+def test_keras_recipe_head_flatten_dense_no_avgpool():
+    """resnet.py:17-24 -- ResNet50(include_top=False) -> Flatten -> Dense(n_classes, softmax), every layer trainable,
+    SGD(lr=0.001), categorical cross-entropy -- written against the torchvision graph the oracle can run:
+    `model.avgpool = nn.Identity()` and `model.fc = Sequential(Linear(2048*h*w, 10), LogSoftmax)` (torchvision's
+    forward flattens in between).  One training step + eval against the oracle: fp32 parity mode at N=16, 96 px
+    (north-star tolerances, fp64-arbitrated behind the step); bf16 at N=64, 128 px (loss within 1e-2 -- BatchNorm over
+    the 144 samples per channel of the small case turns bf16 rounding into several per cent of loss, for stock bf16
+    autocast just as for these kernels)."""
+    import b200net
+    import torchvision
+
+    def build(factory, side):
+        torch.manual_seed(11)
+        m = factory()
+        m.avgpool = nn.Identity()
+        m.fc = nn.Sequential(nn.Linear(2048 * side * side, 10), nn.LogSoftmax(dim=1))
+        return m
+
+    tv = lambda: torchvision.models.resnet50(weights=None)
+    for prec, n, hw, side in (("fp32", 16, 96, 3), ("bf16", 64, 128, 4)):
+        b200net.set_precision(prec)
+        try:
+            ref = build(tv, side)
+            ours = build(lambda: b200net.models.resnet50(pretrained=False), side)
+            ours.load_state_dict(ref.state_dict())
+            ours.to(DEV)
+            got = _run_ours(ours, "A", n=n, hw=hw, steps=1)
+            exp = O.run_case(ref, "A", n=n, hw=hw, steps=1)
+            print("keras-recipe head [%s]: loss ours %.6f oracle %.6f" % (prec, got["losses"][0], exp["losses"][0]))
+            if prec == "fp32":
+                ref64 = build(tv, side).double()
+                e64 = O.run_case(ref64, "A", n=n, hw=hw, steps=1)
+                assert abs(got["losses"][0] - exp["losses"][0]) <= 1e-4 * abs(exp["losses"][0])
+                assert _relmax(got["logps"][0], exp["logps"][0]) <= 1e-4
+                assert _relmax(got["eval_logps"], exp["eval_logps"]) <= O.arbitrated_tol(exp["eval_logps"], e64["eval_logps"], 1e-4)
+                sd, sdr, sd64 = ours.state_dict(), ref.state_dict(), ref64.state_dict()
+                for k in ("fc.0.weight", "fc.0.bias", "layer4.2.conv3.weight", "conv1.weight"):
+                    assert _relmax_w(sd[k], sdr[k]) <= O.arbitrated_tol(sdr[k], sd64[k], 1e-3), k
+            else:
+                assert abs(got["losses"][0] - exp["losses"][0]) <= 1e-2 * abs(exp["losses"][0]), (got["losses"], exp["losses"])
+        finally:
+            b200net.set_precision("bf16")
+
+
 def test_standalone_modules_match_torch_fp32():
     """Layer-by-layer use (NCHW in/out) of the drop-in modules: Bottleneck forward/backward vs torchvision."""
     import b200net
