@@ -16,7 +16,7 @@ hand-written CUDA kernels in libb200net.so (C-ABI: include/b200net.h); importing
 library raises.
 """
 from . import _C  # noqa: F401  (fails loudly when libb200net.so is missing)
-from . import ops, functional, nn, models, optim, utils, parallel, bert  # noqa: F401
+from . import ops, functional, nn, models, optim, utils, parallel, bert, text  # noqa: F401
 from .functional import set_precision, get_precision, set_cuda_graphs  # noqa: F401
 
 __version__ = "0.1.0"
