@@ -406,6 +406,8 @@ def ddp_check(model, criterion, x_dev, y_dev, world):
         ref = p.detach().clone()
         dist.broadcast(ref, 0)
         worst_param = max(worst_param, float((ref - p.detach()).abs().max()))
+    from b200net import functional as BF
+    drop0 = BF._DROPOUT_CALLS[0]           # both backward passes must draw the same dropout mask in the head
     model.zero_grad(set_to_none=True)
     with model.no_sync():
         criterion(model(x_dev), y_dev).backward()
@@ -414,6 +416,7 @@ def ddp_check(model, criterion, x_dev, y_dev, world):
         dist.all_reduce(g, op=dist.ReduceOp.SUM)
         g.div_(world)
     model.zero_grad(set_to_none=True)
+    BF._DROPOUT_CALLS[0] = drop0
     criterion(model(x_dev), y_dev).backward()
     torch.cuda.synchronize()
     worst = 0.0
