@@ -25,8 +25,20 @@ namespace b200 {
 enum { MODE_FPROP = 0, MODE_DGRAD = 1, MODE_WGRAD = 2 };
 constexpr int CONV_MAX_TAPS = 9;
 constexpr int CONV_KR_MAX = 128;  // wgrad: most pixel rows per k-block (multiple of 16); 64 with 256-column tiles
-constexpr int CONV_STAGING_BYTES = 2 * 128 * 128;  // epilogue: two [128 rows][64 bf16] swizzled tiles for TMA stores
-constexpr int CONV_STATS_RED_BYTES = 3 * 64 * 2 * 4;  // epilogue: cross-warp scratch of the fused BN statistics
+constexpr int CONV_STAGING_TILE = 128 * 128;        // epilogue: one [128 rows][64 bf16] swizzled tile
+// staging tiles per epilogue group (template parameter NSTG): 2 lets the TMA store of one column group overlap the
+// packing of the next (what the short reductions need: their epilogue is the critical path), 1 leaves 32 KB more for
+// operand stages (what the deep reductions need)
+constexpr int CONV_STATS_RED_BYTES = 2 * 128 * 4;  // epilogue: per-group broadcast scratch (64 scales + 64 shifts of the affine epilogue)
+// Threads: warp 0 = TMA producer, warp 1 = MMA issuer, warps 2..9 = EIGHT epilogue warps in two groups of four.  A
+// warp may only read the TMEM lanes of its quarter (warp % 4), so the two groups cover the same 128 accumulator rows
+// and split the 64-column groups of a tile between them (group e takes column groups e, e+2, ...): with four warps
+// the epilogue of a 128x256 tile (TMEM -> bf16 -> swizzled smem -> TMA store, plus the BatchNorm column sums) took
+// longer than the main loop of every layer with fewer than ~4 k-blocks (the 64->256, 128->512, 256->1024 1x1
+// convolutions ran at half of their HBM roofline); two groups halve it and give every scheduler two warps to hide
+// the tcgen05.ld / shared-memory latencies behind each other.
+constexpr int CONV_THREADS = 320;
+constexpr int CONV_EPI_WARPS = 8;
 
 struct ConvTap {
   int dw, dh;  // shift of the activation box (input-pixel units) for this tap
@@ -68,11 +80,11 @@ struct ConvParams {
 // wgrad stage geometry: 128-column tiles use 128-pixel k-blocks, 256-column tiles 64-pixel k-blocks (same bytes)
 #define CONV_WGRAD_KR(BN_) ((BN_) == 256 ? 64 : 128)
 
-template <int BN, int STAGES, int MODE, int CG = 1>
+template <int BN, int STAGES, int MODE, int CG = 1, int NSTG = 1>
 constexpr int conv_smem_bytes() {
   constexpr int a = MODE == MODE_WGRAD ? 2 * CONV_WGRAD_KR(BN) * 128 : GEMM_BM * 128 * (CG == 3 ? 2 : 1);
   constexpr int b = MODE == MODE_WGRAD ? (BN / 64) * CONV_WGRAD_KR(BN) * 128 : BN * 128 / (CG == 2 ? 2 : 1);
-  return STAGES * (a + b) + (MODE == MODE_WGRAD ? 0 : CONV_STAGING_BYTES + CONV_STATS_RED_BYTES) + 1024 + 256;
+  return STAGES * (a + b) + (MODE == MODE_WGRAD ? 0 : 2 * NSTG * CONV_STAGING_TILE + CONV_STATS_RED_BYTES) + 1024 + 256;
 }
 
 // Persistent kernel: grid = min(#tiles, #SMs); every CTA walks tiles blockIdx.x, blockIdx.x + gridDim.x, ...
@@ -131,13 +143,14 @@ __device__ __forceinline__ ConvTile conv_decode_tile(const ConvParams& P, int ti
 // (32 KB per 128x256x64 unit instead of 48): the single-tile kernel is bound by L2 -> SM operand traffic
 // (~115 GB/s per SM: 0.43 us per 48 KB k-block against 0.28 us of MMA time).  The two accumulators fill TMEM, so the
 // epilogue of an item no longer overlaps the next item's main loop: worth it when the reduction is deep.
-template <int BN, int STAGES, int MODE, int CG = 1>
-__global__ void __launch_bounds__(GEMM_THREADS, 1)
+template <int BN, int STAGES, int MODE, int CG = 1, int NSTG = 1>
+__global__ void __launch_bounds__(CONV_THREADS, 1)
 conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                   const __grid_constant__ CUtensorMap tmO, const __grid_constant__ ConvParams P) {
   constexpr int A_BYTES = MODE == MODE_WGRAD ? 2 * CONV_WGRAD_KR(BN) * 128 : GEMM_BM * 128 * (CG == 3 ? 2 : 1);
   constexpr int B_BYTES = MODE == MODE_WGRAD ? (BN / 64) * CONV_WGRAD_KR(BN) * 128 : BN * 128 / (CG == 2 ? 2 : 1);
   static_assert(CG == 1 || (MODE != MODE_WGRAD && BN == 256), "CG 2 / 3: fprop / dgrad with 256-wide tiles");
+  constexpr int CONV_STAGING_BYTES = 2 * NSTG * CONV_STAGING_TILE;
   constexpr int STG_BYTES = MODE == MODE_WGRAD ? 0 : CONV_STAGING_BYTES + CONV_STATS_RED_BYTES;
   constexpr uint32_t TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;   // two accumulators
   static_assert(2 * BN <= 512, "two accumulators must fit TMEM");
@@ -148,7 +161,7 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   uint8_t* smA = smem;
   uint8_t* smB = smem + STAGES * A_BYTES;
   uint8_t* smStage = smem + STAGES * (A_BYTES + B_BYTES);   // 1024-aligned: stage sizes are multiples of 1024
-  float* smRed = reinterpret_cast<float*>(smStage + CONV_STAGING_BYTES);   // [3][64][2]
+  float* smRedBase = reinterpret_cast<float*>(smStage + CONV_STAGING_BYTES);   // per group: [128]
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + STAGES * (A_BYTES + B_BYTES) + STG_BYTES);
   uint64_t* empty = full + STAGES;
   uint64_t* tmem_full = empty + STAGES;    // [2]
@@ -181,7 +194,7 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 #pragma unroll
     for (int b = 0; b < 2; ++b) {
       mbar_init(&tmem_full[b], 1);
-      mbar_init(&tmem_empty[b], CG == 2 ? 8 : 4);   // one arrive per epilogue warp (of both CTAs of a pair)
+      mbar_init(&tmem_empty[b], CG == 2 ? 2 * CONV_EPI_WARPS : CONV_EPI_WARPS);   // one arrive per epilogue warp (of both CTAs of a pair)
     }
     mbar_fence_init();
   }
@@ -365,16 +378,20 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     }
     __syncwarp();
   } else {
-    // ------------------------------------------------------------ epilogue warps
+    // ------------------------------------------------------------ epilogue warps (two groups of four)
     const int q = warp & 3;
     const int l = q * 32 + lane;  // accumulator row
+    const int eg = (warp - 2) >> 2;              // epilogue group 0 / 1
+    const int bar_id = 1 + eg;                   // named barrier of the group (128 threads)
+    float* smRed = smRedBase + eg * 128;
     uint32_t it = 0;
-    uint32_t stage_ctr = 0;       // staging-tile ring position (TMA-store epilogue)
+    uint32_t stage_ctr = 0;                      // which of the group's two staging tiles comes next
     // fused BatchNorm statistics: this thread's running column sums over ALL tiles of this CTA (the launcher makes
-    // gridDim a multiple of n_tiles, so a CTA only ever sees one output-column tile)
-    float st_acc[BN / 64][4];
+    // gridDim a multiple of n_tiles, so a CTA only ever sees one output-column tile); slot gi = column group eg + 2*gi
+    constexpr int GPG = (BN / 64 + 1) / 2;       // column groups per epilogue group
+    float st_acc[GPG][4];
 #pragma unroll
-    for (int g = 0; g < BN / 64; ++g) { st_acc[g][0] = 0.f; st_acc[g][1] = 0.f; st_acc[g][2] = 0.f; st_acc[g][3] = 0.f; }
+    for (int g = 0; g < GPG; ++g) { st_acc[g][0] = 0.f; st_acc[g][1] = 0.f; st_acc[g][2] = 0.f; st_acc[g][3] = 0.f; }
     for (int w = walk_id; w < walk_total; w += walk_n, ++it)
     for (int half = 0; half < (CG == 3 ? 2 : 1); ++half) {      // CG == 3: the item's two pixel tiles, one after the other
       const int tile = tile_of(w, CG == 3 ? half : rank);
@@ -403,18 +420,19 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         // ---- TMA-store epilogue: TMEM -> registers -> bf16 -> 128B-swizzled smem tile [128 px][64 ch] -> one bulk
         // tensor store per 64-channel group (full 128-byte lines, bounds clipped by the TMA unit).  Two staging
         // tiles alternate so the store of group g overlaps the TMEM reads / packing of group g+1.
-        const bool elected = (warp == 2 && lane == 0);
+        const bool elected = (((warp - 2) & 3) == 0 && lane == 0);
 #pragma unroll
-        for (int g = 0; g < BN / 64; ++g) {
-          if (T.n0 + g * 64 >= P.ncols) break;     // uniform across the CTA
-          uint8_t* stg = smStage + (stage_ctr & 1u) * (CONV_STAGING_BYTES / 2);
-          if (elected) tma_store_wait_read<1>();   // the store that last used this tile has finished reading it
+        for (int gi = 0; gi < GPG; ++gi) {
+          const int g = eg + 2 * gi;
+          if (g >= BN / 64 || T.n0 + g * 64 >= P.ncols) break;     // uniform across the group
+          uint8_t* stg = smStage + (eg * NSTG + (NSTG == 2 ? (stage_ctr & 1u) : 0u)) * CONV_STAGING_TILE;
+          if (elected) tma_store_wait_read<NSTG - 1>();   // the store that last used this tile has finished reading it
           const bool affine = MODE == MODE_FPROP && P.ep_scale != nullptr;
           if (affine) {   // this group's 64 per-channel scales and shifts -> smem (read back as broadcasts)
             const int col = T.n0 + g * 64 + (l & 63);
             smRed[l] = l < 64 ? P.ep_scale[col] : P.ep_shift[col];
           }
-          asm volatile("bar.sync 1, 128;" ::: "memory");
+          asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
           // residual (eval-mode block output): this thread's 64 channels of its pixel, issued before the TMEM reads
           uint4 resv[8];
           const bool has_res = affine && P.ep_res != nullptr;
@@ -461,7 +479,7 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             }
           }
           fence_proxy_async_smem();
-          asm volatile("bar.sync 1, 128;" ::: "memory");
+          asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
           if (elected) {
             if (P.accumulate) tma_reduce_add_4d(&tmO, stg, T.n0 + g * 64, T.q0, T.p0, T.i0);
             else tma_store_4d(&tmO, stg, T.n0 + g * 64, T.q0, T.p0, T.i0);
@@ -477,8 +495,8 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
               const uint32_t w = *reinterpret_cast<const uint32_t*>(stg + row * 128 + (((lane >> 2) ^ (row & 7)) << 4) +
                                                                      ((lane & 3) << 2));
               const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w));
-              st_acc[g][0] += f.x; st_acc[g][1] = fmaf(f.x, f.x, st_acc[g][1]);
-              st_acc[g][2] += f.y; st_acc[g][3] = fmaf(f.y, f.y, st_acc[g][3]);
+              st_acc[gi][0] += f.x; st_acc[gi][1] = fmaf(f.x, f.x, st_acc[gi][1]);
+              st_acc[gi][2] += f.y; st_acc[gi][3] = fmaf(f.y, f.y, st_acc[gi][3]);
             }
           }
           ++stage_ctr;
@@ -492,7 +510,7 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         continue;
       }
 #pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
+      for (int c = eg; c < BN / 32; c += 2) {      // 32-column chunks alternate between the two epilogue groups
         uint32_t r[32];
         if (have_work) {
           tmem_ld_32x32b_x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * BN + static_cast<uint32_t>(c * 32), r);
@@ -565,24 +583,27 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         else mbar_arrive(&tmem_empty[buf]);
       }
     }
-    if (MODE != MODE_WGRAD && P.tma_store && warp == 2 && lane == 0) tma_store_wait<0>();  // smem must outlive the stores
+    if (MODE != MODE_WGRAD && P.tma_store && ((warp - 2) & 3) == 0 && lane == 0) tma_store_wait<0>();  // smem must outlive the stores
     if (MODE == MODE_FPROP && P.tma_store && P.stats != nullptr) {
-      // one row of partial statistics per CTA: warps 1..3 hand their sums to warp 0 through smem
+      // one row of partial statistics per CTA: warps 1..3 of a group hand their sums to warp 0 through the group's
+      // staging tile (idle now: its last store has completed)
+      float* smFin = reinterpret_cast<float*>(smStage + eg * NSTG * CONV_STAGING_TILE);
       const int n0 = (blockIdx.x % P.n_tiles) * BN;
 #pragma unroll
-      for (int g = 0; g < BN / 64; ++g) {
-        if (n0 + g * 64 >= P.ncols) break;
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+      for (int gi = 0; gi < GPG; ++gi) {
+        const int g = eg + 2 * gi;
+        if (g >= BN / 64 || n0 + g * 64 >= P.ncols) break;
+        asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
         if (q != 0) {
-          float* r = smRed + ((q - 1) * 64 + 2 * lane) * 2;
-          r[0] = st_acc[g][0]; r[1] = st_acc[g][1]; r[2] = st_acc[g][2]; r[3] = st_acc[g][3];
+          float* r = smFin + ((q - 1) * 64 + 2 * lane) * 2;
+          r[0] = st_acc[gi][0]; r[1] = st_acc[gi][1]; r[2] = st_acc[gi][2]; r[3] = st_acc[gi][3];
         }
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+        asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
         if (q == 0) {
-          float a0 = st_acc[g][0], a1 = st_acc[g][1], b0 = st_acc[g][2], b1 = st_acc[g][3];
+          float a0 = st_acc[gi][0], a1 = st_acc[gi][1], b0 = st_acc[gi][2], b1 = st_acc[gi][3];
 #pragma unroll
           for (int w2 = 0; w2 < 3; ++w2) {
-            const float* r = smRed + (w2 * 64 + 2 * lane) * 2;
+            const float* r = smFin + (w2 * 64 + 2 * lane) * 2;
             a0 += r[0]; a1 += r[1]; b0 += r[2]; b1 += r[3];
           }
           // row = blockIdx.x / n_tiles: the n_tiles CTAs of a row cover the column tiles exactly once
@@ -657,11 +678,12 @@ inline int conv_stats_grid(int total_tiles, int n_tiles, int num_ctas) {
   return g < n_tiles ? n_tiles : g;
 }
 
-template <int BN, int STAGES, int MODE, int CG = 1>
+template <int BN, int STAGES, int MODE, int CG = 1, int NSTG = 1>
 inline int launch_conv_cfg(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, const ConvParams& P,
                            int num_ctas, cudaStream_t st) {
-  auto kern = conv_sm100_kernel<BN, STAGES, MODE, CG>;
-  constexpr int smem = conv_smem_bytes<BN, STAGES, MODE, CG>();
+  auto kern = conv_sm100_kernel<BN, STAGES, MODE, CG, NSTG>;
+  constexpr int smem = conv_smem_bytes<BN, STAGES, MODE, CG, NSTG>();
+  static_assert(smem <= 232448, "conv kernel: shared memory budget exceeded");
   static int attr_state[B200_MAX_DEVICES] = {0};
   if (cudaError_t e = ensure_dyn_smem(kern, smem, attr_state)) return 300 + static_cast<int>(e);
   int grid = P.total_tiles < num_ctas ? P.total_tiles : num_ctas;
@@ -673,7 +695,7 @@ inline int launch_conv_cfg(const CUtensorMap& ta, const CUtensorMap& tb, const C
     if (clusters < 1) clusters = 1;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(2 * clusters);
-    cfg.blockDim = dim3(GEMM_THREADS);
+    cfg.blockDim = dim3(CONV_THREADS);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = st;
     cudaLaunchAttribute attr[1];
@@ -686,7 +708,7 @@ inline int launch_conv_cfg(const CUtensorMap& ta, const CUtensorMap& tb, const C
     cudaError_t e2 = cudaLaunchKernelEx(&cfg, kern, ta, tb, to, P);
     return e2 == cudaSuccess ? 0 : 400 + static_cast<int>(e2);
   }
-  kern<<<grid, GEMM_THREADS, smem, st>>>(ta, tb, to, P);
+  kern<<<grid, CONV_THREADS, smem, st>>>(ta, tb, to, P);
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? 0 : 400 + static_cast<int>(e);
 }
