@@ -303,6 +303,28 @@ static int32_t implicit_dgrad(const b200_conv_desc* d, const ConvGeom& g, const 
   if (rc) return fail(B200_CUDA_ERROR, "conv_dgrad: weight tensor map failed (%d)", rc);
   const int bn = pick_bn(d, g, d->C);
   const int classes = d->stride == 1 ? 1 : 4;
+  static const bool no_tma_store = getenv("B200_NO_TMA_STORE") != nullptr;
+  static const bool no_tma_reduce = getenv("B200_NO_TMA_REDUCE") != nullptr;
+  static const bool no_strided_tma = getenv("B200_NO_STRIDED_TMA_STORE") != nullptr;
+  const bool vec_ok_dx = (reinterpret_cast<uintptr_t>(dx) & 15) == 0 && d->C % 8 == 0;
+  const bool tma_out = !no_tma_store && vec_ok_dx && (d->stride == 1 || !no_strided_tma) && (!accumulate || !no_tma_reduce);
+  if (classes > 1 && !accumulate && tma_out) {
+    // Parity classes that no filter tap reaches (three of the four for a 1x1 stride-2 convolution) are plain zeros:
+    // clear the gradient once instead of running a GEMM launch per empty class that only stores zeros.
+    bool any_empty = false;
+    for (int cls = 0; cls < classes; ++cls) {
+      const int ph = cls / 2, pw = cls % 2;
+      int nt = 0;
+      for (int r = 0; r < d->R; ++r)
+        for (int s2 = 0; s2 < d->S; ++s2)
+          if ((ph + d->pad - r) % d->stride == 0 && (pw + d->pad - s2) % d->stride == 0) ++nt;
+      if (nt == 0) any_empty = true;
+    }
+    if (any_empty) {
+      cudaMemsetAsync(dx, 0, (size_t)d->N * d->H * d->W * d->C * 2, st);
+      launch_counter() += 1;
+    }
+  }
   for (int cls = 0; cls < classes; ++cls) {
     const int ph = d->stride == 1 ? 0 : cls / 2, pw = d->stride == 1 ? 0 : cls % 2;
     ConvParams P{};
@@ -324,7 +346,7 @@ static int32_t implicit_dgrad(const b200_conv_desc* d, const ConvGeom& g, const 
         P.taps[P.ntaps++] = ConvTap{vw / d->stride, vh / d->stride, (r * d->S + s2) * d->C};
       }
     }
-    if (P.ntaps == 0 && accumulate) continue;  // nothing to add for this parity class
+    if (P.ntaps == 0 && (accumulate || (classes > 1 && tma_out))) continue;  // nothing to add / already cleared
     const PixelBox b = choose_pixel_box(Wq, Hq, Nq, GEMM_BM, 1, 1);
     P.bw = b.bw; P.bh = b.bh; P.bn = b.bn; P.tiles_w = b.tiles_w; P.tiles_h = b.tiles_h; P.tiles_n = b.tiles_n;
     P.a_mul = 1;
@@ -346,11 +368,10 @@ static int32_t implicit_dgrad(const b200_conv_desc* d, const ConvGeom& g, const 
     P.pair_mode = pair_mode_for(P.ntaps * P.cchunks);
     P.total_pairs = pair_items(bn, tiles, P.n_tiles, false, P.pair_mode);
     CUtensorMap to;
-    static const bool no_tma_store = getenv("B200_NO_TMA_STORE") != nullptr;
-    // strided (parity-class) outputs keep the per-thread store path; accumulation uses the TMA reduce-add
-    static const bool no_tma_reduce = getenv("B200_NO_TMA_REDUCE") != nullptr;
-    P.tma_store = !no_tma_store && P.vec_ok && d->stride == 1 && (!accumulate || !no_tma_reduce);
-    rc = make_tmap_bf16_nhwc(&to, dx, P.Nout, P.Hout, P.Wout, d->C, b.bw, b.bh, b.bn, 1);
+    // bf16 outputs leave through TMA stores (TMA reduce-add when accumulating); for a parity class of a stride-2
+    // layer the output map walks every second pixel (elementStrides) starting at the class's (ph, pw)
+    P.tma_store = tma_out;
+    rc = make_tmap_bf16_nhwc(&to, dx, P.Nout, P.Hout, P.Wout, d->C, b.bw, b.bh, b.bn, d->stride);
     if (rc) return fail(B200_CUDA_ERROR, "conv_dgrad: output tensor map failed (%d)", rc);
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     timing_begin(e0, e1, st);

@@ -481,8 +481,10 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           fence_proxy_async_smem();
           asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
           if (elected) {
-            if (P.accumulate) tma_reduce_add_4d(&tmO, stg, T.n0 + g * 64, T.q0, T.p0, T.i0);
-            else tma_store_4d(&tmO, stg, T.n0 + g * 64, T.q0, T.p0, T.i0);
+            // strided outputs (the parity classes of a stride-2 dgrad): the output map walks every o_mul-th pixel
+            const int sw = T.q0 * P.o_mul + P.o_off_w, sh = T.p0 * P.o_mul + P.o_off_h;
+            if (P.accumulate) tma_reduce_add_4d(&tmO, stg, T.n0 + g * 64, sw, sh, T.i0);
+            else tma_store_4d(&tmO, stg, T.n0 + g * 64, sw, sh, T.i0);
             tma_store_commit();
           }
           if (MODE == MODE_FPROP && P.stats != nullptr) {
