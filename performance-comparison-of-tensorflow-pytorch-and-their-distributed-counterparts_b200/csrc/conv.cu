@@ -8,6 +8,7 @@
 #include "gemm_sm100.cuh"
 #include "conv_sm100.cuh"
 #include "wgrad_sm100.cuh"
+#include "conv_halo_sm100.cuh"
 #include <vector>
 #include <stdlib.h>
 #include <utility>
@@ -241,11 +242,44 @@ static inline int pick_bn(const b200_conv_desc*, const ConvGeom&, int cols) {
   return cols > 128 ? 256 : (cols > 64 ? 128 : 64);
 }
 
+// Halo-resident variant (conv_halo_sm100.cuh) for "same" RxS stride-1 convolutions: a tile is bh full image rows,
+// the taps are descriptor shifts into one halo tile per channel chunk.  Worth it where the activation boxes dominate
+// the operand traffic, i.e. narrow layers.  OFF by default: on 64->64 3x3 at 40x40 it moves less than half the
+// L2 -> SM bytes and is still slower (60.6 vs 54.2 us forward); B200_HALO_MAX_C=<max channels> turns it on.
+static inline bool halo_conv_ok(const b200_conv_desc* d, const ConvGeom& g, int cin, int cout) {
+  static const int max_c = getenv("B200_HALO_MAX_C") ? atoi(getenv("B200_HALO_MAX_C")) : 0;
+  if (max_c <= 0 || d->stride != 1 || d->R * d->S <= 1 || g.Wo != d->W || g.Ho != d->H) return false;
+  if (2 * d->pad != d->R - 1 || 2 * d->pad != d->S - 1) return false;
+  const int wh = d->W + d->S - 1;
+  if ((d->R - 1) * wh + d->S - 1 + GEMM_BM > HALO_ROWS) return false;       // the last tap's view must stay inside the stage
+  const int bh = GEMM_BM / wh;
+  if (bh < 1 || (bh + d->R - 1) * wh > HALO_ROWS || bh + d->R - 1 > 256) return false;
+  const int bh_eff = bh < d->H ? bh : d->H;
+  if (bh_eff * d->W * 10 < GEMM_BM * 7) return false;                        // at least 70 % of the MMA rows are pixels
+  return cin <= max_c && cout <= max_c * 4;
+}
+static inline PixelBox halo_box(const b200_conv_desc* d) {
+  const int wh = d->W + d->S - 1;
+  int bh = GEMM_BM / wh;
+  if (bh > d->H) bh = d->H;
+  return PixelBox{wh, bh, 1, 1, (d->H + bh - 1) / bh, d->N};
+}
+
 // fprop (mode 0) and dgrad (mode 1) of one pixel grid / tap set
 static inline PixelBox fprop_box(const b200_conv_desc* d, const ConvGeom& g) {
   const bool flat = is_flat(d);
   const int Wq = flat ? (int)g.M : g.Wo, Hq = flat ? 1 : g.Ho, Nq = flat ? 1 : d->N;
+  if (halo_conv_ok(d, g, d->C, d->K)) return halo_box(d);
   return choose_pixel_box(Wq, Hq, Nq, GEMM_BM, 1, d->stride);
+}
+
+template <int MODE>
+static int launch_conv_halo(int bn, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to,
+                            const ConvParams& P, const HaloParams& HP, cudaStream_t st) {
+  const int ctas = num_sms();
+  if (bn == 256) return launch_conv_halo_cfg<256, 4, MODE, 2>(ta, tb, to, P, HP, ctas, st);
+  if (bn == 128) return launch_conv_halo_cfg<128, 4, MODE, 3>(ta, tb, to, P, HP, ctas, st);
+  return launch_conv_halo_cfg<64, 8, MODE, 3>(ta, tb, to, P, HP, ctas, st);
 }
 
 static int32_t implicit_fprop(const b200_conv_desc* d, const ConvGeom& g, const void* x, const void* w, void* y,
@@ -265,13 +299,20 @@ static int32_t implicit_fprop(const b200_conv_desc* d, const ConvGeom& g, const 
   P.ncols = d->K; P.out_fp32 = 0; P.accumulate = 0;
   P.vec_ok = (reinterpret_cast<uintptr_t>(y) & 15) == 0 && d->K % 8 == 0;
   CUtensorMap ta, tb;
+  const bool halo = halo_conv_ok(d, g, d->C, d->K);
+  HaloParams HP{};
+  if (halo) {
+    HP.wh = b.bw; HP.rows = (b.bh + d->R - 1) * b.bw; HP.org_w = -d->pad; HP.org_h = -d->pad;
+    for (int r = 0; r < d->R; ++r)
+      for (int s2 = 0; s2 < d->S; ++s2) HP.toff[r * d->S + s2] = r * b.bw + s2;
+  }
   int rc = flat ? make_tmap_bf16_nhwc(&ta, x, 1, 1, (int)g.M, d->C, b.bw, b.bh, b.bn, 1)
-                : make_tmap_bf16_nhwc(&ta, x, d->N, d->H, d->W, d->C, b.bw, b.bh, b.bn, d->stride);
+                : make_tmap_bf16_nhwc(&ta, x, d->N, d->H, d->W, d->C, b.bw, halo ? b.bh + d->R - 1 : b.bh, b.bn, d->stride);
   if (rc) return fail(B200_CUDA_ERROR, "conv_fprop: activation tensor map failed (%d)", rc);
   const int bn = pick_bn(d, g, d->K);
   const long long tiles = (long long)b.tiles_w * b.tiles_h * b.tiles_n;
   P.n_tiles = (d->K + bn - 1) / bn;
-  P.pair_mode = pair_mode_for(d->R * d->S * (d->C / 64));
+  P.pair_mode = halo ? 0 : pair_mode_for(d->R * d->S * (d->C / 64));
   P.total_pairs = pair_items(bn, tiles, P.n_tiles, stats != nullptr, P.pair_mode);
   rc = make_tmap_bf16_2d(&tb, w, g.RSC, d->K, g.ldw, 64, (P.total_pairs > 0 && P.pair_mode == 2) ? bn / 2 : bn);
   if (rc) return fail(B200_CUDA_ERROR, "conv_fprop: weight tensor map failed (%d)", rc);
@@ -289,7 +330,7 @@ static int32_t implicit_fprop(const b200_conv_desc* d, const ConvGeom& g, const 
   if (rc) return fail(B200_CUDA_ERROR, "conv_fprop: output tensor map failed (%d)", rc);
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   timing_begin(e0, e1, st);
-  rc = launch_conv_mode<MODE_FPROP>(bn, ta, tb, to, P, st);
+  rc = halo ? launch_conv_halo<MODE_FPROP>(bn, ta, tb, to, P, HP, st) : launch_conv_mode<MODE_FPROP>(bn, ta, tb, to, P, st);
   timing_end(e0, e1, 2.0 * g.M * d->K * g.RSC, st);
   if (rc) return fail(B200_CUDA_ERROR, "conv_fprop: launch failed (%d)", rc);
   return B200_OK;
@@ -347,7 +388,16 @@ static int32_t implicit_dgrad(const b200_conv_desc* d, const ConvGeom& g, const 
       }
     }
     if (P.ntaps == 0 && (accumulate || (classes > 1 && tma_out))) continue;  // nothing to add / already cleared
-    const PixelBox b = choose_pixel_box(Wq, Hq, Nq, GEMM_BM, 1, 1);
+    // halo-resident variant: dgrad of a "same" stride-1 convolution is again one (roles of C and K swapped)
+    const bool halo = classes == 1 && tma_out && halo_conv_ok(d, g, d->K, d->C);
+    HaloParams HP{};
+    const PixelBox b = halo ? halo_box(d) : choose_pixel_box(Wq, Hq, Nq, GEMM_BM, 1, 1);
+    if (halo) {
+      int mw = 1 << 30, mh = 1 << 30;
+      for (int t = 0; t < P.ntaps; ++t) { if (P.taps[t].dw < mw) mw = P.taps[t].dw; if (P.taps[t].dh < mh) mh = P.taps[t].dh; }
+      HP.wh = b.bw; HP.rows = (b.bh + d->R - 1) * b.bw; HP.org_w = mw; HP.org_h = mh;
+      for (int t = 0; t < P.ntaps; ++t) HP.toff[t] = (P.taps[t].dh - mh) * b.bw + (P.taps[t].dw - mw);
+    }
     P.bw = b.bw; P.bh = b.bh; P.bn = b.bn; P.tiles_w = b.tiles_w; P.tiles_h = b.tiles_h; P.tiles_n = b.tiles_n;
     P.a_mul = 1;
     P.cchunks = d->K / 64;
@@ -358,14 +408,14 @@ static int32_t implicit_dgrad(const b200_conv_desc* d, const ConvGeom& g, const 
     P.vec_ok = (reinterpret_cast<uintptr_t>(dx) & 15) == 0 && d->C % 8 == 0;
     CUtensorMap ta;
     rc = flat ? make_tmap_bf16_nhwc(&ta, dy, 1, 1, (int)g.M, d->K, b.bw, b.bh, b.bn, 1)
-              : make_tmap_bf16_nhwc(&ta, dy, d->N, g.Ho, g.Wo, d->K, b.bw, b.bh, b.bn, 1);
+              : make_tmap_bf16_nhwc(&ta, dy, d->N, g.Ho, g.Wo, d->K, b.bw, halo ? b.bh + d->R - 1 : b.bh, b.bn, 1);
     if (rc) return fail(B200_CUDA_ERROR, "conv_dgrad: gradient tensor map failed (%d)", rc);
     const long long tiles = (long long)b.tiles_w * b.tiles_h * b.tiles_n;
     P.n_tiles = (d->C + bn - 1) / bn;
     P.m_tiles = 1;
     if (tiles * P.n_tiles > 0x7fffffffLL) return fail(B200_UNSUPPORTED, "conv_dgrad: too many tiles");
     P.total_tiles = (int)(tiles * P.n_tiles);
-    P.pair_mode = pair_mode_for(P.ntaps * P.cchunks);
+    P.pair_mode = halo ? 0 : pair_mode_for(P.ntaps * P.cchunks);
     P.total_pairs = pair_items(bn, tiles, P.n_tiles, false, P.pair_mode);
     CUtensorMap to;
     // bf16 outputs leave through TMA stores (TMA reduce-add when accumulating); for a parity class of a stride-2
@@ -375,7 +425,7 @@ static int32_t implicit_dgrad(const b200_conv_desc* d, const ConvGeom& g, const 
     if (rc) return fail(B200_CUDA_ERROR, "conv_dgrad: output tensor map failed (%d)", rc);
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     timing_begin(e0, e1, st);
-    rc = launch_conv_mode<MODE_DGRAD>(bn, ta, tb, to, P, st);
+    rc = halo ? launch_conv_halo<MODE_DGRAD>(bn, ta, tb, to, P, HP, st) : launch_conv_mode<MODE_DGRAD>(bn, ta, tb, to, P, st);
     timing_end(e0, e1, 2.0 * Wq * Hq * Nq * (double)d->C * d->K * P.ntaps, st);
     if (rc) return fail(B200_CUDA_ERROR, "conv_dgrad: launch failed (%d)", rc);
   }

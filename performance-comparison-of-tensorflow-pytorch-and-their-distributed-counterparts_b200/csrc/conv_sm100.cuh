@@ -39,6 +39,14 @@ constexpr int CONV_STATS_RED_BYTES = 2 * 128 * 4;  // epilogue: per-group broadc
 // the tcgen05.ld / shared-memory latencies behind each other.
 constexpr int CONV_THREADS = 320;
 constexpr int CONV_EPI_WARPS = 8;
+// 64-column tiles have a single 64-channel column group: instead of leaving one epilogue group idle, the two groups
+// take ALTERNATE tiles (group g drains accumulator buffer g), so an accumulator is released by four warps, not eight.
+template <int BN, int CG>
+__host__ __device__ constexpr bool conv_epi_alternates() { return BN == 64 && CG == 1; }
+template <int BN, int CG>
+__host__ __device__ constexpr int conv_tmem_empty_arrivals() {
+  return CG == 2 ? 2 * CONV_EPI_WARPS : (conv_epi_alternates<BN, CG>() ? CONV_EPI_WARPS / 2 : CONV_EPI_WARPS);
+}
 
 struct ConvTap {
   int dw, dh;  // shift of the activation box (input-pixel units) for this tap
@@ -131,6 +139,285 @@ __device__ __forceinline__ ConvTile conv_decode_tile(const ConvParams& P, int ti
   return t;
 }
 
+// The epilogue warps' whole job, shared by the convolution kernels: for every tile of this CTA's walk, drain the
+// accumulator (TMEM -> registers), apply the affine / residual / ReLU epilogue if asked, round to bf16, stage the tile
+// in 128B-swizzled shared memory and hand it to the TMA unit (plain store or reduce-add), accumulate the fused
+// BatchNorm column sums, release the accumulator; at the end write this CTA's row of partial statistics.
+template <int BN, int MODE, int CG, int NSTG>
+__device__ __forceinline__ void conv_epilogue_warps(const CUtensorMap& tmO, const ConvParams& P, uint8_t* smStage,
+                                                    float* smRedBase, uint64_t* tmem_full, uint64_t* tmem_empty,
+                                                    uint32_t tmem_base, int warp, int lane, int rank, int walk_id,
+                                                    int walk_n, int walk_total) {
+  auto tile_of = [&](int w, int r) -> int {
+    if (CG == 1) return w;
+    return (w % P.n_tiles) + P.n_tiles * (2 * (w / P.n_tiles) + r);
+  };
+  // ------------------------------------------------------------ epilogue warps (two groups of four)
+  const int q = warp & 3;
+  const int l = q * 32 + lane;  // accumulator row
+  const int eg = (warp - 2) >> 2;              // epilogue group 0 / 1
+  const int bar_id = 1 + eg;                   // named barrier of the group (128 threads)
+  float* smRed = smRedBase + eg * 128;
+  uint32_t it = 0;
+  uint32_t stage_ctr = 0;                      // which of the group's two staging tiles comes next
+  // fused BatchNorm statistics: this thread's running column sums over ALL tiles of this CTA (the launcher makes
+  // gridDim a multiple of n_tiles, so a CTA only ever sees one output-column tile); slot gi = column group eg + 2*gi
+  constexpr bool ALT = conv_epi_alternates<BN, CG>();
+  constexpr int GPG = (BN / 64 + 1) / 2;       // column groups per epilogue group
+  float st_acc[GPG][4];
+#pragma unroll
+  for (int g = 0; g < GPG; ++g) { st_acc[g][0] = 0.f; st_acc[g][1] = 0.f; st_acc[g][2] = 0.f; st_acc[g][3] = 0.f; }
+  for (int w = walk_id; w < walk_total; w += walk_n, ++it)
+  for (int half = 0; half < (CG == 3 ? 2 : 1); ++half) {      // CG == 3: the item's two pixel tiles, one after the other
+    const int tile = tile_of(w, CG == 3 ? half : rank);
+    const ConvTile T = conv_decode_tile<BN, MODE>(P, tile);
+    const uint32_t buf = CG == 3 ? (uint32_t)half : (it & 1), use = CG == 3 ? it : (it >> 1);
+    if (ALT && buf != static_cast<uint32_t>(eg)) continue;      // the other group's tile
+    const bool have_work = T.kb_end > T.kb_begin;
+    mbar_wait(&tmem_full[buf], use & 1);
+    tc_fence_after();
+    bool row_ok;
+    long long row_off;
+    if (MODE != MODE_WGRAD) {
+      const int iw = l % P.bw;
+      const int t = l / P.bw;
+      const int ih = t % P.bh;
+      const int in = t / P.bh;
+      const int ow = (T.q0 + iw) * P.o_mul + P.o_off_w;
+      const int oh = (T.p0 + ih) * P.o_mul + P.o_off_h;
+      const int on = T.i0 + in;
+      row_ok = in < P.bn && ow < P.Wout && oh < P.Hout && on < P.Nout;
+      row_off = ((static_cast<long long>(on) * P.Hout + oh) * P.Wout + ow) * P.ldo;
+    } else {
+      row_ok = (T.m0 + l) < P.mrows;
+      row_off = static_cast<long long>(T.split) * P.split_stride + static_cast<long long>(T.m0 + l) * P.ldo;
+    }
+    if (MODE != MODE_WGRAD && P.tma_store) {
+      // ---- TMA-store epilogue: TMEM -> registers -> bf16 -> 128B-swizzled smem tile [128 px][64 ch] -> one bulk
+      // tensor store per 64-channel group (full 128-byte lines, bounds clipped by the TMA unit).  Two staging
+      // tiles alternate so the store of group g overlaps the TMEM reads / packing of group g+1.
+      const bool elected = (((warp - 2) & 3) == 0 && lane == 0);
+#pragma unroll
+      for (int gi = 0; gi < GPG; ++gi) {
+        const int g = ALT ? gi : eg + 2 * gi;
+        if (g >= BN / 64 || T.n0 + g * 64 >= P.ncols) break;     // uniform across the group
+        uint8_t* stg = smStage + (eg * NSTG + (NSTG == 2 ? (stage_ctr & 1u) : 0u)) * CONV_STAGING_TILE;
+        if (elected) tma_store_wait_read<NSTG - 1>();   // the store that last used this tile has finished reading it
+        const bool affine = MODE == MODE_FPROP && P.ep_scale != nullptr;
+        if (affine) {   // this group's 64 per-channel scales and shifts -> smem (read back as broadcasts)
+          const int col = T.n0 + g * 64 + (l & 63);
+          smRed[l] = l < 64 ? P.ep_scale[col] : P.ep_shift[col];
+        }
+        asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
+        // residual (eval-mode block output): this thread's 64 channels of its pixel, issued before the TMEM reads
+        uint4 resv[8];
+        const bool has_res = affine && P.ep_res != nullptr;
+        if (has_res && row_ok) {
+          const uint4* rp = reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(P.ep_res) +
+                                                           row_off + T.n0 + g * 64);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) resv[j] = rp[j];
+        }
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          uint32_t r[32];
+          if (have_work) {
+            tmem_ld_32x32b_x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * BN +
+                                   static_cast<uint32_t>(g * 64 + h * 32), r);
+            tmem_ld_wait();
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) r[j] = 0u;
+          }
+          if (affine) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              float v = fmaf(__uint_as_float(r[j]), smRed[h * 32 + j], smRed[64 + h * 32 + j]);
+              if (has_res && row_ok) {
+                const __nv_bfloat16* rb = reinterpret_cast<const __nv_bfloat16*>(&resv[h * 4 + (j >> 3)]);
+                v += __bfloat162float(rb[j & 7]);
+              }
+              if (P.ep_relu) v = fmaxf(v, 0.f);
+              r[j] = __float_as_uint(v);
+            }
+          }
+          uint8_t* rowp = stg + l * 128;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            uint4 v;
+            v.x = pack_bf16x2(__uint_as_float(r[8 * j + 0]), __uint_as_float(r[8 * j + 1]));
+            v.y = pack_bf16x2(__uint_as_float(r[8 * j + 2]), __uint_as_float(r[8 * j + 3]));
+            v.z = pack_bf16x2(__uint_as_float(r[8 * j + 4]), __uint_as_float(r[8 * j + 5]));
+            v.w = pack_bf16x2(__uint_as_float(r[8 * j + 6]), __uint_as_float(r[8 * j + 7]));
+            if (MODE == MODE_FPROP && !row_ok) v = make_uint4(0u, 0u, 0u, 0u);   // keep the fused statistics clean
+            const int chunk = (h * 4 + j) ^ (l & 7);
+            *reinterpret_cast<uint4*>(rowp + chunk * 16) = v;
+          }
+        }
+        fence_proxy_async_smem();
+        asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
+        if (elected) {
+          // strided outputs (the parity classes of a stride-2 dgrad): the output map walks every o_mul-th pixel
+          const int sw = T.q0 * P.o_mul + P.o_off_w, sh = T.p0 * P.o_mul + P.o_off_h;
+          if (P.accumulate) tma_reduce_add_4d(&tmO, stg, T.n0 + g * 64, sw, sh, T.i0);
+          else tma_store_4d(&tmO, stg, T.n0 + g * 64, sw, sh, T.i0);
+          tma_store_commit();
+        }
+        if (MODE == MODE_FPROP && P.stats != nullptr) {
+          // Fused BatchNorm statistics: column sums of the bf16 tile that was just staged.  Thread (warp q, lane)
+          // owns columns 2*lane, 2*lane+1 over rows 32q..32q+31 (one conflict-free 4-byte smem read per row) and
+          // keeps the sums in registers until the CTA has finished all of its tiles.
+#pragma unroll 8
+          for (int i = 0; i < 32; ++i) {
+            const int row = q * 32 + i;
+            const uint32_t w = *reinterpret_cast<const uint32_t*>(stg + row * 128 + (((lane >> 2) ^ (row & 7)) << 4) +
+                                                                   ((lane & 3) << 2));
+            const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w));
+            st_acc[gi][0] += f.x; st_acc[gi][1] = fmaf(f.x, f.x, st_acc[gi][1]);
+            st_acc[gi][2] += f.y; st_acc[gi][3] = fmaf(f.y, f.y, st_acc[gi][3]);
+          }
+        }
+        ++stage_ctr;
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {
+        if (CG == 2) mbar_arrive_leader(&tmem_empty[buf]);
+        else mbar_arrive(&tmem_empty[buf]);
+      }
+      continue;
+    }
+#pragma unroll 1
+    for (int c = ALT ? 0 : eg; c < BN / 32; c += ALT ? 1 : 2) {   // 32-column chunks alternate between the two epilogue groups
+      uint32_t r[32];
+      if (have_work) {
+        tmem_ld_32x32b_x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * BN + static_cast<uint32_t>(c * 32), r);
+        tmem_ld_wait();
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) r[j] = 0u;
+      }
+      const int col0 = T.n0 + c * 32;
+      if (!row_ok || col0 >= P.ncols) continue;
+      if (P.out_fp32) {
+        float* p = reinterpret_cast<float*>(P.out) + row_off + col0;
+        if (P.vec_ok && col0 + 32 <= P.ncols) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            float4 v = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]),
+                                   __uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3]));
+            if (P.accumulate) {
+              float4 o = reinterpret_cast<float4*>(p)[j];
+              v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w;
+            }
+            reinterpret_cast<float4*>(p)[j] = v;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (col0 + j < P.ncols) p[j] = (P.accumulate ? p[j] : 0.f) + __uint_as_float(r[j]);
+        }
+      } else {
+        __nv_bfloat16* p = reinterpret_cast<__nv_bfloat16*>(P.out) + row_off + col0;
+        if (P.vec_ok && col0 + 32 <= P.ncols) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            float f[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(r[8 * j + e]);
+            if (P.accumulate) {
+              uint4 o = reinterpret_cast<uint4*>(p)[j];
+              const __nv_bfloat162* ob = reinterpret_cast<const __nv_bfloat162*>(&o);
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                float2 t2 = __bfloat1622float2(ob[e]);
+                f[2 * e] += t2.x;
+                f[2 * e + 1] += t2.y;
+              }
+            }
+            uint4 v;
+            v.x = pack_bf16x2(f[0], f[1]);
+            v.y = pack_bf16x2(f[2], f[3]);
+            v.z = pack_bf16x2(f[4], f[5]);
+            v.w = pack_bf16x2(f[6], f[7]);
+            reinterpret_cast<uint4*>(p)[j] = v;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (col0 + j < P.ncols) {
+              float f = __uint_as_float(r[j]);
+              if (P.accumulate) f += __bfloat162float(p[j]);
+              p[j] = __float2bfloat16_rn(f);
+            }
+        }
+      }
+    }
+    // this warp has finished reading the accumulator: hand it back to the MMA issuer
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0) {
+      if (CG == 2) mbar_arrive_leader(&tmem_empty[buf]);
+      else mbar_arrive(&tmem_empty[buf]);
+    }
+  }
+  if (MODE != MODE_WGRAD && P.tma_store && ((warp - 2) & 3) == 0 && lane == 0) tma_store_wait<0>();  // smem must outlive the stores
+  if (MODE == MODE_FPROP && P.tma_store && P.stats != nullptr) {
+    // one row of partial statistics per CTA: warps 1..3 of a group hand their sums to warp 0 through the group's
+    // staging tile (idle now: its last store has completed)
+    float* smFin = reinterpret_cast<float*>(smStage + eg * NSTG * CONV_STAGING_TILE);
+    const int n0 = (blockIdx.x % P.n_tiles) * BN;
+    if constexpr (ALT) {
+      // both groups hold sums of the same 64 columns (over alternate tiles): the warps park theirs in their own group's
+      // staging tile, the eight meet, one warp adds them up in a fixed order
+      asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
+      if (n0 < P.ncols) {
+        {
+          float* r = smFin + (q * 64 + 2 * lane) * 2;
+          r[0] = st_acc[0][0]; r[1] = st_acc[0][1]; r[2] = st_acc[0][2]; r[3] = st_acc[0][3];
+        }
+        asm volatile("bar.sync 3, 256;" ::: "memory");
+        if (warp == 2) {
+          float a0 = 0.f, a1 = 0.f, b0 = 0.f, b1 = 0.f;
+#pragma unroll
+          for (int w2 = 0; w2 < 8; ++w2) {
+            const float* r = reinterpret_cast<const float*>(smStage + (w2 >> 2) * NSTG * CONV_STAGING_TILE) +
+                             ((w2 & 3) * 64 + 2 * lane) * 2;
+            a0 += r[0]; a1 += r[1]; b0 += r[2]; b1 += r[3];
+          }
+          float* dst = P.stats + (static_cast<long long>(blockIdx.x / P.n_tiles) * 2) * P.ncols + n0 + 2 * lane;
+          *reinterpret_cast<float2*>(dst) = make_float2(a0, b0);
+          *reinterpret_cast<float2*>(dst + P.ncols) = make_float2(a1, b1);
+        }
+      }
+      return;
+    }
+#pragma unroll
+    for (int gi = 0; gi < GPG; ++gi) {
+      const int g = eg + 2 * gi;
+      if (g >= BN / 64 || n0 + g * 64 >= P.ncols) break;
+      asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
+      if (q != 0) {
+        float* r = smFin + ((q - 1) * 64 + 2 * lane) * 2;
+        r[0] = st_acc[gi][0]; r[1] = st_acc[gi][1]; r[2] = st_acc[gi][2]; r[3] = st_acc[gi][3];
+      }
+      asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
+      if (q == 0) {
+        float a0 = st_acc[gi][0], a1 = st_acc[gi][1], b0 = st_acc[gi][2], b1 = st_acc[gi][3];
+#pragma unroll
+        for (int w2 = 0; w2 < 3; ++w2) {
+          const float* r = smFin + (w2 * 64 + 2 * lane) * 2;
+          a0 += r[0]; a1 += r[1]; b0 += r[2]; b1 += r[3];
+        }
+        // row = blockIdx.x / n_tiles: the n_tiles CTAs of a row cover the column tiles exactly once
+        float* dst = P.stats + (static_cast<long long>(blockIdx.x / P.n_tiles) * 2) * P.ncols + n0 + g * 64 + 2 * lane;
+        *reinterpret_cast<float2*>(dst) = make_float2(a0, b0);
+        *reinterpret_cast<float2*>(dst + P.ncols) = make_float2(a1, b1);
+      }
+    }
+  }
+}
+
 // CG = 2 (fprop / dgrad, BN = 256): the CTA PAIR of a cluster shares one M = 256 MMA (tcgen05 cta_group::2).  Each
 // CTA keeps its own pixel tile (A, accumulator, epilogue) but loads only HALF of the B tile -- the leader's MMA reads
 // both halves -- so a k-block costs 16 + 16 KB of L2->SM traffic per CTA instead of 16 + 32 KB: the 128x256 tile was
@@ -194,7 +481,7 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 #pragma unroll
     for (int b = 0; b < 2; ++b) {
       mbar_init(&tmem_full[b], 1);
-      mbar_init(&tmem_empty[b], CG == 2 ? 2 * CONV_EPI_WARPS : CONV_EPI_WARPS);   // one arrive per epilogue warp (of both CTAs of a pair)
+      mbar_init(&tmem_empty[b], conv_tmem_empty_arrivals<BN, CG>());   // one arrive per epilogue warp (of both CTAs of a pair)
     }
     mbar_fence_init();
   }
@@ -216,7 +503,7 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer
-    if (lane == 0) {
+    if (elect_one()) {
       int stage = 0;          // ring position and phase run continuously across tiles
       uint32_t phase = 0;
       for (int w = walk_id; w < walk_total; w += walk_n) {
@@ -326,7 +613,47 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     __syncwarp();
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer
-    if (lane == 0 && rank == 0) {
+    if constexpr (MODE != MODE_WGRAD && CG == 1) {
+      // fprop / dgrad, one CTA per tile.  tools/umma_rate_probe.cu: the tensor pipe takes 128 * N / 256 cycles per MMA
+      // only for N = 256 (62 cycles at N = 64, 75 at N = 128) and buffers barely two MMAs ahead of the issuing
+      // thread, so whatever that thread does between k-blocks beyond ~2 MMA times is added to the tile.  Hence: the
+      // ring is walked with the stage index UNROLLED (barrier addresses and descriptors are immediates off one base),
+      // the reduction length is the same for every tile (no tile decode here) and the tile boundary is a counter.
+      if (elect_one()) {
+        constexpr uint32_t idesc = umma_idesc_bf16(GEMM_BM, BN, false, MODE != MODE_FPROP);
+        const int nkb = P.ntaps * P.cchunks;
+        int tiles_left = walk_id < walk_total ? (walk_total - walk_id + walk_n - 1) / walk_n : 0;
+        const uint64_t a_desc0 = umma_smem_desc(smem_u32(smA), 16, 1024);
+        const uint64_t b_desc0 = MODE == MODE_FPROP ? umma_smem_desc(smem_u32(smB), 16, 1024) : umma_smem_desc(smem_u32(smB), 8192, 1024);
+        uint32_t phase = 0, it = 0;
+        int kb = 0;
+        uint32_t d_tmem = tmem_base;
+        if (tiles_left > 0) {
+          mbar_wait(&tmem_empty[0], 1);
+          tc_fence_after();
+        }
+        while (tiles_left > 0) {
+#pragma unroll
+          for (int s = 0; s < STAGES; ++s) {
+            mbar_wait(&full[s], phase);
+            tc_fence_after();
+            umma_f16_x4(d_tmem, a_desc0 + static_cast<uint64_t>(s * (A_BYTES >> 4)), b_desc0 + static_cast<uint64_t>(s * (B_BYTES >> 4)),
+                        2u, MODE == MODE_FPROP ? 2u : 128u, idesc, kb ? 1u : 0u);
+            umma_commit(&empty[s]);
+            if (++kb == nkb) {
+              umma_commit(&tmem_full[it & 1]);
+              kb = 0;
+              ++it;
+              if (--tiles_left == 0) break;
+              mbar_wait(&tmem_empty[it & 1], ((it >> 1) & 1) ^ 1);   // epilogue has drained this accumulator
+              tc_fence_after();
+              d_tmem = tmem_base + (it & 1) * BN;
+            }
+          }
+          phase ^= 1;
+        }
+      }
+    } else if (rank == 0 && elect_one()) {
       constexpr uint32_t idesc = umma_idesc_bf16(GEMM_BM * (CG == 2 ? 2 : 1), BN, MODE == MODE_WGRAD, MODE != MODE_FPROP);
       int stage = 0;
       uint32_t phase = 0;
@@ -347,7 +674,12 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           tc_fence_after();
           const uint32_t a_addr = smem_u32(smA + s * A_BYTES);
           const uint32_t b_addr = smem_u32(smB + s * B_BYTES);
-          if (MODE != MODE_WGRAD) {
+          if (MODE != MODE_WGRAD && CG == 1) {
+            // one asm block per k-block: four k-steps, descriptors advanced inside (see umma_f16_x4)
+            umma_f16_x4(d_tmem, umma_smem_desc(a_addr, 16, 1024),
+                        MODE == MODE_FPROP ? umma_smem_desc(b_addr, 16, 1024) : umma_smem_desc(b_addr, 8192, 1024), 2u,
+                        MODE == MODE_FPROP ? 2u : 128u, idesc, first ? 0u : 1u);
+          } else if (MODE != MODE_WGRAD) {
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
               const uint64_t adesc = umma_smem_desc(a_addr + k * 32, 16, 1024);
@@ -378,243 +710,8 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     }
     __syncwarp();
   } else {
-    // ------------------------------------------------------------ epilogue warps (two groups of four)
-    const int q = warp & 3;
-    const int l = q * 32 + lane;  // accumulator row
-    const int eg = (warp - 2) >> 2;              // epilogue group 0 / 1
-    const int bar_id = 1 + eg;                   // named barrier of the group (128 threads)
-    float* smRed = smRedBase + eg * 128;
-    uint32_t it = 0;
-    uint32_t stage_ctr = 0;                      // which of the group's two staging tiles comes next
-    // fused BatchNorm statistics: this thread's running column sums over ALL tiles of this CTA (the launcher makes
-    // gridDim a multiple of n_tiles, so a CTA only ever sees one output-column tile); slot gi = column group eg + 2*gi
-    constexpr int GPG = (BN / 64 + 1) / 2;       // column groups per epilogue group
-    float st_acc[GPG][4];
-#pragma unroll
-    for (int g = 0; g < GPG; ++g) { st_acc[g][0] = 0.f; st_acc[g][1] = 0.f; st_acc[g][2] = 0.f; st_acc[g][3] = 0.f; }
-    for (int w = walk_id; w < walk_total; w += walk_n, ++it)
-    for (int half = 0; half < (CG == 3 ? 2 : 1); ++half) {      // CG == 3: the item's two pixel tiles, one after the other
-      const int tile = tile_of(w, CG == 3 ? half : rank);
-      const ConvTile T = conv_decode_tile<BN, MODE>(P, tile);
-      const uint32_t buf = CG == 3 ? (uint32_t)half : (it & 1), use = CG == 3 ? it : (it >> 1);
-      const bool have_work = T.kb_end > T.kb_begin;
-      mbar_wait(&tmem_full[buf], use & 1);
-      tc_fence_after();
-      bool row_ok;
-      long long row_off;
-      if (MODE != MODE_WGRAD) {
-        const int iw = l % P.bw;
-        const int t = l / P.bw;
-        const int ih = t % P.bh;
-        const int in = t / P.bh;
-        const int ow = (T.q0 + iw) * P.o_mul + P.o_off_w;
-        const int oh = (T.p0 + ih) * P.o_mul + P.o_off_h;
-        const int on = T.i0 + in;
-        row_ok = in < P.bn && ow < P.Wout && oh < P.Hout && on < P.Nout;
-        row_off = ((static_cast<long long>(on) * P.Hout + oh) * P.Wout + ow) * P.ldo;
-      } else {
-        row_ok = (T.m0 + l) < P.mrows;
-        row_off = static_cast<long long>(T.split) * P.split_stride + static_cast<long long>(T.m0 + l) * P.ldo;
-      }
-      if (MODE != MODE_WGRAD && P.tma_store) {
-        // ---- TMA-store epilogue: TMEM -> registers -> bf16 -> 128B-swizzled smem tile [128 px][64 ch] -> one bulk
-        // tensor store per 64-channel group (full 128-byte lines, bounds clipped by the TMA unit).  Two staging
-        // tiles alternate so the store of group g overlaps the TMEM reads / packing of group g+1.
-        const bool elected = (((warp - 2) & 3) == 0 && lane == 0);
-#pragma unroll
-        for (int gi = 0; gi < GPG; ++gi) {
-          const int g = eg + 2 * gi;
-          if (g >= BN / 64 || T.n0 + g * 64 >= P.ncols) break;     // uniform across the group
-          uint8_t* stg = smStage + (eg * NSTG + (NSTG == 2 ? (stage_ctr & 1u) : 0u)) * CONV_STAGING_TILE;
-          if (elected) tma_store_wait_read<NSTG - 1>();   // the store that last used this tile has finished reading it
-          const bool affine = MODE == MODE_FPROP && P.ep_scale != nullptr;
-          if (affine) {   // this group's 64 per-channel scales and shifts -> smem (read back as broadcasts)
-            const int col = T.n0 + g * 64 + (l & 63);
-            smRed[l] = l < 64 ? P.ep_scale[col] : P.ep_shift[col];
-          }
-          asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
-          // residual (eval-mode block output): this thread's 64 channels of its pixel, issued before the TMEM reads
-          uint4 resv[8];
-          const bool has_res = affine && P.ep_res != nullptr;
-          if (has_res && row_ok) {
-            const uint4* rp = reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(P.ep_res) +
-                                                             row_off + T.n0 + g * 64);
-#pragma unroll
-            for (int j = 0; j < 8; ++j) resv[j] = rp[j];
-          }
-#pragma unroll
-          for (int h = 0; h < 2; ++h) {
-            uint32_t r[32];
-            if (have_work) {
-              tmem_ld_32x32b_x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * BN +
-                                     static_cast<uint32_t>(g * 64 + h * 32), r);
-              tmem_ld_wait();
-            } else {
-#pragma unroll
-              for (int j = 0; j < 32; ++j) r[j] = 0u;
-            }
-            if (affine) {
-#pragma unroll
-              for (int j = 0; j < 32; ++j) {
-                float v = fmaf(__uint_as_float(r[j]), smRed[h * 32 + j], smRed[64 + h * 32 + j]);
-                if (has_res && row_ok) {
-                  const __nv_bfloat16* rb = reinterpret_cast<const __nv_bfloat16*>(&resv[h * 4 + (j >> 3)]);
-                  v += __bfloat162float(rb[j & 7]);
-                }
-                if (P.ep_relu) v = fmaxf(v, 0.f);
-                r[j] = __float_as_uint(v);
-              }
-            }
-            uint8_t* rowp = stg + l * 128;
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              uint4 v;
-              v.x = pack_bf16x2(__uint_as_float(r[8 * j + 0]), __uint_as_float(r[8 * j + 1]));
-              v.y = pack_bf16x2(__uint_as_float(r[8 * j + 2]), __uint_as_float(r[8 * j + 3]));
-              v.z = pack_bf16x2(__uint_as_float(r[8 * j + 4]), __uint_as_float(r[8 * j + 5]));
-              v.w = pack_bf16x2(__uint_as_float(r[8 * j + 6]), __uint_as_float(r[8 * j + 7]));
-              if (MODE == MODE_FPROP && !row_ok) v = make_uint4(0u, 0u, 0u, 0u);   // keep the fused statistics clean
-              const int chunk = (h * 4 + j) ^ (l & 7);
-              *reinterpret_cast<uint4*>(rowp + chunk * 16) = v;
-            }
-          }
-          fence_proxy_async_smem();
-          asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
-          if (elected) {
-            // strided outputs (the parity classes of a stride-2 dgrad): the output map walks every o_mul-th pixel
-            const int sw = T.q0 * P.o_mul + P.o_off_w, sh = T.p0 * P.o_mul + P.o_off_h;
-            if (P.accumulate) tma_reduce_add_4d(&tmO, stg, T.n0 + g * 64, sw, sh, T.i0);
-            else tma_store_4d(&tmO, stg, T.n0 + g * 64, sw, sh, T.i0);
-            tma_store_commit();
-          }
-          if (MODE == MODE_FPROP && P.stats != nullptr) {
-            // Fused BatchNorm statistics: column sums of the bf16 tile that was just staged.  Thread (warp q, lane)
-            // owns columns 2*lane, 2*lane+1 over rows 32q..32q+31 (one conflict-free 4-byte smem read per row) and
-            // keeps the sums in registers until the CTA has finished all of its tiles.
-#pragma unroll 8
-            for (int i = 0; i < 32; ++i) {
-              const int row = q * 32 + i;
-              const uint32_t w = *reinterpret_cast<const uint32_t*>(stg + row * 128 + (((lane >> 2) ^ (row & 7)) << 4) +
-                                                                     ((lane & 3) << 2));
-              const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w));
-              st_acc[gi][0] += f.x; st_acc[gi][1] = fmaf(f.x, f.x, st_acc[gi][1]);
-              st_acc[gi][2] += f.y; st_acc[gi][3] = fmaf(f.y, f.y, st_acc[gi][3]);
-            }
-          }
-          ++stage_ctr;
-        }
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) {
-          if (CG == 2) mbar_arrive_leader(&tmem_empty[buf]);
-          else mbar_arrive(&tmem_empty[buf]);
-        }
-        continue;
-      }
-#pragma unroll 1
-      for (int c = eg; c < BN / 32; c += 2) {      // 32-column chunks alternate between the two epilogue groups
-        uint32_t r[32];
-        if (have_work) {
-          tmem_ld_32x32b_x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * BN + static_cast<uint32_t>(c * 32), r);
-          tmem_ld_wait();
-        } else {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) r[j] = 0u;
-        }
-        const int col0 = T.n0 + c * 32;
-        if (!row_ok || col0 >= P.ncols) continue;
-        if (P.out_fp32) {
-          float* p = reinterpret_cast<float*>(P.out) + row_off + col0;
-          if (P.vec_ok && col0 + 32 <= P.ncols) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              float4 v = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]),
-                                     __uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3]));
-              if (P.accumulate) {
-                float4 o = reinterpret_cast<float4*>(p)[j];
-                v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w;
-              }
-              reinterpret_cast<float4*>(p)[j] = v;
-            }
-          } else {
-#pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (col0 + j < P.ncols) p[j] = (P.accumulate ? p[j] : 0.f) + __uint_as_float(r[j]);
-          }
-        } else {
-          __nv_bfloat16* p = reinterpret_cast<__nv_bfloat16*>(P.out) + row_off + col0;
-          if (P.vec_ok && col0 + 32 <= P.ncols) {
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              float f[8];
-#pragma unroll
-              for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(r[8 * j + e]);
-              if (P.accumulate) {
-                uint4 o = reinterpret_cast<uint4*>(p)[j];
-                const __nv_bfloat162* ob = reinterpret_cast<const __nv_bfloat162*>(&o);
-#pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                  float2 t2 = __bfloat1622float2(ob[e]);
-                  f[2 * e] += t2.x;
-                  f[2 * e + 1] += t2.y;
-                }
-              }
-              uint4 v;
-              v.x = pack_bf16x2(f[0], f[1]);
-              v.y = pack_bf16x2(f[2], f[3]);
-              v.z = pack_bf16x2(f[4], f[5]);
-              v.w = pack_bf16x2(f[6], f[7]);
-              reinterpret_cast<uint4*>(p)[j] = v;
-            }
-          } else {
-#pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (col0 + j < P.ncols) {
-                float f = __uint_as_float(r[j]);
-                if (P.accumulate) f += __bfloat162float(p[j]);
-                p[j] = __float2bfloat16_rn(f);
-              }
-          }
-        }
-      }
-      // this warp has finished reading the accumulator: hand it back to the MMA issuer
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) {
-        if (CG == 2) mbar_arrive_leader(&tmem_empty[buf]);
-        else mbar_arrive(&tmem_empty[buf]);
-      }
-    }
-    if (MODE != MODE_WGRAD && P.tma_store && ((warp - 2) & 3) == 0 && lane == 0) tma_store_wait<0>();  // smem must outlive the stores
-    if (MODE == MODE_FPROP && P.tma_store && P.stats != nullptr) {
-      // one row of partial statistics per CTA: warps 1..3 of a group hand their sums to warp 0 through the group's
-      // staging tile (idle now: its last store has completed)
-      float* smFin = reinterpret_cast<float*>(smStage + eg * NSTG * CONV_STAGING_TILE);
-      const int n0 = (blockIdx.x % P.n_tiles) * BN;
-#pragma unroll
-      for (int gi = 0; gi < GPG; ++gi) {
-        const int g = eg + 2 * gi;
-        if (g >= BN / 64 || n0 + g * 64 >= P.ncols) break;
-        asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
-        if (q != 0) {
-          float* r = smFin + ((q - 1) * 64 + 2 * lane) * 2;
-          r[0] = st_acc[gi][0]; r[1] = st_acc[gi][1]; r[2] = st_acc[gi][2]; r[3] = st_acc[gi][3];
-        }
-        asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
-        if (q == 0) {
-          float a0 = st_acc[gi][0], a1 = st_acc[gi][1], b0 = st_acc[gi][2], b1 = st_acc[gi][3];
-#pragma unroll
-          for (int w2 = 0; w2 < 3; ++w2) {
-            const float* r = smFin + (w2 * 64 + 2 * lane) * 2;
-            a0 += r[0]; a1 += r[1]; b0 += r[2]; b1 += r[3];
-          }
-          // row = blockIdx.x / n_tiles: the n_tiles CTAs of a row cover the column tiles exactly once
-          float* dst = P.stats + (static_cast<long long>(blockIdx.x / P.n_tiles) * 2) * P.ncols + n0 + g * 64 + 2 * lane;
-          *reinterpret_cast<float2*>(dst) = make_float2(a0, b0);
-          *reinterpret_cast<float2*>(dst + P.ncols) = make_float2(a1, b1);
-        }
-      }
-    }
+    conv_epilogue_warps<BN, MODE, CG, NSTG>(tmO, P, smStage, smRedBase, tmem_full, tmem_empty, tmem_base, warp, lane, rank,
+                                            walk_id, walk_n, walk_total);
   }
 
   tc_fence_before();

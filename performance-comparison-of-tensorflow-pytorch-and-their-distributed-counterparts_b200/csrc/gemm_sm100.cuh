@@ -81,7 +81,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer (one lane)
-    if (lane == 0) {
+    if (elect_one()) {
       int i = 0;
       for (int kb = kb_begin; kb < kb_end; ++kb, ++i) {
         const int s = i % STAGES;
@@ -109,7 +109,7 @@ gemm_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     __syncwarp();
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer (one lane)
-    if (lane == 0) {
+    if (elect_one()) {
       constexpr uint32_t idesc = umma_idesc_bf16(GEMM_BM, BN, A_MN, B_MN);
       int i = 0;
       for (int kb = kb_begin; kb < kb_end; ++kb, ++i) {

@@ -13,6 +13,18 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
 
+// One lane of a converged warp (elect.sync): the compiler knows the guarded region runs on a single lane, so
+// instructions with uniform-register operands (tcgen05.mma, tcgen05.commit, TMA) inside it need no scalarisation loop.
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(pred));
+  return pred != 0;
+}
+
 // ---------------------------------------------------------------- mbarrier
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
@@ -136,6 +148,34 @@ __device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t adesc, uint64
       "setp.ne.b32 p, %4, 0;\n\t"
       "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
       "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+
+// Four (or `steps`) consecutive k-steps of one k-block in ONE asm block: D (+)= A_k * B_k for k = 0..3 with the
+// operand descriptors advanced by a_step / b_step (in the descriptors' 16-byte address units) between steps.
+// Measured reason: issued one by one, each tcgen05.mma costs the issuing thread ~16 uniform-datapath instructions
+// (address -> descriptor shifts and masks for both operands, plus the scalarisation loop the compiler wraps around an
+// instruction with uniform-register operands) -- ~190 cycles per MMA, more than the 32 / 64 / 128 cycles the tensor
+// core needs for N = 64 / 128 / 256, so the kernels were bound by MMA ISSUE, not by the tensor pipe.
+__device__ __forceinline__ void umma_f16_x4(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t a_step,
+                                            uint32_t b_step, uint32_t idesc, uint32_t accumulate_first) {
+  asm volatile(
+      "{\n\t.reg .pred p, q;\n\t.reg .b64 a, b, sa, sb;\n\t"
+      "setp.ne.b32 p, %6, 0;\n\t"
+      "setp.eq.b32 q, 0, 0;\n\t"
+      "cvt.u64.u32 sa, %4;\n\t"
+      "cvt.u64.u32 sb, %5;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "add.u64 a, %1, sa;\n\t"
+      "add.u64 b, %2, sb;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], a, b, %3, q;\n\t"
+      "add.u64 a, a, sa;\n\t"
+      "add.u64 b, b, sb;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], a, b, %3, q;\n\t"
+      "add.u64 a, a, sa;\n\t"
+      "add.u64 b, b, sb;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], a, b, %3, q;\n\t}" ::"r"(d_tmem),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(a_step), "r"(b_step), "r"(accumulate_first)
       : "memory");
 }
 

@@ -117,7 +117,7 @@ wgrad_sm100_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_consta
 
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer
-    if (lane == 0 && have_work) {
+    if (have_work && elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
       int tw = kb_begin % P.tiles_w, th = (kb_begin / P.tiles_w) % P.tiles_h, tn = kb_begin / (P.tiles_w * P.tiles_h);
@@ -151,7 +151,7 @@ wgrad_sm100_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_consta
     __syncwarp();
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer
-    if (lane == 0 && have_work) {
+    if (have_work && elect_one()) {
       const uint32_t idesc = umma_idesc_bf16(128, nb * 64, true, true);
       const int ksteps = P.kr >> 4;
       int stage = 0;

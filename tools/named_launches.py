@@ -71,6 +71,9 @@ for p in params:
 opt = b200net.optim.SGD(params, lr=0.001)
 ops_list += [("mt_sgd", lambda: opt.step(), 12.0 * sum(p.numel() for p in params), 0)]
 
+if os.environ.get("NAMED_ONLY"):     # e.g. NAMED_ONLY=b_fprop,b_dgrad for a source-level capture of one kernel
+    want = set(os.environ["NAMED_ONLY"].split(","))
+    ops_list = [o for o in ops_list if o[0] in want]
 for _, fn, _, _ in ops_list:      # warm-up (sizes the workspaces, sets function attributes)
     fn(); fn()
 torch.cuda.synchronize()
