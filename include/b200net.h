@@ -210,6 +210,23 @@ int32_t b200_maxpool3x3s2_fwd(const void* x, void* y, uint8_t* argmax, int32_t N
                               int32_t dtype, void* stream);
 int32_t b200_maxpool3x3s2_bwd(const void* dy, const uint8_t* argmax, void* dx, int32_t N, int32_t H, int32_t W,
                               int32_t C, int32_t dtype, void* stream);
+/* The stem's BatchNorm -> ReLU -> MaxPool2d(3, 2, 1) in one pass each way (torchvision ResNet.forward bn1 / relu /
+ * maxpool of models.resnet50, pytorch_training_inference_on_image.ipynb:389, repr :455-458): the ReLU output and the pooling
+ * input gradient -- the largest tensors of the step -- are never written.
+ *   fwd: pooled[N,Ho,Wo,C] = maxpool(relu(y * scale + shift)); argmax (one byte per pooled element) may be NULL;
+ *        scale == shift == NULL pools y as it is.
+ *   bwd: dy[N,H,W,C] = BatchNorm-backward(relu-backward(maxpool-backward(dpool))) with batch statistics mean / invstd;
+ *        dgamma / dbeta may be NULL; ws as for b200_bn_backward (b200_bn_workspace_bytes(N*H*W, C)).
+ * C % 8 == 0 (bf16) / C % 4 == 0 (fp32), 16-byte aligned tensors; B200_UNSUPPORTED otherwise.
+ * b200_maxpool3x3s2_bwd_rows: the pooling backward alone with the same indexing (b200_maxpool3x3s2_bwd uses it). */
+int32_t b200_bn_relu_maxpool_fwd(const void* y, const float* scale, const float* shift, void* pooled, uint8_t* argmax,
+                                 int32_t N, int32_t H, int32_t W, int32_t C, int32_t dtype, void* stream);
+int32_t b200_maxpool_bn_bwd(const void* dpool, const uint8_t* argmax, const void* pooled, const void* y, void* dy,
+                            int32_t N, int32_t H, int32_t W, int32_t C, int32_t dtype, const float* gamma,
+                            const float* mean, const float* invstd, float* dgamma, float* dbeta, void* ws,
+                            int64_t ws_bytes, void* stream);
+int32_t b200_maxpool3x3s2_bwd_rows(const void* dy, const uint8_t* argmax, void* dx, int32_t N, int32_t H, int32_t W,
+                                   int32_t C, int32_t dtype, void* stream);
 /* y[N,C] fp32 = mean over HW */
 int32_t b200_avgpool_fwd(const void* x, float* y, int32_t N, int32_t HW, int32_t C, int32_t dtype, void* stream);
 int32_t b200_avgpool_bwd(const float* dy, void* dx, int32_t N, int32_t HW, int32_t C, int32_t dtype, void* stream);

@@ -578,6 +578,14 @@ __global__ void bn_eval_coeffs_kernel(const float* gamma, const float* beta, con
   shift[c] = (beta ? beta[c] : 0.f) - rm[c] * sc;
 }
 
+// for stem_pool.cu (its own reduction pass feeds the same finalize kernel)
+int bn_max_partial_blocks() { return BN_MAX_BLOCKS; }
+int32_t bn_finalize_bwd_launch(const float* part, int nblk, int C, double n, const float* gamma, const float* invstd,
+                               float* dgamma, float* dbeta, float* coef, cudaStream_t st) {
+  bn_finalize_bwd_kernel<<<(C + FIN_CX - 1) / FIN_CX, dim3(FIN_CX, FIN_RY), 0, st>>>(part, nblk, C, n, gamma, invstd, dgamma, dbeta, coef);
+  return check_launch("bn_finalize_bwd");
+}
+
 }  // namespace b200
 
 using namespace b200;

@@ -194,6 +194,11 @@ extern "C" int32_t b200_maxpool3x3s2_fwd(const void* x, void* y, uint8_t* argmax
   const long long total = (long long)N * Ho * Wo * C;
   cudaStream_t st = as_stream(stream);
   const bool al = ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y) | reinterpret_cast<uintptr_t>(argmax)) & 15) == 0;
+  // vectorisable shapes: the row-per-block kernel of stem_pool.cu (32-bit indexing)
+  const int vecw = dtype == B200_BF16 ? 8 : 4;
+  if (al && (dtype == B200_F32 || dtype == B200_BF16) && C % vecw == 0 && C / vecw <= 256 && 256 % (C / vecw) == 0 &&
+      (long long)N * H < (1LL << 30))
+    return b200_bn_relu_maxpool_fwd(x, nullptr, nullptr, y, argmax, N, H, W, C, dtype, stream);
   if (dtype == B200_F32 && al && C % 4 == 0) maxpool_fwd_vec_kernel<float, 4><<<pgrid(total / 4), 256, 0, st>>>((const float*)x, (float*)y, argmax, N, H, W, C, Ho, Wo);
   else if (dtype == B200_BF16 && al && C % 8 == 0) maxpool_fwd_vec_kernel<__nv_bfloat16, 8><<<pgrid(total / 8), 256, 0, st>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, argmax, N, H, W, C, Ho, Wo);
   else if (dtype == B200_F32) maxpool_fwd_kernel<float><<<pgrid(total), 256, 0, st>>>((const float*)x, (float*)y, argmax, N, H, W, C, Ho, Wo);
@@ -209,6 +214,10 @@ extern "C" int32_t b200_maxpool3x3s2_bwd(const void* dy, const uint8_t* argmax, 
   const long long total = (long long)N * H * W * C;
   cudaStream_t st = as_stream(stream);
   const bool al = ((reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(dx) | reinterpret_cast<uintptr_t>(argmax)) & 15) == 0;
+  {
+    const int32_t rc = b200_maxpool3x3s2_bwd_rows(dy, argmax, dx, N, H, W, C, dtype, stream);   // stem_pool.cu
+    if (rc != B200_UNSUPPORTED) return rc;
+  }
   if (dtype == B200_F32 && al && C % 4 == 0) maxpool_bwd_vec_kernel<float, 4><<<pgrid(total / 4), 256, 0, st>>>((const float*)dy, argmax, (float*)dx, N, H, W, C, Ho, Wo);
   else if (dtype == B200_BF16 && al && C % 8 == 0) maxpool_bwd_vec_kernel<__nv_bfloat16, 8><<<pgrid(total / 8), 256, 0, st>>>((const __nv_bfloat16*)dy, argmax, (__nv_bfloat16*)dx, N, H, W, C, Ho, Wo);
   else if (dtype == B200_F32) maxpool_bwd_kernel<float><<<pgrid(total), 256, 0, st>>>((const float*)dy, argmax, (float*)dx, N, H, W, C, Ho, Wo);

@@ -168,7 +168,7 @@ def _bn_coeffs(bn, y, bump_nbt=True, partials=None):
 # ------------------------------------------------------------------ the backbone as one autograd node
 class _Unit(object):
     """Saved state of one conv -> BN (-> +residual) (-> ReLU) unit."""
-    __slots__ = ("conv", "bn", "x", "y", "z", "mask", "mean", "invstd", "relu", "geom", "staged")
+    __slots__ = ("conv", "bn", "x", "y", "z", "mask", "mean", "invstd", "relu", "geom", "staged", "pool")
 
 
 # L2-aware walk order (B200_L2_WALK=1; OFF by default): a bandwidth kernel that starts where its producer finished
@@ -180,9 +180,12 @@ _L2_WALK = os.environ.get("B200_L2_WALK") is not None
 _STEM_PAIRS = os.environ.get("B200_STEM_IM2COL") is None
 _FOLD_EVAL_BN = os.environ.get("B200_NO_FOLD_EVAL_BN") is None
 _FOLD_EVAL_RESIDUAL = os.environ.get("B200_FOLD_EVAL_RESIDUAL") is not None
+# stem: BatchNorm -> ReLU -> MaxPool as one pass each way (csrc/stem_pool.cu); B200_NO_FUSED_STEM_POOL=1 = separate kernels
+_FUSE_STEM_POOL = os.environ.get("B200_NO_FUSED_STEM_POOL") is None
 
 
-def _unit_forward(conv, bn, x, relu, residual, save, stage=False):
+def _unit_forward(conv, bn, x, relu, residual, save, stage=False, pool=False):
+    """conv -> BN (-> + residual) (-> ReLU); pool=True (the stem) appends MaxPool2d(3, 2, 1).  Returns (output, unit)."""
     K, R, S, stride, pad = _conv_geom(conv)
     staged = None
     if stage and stride == 2 and S <= 8 and x.shape[-1] == 4 and _STEM_PAIRS:
@@ -217,18 +220,35 @@ def _unit_forward(conv, bn, x, relu, residual, save, stage=False):
             scale, shift = ops.bn_eval_coeffs(bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.eps)
             z = ops.conv_fprop_affine(x, wp, K, R, S, stride, pad, scale, shift, relu, residual)
             if z is not None:
-                return z, None
+                return (ops.maxpool_fwd(z, False)[0] if pool else z), None
         y, partials = ops.conv_fprop(x, wp, K, R, S, stride, pad), None
     scale, shift, mean, invstd = _bn_coeffs(bn, y, bump_nbt=False, partials=partials)
+    fuse_pool = (pool and relu and residual is None and _FUSE_STEM_POOL
+                 and y.shape[-1] % (8 if y.dtype == torch.bfloat16 else 4) == 0
+                 and 256 % (y.shape[-1] // (8 if y.dtype == torch.bfloat16 else 4)) == 0)
     if not save:
+        if fuse_pool:
+            return ops.bn_relu_maxpool_fwd(y, scale, shift, False)[0], None
         # y is dead after the apply -> write in place
-        return ops.bn_apply(y, scale, shift, relu, residual, out=y, reverse=_L2_WALK), None
-    z, mask = ops.bn_apply(y, scale, shift, relu, residual, want_mask=True, reverse=_L2_WALK)
+        z = ops.bn_apply(y, scale, shift, relu, residual, out=y, reverse=_L2_WALK)
+        return (ops.maxpool_fwd(z, False)[0] if pool else z), None
     u = _Unit()
-    u.conv, u.bn, u.x, u.y, u.z, u.mean, u.invstd, u.relu = conv, bn, x, y, z, mean, invstd, relu
-    u.mask = mask
+    u.conv, u.bn, u.x, u.y, u.mean, u.invstd, u.relu = conv, bn, x, y, mean, invstd, relu
     u.staged = staged
     u.geom = (K, R, S, stride, pad)
+    u.pool = None
+    if fuse_pool:
+        # the ReLU output is never materialised: pooled values + argmax are all the backward needs besides y
+        out, idx = ops.bn_relu_maxpool_fwd(y, scale, shift, True)
+        u.z = u.mask = None
+        u.pool = ("fused", idx, out)
+        return out, u
+    z, mask = ops.bn_apply(y, scale, shift, relu, residual, want_mask=True, reverse=_L2_WALK)
+    u.z, u.mask = z, mask
+    if pool:
+        out, idx = ops.maxpool_fwd(z, True)
+        u.pool = ("plain", idx, z.shape)
+        return out, u
     return z, u
 
 
@@ -261,7 +281,7 @@ def _under(fc, m, model):
 
 class _BackboneState(object):
     """What the backbone's backward needs from its forward."""
-    __slots__ = ("unit0", "blocks", "pool_idx", "stem_shape", "final_shape", "dtype", "pool")
+    __slots__ = ("unit0", "blocks", "final_shape", "dtype", "pool")
 
 
 def _backbone_fwd(model, x, save, x_needs_grad, pool=True):
@@ -282,9 +302,8 @@ def _backbone_fwd(model, x, save, x_needs_grad, pool=True):
         xh = x.contiguous()               # already the stem's layout (b200net.utils.GpuPreprocess): nothing to convert
     else:
         xh = ops.to_nhwc(x, dtype, cp)
-    z, u0 = _unit_forward(model.conv1, model.bn1, xh, True, None, save, stage=cp is not None and not x_needs_grad)
-    stem_shape = z.shape
-    cur, pool_idx = ops.maxpool_fwd(z, save)
+    cur, u0 = _unit_forward(model.conv1, model.bn1, xh, True, None, save, stage=cp is not None and not x_needs_grad,
+                            pool=True)
     blocks = []
     for layer in (model.layer1, model.layer2, model.layer3, model.layer4):
         for blk in layer:
@@ -302,8 +321,7 @@ def _backbone_fwd(model, x, save, x_needs_grad, pool=True):
         return feat, None
     st = _BackboneState()
     st.pool = pool
-    st.unit0, st.blocks, st.pool_idx, st.stem_shape, st.final_shape, st.dtype = u0, blocks, pool_idx, stem_shape, \
-        cur.shape, dtype
+    st.unit0, st.blocks, st.final_shape, st.dtype = u0, blocks, cur.shape, dtype
     return feat, st
 
 
@@ -353,9 +371,17 @@ def _backbone_bwd(st, dfeat, params, param_needs, x_needs_grad, sink, cut=None, 
         if u.mean is None:
             raise RuntimeError("b200net: backward through BatchNorm in eval mode is not supported on this path")
         need_bn = u.bn.weight is not None and (u.bn.weight.requires_grad or u.bn.bias.requires_grad)
-        dy, dres, dgamma, dbeta = ops.bn_backward(dz, u.z if u.relu else None, u.y, u.bn.weight, u.mean, u.invstd,
-                                                  u.relu, want_dres=want_dres, want_param_grads=need_bn, mask=u.mask,
-                                                  walk=1 if _L2_WALK else 0)
+        if u.pool is not None and u.pool[0] == "fused":
+            # dz is the gradient of the POOLED output: maxpool / ReLU / BatchNorm backward in one reduction + one dx pass
+            dy, dgamma, dbeta = ops.maxpool_bn_bwd(dz, u.pool[1], u.pool[2], u.y, u.bn.weight, u.mean, u.invstd,
+                                                   want_param_grads=need_bn)
+            dres = None
+        else:
+            if u.pool is not None:
+                dz = ops.maxpool_bwd(dz, u.pool[1], u.pool[2])
+            dy, dres, dgamma, dbeta = ops.bn_backward(dz, u.z if u.relu else None, u.y, u.bn.weight, u.mean, u.invstd,
+                                                      u.relu, want_dres=want_dres, want_param_grads=need_bn,
+                                                      mask=u.mask, walk=1 if _L2_WALK else 0)
         if need_bn:
             if u.bn.bias.requires_grad:
                 emit(u.bn.bias, dbeta)
@@ -413,9 +439,8 @@ def _backbone_bwd(st, dfeat, params, param_needs, x_needs_grad, sink, cut=None, 
             dgrad(ud, dyd, out=dcur, accumulate=True)
         else:
             dcur = dgrad(u1, dy1, out=g, accumulate=True)
-    dz0 = ops.maxpool_bwd(dcur, st.pool_idx, st.stem_shape)
     u0 = st.unit0
-    dy0, _ = unit_backward(u0, dz0, want_dres=False)
+    dy0, _ = unit_backward(u0, dcur, want_dres=False)
     dx = None
     if x_needs_grad:
         dx = ops.to_nchw(dgrad(u0, dy0))[:, :u0.conv.in_channels].contiguous()

@@ -370,6 +370,35 @@ def maxpool_bwd(dy, idx, x_shape):
     return dx
 
 
+def bn_relu_maxpool_fwd(y, scale, shift, want_index):
+    """maxpool3x3s2(relu(y * scale + shift)) straight from the convolution output (b200_bn_relu_maxpool_fwd)."""
+    N, H, W, C = y.shape
+    Ho, Wo = (H - 1) // 2 + 1, (W - 1) // 2 + 1
+    pooled = torch.empty((N, Ho, Wo, C), dtype=y.dtype, device=y.device)
+    idx = torch.empty((N, Ho, Wo, C), dtype=torch.uint8, device=y.device) if want_index else None
+    check(lib.b200_bn_relu_maxpool_fwd(y.data_ptr(), scale.data_ptr(), shift.data_ptr(), pooled.data_ptr(),
+                                       idx.data_ptr() if idx is not None else None, N, H, W, C, _dt(y), _stream()),
+          "bn_relu_maxpool_fwd")
+    return pooled, idx
+
+
+def maxpool_bn_bwd(dpool, idx, pooled, y, gamma, mean, invstd, want_param_grads=True):
+    """Gradient of the convolution output y through BatchNorm (batch statistics) -> ReLU -> maxpool3x3s2, from the
+    pooled gradient (b200_maxpool_bn_bwd).  Returns (dy, dgamma, dbeta)."""
+    N, H, W, C = y.shape
+    dy = torch.empty_like(y)
+    pg = torch.empty((2, C), dtype=torch.float32, device=y.device) if want_param_grads else None
+    ws, n = _bn_ws(N * H * W, C, y.device)
+    check(lib.b200_maxpool_bn_bwd(dpool.data_ptr(), idx.data_ptr(), pooled.data_ptr(), y.data_ptr(), dy.data_ptr(),
+                                  N, H, W, C, _dt(y), gamma.data_ptr() if gamma is not None else None, mean.data_ptr(),
+                                  invstd.data_ptr(), pg[0].data_ptr() if pg is not None else None,
+                                  pg[1].data_ptr() if pg is not None else None, ws.data_ptr(), n, _stream()),
+          "maxpool_bn_bwd")
+    if pg is None:
+        return dy, None, None
+    return dy, pg[0], pg[1]
+
+
 def avgpool_fwd(x):
     N, H, W, C = x.shape
     y = torch.empty((N, C), dtype=torch.float32, device=x.device)

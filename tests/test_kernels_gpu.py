@@ -375,6 +375,52 @@ def test_maxpool_avgpool(prec, N, H, W, C):
     assert _rel(dxa, (da.double() / (H * W))[:, None, None, :].expand(N, H, W, C)) < TOL[prec]
 
 
+@pytest.mark.parametrize("prec", ["fp32", "bf16"])
+@pytest.mark.parametrize("N,H,W,C", [(4, 80, 80, 64), (3, 15, 13, 64), (2, 9, 10, 32), (5, 8, 8, 128)])
+def test_stem_bn_relu_maxpool_one_pass(prec, N, H, W, C):
+    """b200_bn_relu_maxpool_fwd / b200_maxpool_bn_bwd (the stem's BatchNorm -> ReLU -> MaxPool in one pass each way):
+    pooled values and argmax are bit-identical to the separate apply + pool kernels, the gradient matches both the
+    separate kernels and (fp32) torch's fp64 autograd through batch_norm -> relu -> max_pool2d."""
+    from b200net import ops
+    dt = DT[prec]
+    y = _rand((N, H, W, C), dt, 51, scale=2.0)
+    gamma = (torch.rand(C, device=_dev()) + 0.5)
+    beta = torch.randn(C, device=_dev()) * 0.3
+    mean, invstd, scale, shift = ops.bn_train_stats(y, gamma, beta, None, None, 0.0, 1e-5)
+    z, mask = ops.bn_apply(y, scale, shift, True, None, want_mask=True)
+    p_ref, i_ref = ops.maxpool_fwd(z, True)
+    p, i = ops.bn_relu_maxpool_fwd(y, scale, shift, True)
+    assert torch.equal(p, p_ref)
+    assert torch.equal(ops.bn_relu_maxpool_fwd(y, scale, shift, False)[0], p_ref)
+    # the arg-max names an element of the window that holds the pooled value (where different raw values round to
+    # the same output, the one-pass kernel picks the larger raw value, apply-then-pool the first by position)
+    pp = torch.arange(p.shape[1], device=_dev())[None, :, None, None]
+    qq = torch.arange(p.shape[2], device=_dev())[None, None, :, None]
+    hh, ww = 2 * pp - 1 + (i // 3).long(), 2 * qq - 1 + (i % 3).long()
+    assert bool(((hh >= 0) & (hh < H) & (ww >= 0) & (ww < W)).all())
+    nn = torch.arange(N, device=_dev())[:, None, None, None].expand_as(hh)
+    cc = torch.arange(C, device=_dev())[None, None, None, :].expand_as(hh)
+    assert torch.equal(z[nn, hh, ww, cc], p)
+    assert ((i != i_ref) & (p > 0)).float().mean().item() < (1e-4 if prec == "fp32" else 0.05)
+    dpool = _rand(tuple(p.shape), dt, 52)
+    dz = ops.maxpool_bwd(dpool, i, z.shape)
+    dy_ref, _, dg_ref, db_ref = ops.bn_backward(dz, None, y, gamma, mean, invstd, True, mask=mask)
+    dy, dg, db = ops.maxpool_bn_bwd(dpool, i, p, y, gamma, mean, invstd)
+    # the separate kernels round the pooling gradient to bf16 before the BatchNorm reduction, the fused pass does not
+    tol_pg = 1e-5 if prec == "fp32" else 5e-3
+    assert _rel(dg, dg_ref) < tol_pg and _rel(db, db_ref) < tol_pg
+    assert _rel(dy, dy_ref) < (1e-5 if prec == "fp32" else 1e-2)
+    assert ops.maxpool_bn_bwd(dpool, i, p, y, gamma, mean, invstd, want_param_grads=False)[1] is None
+    if prec == "fp32":
+        yd = y.permute(0, 3, 1, 2).double().requires_grad_(True)
+        gd, bd = gamma.double().requires_grad_(True), beta.double().requires_grad_(True)
+        out = TF.max_pool2d(torch.relu(TF.batch_norm(yd, None, None, gd, bd, True, 0.0, 1e-5)), 3, 2, 1)
+        out.backward(dpool.permute(0, 3, 1, 2).double())
+        assert _rel(p.permute(0, 3, 1, 2), out.detach()) < 1e-5
+        assert _rel(dy.permute(0, 3, 1, 2), yd.grad) < 1e-4
+        assert _rel(dg, gd.grad) < 1e-4 and _rel(db, bd.grad) < 1e-4
+
+
 # ---------------------------------------------------------------------------------------------- head
 def test_head_functions_match_torch():
     import b200net
