@@ -12,6 +12,7 @@
 namespace b200 {
 
 constexpr int BN_THREADS = 256;
+constexpr int BN_STREAM_U = 4;       // 16-byte vectors of each stream a thread of the elementwise kernels keeps in flight
 constexpr int BN_MAX_BLOCKS = 296;  // 2 x 148 SMs (each thread keeps four rows of 16-byte loads in flight)
 
 static inline int pow2_ceil(int v) {
@@ -254,7 +255,7 @@ bn_finalize_bwd_kernel(const float* __restrict__ part, int nblk, int C, double n
 
 // FIXEDC: the grid stride is a multiple of nvec, so a thread always lands on the same channel vector and keeps its
 // per-channel constants in registers (the streaming loop is then loads + FMAs + store only).
-template <typename T, int VEC, bool FIXEDC>
+template <typename T, int VEC, bool FIXEDC, int SU = 2>
 __global__ void __launch_bounds__(BN_THREADS)
 bn_apply_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __restrict__ y, uint8_t* __restrict__ mask,
                 long long nvec_total, int nvec, const float* __restrict__ scale, const float* __restrict__ shift,
@@ -272,23 +273,32 @@ bn_apply_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __restric
     for (int e = 0; e < VEC; ++e) { sc[e] = scale[c + e]; sh[e] = shift[c + e]; }
   }
   if constexpr (FIXEDC && VEC > 1) {
-    // streaming loop, two 16-byte vectors (plus residuals) in flight per thread
-    for (; i < nvec_total; i += 2 * stride) {
-      const bool has1 = i + stride < nvec_total;
-      const long long e0 = B200_IDX(i), e1 = has1 ? B200_IDX(i + stride) : 0;
-      float x0[VEC], x1[VEC], r0[VEC], r1[VEC];
-      load_vec(x + e0 * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(x0));
-      if (has1) load_vec(x + e1 * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(x1));
-      if (res) {
-        load_vec(res + e0 * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(r0));
-        if (has1) load_vec(res + e1 * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(r1));
+    // streaming loop: SU raw 16-byte vectors (plus residuals) in flight per thread, unpacked only when consumed.
+    // Measured on [409600 x 256] bf16: SU = 2 (63 registers, four blocks per SM) 85 us / 109 us with a residual;
+    // SU = 4 (93 registers, two blocks per SM) 97 us / 117 us -- for this kernel more resident threads beat more loads
+    // per thread, for the dx pass below it is the other way round.
+    for (; i < nvec_total; i += SU * stride) {
+      uint4 xr[SU], rr[SU];
+      long long ei[SU];
+      bool ok[SU];
+#pragma unroll
+      for (int u = 0; u < SU; ++u) {
+        const long long idx = i + u * stride;
+        ok[u] = idx < nvec_total;
+        ei[u] = ok[u] ? B200_IDX(idx) : 0;
       }
 #pragma unroll
-      for (int half = 0; half < 2; ++half) {
-        if (half == 1 && !has1) break;
-        float (&xv)[VEC] = half ? x1 : x0;
-        float (&rv)[VEC] = half ? r1 : r0;
-        const long long ii = half ? e1 : e0;
+      for (int u = 0; u < SU; ++u) {
+        if (!ok[u]) continue;
+        xr[u] = *reinterpret_cast<const uint4*>(x + ei[u] * VEC);
+        if (res) rr[u] = *reinterpret_cast<const uint4*>(res + ei[u] * VEC);
+      }
+#pragma unroll
+      for (int u = 0; u < SU; ++u) {
+        if (!ok[u]) continue;
+        float xv[VEC], rv[VEC];
+        unpack16(xr[u], xv);
+        if (res) unpack16(rr[u], rv);
         uint32_t m = 0;
 #pragma unroll
         for (int e = 0; e < VEC; ++e) {
@@ -297,11 +307,11 @@ bn_apply_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __restric
           if (relu) v = fmaxf(v, 0.f);
           xv[e] = v;
         }
-        store_vec(y + ii * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(xv));
+        store_vec(y + ei[u] * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(xv));
         if (mask) {
 #pragma unroll
           for (int e = 0; e < VEC; ++e) m |= (to_f(from_f<T>(xv[e])) > 0.f ? 1u : 0u) << e;
-          mask[ii] = (uint8_t)m;
+          mask[ei[u]] = (uint8_t)m;
         }
       }
     }
@@ -360,41 +370,47 @@ bn_bwd_dx_kernel(const T* __restrict__ dz, const T* __restrict__ z, const uint8_
     for (int e = 0; e < VEC; ++e) { cA[e] = coef[c + e]; cB[e] = coef[C + c + e]; cC[e] = coef[2 * C + c + e]; mu[e] = mean[c + e]; }
   }
   if constexpr (FIXEDC && VEC > 1) {
-    // streaming loop, two vectors of each input in flight per thread
-    for (; i < nvec_total; i += 2 * stride) {
-      const bool has1 = i + stride < nvec_total;
-      const long long e0 = B200_IDX(i), e1 = has1 ? B200_IDX(i + stride) : 0;
-      float g0[VEC], g1[VEC], x0[VEC], x1[VEC], z0[VEC], z1[VEC];
-      uint32_t m0 = 0xffffffffu, m1 = 0xffffffffu;
-      load_vec(dz + e0 * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(g0));
-      load_vec(x + e0 * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(x0));
-      if (DMODE == DM_Z) load_vec(z + e0 * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(z0));
-      if (DMODE == DM_MASK) m0 = mask[e0];
-      if (has1) {
-        load_vec(dz + e1 * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(g1));
-        load_vec(x + e1 * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(x1));
-        if (DMODE == DM_Z) load_vec(z + e1 * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(z1));
-        if (DMODE == DM_MASK) m1 = mask[e1];
+    // streaming loop: BN_STREAM_U raw vectors of each input in flight per thread.  With two, ~34 KB per SM were in
+    // flight against the ~45 KB that 6.5 TB/s at ~1 us of loaded latency needs (ncu: 4.0 TB/s, issue slots 75 % idle);
+    // with four the reduce + dx pair on [409600 x 256] went 245 -> 198 us.
+    for (; i < nvec_total; i += BN_STREAM_U * stride) {
+      uint4 gr[BN_STREAM_U], xr[BN_STREAM_U], zr[BN_STREAM_U];
+      uint32_t mk[BN_STREAM_U];
+      long long ei[BN_STREAM_U];
+      bool ok[BN_STREAM_U];
+#pragma unroll
+      for (int u = 0; u < BN_STREAM_U; ++u) {
+        const long long idx = i + u * stride;
+        ok[u] = idx < nvec_total;
+        ei[u] = ok[u] ? B200_IDX(idx) : 0;
       }
 #pragma unroll
-      for (int half = 0; half < 2; ++half) {
-        if (half == 1 && !has1) break;
-        float (&gv)[VEC] = half ? g1 : g0;
-        float (&xv)[VEC] = half ? x1 : x0;
-        float (&zv)[VEC] = half ? z1 : z0;
-        const uint32_t m = half ? m1 : m0;
-        const long long ii = half ? e1 : e0;
+      for (int u = 0; u < BN_STREAM_U; ++u) {
+        mk[u] = 0xffffffffu;
+        if (!ok[u]) continue;
+        gr[u] = *reinterpret_cast<const uint4*>(dz + ei[u] * VEC);
+        xr[u] = *reinterpret_cast<const uint4*>(x + ei[u] * VEC);
+        if (DMODE == DM_Z) zr[u] = *reinterpret_cast<const uint4*>(z + ei[u] * VEC);
+        if (DMODE == DM_MASK) mk[u] = mask[ei[u]];
+      }
+#pragma unroll
+      for (int u = 0; u < BN_STREAM_U; ++u) {
+        if (!ok[u]) continue;
+        float gv[VEC], xv[VEC], zv[VEC];
+        unpack16(gr[u], gv);
+        unpack16(xr[u], xv);
+        if (DMODE == DM_Z) unpack16(zr[u], zv);
 #pragma unroll
         for (int e = 0; e < VEC; ++e) {
           bool on = true;
           if (DMODE == DM_Z) on = zv[e] > 0.f;
-          if (DMODE == DM_MASK) on = (m >> e) & 1u;
+          if (DMODE == DM_MASK) on = (mk[u] >> e) & 1u;
           const float g = on ? gv[e] : 0.f;
           gv[e] = g;
           xv[e] = cA[e] * g - cC[e] - cB[e] * (xv[e] - mu[e]);
         }
-        store_vec(dx + ii * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(xv));
-        if (dres) store_vec(dres + ii * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(gv));
+        store_vec(dx + ei[u] * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(xv));
+        if (dres) store_vec(dres + ei[u] * VEC, reinterpret_cast<float(&)[VecTraits<T>::W]>(gv));
       }
     }
     return;
@@ -526,7 +542,7 @@ static int32_t bn_apply_impl(const T* x, const T* res, T* y, uint8_t* mask, long
     constexpr int V = VecTraits<T>::W;
     bool fixed;
     const int grid = ew_grid_fixed(rows * (C / V), C / V, &fixed);
-    if (fixed) bn_apply_kernel<T, V, true><<<grid, BN_THREADS, 0, st>>>(x, res, y, mask, rows * (C / V), C / V, scale, shift, relu, reverse);
+    if (fixed) bn_apply_kernel<T, V, true, 2><<<grid, BN_THREADS, 0, st>>>(x, res, y, mask, rows * (C / V), C / V, scale, shift, relu, reverse);
     else bn_apply_kernel<T, V, false><<<grid, BN_THREADS, 0, st>>>(x, res, y, mask, rows * (C / V), C / V, scale, shift, relu, reverse);
   } else {
     if (mask) return fail(B200_UNSUPPORTED, "bn_apply: the ReLU mask needs C %% %d == 0 and 16-byte aligned tensors", VecTraits<T>::W);
