@@ -132,25 +132,33 @@ sgemm_small_kernel(const float* __restrict__ A, const float* __restrict__ B, flo
   const int tx = t & 15, ty = t >> 4;
   const int m0 = blockIdx.y * 32, n0 = blockIdx.x * 32;
   float acc[2][2] = {{0.f, 0.f}, {0.f, 0.f}};
-  for (int k0 = 0; k0 < K; k0 += 32) {
+  // the next k-tile's eight global loads are in flight while the current one is multiplied (the loop used to be
+  // load -> sync -> multiply -> sync: one global-memory latency per 32 k, 82 us for the head's [256 x 2048] x [512 x 2048]^T)
+  float ra[4], rb[4];
+  auto fetch = [&](int k0) {
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       const int idx = t + j * 256;
       int m, k;
       if (!A_MN) { k = idx & 31; m = idx >> 5; } else { m = idx & 31; k = idx >> 5; }
       const int gm = m0 + m, gk = k0 + k;
-      float v = 0.f;
-      if (gm < M && gk < K) v = A_MN ? A[(long long)gk * lda + gm] : A[(long long)gm * lda + gk];
-      As[k][m] = v;
+      ra[j] = (gm < M && gk < K) ? (A_MN ? A[(long long)gk * lda + gm] : A[(long long)gm * lda + gk]) : 0.f;
       int n;
       if (!B_MN) { k = idx & 31; n = idx >> 5; } else { n = idx & 31; k = idx >> 5; }
-      const int gn = n0 + n;
-      const int gk2 = k0 + k;
-      v = 0.f;
-      if (gn < N && gk2 < K) v = B_MN ? B[(long long)gk2 * ldb + gn] : B[(long long)gn * ldb + gk2];
-      Bs[k][n] = v;
+      const int gn = n0 + n, gk2 = k0 + k;
+      rb[j] = (gn < N && gk2 < K) ? (B_MN ? B[(long long)gk2 * ldb + gn] : B[(long long)gn * ldb + gk2]) : 0.f;
+    }
+  };
+  fetch(0);
+  for (int k0 = 0; k0 < K; k0 += 32) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int idx = t + j * 256;
+      if (!A_MN) As[idx & 31][idx >> 5] = ra[j]; else As[idx >> 5][idx & 31] = ra[j];
+      if (!B_MN) Bs[idx & 31][idx >> 5] = rb[j]; else Bs[idx >> 5][idx & 31] = rb[j];
     }
     __syncthreads();
+    if (k0 + 32 < K) fetch(k0 + 32);
 #pragma unroll
     for (int kk = 0; kk < 32; ++kk) {
       const float a0 = As[kk][ty], a1 = As[kk][ty + 16];
