@@ -242,21 +242,33 @@ static inline int pick_bn(const b200_conv_desc*, const ConvGeom&, int cols) {
   return cols > 128 ? 256 : (cols > 64 ? 128 : 64);
 }
 
-// Halo-resident variant (conv_halo_sm100.cuh) for "same" RxS stride-1 convolutions: a tile is bh full image rows,
-// the taps are descriptor shifts into one halo tile per channel chunk.  Worth it where the activation boxes dominate
-// the operand traffic, i.e. narrow layers.  OFF by default: on 64->64 3x3 at 40x40 it moves less than half the
-// L2 -> SM bytes and is still slower (60.6 vs 54.2 us forward); B200_HALO_MAX_C=<max channels> turns it on.
-static inline bool halo_conv_ok(const b200_conv_desc* d, const ConvGeom& g, int cin, int cout) {
-  static const int max_c = getenv("B200_HALO_MAX_C") ? atoi(getenv("B200_HALO_MAX_C")) : 0;
-  if (max_c <= 0 || d->stride != 1 || d->R * d->S <= 1 || g.Wo != d->W || g.Ho != d->H) return false;
-  if (2 * d->pad != d->R - 1 || 2 * d->pad != d->S - 1) return false;
+// Weights-stationary variant (conv_halo_sm100.cuh): the CTA's weight tile (all taps x channel chunks) stays in shared
+// memory and only activations stream.  kind 1 = 1x1 stride-1 layers whose reduction fits the weight slots (4 k-blocks
+// at 256 output columns, 8 at 128 / 64); kind 2 = "same" 3x3 stride-1 layers with 64 -> 64 channels, whose activations
+// come as one halo tile per tile of bh full image rows and whose taps are descriptor shifts.  `cin` = reduction
+// channels, `cout` = output columns (swapped for dgrad).  B200_WS = bit mask of the kinds to use.  Default 2: measured
+// on the N = 256 / 160 px layer table, kind 2 takes 64 -> 64 3x3 at 40x40 from 53.6 / 52.6 us (fprop / dgrad) to
+// 38.8 / 37.7 us, while kind 1 LOSES on every 1x1 class (64 -> 256: 48.5 -> 58.9 us, 256 -> 1024 at 10x10: 18.7 ->
+// 21.3 us): those tiles have 1-4 k-blocks and are bound by the epilogue (fused statistics), not by operand traffic,
+// and this kernel has one staging tile per epilogue group where the shallow variant of conv_sm100_kernel has two.
+static inline int ws_kind(const b200_conv_desc* d, const ConvGeom& g, int cin, int cout) {
+  static const int mask = getenv("B200_WS") ? atoi(getenv("B200_WS")) : 2;
+  if (mask == 0 || d->stride != 1 || cin % 64 != 0 || cout % 8 != 0) return 0;
+  const int bn = pick_bn(d, g, cout);
+  const int chunks = cin / 64;
+  if (d->R == 1 && d->S == 1 && d->pad == 0) {
+    if (!(mask & 1)) return 0;
+    return chunks <= (bn == 256 ? 4 : 8) ? 1 : 0;
+  }
+  if (!(mask & 2) || d->R != 3 || d->S != 3 || d->pad != 1 || bn != 64 || chunks != 1) return 0;
+  if (g.Wo != d->W || g.Ho != d->H) return 0;
   const int wh = d->W + d->S - 1;
-  if ((d->R - 1) * wh + d->S - 1 + GEMM_BM > HALO_ROWS) return false;       // the last tap's view must stay inside the stage
+  if ((d->R - 1) * wh + d->S - 1 + GEMM_BM > HALO_ROWS) return 0;           // the last tap's view must stay inside the stage
   const int bh = GEMM_BM / wh;
-  if (bh < 1 || (bh + d->R - 1) * wh > HALO_ROWS || bh + d->R - 1 > 256) return false;
+  if (bh < 1 || (bh + d->R - 1) * wh > HALO_ROWS || bh + d->R - 1 > 256) return 0;
   const int bh_eff = bh < d->H ? bh : d->H;
-  if (bh_eff * d->W * 10 < GEMM_BM * 7) return false;                        // at least 70 % of the MMA rows are pixels
-  return cin <= max_c && cout <= max_c * 4;
+  if (bh_eff * d->W * 10 < GEMM_BM * 7) return 0;                            // at least 70 % of the MMA rows are pixels
+  return 2;
 }
 static inline PixelBox halo_box(const b200_conv_desc* d) {
   const int wh = d->W + d->S - 1;
@@ -269,17 +281,18 @@ static inline PixelBox halo_box(const b200_conv_desc* d) {
 static inline PixelBox fprop_box(const b200_conv_desc* d, const ConvGeom& g) {
   const bool flat = is_flat(d);
   const int Wq = flat ? (int)g.M : g.Wo, Hq = flat ? 1 : g.Ho, Nq = flat ? 1 : d->N;
-  if (halo_conv_ok(d, g, d->C, d->K)) return halo_box(d);
+  if (ws_kind(d, g, d->C, d->K) == 2) return halo_box(d);
   return choose_pixel_box(Wq, Hq, Nq, GEMM_BM, 1, d->stride);
 }
 
 template <int MODE>
-static int launch_conv_halo(int bn, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to,
-                            const ConvParams& P, const HaloParams& HP, cudaStream_t st) {
+static int launch_conv_ws(int kind, int bn, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to,
+                          const ConvParams& P, const HaloParams& HP, cudaStream_t st) {
   const int ctas = num_sms();
-  if (bn == 256) return launch_conv_halo_cfg<256, 4, MODE, 2>(ta, tb, to, P, HP, ctas, st);
-  if (bn == 128) return launch_conv_halo_cfg<128, 4, MODE, 3>(ta, tb, to, P, HP, ctas, st);
-  return launch_conv_halo_cfg<64, 8, MODE, 3>(ta, tb, to, P, HP, ctas, st);
+  if (kind == 2) return launch_conv_ws_cfg<64, 9, MODE, 3, HALO_ROWS, 9>(ta, tb, to, P, HP, ctas, st);
+  if (bn == 256) return launch_conv_ws_cfg<256, 4, MODE, 4, GEMM_BM, 1>(ta, tb, to, P, HP, ctas, st);
+  if (bn == 128) return launch_conv_ws_cfg<128, 8, MODE, 4, GEMM_BM, 1>(ta, tb, to, P, HP, ctas, st);
+  return launch_conv_ws_cfg<64, 8, MODE, 6, GEMM_BM, 1>(ta, tb, to, P, HP, ctas, st);
 }
 
 static int32_t implicit_fprop(const b200_conv_desc* d, const ConvGeom& g, const void* x, const void* w, void* y,
@@ -299,10 +312,12 @@ static int32_t implicit_fprop(const b200_conv_desc* d, const ConvGeom& g, const 
   P.ncols = d->K; P.out_fp32 = 0; P.accumulate = 0;
   P.vec_ok = (reinterpret_cast<uintptr_t>(y) & 15) == 0 && d->K % 8 == 0;
   CUtensorMap ta, tb;
-  const bool halo = halo_conv_ok(d, g, d->C, d->K);
+  const int ws = ws_kind(d, g, d->C, d->K);
+  const bool halo = ws == 2;
   HaloParams HP{};
+  HP.wh = b.bw; HP.rows = b.bw * b.bh * b.bn;                    // kind 1: the plain pixel box, no shifts
   if (halo) {
-    HP.wh = b.bw; HP.rows = (b.bh + d->R - 1) * b.bw; HP.org_w = -d->pad; HP.org_h = -d->pad;
+    HP.rows = (b.bh + d->R - 1) * b.bw; HP.org_w = -d->pad; HP.org_h = -d->pad;
     for (int r = 0; r < d->R; ++r)
       for (int s2 = 0; s2 < d->S; ++s2) HP.toff[r * d->S + s2] = r * b.bw + s2;
   }
@@ -312,7 +327,7 @@ static int32_t implicit_fprop(const b200_conv_desc* d, const ConvGeom& g, const 
   const int bn = pick_bn(d, g, d->K);
   const long long tiles = (long long)b.tiles_w * b.tiles_h * b.tiles_n;
   P.n_tiles = (d->K + bn - 1) / bn;
-  P.pair_mode = halo ? 0 : pair_mode_for(d->R * d->S * (d->C / 64));
+  P.pair_mode = ws ? 0 : pair_mode_for(d->R * d->S * (d->C / 64));
   P.total_pairs = pair_items(bn, tiles, P.n_tiles, stats != nullptr, P.pair_mode);
   rc = make_tmap_bf16_2d(&tb, w, g.RSC, d->K, g.ldw, 64, (P.total_pairs > 0 && P.pair_mode == 2) ? bn / 2 : bn);
   if (rc) return fail(B200_CUDA_ERROR, "conv_fprop: weight tensor map failed (%d)", rc);
@@ -330,7 +345,7 @@ static int32_t implicit_fprop(const b200_conv_desc* d, const ConvGeom& g, const 
   if (rc) return fail(B200_CUDA_ERROR, "conv_fprop: output tensor map failed (%d)", rc);
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   timing_begin(e0, e1, st);
-  rc = halo ? launch_conv_halo<MODE_FPROP>(bn, ta, tb, to, P, HP, st) : launch_conv_mode<MODE_FPROP>(bn, ta, tb, to, P, st);
+  rc = ws ? launch_conv_ws<MODE_FPROP>(ws, bn, ta, tb, to, P, HP, st) : launch_conv_mode<MODE_FPROP>(bn, ta, tb, to, P, st);
   timing_end(e0, e1, 2.0 * g.M * d->K * g.RSC, st);
   if (rc) return fail(B200_CUDA_ERROR, "conv_fprop: launch failed (%d)", rc);
   return B200_OK;
@@ -388,10 +403,13 @@ static int32_t implicit_dgrad(const b200_conv_desc* d, const ConvGeom& g, const 
       }
     }
     if (P.ntaps == 0 && (accumulate || (classes > 1 && tma_out))) continue;  // nothing to add / already cleared
-    // halo-resident variant: dgrad of a "same" stride-1 convolution is again one (roles of C and K swapped)
-    const bool halo = classes == 1 && tma_out && halo_conv_ok(d, g, d->K, d->C);
+    // weights-stationary variant: dgrad of a stride-1 convolution is again one (roles of C and K swapped)
+    const int ws = (classes == 1 && tma_out) ? ws_kind(d, g, d->K, d->C) : 0;
+    const bool halo = ws == 2;
     HaloParams HP{};
     const PixelBox b = halo ? halo_box(d) : choose_pixel_box(Wq, Hq, Nq, GEMM_BM, 1, 1);
+    HP.wh = b.bw; HP.rows = b.bw * b.bh * b.bn;
+    if (ws == 1) { HP.org_w = P.ntaps ? P.taps[0].dw : 0; HP.org_h = P.ntaps ? P.taps[0].dh : 0; }
     if (halo) {
       int mw = 1 << 30, mh = 1 << 30;
       for (int t = 0; t < P.ntaps; ++t) { if (P.taps[t].dw < mw) mw = P.taps[t].dw; if (P.taps[t].dh < mh) mh = P.taps[t].dh; }
@@ -415,7 +433,7 @@ static int32_t implicit_dgrad(const b200_conv_desc* d, const ConvGeom& g, const 
     P.m_tiles = 1;
     if (tiles * P.n_tiles > 0x7fffffffLL) return fail(B200_UNSUPPORTED, "conv_dgrad: too many tiles");
     P.total_tiles = (int)(tiles * P.n_tiles);
-    P.pair_mode = halo ? 0 : pair_mode_for(P.ntaps * P.cchunks);
+    P.pair_mode = ws ? 0 : pair_mode_for(P.ntaps * P.cchunks);
     P.total_pairs = pair_items(bn, tiles, P.n_tiles, false, P.pair_mode);
     CUtensorMap to;
     // bf16 outputs leave through TMA stores (TMA reduce-add when accumulating); for a parity class of a stride-2
@@ -425,7 +443,7 @@ static int32_t implicit_dgrad(const b200_conv_desc* d, const ConvGeom& g, const 
     if (rc) return fail(B200_CUDA_ERROR, "conv_dgrad: output tensor map failed (%d)", rc);
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     timing_begin(e0, e1, st);
-    rc = halo ? launch_conv_halo<MODE_DGRAD>(bn, ta, tb, to, P, HP, st) : launch_conv_mode<MODE_DGRAD>(bn, ta, tb, to, P, st);
+    rc = ws ? launch_conv_ws<MODE_DGRAD>(ws, bn, ta, tb, to, P, HP, st) : launch_conv_mode<MODE_DGRAD>(bn, ta, tb, to, P, st);
     timing_end(e0, e1, 2.0 * Wq * Hq * Nq * (double)d->C * d->K * P.ntaps, st);
     if (rc) return fail(B200_CUDA_ERROR, "conv_dgrad: launch failed (%d)", rc);
   }
