@@ -251,11 +251,18 @@ static inline int pick_bn(const b200_conv_desc*, const ConvGeom&, int cols) {
 // 38.8 / 37.7 us, while kind 1 LOSES on every 1x1 class (64 -> 256: 48.5 -> 58.9 us, 256 -> 1024 at 10x10: 18.7 ->
 // 21.3 us): those tiles have 1-4 k-blocks and are bound by the epilogue (fused statistics), not by operand traffic,
 // and this kernel has one staging tile per epilogue group where the shallow variant of conv_sm100_kernel has two.
-static inline int ws_kind(const b200_conv_desc* d, const ConvGeom& g, int cin, int cout) {
-  static const int mask = getenv("B200_WS") ? atoi(getenv("B200_WS")) : 2;
+// kind 3 (mask bit 2, fprop only) = "valid" 4 x 1 stride-1 layers with 64 -> 64 channels -- the row-pair
+// staged stem: a tile is the usual bw x bh pixel box, its activations ONE box of bh + R - 1 rows, a tap a shift by bw rows.
+static inline int ws_kind(const b200_conv_desc* d, const ConvGeom& g, int cin, int cout, bool dgrad = false) {
+  static const int mask = getenv("B200_WS") ? atoi(getenv("B200_WS")) : 6;
   if (mask == 0 || d->stride != 1 || cin % 64 != 0 || cout % 8 != 0) return 0;
   const int bn = pick_bn(d, g, cout);
   const int chunks = cin / 64;
+  if ((mask & 4) && !dgrad && d->S == 1 && d->R == 4 && d->pad == 0 && bn == 64 && chunks == 1) {
+    const PixelBox b = choose_pixel_box(g.Wo, g.Ho, d->N, GEMM_BM, 1, 1);
+    if (b.bn == 1 && (b.bh + d->R - 1) * b.bw <= HALO_ROWS && (d->R - 1) * b.bw + GEMM_BM <= HALO_ROWS) return 3;
+    return 0;
+  }
   if (d->R == 1 && d->S == 1 && d->pad == 0) {
     if (!(mask & 1)) return 0;
     return chunks <= (bn == 256 ? 4 : 8) ? 1 : 0;
@@ -290,6 +297,12 @@ static int launch_conv_ws(int kind, int bn, const CUtensorMap& ta, const CUtenso
                           const ConvParams& P, const HaloParams& HP, cudaStream_t st) {
   const int ctas = num_sms();
   if (kind == 2) return launch_conv_ws_cfg<64, 9, MODE, 3, HALO_ROWS, 9>(ta, tb, to, P, HP, ctas, st);
+  if (kind == 3) {
+    if constexpr (MODE == MODE_FPROP) {
+      return launch_conv_ws_cfg<64, 4, MODE, 3, HALO_ROWS, 4>(ta, tb, to, P, HP, ctas, st);
+    }
+    return 250;
+  }
   if (bn == 256) return launch_conv_ws_cfg<256, 4, MODE, 4, GEMM_BM, 1>(ta, tb, to, P, HP, ctas, st);
   if (bn == 128) return launch_conv_ws_cfg<128, 8, MODE, 4, GEMM_BM, 1>(ta, tb, to, P, HP, ctas, st);
   return launch_conv_ws_cfg<64, 8, MODE, 6, GEMM_BM, 1>(ta, tb, to, P, HP, ctas, st);
@@ -313,7 +326,7 @@ static int32_t implicit_fprop(const b200_conv_desc* d, const ConvGeom& g, const 
   P.vec_ok = (reinterpret_cast<uintptr_t>(y) & 15) == 0 && d->K % 8 == 0;
   CUtensorMap ta, tb;
   const int ws = ws_kind(d, g, d->C, d->K);
-  const bool halo = ws == 2;
+  const bool halo = ws >= 2;
   HaloParams HP{};
   HP.wh = b.bw; HP.rows = b.bw * b.bh * b.bn;                    // kind 1: the plain pixel box, no shifts
   if (halo) {
@@ -404,7 +417,7 @@ static int32_t implicit_dgrad(const b200_conv_desc* d, const ConvGeom& g, const 
     }
     if (P.ntaps == 0 && (accumulate || (classes > 1 && tma_out))) continue;  // nothing to add / already cleared
     // weights-stationary variant: dgrad of a stride-1 convolution is again one (roles of C and K swapped)
-    const int ws = (classes == 1 && tma_out) ? ws_kind(d, g, d->K, d->C) : 0;
+    const int ws = (classes == 1 && tma_out) ? ws_kind(d, g, d->K, d->C, true) : 0;
     const bool halo = ws == 2;
     HaloParams HP{};
     const PixelBox b = halo ? halo_box(d) : choose_pixel_box(Wq, Hq, Nq, GEMM_BM, 1, 1);
