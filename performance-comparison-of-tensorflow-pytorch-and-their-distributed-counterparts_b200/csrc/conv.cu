@@ -208,7 +208,7 @@ static int launch_conv_mode(int bn, const CUtensorMap& ta, const CUtensorMap& tb
     // the stages.  Measured: 64->256 1x1 forward 59.5 -> 48.3 us (0.83 of its HBM roofline), 128->512 34 -> 28 us,
     // 256->1024 22.5 -> 18.4 us, while 512->256 / 512->1024 lose 2 us with the shallow variant.
     static const int shallow_kb = getenv("B200_SHALLOW_KB") ? atoi(getenv("B200_SHALLOW_KB")) : 4;
-    const bool shallow = P.ntaps * P.cchunks <= shallow_kb;
+    const bool shallow = P.ntaps * P.cchunks <= shallow_kb || P.res_tma;   // the TMA residual needs two staging tiles
     if (bn == 256) return shallow ? launch_conv_cfg<256, 3, MODE, 1, 2>(ta, tb, to, P, ctas, st)
                                   : launch_conv_cfg<256, 4, MODE, 1, 1>(ta, tb, to, P, ctas, st);
     if (bn == 128) return shallow ? launch_conv_cfg<128, 5, MODE, 1, 2>(ta, tb, to, P, ctas, st)
@@ -353,6 +353,16 @@ static int32_t implicit_fprop(const b200_conv_desc* d, const ConvGeom& g, const 
   P.stats = stats;
   P.ep_scale = ep_scale; P.ep_shift = ep_shift; P.ep_relu = ep_relu; P.ep_res = ep_res;
   if (ep_scale && !P.tma_store) return fail(B200_UNSUPPORTED, "conv_fprop_affine: needs the TMA-store epilogue");
+  // residual of an eval-mode block output: fetched by TMA into the staging tile when every tile has all of its
+  // column groups (B200_RES_TMA=0: per-thread loads, measured LSU-bound)
+  static const bool res_tma_on = !(getenv("B200_RES_TMA") && atoi(getenv("B200_RES_TMA")) == 0);
+  P.res_tma = 0;
+  if (ep_res && res_tma_on && !ws && P.total_pairs == 0 && bn >= 128 && d->K % bn == 0 &&
+      (reinterpret_cast<uintptr_t>(ep_res) & 15) == 0) {
+    rc = make_tmap_bf16_nhwc(&P.tmR, ep_res, Nq, Hq, Wq, d->K, b.bw, b.bh, b.bn, 1);
+    if (rc) return fail(B200_CUDA_ERROR, "conv_fprop_affine: residual tensor map failed (%d)", rc);
+    P.res_tma = 1;
+  }
   if (stats && !P.tma_store) return fail(B200_UNSUPPORTED, "conv_fprop_bnstats: needs the TMA-store epilogue");
   rc = make_tmap_bf16_nhwc(&to, y, Nq, Hq, Wq, d->K, b.bw, b.bh, b.bn, 1);
   if (rc) return fail(B200_CUDA_ERROR, "conv_fprop: output tensor map failed (%d)", rc);

@@ -83,6 +83,9 @@ struct ConvParams {
   const void* ep_res;                //   optional residual tensor (same NHWC shape as the output), added before act
   float* stats;                      // fprop + tma_store: per-pixel-tile column sums [pixel tile][2][ncols] of the
                                      // bf16-rounded output (sum, sum of squares) for the BatchNorm that follows
+  int res_tma;                       // ep_res arrives by TMA into the staging tile (tmR; kernels with two staging
+                                     // tiles per epilogue group, ncols a multiple of the tile width)
+  alignas(64) CUtensorMap tmR;       // residual tensor, same geometry as the output map
 };
 
 // wgrad stage geometry: 128-column tiles use 128-pixel k-blocks, 256-column tiles 64-pixel k-blocks (same bytes)
@@ -147,7 +150,7 @@ template <int BN, int MODE, int CG, int NSTG>
 __device__ __forceinline__ void conv_epilogue_warps(const CUtensorMap& tmO, const ConvParams& P, uint8_t* smStage,
                                                     float* smRedBase, uint64_t* tmem_full, uint64_t* tmem_empty,
                                                     uint32_t tmem_base, int warp, int lane, int rank, int walk_id,
-                                                    int walk_n, int walk_total) {
+                                                    int walk_n, int walk_total, uint64_t* res_bar = nullptr) {
   auto tile_of = [&](int w, int r) -> int {
     if (CG == 1) return w;
     return (w % P.n_tiles) + P.n_tiles * (2 * (w / P.n_tiles) + r);
@@ -167,6 +170,19 @@ __device__ __forceinline__ void conv_epilogue_warps(const CUtensorMap& tmO, cons
   float st_acc[GPG][4];
 #pragma unroll
   for (int g = 0; g < GPG; ++g) { st_acc[g][0] = 0.f; st_acc[g][1] = 0.f; st_acc[g][2] = 0.f; st_acc[g][3] = 0.f; }
+  // Residual by TMA (eval-mode block outputs: conv3 + BatchNorm + add + ReLU in one kernel).  The group's work is a
+  // stream of items (tile, column group); item k uses staging tile k & 1.  The residual tile of item k + 1 is fetched
+  // into the OTHER staging tile while item k is processed (its previous store has drained by then), lands on
+  // res_bar[eg * 2 + (k & 1)], and the threads add it from the same swizzled chunks they then overwrite in place.
+  const bool res_tma = NSTG == 2 && CG == 1 && MODE == MODE_FPROP && P.res_tma && res_bar != nullptr;
+  auto res_fetch = [&](int w_item, int gi_item, uint32_t k) {      // elected thread only
+    const ConvTile Tn = conv_decode_tile<BN, MODE>(P, w_item);
+    uint8_t* dst = smStage + (eg * NSTG + (k & 1u)) * CONV_STAGING_TILE;
+    uint64_t* bar = &res_bar[eg * 2 + (k & 1u)];
+    mbar_expect_tx(bar, static_cast<uint32_t>(P.bw * P.bh * P.bn) * 128u);     // the box, not the staging tile
+    tma_load_4d(dst, &P.tmR, bar, Tn.n0 + (eg + 2 * gi_item) * 64, Tn.q0, Tn.p0, Tn.i0);
+  };
+  if (res_tma && ((warp - 2) & 3) == 0 && lane == 0 && walk_id < walk_total) res_fetch(walk_id, 0, 0u);
   for (int w = walk_id; w < walk_total; w += walk_n, ++it)
   for (int half = 0; half < (CG == 3 ? 2 : 1); ++half) {      // CG == 3: the item's two pixel tiles, one after the other
     const int tile = tile_of(w, CG == 3 ? half : rank);
@@ -202,7 +218,7 @@ __device__ __forceinline__ void conv_epilogue_warps(const CUtensorMap& tmO, cons
         const int g = ALT ? gi : eg + 2 * gi;
         if (g >= BN / 64 || T.n0 + g * 64 >= P.ncols) break;     // uniform across the group
         uint8_t* stg = smStage + (eg * NSTG + (NSTG == 2 ? (stage_ctr & 1u) : 0u)) * CONV_STAGING_TILE;
-        if (elected) tma_store_wait_read<NSTG - 1>();   // the store that last used this tile has finished reading it
+        if (elected && !res_tma) tma_store_wait_read<NSTG - 1>();   // the store that last used this tile has finished reading it
         const bool affine = MODE == MODE_FPROP && P.ep_scale != nullptr;
         if (affine) {   // this group's 64 per-channel scales and shifts -> smem (read back as broadcasts)
           const int col = T.n0 + g * 64 + (l & 63);
@@ -211,7 +227,7 @@ __device__ __forceinline__ void conv_epilogue_warps(const CUtensorMap& tmO, cons
         asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
         // residual (eval-mode block output): this thread's 64 channels of its pixel, issued before the TMEM reads
         uint4 resv[8];
-        const bool has_res = affine && P.ep_res != nullptr;
+        const bool has_res = affine && P.ep_res != nullptr && !res_tma;
         if (has_res && row_ok) {
           const uint4* rp = reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(P.ep_res) +
                                                            row_off + T.n0 + g * 64);
@@ -229,6 +245,17 @@ __device__ __forceinline__ void conv_epilogue_warps(const CUtensorMap& tmO, cons
 #pragma unroll
             for (int j = 0; j < 32; ++j) r[j] = 0u;
           }
+          uint8_t* rowp = stg + l * 128;
+          if (res_tma && h == 0) {
+            // the other staging tile's store (item k - 1) has had the TMEM read to drain: fetch the next item's
+            // residual into it, then wait for this item's
+            if (elected) {
+              tma_store_wait_read<0>();
+              if (gi + 1 < GPG) res_fetch(w, gi + 1, stage_ctr + 1u);
+              else if (w + walk_n < walk_total) res_fetch(w + walk_n, 0, stage_ctr + 1u);
+            }
+            mbar_wait(&res_bar[eg * 2 + (stage_ctr & 1u)], (stage_ctr >> 1) & 1u);
+          }
           if (affine) {
 #pragma unroll
             for (int j = 0; j < 32; ++j) {
@@ -237,11 +264,15 @@ __device__ __forceinline__ void conv_epilogue_warps(const CUtensorMap& tmO, cons
                 const __nv_bfloat16* rb = reinterpret_cast<const __nv_bfloat16*>(&resv[h * 4 + (j >> 3)]);
                 v += __bfloat162float(rb[j & 7]);
               }
+              if (res_tma) {
+                if ((j & 7) == 0) resv[j >> 3] = *reinterpret_cast<const uint4*>(rowp + (((h * 4 + (j >> 3)) ^ (l & 7)) << 4));
+                const __nv_bfloat16* rb = reinterpret_cast<const __nv_bfloat16*>(&resv[j >> 3]);
+                v += __bfloat162float(rb[j & 7]);
+              }
               if (P.ep_relu) v = fmaxf(v, 0.f);
               r[j] = __float_as_uint(v);
             }
           }
-          uint8_t* rowp = stg + l * 128;
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             uint4 v;
@@ -453,7 +484,8 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   uint64_t* empty = full + STAGES;
   uint64_t* tmem_full = empty + STAGES;    // [2]
   uint64_t* tmem_empty = tmem_full + 2;    // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  uint64_t* res_bar = tmem_empty + 2;      // [4]: residual tile landed, per epilogue group and staging tile
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_bar + 4);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -483,6 +515,8 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       mbar_init(&tmem_full[b], 1);
       mbar_init(&tmem_empty[b], conv_tmem_empty_arrivals<BN, CG>());   // one arrive per epilogue warp (of both CTAs of a pair)
     }
+#pragma unroll
+    for (int b = 0; b < 4; ++b) mbar_init(&res_bar[b], 1);
     mbar_fence_init();
   }
   if (CG == 2) cluster_sync_all();      // both CTAs' barriers exist before anything remote touches them
@@ -711,7 +745,7 @@ conv_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     __syncwarp();
   } else {
     conv_epilogue_warps<BN, MODE, CG, NSTG>(tmO, P, smStage, smRedBase, tmem_full, tmem_empty, tmem_base, warp, lane, rank,
-                                            walk_id, walk_n, walk_total);
+                                            walk_id, walk_n, walk_total, res_bar);
   }
 
   tc_fence_before();

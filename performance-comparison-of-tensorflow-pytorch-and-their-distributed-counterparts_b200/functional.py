@@ -179,7 +179,7 @@ class _Unit(object):
 _L2_WALK = os.environ.get("B200_L2_WALK") is not None
 _STEM_PAIRS = os.environ.get("B200_STEM_IM2COL") is None
 _FOLD_EVAL_BN = os.environ.get("B200_NO_FOLD_EVAL_BN") is None
-_FOLD_EVAL_RESIDUAL = os.environ.get("B200_FOLD_EVAL_RESIDUAL") is not None
+_FOLD_EVAL_RESIDUAL = os.environ.get("B200_NO_FOLD_EVAL_RESIDUAL") is None
 # stem: BatchNorm -> ReLU -> MaxPool as one pass each way (csrc/stem_pool.cu); B200_NO_FUSED_STEM_POOL=1 = separate kernels
 _FUSE_STEM_POOL = os.environ.get("B200_NO_FUSED_STEM_POOL") is None
 
@@ -213,10 +213,10 @@ def _unit_forward(conv, bn, x, relu, residual, save, stage=False, pool=False):
         y, partials = ops.conv_fprop_bnstats(x, wp, K, R, S, stride, pad)   # BN statistics fused into the epilogue
     else:
         if not save and _FOLD_EVAL_BN and (residual is None or _FOLD_EVAL_RESIDUAL):
-            # eval mode: BatchNorm (running statistics) and ReLU folded into the conv epilogue.  The residual add can
-            # be folded as well (b200_conv_fprop_affine takes the tensor), but with per-thread residual loads the
-            # epilogue becomes LSU-bound: measured 75.6k vs 84.0k img/s at batch 1024, so block outputs keep the
-            # separate apply pass until the residual tile is fetched by TMA.
+            # eval mode: BatchNorm (running statistics), the residual add and ReLU folded into the conv epilogue.  The
+            # residual tile comes in by TMA, prefetched one item ahead into the staging tile the output leaves from
+            # (conv_sm100.cuh, res_tma): batch-1024 inference 103.2k -> 117.6k img/s.  With per-thread residual loads
+            # the epilogue was LSU-bound (75.6k vs 84.0k img/s at the time), B200_RES_TMA=0 brings that path back.
             scale, shift = ops.bn_eval_coeffs(bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.eps)
             z = ops.conv_fprop_affine(x, wp, K, R, S, stride, pad, scale, shift, relu, residual)
             if z is not None:

@@ -259,7 +259,12 @@ def test_conv_fprop_fused_bn_statistics(case):
     assert _rel(rm1, rm2) < 1e-5 and _rel(rv1, rv2) < 1e-5
 
 
-@pytest.mark.parametrize("case", [c for c in CONV_CASES if c[2] % 64 == 0 and c[3] % 64 == 0][:6])
+# conv3-of-a-Bottleneck shapes whose CTAs walk several tiles: the residual arrives by TMA, prefetched one item ahead
+RESIDUAL_CASES = [(64, 40, 64, 256, 1, 1, 0), (64, 20, 128, 512, 1, 1, 0), (256, 10, 256, 1024, 1, 1, 0),
+                  (64, 5, 512, 2048, 1, 1, 0), (64, 20, 512, 128, 1, 1, 0), (3, 7, 64, 256, 1, 1, 0)]
+
+
+@pytest.mark.parametrize("case", [c for c in CONV_CASES if c[2] % 64 == 0 and c[3] % 64 == 0][:6] + RESIDUAL_CASES)
 @pytest.mark.parametrize("relu", [True, False])
 def test_conv_fprop_affine_epilogue(case, relu):
     """Eval-mode BatchNorm (+ReLU) folded into the fprop epilogue == conv followed by the separate apply kernel,
