@@ -253,15 +253,30 @@ static inline int pick_bn(const b200_conv_desc*, const ConvGeom&, int cols) {
 // and this kernel has one staging tile per epilogue group where the shallow variant of conv_sm100_kernel has two.
 // kind 3 (mask bit 2, fprop only) = "valid" 4 x 1 stride-1 layers with 64 -> 64 channels -- the row-pair
 // staged stem: a tile is the usual bw x bh pixel box, its activations ONE box of bh + R - 1 rows, a tap a shift by bw rows.
+// kind 3's pixel box: one image per box (the halo lives inside an image), the fewest tiles, then the tallest box (the
+// halo rows are re-read once per box); bn = 0 when no box satisfies the stage limits
+static inline PixelBox ws3_box(const b200_conv_desc* d, const ConvGeom& g) {
+  PixelBox best{0, 0, 0, 0, 0, 0};
+  long long best_tiles = -1;
+  for (int bw = 1; bw <= g.Wo && bw <= GEMM_BM; ++bw)
+    for (int bh = 1; bh <= g.Ho && bw * bh <= GEMM_BM; ++bh) {
+      if ((bh + d->R - 1) * bw > HALO_ROWS || (d->R - 1) * bw + GEMM_BM > HALO_ROWS || bh + d->R - 1 > 256) continue;
+      const long long tw = (g.Wo + bw - 1) / bw, th = (g.Ho + bh - 1) / bh, tiles = tw * th;
+      if (best_tiles < 0 || tiles < best_tiles || (tiles == best_tiles && bh > best.bh)) {
+        best_tiles = tiles;
+        best = PixelBox{bw, bh, 1, (int)tw, (int)th, d->N};
+      }
+    }
+  return best;
+}
 static inline int ws_kind(const b200_conv_desc* d, const ConvGeom& g, int cin, int cout, bool dgrad = false) {
   static const int mask = getenv("B200_WS") ? atoi(getenv("B200_WS")) : 6;
   if (mask == 0 || d->stride != 1 || cin % 64 != 0 || cout % 8 != 0) return 0;
   const int bn = pick_bn(d, g, cout);
   const int chunks = cin / 64;
   if ((mask & 4) && !dgrad && d->S == 1 && d->R == 4 && d->pad == 0 && bn == 64 && chunks == 1) {
-    const PixelBox b = choose_pixel_box(g.Wo, g.Ho, d->N, GEMM_BM, 1, 1);
-    if (b.bn == 1 && (b.bh + d->R - 1) * b.bw <= HALO_ROWS && (d->R - 1) * b.bw + GEMM_BM <= HALO_ROWS) return 3;
-    return 0;
+    const PixelBox b = ws3_box(d, g);
+    return (b.bn == 1 && b.bw * b.bh * 10 >= GEMM_BM * 7) ? 3 : 0;            // at least 70 % of the MMA rows are pixels
   }
   if (d->R == 1 && d->S == 1 && d->pad == 0) {
     if (!(mask & 1)) return 0;
@@ -288,7 +303,9 @@ static inline PixelBox halo_box(const b200_conv_desc* d) {
 static inline PixelBox fprop_box(const b200_conv_desc* d, const ConvGeom& g) {
   const bool flat = is_flat(d);
   const int Wq = flat ? (int)g.M : g.Wo, Hq = flat ? 1 : g.Ho, Nq = flat ? 1 : d->N;
-  if (ws_kind(d, g, d->C, d->K) == 2) return halo_box(d);
+  const int ws = ws_kind(d, g, d->C, d->K);
+  if (ws == 2) return halo_box(d);
+  if (ws == 3) return ws3_box(d, g);
   return choose_pixel_box(Wq, Hq, Nq, GEMM_BM, 1, d->stride);
 }
 
