@@ -67,6 +67,7 @@ class DistributedDataParallel(_nn.Module):
         self._comm_stream = torch.cuda.Stream(device=self.device, priority=-1) if self.on_cuda else None
         self._verify_shapes(list(module.parameters()))
         self._sync_module_states()
+        self._flatten_buffers()
         self._build_buckets(params, int(bucket_cap_mb * 1024 * 1024))
         self._callback_queued = False
         self._next_to_launch = 0
@@ -103,6 +104,46 @@ class DistributedDataParallel(_nn.Module):
                     for t in ts:
                         t.copy_(flat[off:off + t.numel()].view_as(t))
                         off += t.numel()
+
+    def _flatten_buffers(self):
+        """Re-homes every fp32 buffer (BatchNorm running statistics) into ONE flat tensor, so that the per-step buffer
+        broadcast is a single collective on that tensor -- no pack / unpack kernels, no allocation, no Python walk
+        over 106 tensors -- issued on the communication stream right after the forward that updated the statistics
+        (it overlaps loss + backward; the next training forward only waits on its event).  The module's buffers stay
+        the same tensor objects (state_dict, load_state_dict and in-place updates are unaffected); if the user
+        re-allocates them (`module.to(...)`), the aliasing check in forward() falls back to the coalesced broadcast."""
+        self._buf_flat = None
+        self._buf_event = None
+        if not (self.on_cuda and self.broadcast_buffers and self.world_size > 1):
+            return
+        bufs = [b for b in self.module.buffers() if b.dtype == torch.float32 and b.is_contiguous() and b.numel() > 0]
+        if not bufs:
+            return
+        offs, total = [], 0
+        for b in bufs:
+            offs.append(total)
+            total += (b.numel() + 3) // 4 * 4            # 16-byte aligned slices
+        flat = torch.zeros(total, dtype=torch.float32, device=self.device)
+        with torch.no_grad():
+            for b, off in zip(bufs, offs):
+                view = flat[off:off + b.numel()].view(b.shape)
+                view.copy_(b)
+                b.data = view
+        self._buf_flat, self._bufs = flat, bufs
+        self._buf_ptrs = [b.data_ptr() for b in bufs]
+
+    def _buffers_still_flat(self):
+        return all(b.data_ptr() == p for b, p in zip(self._bufs, self._buf_ptrs))
+
+    def _broadcast_buffers_async(self):
+        """After a training forward: rank 0's statistics -> every rank, on the communication stream."""
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream())
+        self._comm_stream.wait_event(ev)
+        with torch.cuda.stream(self._comm_stream):
+            dist.broadcast(self._buf_flat, 0, group=self.process_group)
+            self._buf_event = torch.cuda.Event()
+            self._buf_event.record(self._comm_stream)
 
     def _sync_module_states(self):
         with torch.no_grad():
@@ -279,16 +320,27 @@ class DistributedDataParallel(_nn.Module):
 
     # ---------------------------------------------------------------- module protocol
     def forward(self, *inputs, **kwargs):
+        flat_bufs = False
         if self.broadcast_buffers and self.module.training and self.world_size > 1:
-            bufs = [b for b in self.module.buffers() if b.dtype.is_floating_point]
-            if bufs:
-                with torch.no_grad():
-                    self._coalesced_broadcast(bufs)
+            flat_bufs = self._buf_flat is not None and self._buffers_still_flat()
+            if flat_bufs:
+                # the broadcast that followed the previous training forward (construction synchronised the first one)
+                if self._buf_event is not None:
+                    torch.cuda.current_stream().wait_event(self._buf_event)
+                    self._buf_event = None
+            else:
+                bufs = [b for b in self.module.buffers() if b.dtype.is_floating_point]
+                if bufs:
+                    with torch.no_grad():
+                        self._coalesced_broadcast(bufs)
         if torch.is_grad_enabled() and self.require_backward_grad_sync:
             F.set_grad_sink(self._sink)
         else:
             F.set_grad_sink(None)
-        return self.module(*inputs, **kwargs)
+        out = self.module(*inputs, **kwargs)
+        if flat_bufs:
+            self._broadcast_buffers_async()
+        return out
 
     class _NoSync(object):
         def __init__(self, ddp):
