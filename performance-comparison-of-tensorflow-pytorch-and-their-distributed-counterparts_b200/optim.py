@@ -42,7 +42,20 @@ def _collect(group):
     return ps, gs
 
 
-class SGD(Optimizer):
+class _FastZeroGrad(object):
+    """`optimizer.zero_grad()` (set_to_none, the default) as a plain loop: torch's version spends ~0.17 ms per call on
+    profiler ranges and per-tensor bookkeeping for ResNet-50's 161 tensors, host time that sits between one step's
+    `loss.item()` and the next forward's first kernel."""
+
+    def zero_grad(self, set_to_none=True):
+        if not set_to_none:
+            return super().zero_grad(set_to_none=False)
+        for group in self.param_groups:
+            for p in group["params"]:
+                p.grad = None
+
+
+class SGD(_FastZeroGrad, Optimizer):
     def __init__(self, params, lr=1e-3, momentum=0.0, dampening=0.0, weight_decay=0.0, nesterov=False):
         if lr < 0.0:
             raise ValueError("Invalid learning rate: {}".format(lr))
@@ -84,7 +97,7 @@ class SGD(Optimizer):
         return loss
 
 
-class Adam(Optimizer):
+class Adam(_FastZeroGrad, Optimizer):
     _decoupled = False
     # transformers.AdamW divides by (sqrt(v) + eps) with the step size lr*sqrt(bc2)/bc1; torch divides by
     # (sqrt(v)/sqrt(bc2) + eps) with lr/bc1.  The two coincide when torch's rule is given eps/sqrt(bc2) at that step,
