@@ -227,7 +227,7 @@ att_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__
   // ---------------------------------------------------------------- MMA 1
   // (lanes 1..31 of warp 0 park at the __syncwarp instead of spinning on the next barrier against their own lane 0)
   if (warp == 0) {
-   if (tid == 0) {
+   if (elect_one()) {      // elect.sync: no scalarisation loop around tcgen05.mma (see conv_sm100.cuh)
     mbar_wait(&bars[0], 0);
     tc_fence_after();
     const uint32_t idesc = umma_idesc_bf16(ATC_ROWS, S, false, false);
@@ -337,7 +337,7 @@ att_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__
 
   // ---------------------------------------------------------------- MMA 2
   if (warp == 0) {
-   if (tid == 0) {
+   if (elect_one()) {      // elect.sync: no scalarisation loop around tcgen05.mma (see conv_sm100.cuh)
     tc_fence_after();
     const uint32_t idesc = umma_idesc_bf16(ATC_ROWS, ATC_D, false, true);
     const uint32_t a_addr = smem_u32(smA2a);
