@@ -35,7 +35,7 @@ GFLOP_PER_IMG_TRAIN = 12.398     # BASELINE.md section 3 / SURVEY 8(d): fwd + dg
 # the dominant kernel -- the forward 64->256 1x1 convolution of layer1 at 40x40 (class c of SURVEY 8(a'), four per
 # step and the longest conv launch of the step) -- next to the ALGORITHMIC bytes of that same launch (read x, write y,
 # read w once).  Source: profiles/r02_ncu_named_launches.txt.
-CONV_TRAFFIC_LAUNCH = "conv_sm100_kernel<256,4,fprop>: 256 x 40x40, 64->256, 1x1 (class c)"
+CONV_TRAFFIC_LAUNCH = "conv_sm100_kernel<256,3,fprop,1,2> with fused BatchNorm statistics: 256 x 40x40, 64->256, 1x1 (class c)"
 CONV_TRAFFIC_BYTES_PER_LAUNCH = None            # filled from profiles/r02_ncu_named_launches.json when present
 CONV_ALGO_BYTES_PER_LAUNCH = 2.0 * (256 * 40 * 40 * 64 + 256 * 40 * 40 * 256 + 256 * 64)
 BERT_GEMM_TRAFFIC_BYTES_PER_LAUNCH = 36.8e6

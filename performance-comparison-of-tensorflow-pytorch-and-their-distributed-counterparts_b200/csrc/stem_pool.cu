@@ -373,7 +373,7 @@ static int32_t stem_bwd_impl(const T* dpool, const uint8_t* amax, const T* poole
   if (int32_t rc = bn_finalize_bwd_launch(part, nblk, C, (double)N * H * W, gamma, invstd, dgamma, dbeta, coef, st)) return rc;
   const int bpi = (Ho + SP_ROWS - 1) / SP_ROWS;
   maxpool_bn_bwd_dx_kernel<T, true><<<N * bpi, SP_THREADS, 0, st>>>(dpool, amax, pooled, y, dy, mean, coef, H, W, C, Ho, Wo, bpi);
-  return check_launch("maxpool_bn_bwd", 3);
+  return check_launch("maxpool_bn_bwd", 2);      // reduce + dx (the finalize launch counted itself)
 }
 
 }  // namespace b200

@@ -2,7 +2,8 @@
 bf16) between cudaProfilerStart/Stop, so that `ncu --set full --profile-from-start off` captures exactly these:
 
     conv classes S (stem), b, c, f, j, p, v of SURVEY.md 8(a'): fprop (with fused BN statistics), dgrad, wgrad
-    bn_apply (+ReLU mask), bn_backward (reduction + finalize + dx), bn_train_stats, mt_sgd, maxpool fwd / bwd
+    bn_apply (+ReLU mask), bn_backward (reduction + finalize + dx), bn_train_stats, mt_sgd, maxpool fwd / bwd,
+    the stem's fused BatchNorm -> ReLU -> MaxPool forward / backward
 
 and writes gpurun_out/named_launches_labels.json = [(label, kernels launched, algorithmic bytes, flops)] in launch order
 (counted with b200_launch_count), which tools/ncu_named_summary.py joins with the ncu CSV.
@@ -65,6 +66,16 @@ pooled, idx = ops.maxpool_fwd(zs, True)
 dpool = torch.randn_like(pooled)
 ops_list += [("maxpool_fwd", lambda: ops.maxpool_fwd(zs, True), 2.0 * (zs.numel() + pooled.numel()) + idx.numel(), 0),
              ("maxpool_bwd", lambda: ops.maxpool_bwd(dpool, idx, zs.shape), 2.0 * (zs.numel() + pooled.numel()) + idx.numel(), 0)]
+# the stem's BatchNorm -> ReLU -> MaxPool as one pass each way (csrc/stem_pool.cu), on the stem output shape
+ys = torch.randn(N, 80, 80, 64, device=dev).to(torch.bfloat16)
+g64, b64 = torch.ones(64, device=dev), torch.zeros(64, device=dev)
+mean_s, invstd_s, scale_s, shift_s = ops.bn_train_stats(ys, g64, b64, None, None, 0.0, 1e-5)
+pooled_s, idx_s = ops.bn_relu_maxpool_fwd(ys, scale_s, shift_s, True)
+dpool_s = torch.randn_like(pooled_s)
+es, ps_ = ys.numel(), pooled_s.numel()
+ops_list += [("stem_pool_fwd", lambda: ops.bn_relu_maxpool_fwd(ys, scale_s, shift_s, True), 2.0 * es + 3.0 * ps_, 0),
+             ("stem_pool_bwd", lambda: ops.maxpool_bn_bwd(dpool_s, idx_s, pooled_s, ys, g64, mean_s, invstd_s),
+              6.0 * es + 10.0 * ps_, 0)]
 params = [torch.nn.Parameter(torch.randn(n, device=dev)) for n in (2048 * 512 * 9 // 4, 512 * 2048, 1024 * 256, 64 * 64)]
 for p in params:
     p.grad = torch.randn_like(p)
