@@ -128,6 +128,13 @@ int32_t b200_conv_dgrad(const b200_conv_desc* d, const void* dy, const void* w_k
 /* dw_oihw[K,C,R,S] fp32 = sum_{n,p,q} dy * x   (deterministic split-K; written in the parameter's own layout) */
 int32_t b200_conv_wgrad(const b200_conv_desc* d, const void* x, const void* dy, float* dw_oihw, void* ws,
                         int64_t ws_bytes, void* stream);
+/* Deferred split-K reductions of the weight gradient (no reference counterpart: launch-count optimisation of the
+ * training step, which otherwise runs 53 tiny reduce kernels).  After b200_wgrad_defer(1), on the same host thread,
+ * b200_conv_wgrad leaves its slabs in the workspace it was given -- each call needs its OWN workspace, alive until the
+ * flush -- and b200_wgrad_flush(stream) writes all the queued dw tensors in one launch per 48 layers.  Layers whose
+ * kernel writes dw directly are unaffected.  b200_wgrad_defer(0) leaves the mode (and drops what is still queued). */
+int32_t b200_wgrad_defer(int32_t on);
+int32_t b200_wgrad_flush(void* stream);
 
 /* ------------------------------------------------------------------ GEMM (Linear layers of the head,
  * pytorch_training_inference_on_image.ipynb:439-443; replaces aten::addmm / mm)

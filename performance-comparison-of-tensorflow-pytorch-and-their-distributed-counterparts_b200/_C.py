@@ -73,6 +73,8 @@ SIGNATURES = {
     "b200_bn_relu_maxpool_fwd": (I32, [P, P, P, P, P, I32, I32, I32, I32, I32, P]),
     "b200_maxpool_bn_bwd": (I32, [P, P, P, P, P, I32, I32, I32, I32, I32, P, P, P, P, P, P, I64, P]),
     "b200_maxpool3x3s2_bwd_rows": (I32, [P, P, P, I32, I32, I32, I32, I32, P]),
+    "b200_wgrad_defer": (I32, [I32]),
+    "b200_wgrad_flush": (I32, [P]),
     "b200_avgpool_fwd": (I32, [P, P, I32, I32, I32, I32, P]),
     "b200_avgpool_bwd": (I32, [P, P, I32, I32, I32, I32, P]),
     "b200_relu_fwd_f32": (I32, [P, P, I64, P]),

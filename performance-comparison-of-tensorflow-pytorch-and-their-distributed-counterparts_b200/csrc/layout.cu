@@ -1,5 +1,6 @@
 // Layout / packing kernels at the PyTorch boundary: NCHW fp32 <-> NHWC (fp32|bf16), OIHW fp32 -> KRSC, casts,
 // im2col / col2im for the explicit-GEMM convolution paths.
+#include <vector>
 #include "common.cuh"
 
 namespace b200 {
@@ -256,6 +257,36 @@ __global__ void reduce_wgrad_kernel(const float* __restrict__ part, int slabs, l
     dw[((long long)k * C + c) * RS + rs] = acc;
   }
 }
+// The same reduction for up to RW_MAX layers in ONE launch.  A training step runs 53 of these tiny reductions (one per
+// convolution, 0.41 ms of a 14 ms step when launched one by one: each is a few microseconds of work behind a kernel
+// boundary); b200_wgrad_defer(1) makes launch_reduce_wgrad queue them (the caller gives every layer its own slab
+// buffer) and b200_wgrad_flush launches them together.  Block b works on job j with blk0[j] <= b < blk0[j + 1].
+constexpr int RW_MAX = 48;
+struct ReduceBatch {
+  const float* part[RW_MAX];
+  float* dw[RW_MAX];
+  long long stride[RW_MAX];
+  int slabs[RW_MAX], K[RW_MAX], C[RW_MAX], RS[RW_MAX], ld[RW_MAX];
+  int blk0[RW_MAX + 1];
+};
+__global__ void __launch_bounds__(256) reduce_wgrad_multi_kernel(const __grid_constant__ ReduceBatch b) {
+  int j = 0;
+  while ((int)blockIdx.x >= b.blk0[j + 1]) ++j;
+  const int lb = (int)blockIdx.x - b.blk0[j], nb = b.blk0[j + 1] - b.blk0[j];
+  const float* __restrict__ part = b.part[j];
+  float* __restrict__ dw = b.dw[j];
+  const int K = b.K[j], C = b.C[j], RS = b.RS[j], ld = b.ld[j], slabs = b.slabs[j];
+  const long long slab_stride = b.stride[j];
+  const int RSC = RS * C;
+  const int total = K * RSC;                     // < 2^31: a convolution weight
+  for (int i = lb * 256 + (int)threadIdx.x; i < total; i += nb * 256) {
+    const int k = i / RSC, jj = i - k * RSC;
+    const int rs = jj / C, c = jj - rs * C;
+    float acc = 0.f;
+    for (int s = 0; s < slabs; ++s) acc += part[s * slab_stride + (long long)k * ld + jj];
+    dw[((long long)k * C + c) * RS + rs] = acc;
+  }
+}
 // partial slabs -> plain [rows][ldo] (fp32 or bf16), optional accumulate
 template <typename T>
 __global__ void reduce_plain_kernel(const float* __restrict__ part, int slabs, long long slab_stride, int rows,
@@ -316,10 +347,59 @@ int32_t launch_col2im(const float* dcol, void* dx, int dtype, int N, int H, int 
     col2im_kernel<__nv_bfloat16><<<grid_for(total), 256, 0, st>>>(dcol, (__nv_bfloat16*)dx, N, H, W, C, R, S, stride, pad, Ho, Wo, ld, accumulate);
   return check_launch("col2im");
 }
+struct ReduceJob {
+  const float* part;
+  float* dw;
+  long long stride;
+  int slabs, K, C, RS, ld;
+};
+struct ReduceQueue {
+  bool on = false;
+  std::vector<ReduceJob> jobs;
+};
+static ReduceQueue& reduce_queue() {      // per host thread: autograd runs the backward on its own worker thread
+  static thread_local ReduceQueue q;
+  return q;
+}
 int32_t launch_reduce_wgrad(const float* part, int slabs, long long slab_stride, int K, int C, int RS, int ld,
                             float* dw, cudaStream_t st) {
+  ReduceQueue& q = reduce_queue();
+  if (q.on && (long long)K * RS * C < (1LL << 31)) {
+    q.jobs.push_back(ReduceJob{part, dw, slab_stride, slabs, K, C, RS, ld});
+    return B200_OK;
+  }
   reduce_wgrad_kernel<<<grid_for((long long)K * RS * C), 256, 0, st>>>(part, slabs, slab_stride, K, C, RS, ld, dw);
   return check_launch("reduce_wgrad");
+}
+int32_t reduce_wgrad_flush(cudaStream_t st) {
+  ReduceQueue& q = reduce_queue();
+  size_t at = 0;
+  int launches = 0;
+  while (at < q.jobs.size()) {
+    ReduceBatch b{};
+    int n = 0, blocks = 0;
+    for (; at < q.jobs.size() && n < RW_MAX; ++at, ++n) {
+      const ReduceJob& jb = q.jobs[at];
+      b.part[n] = jb.part; b.dw[n] = jb.dw; b.stride[n] = jb.stride;
+      b.slabs[n] = jb.slabs; b.K[n] = jb.K; b.C[n] = jb.C; b.RS[n] = jb.RS; b.ld[n] = jb.ld;
+      const long long total = (long long)jb.K * jb.RS * jb.C;
+      long long nb = (total + 1023) / 1024;           // four elements per thread
+      if (nb > 2 * num_sms()) nb = 2 * num_sms();
+      if (nb < 1) nb = 1;
+      b.blk0[n] = blocks;
+      blocks += (int)nb;
+    }
+    for (int i = n; i <= RW_MAX; ++i) b.blk0[i] = blocks;
+    reduce_wgrad_multi_kernel<<<blocks, 256, 0, st>>>(b);
+    ++launches;
+  }
+  q.jobs.clear();
+  return launches ? check_launch("reduce_wgrad_multi", launches) : B200_OK;
+}
+void reduce_wgrad_defer(bool on) {
+  ReduceQueue& q = reduce_queue();
+  q.on = on;
+  if (!on) q.jobs.clear();
 }
 int32_t launch_reduce_plain(const float* part, int slabs, long long slab_stride, int rows, int cols, long long ldp,
                             void* out, long long ldo, int out_dtype, int accumulate, cudaStream_t st) {
@@ -451,3 +531,14 @@ extern "C" int32_t b200_im2col(const void* x, void* col, int32_t N, int32_t H, i
   if (Ho <= 0 || Wo <= 0) return fail(B200_INVALID_ARG, "im2col: filter larger than input");
   return launch_im2col(x, col, dtype, N, H, W, C, R, S, stride, pad, Ho, Wo, ld, as_stream(stream));
 }
+
+// Deferred weight-gradient reductions (see reduce_wgrad_multi_kernel): between b200_wgrad_defer(1) and
+// b200_wgrad_flush on the SAME host thread, b200_conv_wgrad leaves its split-K slabs in the workspace it was given
+// (so every call needs its own) and dw is written by the flush.  b200_wgrad_defer(0) ends the mode and drops anything
+// still queued.
+extern "C" int32_t b200_wgrad_defer(int32_t on) {
+  reduce_wgrad_defer(on != 0);
+  return B200_OK;
+}
+extern "C" int32_t b200_wgrad_flush(void* stream) { return reduce_wgrad_flush(as_stream(stream)); }
+

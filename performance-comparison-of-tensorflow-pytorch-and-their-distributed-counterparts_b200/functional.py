@@ -180,6 +180,7 @@ _L2_WALK = os.environ.get("B200_L2_WALK") is not None
 _STEM_PAIRS = os.environ.get("B200_STEM_IM2COL") is None
 _FOLD_EVAL_BN = os.environ.get("B200_NO_FOLD_EVAL_BN") is None
 _FOLD_EVAL_RESIDUAL = os.environ.get("B200_NO_FOLD_EVAL_RESIDUAL") is None
+_WGRAD_DEFER = os.environ.get("B200_NO_WGRAD_DEFER") is None
 # stem: BatchNorm -> ReLU -> MaxPool as one pass each way (csrc/stem_pool.cu); B200_NO_FUSED_STEM_POOL=1 = separate kernels
 _FUSE_STEM_POOL = os.environ.get("B200_NO_FUSED_STEM_POOL") is None
 
@@ -377,6 +378,14 @@ def _side_stream(device):
 
 
 def _backbone_bwd(st, dfeat, params, param_needs, x_needs_grad, sink, cut=None, cut_after=()):
+    try:
+        return _backbone_bwd_impl(st, dfeat, params, param_needs, x_needs_grad, sink, cut, cut_after)
+    finally:
+        if dfeat.is_cuda:
+            ops.wgrad_defer(False)       # leave the deferred-reduction mode of this host thread, whatever happened
+
+
+def _backbone_bwd_impl(st, dfeat, params, param_needs, x_needs_grad, sink, cut=None, cut_after=()):
     """Reverse walk: BN backward (mask from the saved byte mask) -> wgrad -> dgrad; the block-input gradient is the
     residual gradient with conv1's dgrad accumulated in the GEMM epilogue.  Returns (dx or None, [grad per param]).
 
@@ -396,14 +405,35 @@ def _backbone_bwd(st, dfeat, params, param_needs, x_needs_grad, sink, cut=None, 
     keep = []        # tensors the side stream reads: kept alive until the streams are joined
     forked = [False]
 
+    # Deferred split-K reductions: the 53 per-layer reduce launches of the weight gradients (0.41 ms of the step when
+    # launched one by one) become one launch per graph segment (ops.wgrad_flush).  Each deferred layer keeps its own
+    # slab buffer until then, and its gradient is handed on (to DDP's bucket copy, to .grad) only after the flush.  Not in
+    # eager DDP mode, where a bucket should start its all-reduce as soon as its last gradient exists.
+    defer = _WGRAD_DEFER and dfeat.is_cuda and not overlap and (sink is None or capturing)
+    slab_bufs, pending = [], []
+    if defer:
+        ops.wgrad_defer(True)
+
+    def flush():
+        if defer and pending:
+            ops.wgrad_flush()
+            for p, g in pending:
+                grads[id(p)] = sink(p, g) if sink is not None else g
+            del pending[:]
+            del slab_bufs[:]
+
     def join():
+        flush()
         if overlap and forked[0]:
             main.wait_stream(side)
             forked[0] = False
             del keep[:]
 
-    def emit(p, g):
-        grads[id(p)] = sink(p, g) if sink is not None else g
+    def emit(p, g, deferred=False):
+        if deferred:
+            pending.append((p, g))
+        else:
+            grads[id(p)] = sink(p, g) if sink is not None else g
 
     def unit_backward(u, dz, want_dres):
         if u.mean is None:
@@ -428,7 +458,18 @@ def _backbone_bwd(st, dfeat, params, param_needs, x_needs_grad, sink, cut=None, 
         K, R, S, stride, pad = u.geom
         if u.conv.weight.requires_grad:
             def wgrad():
-                dw = ops.conv_wgrad(u.x, dy, K, R, S, stride, pad)
+                # layers whose gradient is post-processed by torch ops right away (the staged / channel-padded stem)
+                # cannot wait for the flush
+                plain = u.staged is None and u.x.shape[-1] == u.conv.in_channels
+                if defer and not plain:
+                    flush()
+                    ops.wgrad_defer(False)
+                dw = ops.conv_wgrad(u.x, dy, K, R, S, stride, pad, own_ws=slab_bufs if (defer and plain) else None)
+                if defer and not plain:
+                    ops.wgrad_defer(True)
+                if defer and plain:
+                    emit(u.conv.weight, dw, deferred=True)
+                    return
                 if u.staged is not None and u.staged[0] == "pairs":
                     # row-pair staged stem: dw is [K][64 = (r2, s, c)][R' = j][1]; filter row r = 2j + r2
                     _, r0, s0 = u.staged

@@ -261,14 +261,28 @@ def conv_dgrad(dy, wp, x_shape, K, R, S, stride, pad, out=None, accumulate=False
     return out
 
 
-def conv_wgrad(x, dy, K, R, S, stride, pad):
+def conv_wgrad(x, dy, K, R, S, stride, pad, own_ws=None):
+    """own_ws: a list -> the call gets a workspace of its own, appended to the list (deferred reductions: the slabs
+    must survive until wgrad_flush)."""
     N, H, W, C = x.shape
     d, dref, ws, Ho, Wo = _desc(N, H, W, C, K, R, S, stride, pad, _dt(x))
     dw = torch.empty((K, C, R, S), dtype=torch.float32, device=x.device)
-    w = workspace(ws[2], x.device)
+    if own_ws is not None:
+        w = torch.empty(max(int(ws[2]), 16), dtype=torch.uint8, device=x.device)
+        own_ws.append(w)
+    else:
+        w = workspace(ws[2], x.device)
     check(lib.b200_conv_wgrad(dref, x.data_ptr(), dy.data_ptr(), dw.data_ptr(), w.data_ptr(), ws[2], _stream()),
           "conv_wgrad")
     return dw
+
+
+def wgrad_defer(on):
+    check(lib.b200_wgrad_defer(1 if on else 0), "wgrad_defer")
+
+
+def wgrad_flush():
+    check(lib.b200_wgrad_flush(_stream()), "wgrad_flush")
 
 
 # ------------------------------------------------------------------ batch norm

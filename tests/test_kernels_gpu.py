@@ -259,6 +259,35 @@ def test_conv_fprop_fused_bn_statistics(case):
     assert _rel(rm1, rm2) < 1e-5 and _rel(rv1, rv2) < 1e-5
 
 
+def test_conv_wgrad_deferred_reductions_match_immediate():
+    """b200_wgrad_defer / b200_wgrad_flush: the split-K slabs of several layers are reduced by ONE launch; the
+    gradients are bit-identical to the per-layer reduction (same summation order), layers that write dw directly
+    are unaffected, and leaving the mode drops nothing silently into later calls."""
+    from b200net import ops
+    dt = torch.bfloat16
+    cases = [(8, 20, 64, 64, 3, 1, 1), (8, 20, 64, 256, 1, 1, 0), (8, 10, 256, 256, 3, 1, 1), (8, 10, 512, 128, 1, 1, 0),
+             (4, 20, 128, 128, 3, 2, 1)]
+    data = []
+    for i, (N, H, C, K, R, stride, pad) in enumerate(cases):
+        Ho = (H + 2 * pad - R) // stride + 1
+        x = _nhwc(_rand((N, C, H, H), dt, 300 + i), dt)
+        dy = _nhwc(_rand((N, K, Ho, Ho), dt, 400 + i), dt)
+        data.append((x, dy, K, R, stride, pad, ops.conv_wgrad(x, dy, K, R, R, stride, pad)))
+    bufs, got = [], []
+    ops.wgrad_defer(True)
+    try:
+        for x, dy, K, R, stride, pad, _ in data:
+            got.append(ops.conv_wgrad(x, dy, K, R, R, stride, pad, own_ws=bufs))
+        ops.wgrad_flush()
+    finally:
+        ops.wgrad_defer(False)
+    torch.cuda.synchronize()
+    for (x, dy, K, R, stride, pad, ref), g in zip(data, got):
+        assert torch.equal(g, ref), (tuple(x.shape), K, R, stride)
+    x, dy, K, R, stride, pad, ref = data[0]            # back in immediate mode
+    assert torch.equal(ops.conv_wgrad(x, dy, K, R, R, stride, pad), ref)
+
+
 # conv3-of-a-Bottleneck shapes whose CTAs walk several tiles: the residual arrives by TMA, prefetched one item ahead
 RESIDUAL_CASES = [(64, 40, 64, 256, 1, 1, 0), (64, 20, 128, 512, 1, 1, 0), (256, 10, 256, 1024, 1, 1, 0),
                   (64, 5, 512, 2048, 1, 1, 0), (64, 20, 512, 128, 1, 1, 0), (3, 7, 64, 256, 1, 1, 0)]
