@@ -124,6 +124,19 @@ def pack_weights_multi(ws, dtype):
     return outs
 
 
+def cast_rows_multi(pairs, dtype):
+    """[(fp32 source [rows][cols] or [n], destination of the same shape in `dtype`)]: all copies / casts in one launch
+    per 48 tensors (b200_pack_weight_multi with R*S = 1: a matrix is a 1x1 convolution weight, a vector one row)."""
+    if not pairs:
+        return
+    K = [int(s.shape[0]) if s.dim() == 2 else 1 for s, _ in pairs]
+    C = [int(s.shape[-1]) for s, _ in pairs]
+    check(lib.b200_pack_weight_multi(len(pairs), _C.ptr_array([s.data_ptr() for s, _ in pairs]),
+                                     _C.ptr_array([d.data_ptr() for _, d in pairs]), _C.i32_array(K), _C.i32_array(C),
+                                     _C.i32_array(C), _C.i32_array([1] * len(pairs)), _C.i32_array(C), _DT[dtype],
+                                     _stream()), "pack_weight_multi")
+
+
 def im2col(x, R, S, stride, pad, ld):
     """NHWC [N,H,W,C] -> staged matrix [N,Ho,Wo,ld] (column (r*S+s)*C+c, zero tail)."""
     N, H, W, C = x.shape
