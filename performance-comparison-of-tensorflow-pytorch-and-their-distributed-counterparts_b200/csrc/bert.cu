@@ -375,10 +375,18 @@ __global__ void embed_bwd_scatter_kernel(const long long* __restrict__ ids, cons
     const long long tt = type_ids != nullptr ? type_ids[row] : 0;
     float v[W];
     load_vec(ds + row * H + col, v);
+    // 16-byte vector reductions (red.global.add.v4.f32, sm_90+): a quarter of the atomic instructions
+    float* wp = dword + id * H + col;
+    if ((reinterpret_cast<uintptr_t>(wp) & 15) == 0) {
 #pragma unroll
-    for (int e = 0; e < W; ++e) {
-      atomicAdd(dword + id * H + col + e, v[e]);
-      if (type_ids != nullptr) atomicAdd(dtype_tab + (tt > 0 ? H : 0) + col + e, v[e]);
+      for (int e = 0; e < W; e += 4) atomicAdd(reinterpret_cast<float4*>(wp + e), make_float4(v[e], v[e + 1], v[e + 2], v[e + 3]));
+    } else {
+#pragma unroll
+      for (int e = 0; e < W; ++e) atomicAdd(wp + e, v[e]);
+    }
+    if (type_ids != nullptr) {
+#pragma unroll
+      for (int e = 0; e < W; ++e) atomicAdd(dtype_tab + (tt > 0 ? H : 0) + col + e, v[e]);
     }
   }
 }
