@@ -251,6 +251,10 @@ static inline int pick_bn(const b200_conv_desc*, const ConvGeom&, int cols) {
 // 38.8 / 37.7 us, while kind 1 LOSES on every 1x1 class (64 -> 256: 48.5 -> 58.9 us, 256 -> 1024 at 10x10: 18.7 ->
 // 21.3 us): those tiles have 1-4 k-blocks and are bound by the epilogue (fused statistics), not by operand traffic,
 // and this kernel has one staging tile per epilogue group where the shallow variant of conv_sm100_kernel has two.
+// kind 4 (mask bit 3, OFF) = "same" 3x3 layers whose weight tile does not fit: halo activations, weights streamed
+// through a ring -- measured slower than the plain kernel (128 -> 128 at 20x20: 32.9 vs 30.2 us, 256 -> 256 at 10x10:
+// 30.6 vs 29.6 us): with a weight barrier per tap the issue loop is no tighter and the activation re-reads it saves
+// were L2 hits anyway.
 // kind 3 (mask bit 2, fprop only) = "valid" 4 x 1 stride-1 layers with 64 -> 64 channels -- the row-pair
 // staged stem: a tile is the usual bw x bh pixel box, its activations ONE box of bh + R - 1 rows, a tap a shift by bw rows.
 // kind 3's pixel box: one image per box (the halo lives inside an image), the fewest tiles, then the tallest box (the
@@ -282,7 +286,9 @@ static inline int ws_kind(const b200_conv_desc* d, const ConvGeom& g, int cin, i
     if (!(mask & 1)) return 0;
     return chunks <= (bn == 256 ? 4 : 8) ? 1 : 0;
   }
-  if (!(mask & 2) || d->R != 3 || d->S != 3 || d->pad != 1 || bn != 64 || chunks != 1) return 0;
+  if (d->R != 3 || d->S != 3 || d->pad != 1) return 0;
+  const bool resident = bn == 64 && chunks == 1;          // kind 2; otherwise kind 4: halo activations, streaming weights
+  if (resident ? !(mask & 2) : !(mask & 8)) return 0;
   if (g.Wo != d->W || g.Ho != d->H) return 0;
   const int wh = d->W + d->S - 1;
   if ((d->R - 1) * wh + d->S - 1 + GEMM_BM > HALO_ROWS) return 0;           // the last tap's view must stay inside the stage
@@ -290,7 +296,7 @@ static inline int ws_kind(const b200_conv_desc* d, const ConvGeom& g, int cin, i
   if (bh < 1 || (bh + d->R - 1) * wh > HALO_ROWS || bh + d->R - 1 > 256) return 0;
   const int bh_eff = bh < d->H ? bh : d->H;
   if (bh_eff * d->W * 10 < GEMM_BM * 7) return 0;                            // at least 70 % of the MMA rows are pixels
-  return 2;
+  return resident ? 2 : 4;
 }
 static inline PixelBox halo_box(const b200_conv_desc* d) {
   const int wh = d->W + d->S - 1;
@@ -304,7 +310,7 @@ static inline PixelBox fprop_box(const b200_conv_desc* d, const ConvGeom& g) {
   const bool flat = is_flat(d);
   const int Wq = flat ? (int)g.M : g.Wo, Hq = flat ? 1 : g.Ho, Nq = flat ? 1 : d->N;
   const int ws = ws_kind(d, g, d->C, d->K);
-  if (ws == 2) return halo_box(d);
+  if (ws == 2 || ws == 4) return halo_box(d);
   if (ws == 3) return ws3_box(d, g);
   return choose_pixel_box(Wq, Hq, Nq, GEMM_BM, 1, d->stride);
 }
@@ -314,6 +320,11 @@ static int launch_conv_ws(int kind, int bn, const CUtensorMap& ta, const CUtenso
                           const ConvParams& P, const HaloParams& HP, cudaStream_t st) {
   const int ctas = num_sms();
   if (kind == 2) return launch_conv_ws_cfg<64, 9, MODE, 3, HALO_ROWS, 9>(ta, tb, to, P, HP, ctas, st);
+  if (kind == 4) {
+    if (bn == 256) return launch_conv_ws_cfg<256, 4, MODE, 2, HALO_ROWS, 9, false>(ta, tb, to, P, HP, ctas, st);
+    if (bn == 128) return launch_conv_ws_cfg<128, 6, MODE, 3, HALO_ROWS, 9, false>(ta, tb, to, P, HP, ctas, st);
+    return launch_conv_ws_cfg<64, 8, MODE, 3, HALO_ROWS, 9, false>(ta, tb, to, P, HP, ctas, st);
+  }
   if (kind == 3) {
     if constexpr (MODE == MODE_FPROP) {
       return launch_conv_ws_cfg<64, 4, MODE, 3, HALO_ROWS, 4>(ta, tb, to, P, HP, ctas, st);
@@ -445,7 +456,7 @@ static int32_t implicit_dgrad(const b200_conv_desc* d, const ConvGeom& g, const 
     if (P.ntaps == 0 && (accumulate || (classes > 1 && tma_out))) continue;  // nothing to add / already cleared
     // weights-stationary variant: dgrad of a stride-1 convolution is again one (roles of C and K swapped)
     const int ws = (classes == 1 && tma_out) ? ws_kind(d, g, d->K, d->C, true) : 0;
-    const bool halo = ws == 2;
+    const bool halo = ws == 2 || ws == 4;
     HaloParams HP{};
     const PixelBox b = halo ? halo_box(d) : choose_pixel_box(Wq, Hq, Nq, GEMM_BM, 1, 1);
     HP.wh = b.bw; HP.rows = b.bw * b.bh * b.bn;

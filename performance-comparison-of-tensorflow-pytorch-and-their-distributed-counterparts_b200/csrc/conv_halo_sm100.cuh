@@ -38,10 +38,12 @@ struct HaloParams {
 
 template <int BN, int BSLOTS, int NA, int A_ROWS>
 constexpr int conv_ws_smem_bytes() {
-  return NA * A_ROWS * 128 + BSLOTS * BN * 128 + 2 * CONV_STAGING_TILE + CONV_STATS_RED_BYTES + 1024 + 512;
+  return NA * A_ROWS * 128 + BSLOTS * BN * 128 + 2 * CONV_STAGING_TILE + CONV_STATS_RED_BYTES + 1024 + 768;
 }
 
-template <int BN, int BSLOTS, int MODE, int NA, int A_ROWS, int NTAPS>
+// RESB = false: the weight tile does not fit (3x3 layers with 128+ channels): the weight slots are a ring that streams
+// one k-block per (tile, chunk, tap), the activations still come as one halo box per chunk.
+template <int BN, int BSLOTS, int MODE, int NA, int A_ROWS, int NTAPS, bool RESB = true>
 __global__ void __launch_bounds__(CONV_THREADS, 1)
 conv_ws_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                      const __grid_constant__ CUtensorMap tmO, const __grid_constant__ ConvParams P,
@@ -57,7 +59,8 @@ conv_ws_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
   uint8_t* smStage = smB + BSLOTS * B_BYTES;
   float* smRedBase = reinterpret_cast<float*>(smStage + 2 * CONV_STAGING_TILE);
   uint64_t* b_full = reinterpret_cast<uint64_t*>(smStage + 2 * CONV_STAGING_TILE + CONV_STATS_RED_BYTES);
-  uint64_t* a_full = b_full + BSLOTS;
+  uint64_t* b_empty = b_full + BSLOTS;     // ring mode only
+  uint64_t* a_full = b_empty + BSLOTS;
   uint64_t* a_empty = a_full + NA;
   uint64_t* tmem_full = a_empty + NA;      // [2]
   uint64_t* tmem_empty = tmem_full + 2;    // [2]
@@ -71,7 +74,7 @@ conv_ws_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
     tma_prefetch_desc(&tmO);
-    for (int s = 0; s < BSLOTS; ++s) mbar_init(&b_full[s], 1);
+    for (int s = 0; s < BSLOTS; ++s) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], 1); }
     for (int s = 0; s < NA; ++s) { mbar_init(&a_full[s], 1); mbar_init(&a_empty[s], 1); }
     for (int b = 0; b < 2; ++b) { mbar_init(&tmem_full[b], 1); mbar_init(&tmem_empty[b], conv_tmem_empty_arrivals<BN, 1>()); }
     mbar_fence_init();
@@ -92,22 +95,24 @@ conv_ws_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     if (elect_one() && walk_id < walk_total) {
       // the weight tile of this CTA's output columns (the same for every tile it walks), slot = chunk * NTAPS + tap
       const int n0 = conv_decode_tile<BN, MODE>(P, walk_id).n0;
-      for (int cc = 0; cc < cchunks; ++cc)
+      auto load_b = [&](int slot, int cc, int t) {
+        uint8_t* b = smB + slot * B_BYTES;
+        mbar_expect_tx(&b_full[slot], B_BYTES);
+        if (MODE == MODE_FPROP) {
+          tma_load_2d(b, &tmB, &b_full[slot], P.taps[t].bcol + cc * 64, n0);               // box {64 c, BN cout}
+        } else {
 #pragma unroll
-        for (int t = 0; t < NTAPS; ++t) {
-          const int slot = cc * NTAPS + t;
-          uint8_t* b = smB + slot * B_BYTES;
-          mbar_expect_tx(&b_full[slot], B_BYTES);
-          if (MODE == MODE_FPROP) {
-            tma_load_2d(b, &tmB, &b_full[slot], P.taps[t].bcol + cc * 64, n0);               // box {64 c, BN cout}
-          } else {
-#pragma unroll
-            for (int h = 0; h < BN / 64; ++h)
-              tma_load_2d(b + h * 8192, &tmB, &b_full[slot], P.taps[t].bcol + n0 + h * 64, cc * 64);   // {64 cin, 64 k}
-          }
+          for (int h = 0; h < BN / 64; ++h)
+            tma_load_2d(b + h * 8192, &tmB, &b_full[slot], P.taps[t].bcol + n0 + h * 64, cc * 64);   // {64 cin, 64 k}
         }
-      int as = 0;
-      uint32_t aph = 0;
+      };
+      if (RESB) {
+        for (int cc = 0; cc < cchunks; ++cc)
+#pragma unroll
+          for (int t = 0; t < NTAPS; ++t) load_b(cc * NTAPS + t, cc, t);
+      }
+      int as = 0, bs = 0;
+      uint32_t aph = 0, bph = 0;
       for (int w = walk_id; w < walk_total; w += walk_n) {
         const ConvTile T = conv_decode_tile<BN, MODE>(P, w);
         for (int cc = 0; cc < cchunks; ++cc) {
@@ -115,6 +120,14 @@ conv_ws_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
           mbar_expect_tx(&a_full[as], a_bytes);
           tma_load_4d(smA + as * A_BYTES, &tmA, &a_full[as], cc * 64, T.q0 * P.a_mul + HP.org_w, T.p0 * P.a_mul + HP.org_h, T.i0);
           if (++as == NA) { as = 0; aph ^= 1; }
+          if (!RESB) {
+#pragma unroll 1
+            for (int t = 0; t < NTAPS; ++t) {
+              mbar_wait(&b_empty[bs], bph ^ 1);
+              load_b(bs, cc, t);
+              if (++bs == BSLOTS) { bs = 0; bph ^= 1; }
+            }
+          }
         }
       }
     }
@@ -129,8 +142,8 @@ conv_ws_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
       uint32_t toff[NTAPS];                 // tap shifts in descriptor units (16 bytes): rows * 128 / 16
 #pragma unroll
       for (int t = 0; t < NTAPS; ++t) toff[t] = static_cast<uint32_t>(HP.toff[t]) * 8u;
-      int as = 0;
-      uint32_t aph = 0, it = 0;
+      int as = 0, bs = 0;
+      uint32_t aph = 0, bph = 0, it = 0;
       bool first_tile = true;
       while (tiles_left > 0) {
         mbar_wait(&tmem_empty[it & 1], ((it >> 1) & 1) ^ 1);   // epilogue has drained this accumulator
@@ -143,12 +156,21 @@ conv_ws_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
           const uint64_t b_desc = b_desc0 + static_cast<uint64_t>(cc * NTAPS * (B_BYTES >> 4));
 #pragma unroll
           for (int t = 0; t < NTAPS; ++t) {
-            if (first_tile) {
-              mbar_wait(&b_full[cc * NTAPS + t], 0);
+            if (RESB) {
+              if (first_tile) {
+                mbar_wait(&b_full[cc * NTAPS + t], 0);
+                tc_fence_after();
+              }
+              umma_f16_x4(d_tmem, a_desc + toff[t], b_desc + static_cast<uint64_t>(t * (B_BYTES >> 4)), 2u,
+                          MODE == MODE_FPROP ? 2u : 128u, idesc, (cc | t) ? 1u : 0u);
+            } else {
+              mbar_wait(&b_full[bs], bph);
               tc_fence_after();
+              umma_f16_x4(d_tmem, a_desc + toff[t], b_desc0 + static_cast<uint64_t>(bs * (B_BYTES >> 4)), 2u,
+                          MODE == MODE_FPROP ? 2u : 128u, idesc, (cc | t) ? 1u : 0u);
+              umma_commit(&b_empty[bs]);
+              if (++bs == BSLOTS) { bs = 0; bph ^= 1; }
             }
-            umma_f16_x4(d_tmem, a_desc + toff[t], b_desc + static_cast<uint64_t>(t * (B_BYTES >> 4)), 2u,
-                        MODE == MODE_FPROP ? 2u : 128u, idesc, (cc | t) ? 1u : 0u);
           }
           umma_commit(&a_empty[as]);          // every tap of this chunk has been issued: the stage is free once they finish
           if (++as == NA) { as = 0; aph ^= 1; }
@@ -174,13 +196,13 @@ conv_ws_sm100_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
 }
 
 // grid: a multiple of the number of output-column tiles (so that a CTA keeps one weight tile), never more than the tiles
-template <int BN, int BSLOTS, int MODE, int NA, int A_ROWS, int NTAPS>
+template <int BN, int BSLOTS, int MODE, int NA, int A_ROWS, int NTAPS, bool RESB = true>
 inline int launch_conv_ws_cfg(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, const ConvParams& P,
                               const HaloParams& HP, int num_ctas, cudaStream_t st) {
-  auto kern = conv_ws_sm100_kernel<BN, BSLOTS, MODE, NA, A_ROWS, NTAPS>;
+  auto kern = conv_ws_sm100_kernel<BN, BSLOTS, MODE, NA, A_ROWS, NTAPS, RESB>;
   constexpr int smem = conv_ws_smem_bytes<BN, BSLOTS, NA, A_ROWS>();
   static_assert(smem <= 232448, "weights-stationary conv kernel: shared memory budget exceeded");
-  if (P.ntaps != NTAPS || P.ntaps * P.cchunks > BSLOTS || HP.rows > A_ROWS) return 250;
+  if (P.ntaps != NTAPS || (RESB && P.ntaps * P.cchunks > BSLOTS) || HP.rows > A_ROWS) return 250;
   static int attr_state[B200_MAX_DEVICES] = {0};
   if (cudaError_t e = ensure_dyn_smem(kern, smem, attr_state)) return 300 + static_cast<int>(e);
   const int grid = conv_stats_grid(P.total_tiles, P.n_tiles, num_ctas);
