@@ -238,7 +238,13 @@ static inline void timing_end(cudaEvent_t e0, cudaEvent_t e1, double flops, cuda
 // Column-tile width of fprop / dgrad: as wide as the output allows.  (Measured on BERT's 768-column Linears, which
 // fill only 1.3 waves with 256-wide tiles: 128-wide tiles = 2.6 waves of half the work are 25-30 % SLOWER, e.g. FFN2
 // forward 39.5 -> 50.9 us -- the kernel is bound by operand traffic from L2 per MMA, which narrower tiles raise.)
-static inline int pick_bn(const b200_conv_desc*, const ConvGeom&, int cols) {
+// Exception, measured on the N = 256 / 160 px layer table after the MMA-issue fixes of round 2: 3x3 layers with exactly
+// 256 output columns run faster on 128-wide tiles (256 -> 256 at 10x10: 29.5 -> 26.8 us forward, 29.3 -> 26.4 us dgrad;
+// 20x20 stride 2: 29.7 -> 26.9 / 48.0 -> 44.3 us) -- 256 pixel tiles on 148 SMs are two very uneven waves of long tiles;
+// 512-column 3x3 layers lose 4 us with them and keep 256.  B200_BN_3X3_256=256 restores the wide tile.
+static inline int pick_bn(const b200_conv_desc* d, const ConvGeom&, int cols) {
+  static const int bn_3x3_256 = getenv("B200_BN_3X3_256") ? atoi(getenv("B200_BN_3X3_256")) : 128;
+  if (d->R * d->S > 1 && cols == 256 && (bn_3x3_256 == 128 || bn_3x3_256 == 64)) return bn_3x3_256;
   return cols > 128 ? 256 : (cols > 64 ? 128 : 64);
 }
 
