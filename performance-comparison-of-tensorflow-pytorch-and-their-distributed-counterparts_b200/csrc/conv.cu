@@ -238,14 +238,23 @@ static inline void timing_end(cudaEvent_t e0, cudaEvent_t e1, double flops, cuda
 // Column-tile width of fprop / dgrad: as wide as the output allows.  (Measured on BERT's 768-column Linears, which
 // fill only 1.3 waves with 256-wide tiles: 128-wide tiles = 2.6 waves of half the work are 25-30 % SLOWER, e.g. FFN2
 // forward 39.5 -> 50.9 us -- the kernel is bound by operand traffic from L2 per MMA, which narrower tiles raise.)
-// Exception, measured on the N = 256 / 160 px layer table after the MMA-issue fixes of round 2: 3x3 layers with exactly
-// 256 output columns run faster on 128-wide tiles (256 -> 256 at 10x10: 29.5 -> 26.8 us forward, 29.3 -> 26.4 us dgrad;
-// 20x20 stride 2: 29.7 -> 26.9 / 48.0 -> 44.3 us) -- 256 pixel tiles on 148 SMs are two very uneven waves of long tiles;
-// 512-column 3x3 layers lose 4 us with them and keep 256.  B200_BN_3X3_256=256 restores the wide tile.
-static inline int pick_bn(const b200_conv_desc* d, const ConvGeom&, int cols) {
-  static const int bn_3x3_256 = getenv("B200_BN_3X3_256") ? atoi(getenv("B200_BN_3X3_256")) : 128;
-  if (d->R * d->S > 1 && cols == 256 && (bn_3x3_256 == 128 || bn_3x3_256 == 64)) return bn_3x3_256;
-  return cols > 128 ? 256 : (cols > 64 ? 128 : 64);
+// Exception, measured on the N = 256 / 160 px layer table after the MMA-issue fixes of round 2: layers with exactly 256
+// output columns and a deep reduction (>= 16 k-blocks) run faster on 128-wide tiles -- 3x3 256 -> 256 at 10x10:
+// 29.5 -> 26.8 us forward, 29.3 -> 26.4 us dgrad; 20x20 stride 2: 29.7 -> 26.9 / 48.0 -> 44.3 us; 1x1 1024 -> 256 forward
+// 17.5 -> 15.8 us and the dgrad of 256 -> 1024 17.3 -> 15.8 us: a few hundred pixel tiles on 148 SMs are two uneven waves
+// of long tiles.  Shallower 256-column layers (512 -> 256: 33.6 -> 36.0 us) and 512-column ones (3x3: +4 us) lose with
+// them and keep 256, and so do problems with many pixel tiles (more than two per SM: VGG's 56x56 maps), where the wave
+// shape does not matter and the narrower tile only adds activation traffic.  `red` = reduction channels (C for fprop,
+// K for dgrad), `dgrad` selects which pixel grid counts.  B200_BN_DEEP256=256 restores the wide tile.
+static inline int pick_bn(const b200_conv_desc* d, const ConvGeom& g, int cols, int red, bool dgrad = false) {
+  static const int bn_deep256 = getenv("B200_BN_DEEP256") ? atoi(getenv("B200_BN_DEEP256")) : 128;
+  const long long pixels = dgrad ? (long long)d->N * d->H * d->W : (long long)g.M;
+  if (cols == 256 && d->R * d->S * (red / 64) >= 16 && pixels <= 256LL * num_sms() &&
+      (bn_deep256 == 128 || bn_deep256 == 64))
+    return bn_deep256;
+  static const int cap = getenv("B200_BN_CAP") ? atoi(getenv("B200_BN_CAP")) : 256;      // experiment knob
+  const int bn = cols > 128 ? 256 : (cols > 64 ? 128 : 64);
+  return bn > cap ? cap : bn;
 }
 
 // Weights-stationary variant (conv_halo_sm100.cuh): the CTA's weight tile (all taps x channel chunks) stays in shared
@@ -282,7 +291,7 @@ static inline PixelBox ws3_box(const b200_conv_desc* d, const ConvGeom& g) {
 static inline int ws_kind(const b200_conv_desc* d, const ConvGeom& g, int cin, int cout, bool dgrad = false) {
   static const int mask = getenv("B200_WS") ? atoi(getenv("B200_WS")) : 6;
   if (mask == 0 || d->stride != 1 || cin % 64 != 0 || cout % 8 != 0) return 0;
-  const int bn = pick_bn(d, g, cout);
+  const int bn = pick_bn(d, g, cout, cin, dgrad);
   const int chunks = cin / 64;
   if ((mask & 4) && !dgrad && d->S == 1 && d->R == 4 && d->pad == 0 && bn == 64 && chunks == 1) {
     const PixelBox b = ws3_box(d, g);
@@ -371,7 +380,7 @@ static int32_t implicit_fprop(const b200_conv_desc* d, const ConvGeom& g, const 
   int rc = flat ? make_tmap_bf16_nhwc(&ta, x, 1, 1, (int)g.M, d->C, b.bw, b.bh, b.bn, 1)
                 : make_tmap_bf16_nhwc(&ta, x, d->N, d->H, d->W, d->C, b.bw, halo ? b.bh + d->R - 1 : b.bh, b.bn, d->stride);
   if (rc) return fail(B200_CUDA_ERROR, "conv_fprop: activation tensor map failed (%d)", rc);
-  const int bn = pick_bn(d, g, d->K);
+  const int bn = pick_bn(d, g, d->K, d->C);
   const long long tiles = (long long)b.tiles_w * b.tiles_h * b.tiles_n;
   P.n_tiles = (d->K + bn - 1) / bn;
   P.pair_mode = ws ? 0 : pair_mode_for(d->R * d->S * (d->C / 64));
@@ -414,7 +423,7 @@ static int32_t implicit_dgrad(const b200_conv_desc* d, const ConvGeom& g, const 
   CUtensorMap tb;
   int rc = make_tmap_bf16_2d(&tb, w, g.RSC, d->K, g.ldw, 64, 64);
   if (rc) return fail(B200_CUDA_ERROR, "conv_dgrad: weight tensor map failed (%d)", rc);
-  const int bn = pick_bn(d, g, d->C);
+  const int bn = pick_bn(d, g, d->C, d->K, true);
   const int classes = d->stride == 1 ? 1 : 4;
   static const bool no_tma_store = getenv("B200_NO_TMA_STORE") != nullptr;
   static const bool no_tma_reduce = getenv("B200_NO_TMA_REDUCE") != nullptr;
@@ -811,7 +820,7 @@ extern "C" int64_t b200_conv_fprop_bnstats_rows(const b200_conv_desc* d) {
   if (off || !implicit_ok(d)) return 0;
   const ConvGeom g = geom(d);
   const PixelBox b = fprop_box(d, g);
-  const int bn = pick_bn(d, g, d->K);
+  const int bn = pick_bn(d, g, d->K, d->C);
   const int n_tiles = (d->K + bn - 1) / bn;
   const long long total = (long long)b.tiles_w * b.tiles_h * b.tiles_n * n_tiles;
   if (total > 0x7fffffffLL) return 0;
