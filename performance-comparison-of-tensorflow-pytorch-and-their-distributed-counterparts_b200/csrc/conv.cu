@@ -594,12 +594,21 @@ static inline WgradPlan2 wgrad_plan2(const b200_conv_desc* d, const ConvGeom& g,
   if (s_want > w.pb_total / 2) s_want = w.pb_total / 2;     // at least two k-blocks per CTA
   if (s_want < 1) s_want = 1;
   int cs = force_cs > 0 ? force_cs : 2;
+  // ... except where four CTAs per tile are the whole split (no slab, the gradient is written directly) and each still
+  // reduces >= 16 k-blocks, so the four-way DSMEM exchange is small next to the main loop: 1024 -> 2048 1x1 stride 2
+  // (25 k-blocks per CTA) 46.1 -> 32.6 us.  1x1 layers only: 512 -> 512 3x3 loses with it (46 -> 75 us; its direct
+  // epilogue scatters into OIHW)
+  if (force_cs <= 0 && d->R * d->S == 1 && s_want > 2 && s_want <= 4 && w.pb_total / 4 >= 16) cs = 4;
   while (cs > 1 && cs > s_want) cs >>= 1;
   w.cluster = cs;
   w.groups = s_want / cs > 0 ? s_want / cs : 1;
   const int S = w.cluster * w.groups;
   w.pb_per = (w.pb_total + S - 1) / S;
   w.direct = w.groups == 1 && (reinterpret_cast<uintptr_t>(dw) & 15) == 0 && (d->R * d->S > 1 || g.ldw == d->C);
+  static const bool dbg = getenv("B200_WGRAD_DEBUG") != nullptr;
+  if (dbg)
+    fprintf(stderr, "wgrad plan: K %d C %d RS %d stride %d | tiles %d x %d, k-blocks %d, s_want %d -> cluster %d x groups %d, direct %d\n",
+            d->K, d->C, d->R * d->S, d->stride, w.m_tiles, w.n_tiles, w.pb_total, s_want, w.cluster, w.groups, (int)w.direct);
   return w;
 }
 
