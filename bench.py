@@ -41,6 +41,37 @@ CONV_ALGO_BYTES_PER_LAUNCH = 2.0 * (256 * 40 * 40 * 64 + 256 * 40 * 40 * 256 + 2
 BERT_GEMM_TRAFFIC_BYTES_PER_LAUNCH = 36.8e6
 
 
+# ResNet-50 convolutions at 160 x 160 by layer class (SURVEY.md 8(a')): spatial size, Cin, Cout, kernel, stride, pad, count
+RESNET50_CONV_CLASSES = [
+    (40, 64, 64, 1, 1, 0, 1), (40, 64, 64, 3, 1, 1, 3), (40, 64, 256, 1, 1, 0, 4), (40, 256, 64, 1, 1, 0, 2),
+    (40, 256, 128, 1, 1, 0, 1), (40, 128, 128, 3, 2, 1, 1), (20, 128, 512, 1, 1, 0, 4), (40, 256, 512, 1, 2, 0, 1),
+    (20, 512, 128, 1, 1, 0, 3), (20, 128, 128, 3, 1, 1, 3), (20, 512, 256, 1, 1, 0, 1), (20, 256, 256, 3, 2, 1, 1),
+    (10, 256, 1024, 1, 1, 0, 6), (20, 512, 1024, 1, 2, 0, 1), (10, 1024, 256, 1, 1, 0, 5), (10, 256, 256, 3, 1, 1, 5),
+    (10, 1024, 512, 1, 1, 0, 1), (10, 512, 512, 3, 2, 1, 1), (5, 512, 2048, 1, 1, 0, 3), (10, 1024, 2048, 1, 2, 0, 1),
+    (5, 2048, 512, 1, 1, 0, 2), (5, 512, 512, 3, 1, 1, 2),
+]
+
+
+def conv_per_layer_roofline_ms(batch, tflops, hbm_gbs):
+    """Sum over the 53 convolutions x {fprop, dgrad, wgrad} of max(tensor time, HBM time) of that launch: flops at the
+    given bf16 peak, algorithmic bytes (activations in and out in bf16, weights once; fp32 weight gradient) at the given
+    HBM rate.  Most 1x1 layers are HBM-bound, the 3x3 ones tensor-bound: a single-bound roofline misstates both."""
+    peak, hbm = tflops * 1e12, hbm_gbs * 1e9
+    total = 0.0
+    for H, C, K, R, st, pad, cnt in RESNET50_CONV_CLASSES:
+        Ho = (H + 2 * pad - R) // st + 1
+        x, y, w = batch * H * H * C, batch * Ho * Ho * K, K * C * R * R
+        flops = 2.0 * batch * Ho * Ho * K * C * R * R
+        t_f = max(flops / peak, 2.0 * (x + y + w) / hbm)
+        t_w = max(flops / peak, (2.0 * (x + y) + 4.0 * w) / hbm)
+        total += cnt * (2 * t_f + t_w)
+    # stem 3 -> 64, 7x7 / 2 (no dgrad: the image needs no gradient); input counted as 8-byte bf16 pixels
+    x, y, w = batch * 160 * 160 * 4, batch * 80 * 80 * 64, 64 * 3 * 49
+    flops = 2.0 * batch * 80 * 80 * 64 * 147
+    total += max(flops / peak, 2.0 * (x + y + w) / hbm) + max(flops / peak, (2.0 * (x + y) + 4.0 * w) / hbm)
+    return total * 1e3
+
+
 def _named_launch_traffic():
     p = os.path.join(ROOT, "profiles", "r02_ncu_named_launches.json")
     if os.path.exists(p):
@@ -637,6 +668,12 @@ def main():
                 "algorithmic_bytes": CONV_ALGO_BYTES_PER_LAUNCH, "traffic_launch": CONV_TRAFFIC_LAUNCH,
                 "traffic_source": "profiles/r02_ncu_named_launches.txt (ncu --set full, dram__bytes_read.sum + "
                                   "dram__bytes_write.sum of that one launch)",
+                "per_layer": {"roofline_ms": conv_per_layer_roofline_ms(B, pk["tflops"], pk["hbm"]),
+                              "measured_ms": ms.value / prof_steps,
+                              "frac": conv_per_layer_roofline_ms(B, pk["tflops"], pk["hbm"]) / (ms.value / prof_steps),
+                              "note": "sum over the step's conv launches of max(tensor time, HBM time) per launch "
+                                      "(sustained bf16 peak, measured HBM copy rate) / measured kernel time of the "
+                                      "same launches; `frac` above is the whole family against the tensor peak only"},
                 "launches_per_step": n.value // prof_steps, "kernel_ms_per_step": ms.value / prof_steps,
                 "executed_gemm_tflop_per_step": fl.value / prof_steps / 1e12}
 
