@@ -74,6 +74,10 @@ int32_t b200_im2col(const void* x, void* col, int32_t N, int32_t H, int32_t W, i
  * which is a quarter of a full im2col matrix.  Stride 2, S <= 8, at most 4 channels. */
 int32_t b200_stem_stage(const void* x_nhwc4, void* out, int32_t N, int32_t H, int32_t W, int32_t R, int32_t S,
                         int32_t pad, void* stream);
+/* The same staged tensor straight from the loaders' fp32 NCHW batch (Cw <= 4 channels): layout conversion and staging
+ * in one pass (pytorch_training_inference_on_image.ipynb:667 hands the model NCHW fp32). */
+int32_t b200_stem_stage_nchw(const float* x_nchw, void* out, int32_t N, int32_t Cw, int32_t H, int32_t W, int32_t R,
+                             int32_t S, int32_t pad, void* stream);
 int32_t b200_stem_pack_weight(const float* w_oihw, void* w_packed, int32_t K, int32_t Cw, int32_t R, int32_t S,
                               void* stream);
 /* Input pipeline: the reference's per-image transform

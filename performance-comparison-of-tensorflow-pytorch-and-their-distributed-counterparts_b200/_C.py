@@ -46,6 +46,7 @@ SIGNATURES = {
                                      POINTER(c_int32), POINTER(c_int32), I32, P]),
     "b200_im2col": (I32, [P, P, I32, I32, I32, I32, I32, I32, I32, I32, I32, I32, P]),
     "b200_stem_stage": (I32, [P, P, I32, I32, I32, I32, I32, I32, P]),
+    "b200_stem_stage_nchw": (I32, [P, P, I32, I32, I32, I32, I32, I32, I32, P]),
     "b200_stem_pack_weight": (I32, [P, P, I32, I32, I32, I32, P]),
     "b200_preprocess_u8": (I32, [P, P, P, P, I32, I32, I32, P, I32, I32, P]),
     "b200_cast": (I32, [P, P, I64, I32, I32, P]),

@@ -202,6 +202,40 @@ stem_stage_kernel(const uint2* __restrict__ x, uint4* __restrict__ out, int N, i
     out[i] = make_uint4(a.x, a.y, b.x, b.y);
   }
 }
+// The same staged tensor straight from the fp32 NCHW batch the loaders produce (Cw <= 4 channels, the rest zero): the
+// layout conversion to 8-byte pixels and the staging are one pass -- the intermediate NHWC4 image is never written.
+__global__ void __launch_bounds__(256)
+stem_stage_nchw_kernel(const float* __restrict__ x, uint4* __restrict__ out, int N, int Cw, int H, int W, int pad, int Hs,
+                       int Wo) {
+  const long long total = (long long)N * Hs * Wo * 8;
+  const long long plane = (long long)H * W;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int t = (int)(i & 7);
+    long long rest = i >> 3;
+    const int q = (int)(rest % Wo);
+    rest /= Wo;
+    const int j = (int)(rest % Hs);
+    const int n = (int)(rest / Hs);
+    const int h = 2 * j + (t >> 2) - pad;
+    const int w = 2 * q + 2 * (t & 3) - pad;
+    float v[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
+    if (h >= 0 && h < H) {
+      const float* row = x + (long long)n * Cw * plane + (long long)h * W;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        if (c >= Cw) break;
+        if (w >= 0 && w < W) v[0][c] = row[c * plane + w];
+        if (w + 1 >= 0 && w + 1 < W) v[1][c] = row[c * plane + w + 1];
+      }
+    }
+    uint4 o;
+    __nv_bfloat162* hp = reinterpret_cast<__nv_bfloat162*>(&o);
+    hp[0] = __floats2bfloat162_rn(v[0][0], v[0][1]); hp[1] = __floats2bfloat162_rn(v[0][2], v[0][3]);
+    hp[2] = __floats2bfloat162_rn(v[1][0], v[1][1]); hp[3] = __floats2bfloat162_rn(v[1][2], v[1][3]);
+    out[i] = o;
+  }
+}
 // OIHW fp32 stem filter [K][Cw <= 4][R][S <= 8] -> [K][R' * 64] bf16 in the column order of stem_stage_kernel:
 // column j*64 + r2*32 + s*4 + c holds w[k][c][2j + r2][s] (zero where r >= R, s >= S or c >= Cw).
 __global__ void stem_pack_weight_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ out, int K, int Cw, int R,
@@ -531,6 +565,19 @@ extern "C" int32_t b200_stem_stage(const void* x, void* out, int32_t N, int32_t 
   const long long total = (long long)N * Hs * Wo * 8;
   stem_stage_kernel<<<grid_for(total, 256, 16), 256, 0, as_stream(stream)>>>((const uint2*)x, (uint4*)out, N, H, W, pad, Hs, Wo);
   return check_launch("stem_stage");
+}
+
+extern "C" int32_t b200_stem_stage_nchw(const float* x_nchw, void* out, int32_t N, int32_t Cw, int32_t H, int32_t W,
+                                        int32_t R, int32_t S, int32_t pad, void* stream) {
+  if (!x_nchw || !out || N <= 0 || Cw <= 0 || Cw > 4 || H <= 0 || W <= 0 || R <= 0 || S <= 0 || S > 8 || pad < 0)
+    return fail(B200_INVALID_ARG, "stem_stage_nchw: bad arguments (at most 4 channels, stride 2, S <= 8)");
+  if (reinterpret_cast<uintptr_t>(out) & 15) return fail(B200_INVALID_ARG, "stem_stage_nchw: misaligned output");
+  const int Ho = (H + 2 * pad - R) / 2 + 1, Wo = (W + 2 * pad - S) / 2 + 1;
+  if (Ho <= 0 || Wo <= 0) return fail(B200_INVALID_ARG, "stem_stage_nchw: filter larger than input");
+  const int Hs = Ho + (R + 1) / 2 - 1;
+  const long long total = (long long)N * Hs * Wo * 8;
+  stem_stage_nchw_kernel<<<grid_for(total, 256, 16), 256, 0, as_stream(stream)>>>(x_nchw, (uint4*)out, N, Cw, H, W, pad, Hs, Wo);
+  return check_launch("stem_stage_nchw");
 }
 
 extern "C" int32_t b200_stem_pack_weight(const float* w_oihw, void* out, int32_t K, int32_t Cw, int32_t R, int32_t S,

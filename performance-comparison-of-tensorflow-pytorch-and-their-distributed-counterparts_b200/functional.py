@@ -181,23 +181,25 @@ _STEM_PAIRS = os.environ.get("B200_STEM_IM2COL") is None
 _FOLD_EVAL_BN = os.environ.get("B200_NO_FOLD_EVAL_BN") is None
 _FOLD_EVAL_RESIDUAL = os.environ.get("B200_NO_FOLD_EVAL_RESIDUAL") is None
 _WGRAD_DEFER = os.environ.get("B200_NO_WGRAD_DEFER") is None
+_STEM_FUSED_STAGE = os.environ.get("B200_NO_FUSED_STEM_STAGE") is None
 # stem: BatchNorm -> ReLU -> MaxPool as one pass each way (csrc/stem_pool.cu); B200_NO_FUSED_STEM_POOL=1 = separate kernels
 _FUSE_STEM_POOL = os.environ.get("B200_NO_FUSED_STEM_POOL") is None
 
 
-def _unit_forward(conv, bn, x, relu, residual, save, stage=False, pool=False):
+def _unit_forward(conv, bn, x, relu, residual, save, stage=False, pool=False, nchw_src=None):
     """conv -> BN (-> + residual) (-> ReLU); pool=True (the stem) appends MaxPool2d(3, 2, 1).  Returns (output, unit)."""
     K, R, S, stride, pad = _conv_geom(conv)
     staged = None
-    if stage and stride == 2 and S <= 8 and x.shape[-1] == 4 and _STEM_PAIRS:
+    if stage and stride == 2 and S <= 8 and _STEM_PAIRS and (nchw_src is not None or x.shape[-1] == 4):
         # Stem (3 -> 64, 7x7/2) in bf16 mode: the channel-padded image is staged ONCE as a row-pair window tensor
         # [N][Ho+3][Wo][64] (128 bytes per output column: the 8-pixel windows of two input rows; a quarter of an
         # im2col matrix) and the convolution becomes a 4x1 stride-1 convolution over 64 "channels" on the implicit
         # tcgen05 path -- filter-row pairs are TMA coordinate shifts, the four taps re-read the staged tensor from L2;
         # fused BN statistics as everywhere; the weight gradient reuses the staged tensor.
-        wp = packed_weight(conv.weight, x.dtype, "stem")
+        wp = packed_weight(conv.weight, torch.bfloat16 if nchw_src is not None else x.dtype, "stem")
         staged = ("pairs", R, S)
-        x = ops.stem_stage(x, R, S, pad)
+        # nchw_src: the loaders' fp32 NCHW batch is staged directly (no NHWC4 intermediate)
+        x = ops.stem_stage_nchw(nchw_src, R, S, pad) if nchw_src is not None else ops.stem_stage(x, R, S, pad)
         R, S, stride, pad = (R + 1) // 2, 1, 1, 0
     elif stage:
         # other narrow-input first layers: the image is staged as an im2col matrix (columns padded to a multiple of
@@ -339,10 +341,15 @@ def _backbone_fwd(model, x, save, x_needs_grad, pool=True):
         prepack_weights(_backbone_convs(model), dtype)
     if x.dtype == torch.bfloat16 and x.dim() == 4 and x.shape[-1] == 4 and cp == 4:
         xh = x.contiguous()               # already the stem's layout (b200net.utils.GpuPreprocess): nothing to convert
+        nchw_src = None
     else:
-        xh = ops.to_nhwc(x, dtype, cp)
+        c1 = model.conv1
+        stage_pairs = (cp == 4 and not x_needs_grad and _STEM_PAIRS and x.dim() == 4 and x.shape[1] <= 4
+                       and c1.stride in ((2, 2), 2) and c1.kernel_size[1] <= 8 and _STEM_FUSED_STAGE)
+        nchw_src = x if stage_pairs else None
+        xh = None if stage_pairs else ops.to_nhwc(x, dtype, cp)
     cur, u0 = _unit_forward(model.conv1, model.bn1, xh, True, None, save, stage=cp is not None and not x_needs_grad,
-                            pool=True)
+                            pool=True, nchw_src=nchw_src)
     blocks = []
     for layer in (model.layer1, model.layer2, model.layer3, model.layer4):
         for blk in layer:

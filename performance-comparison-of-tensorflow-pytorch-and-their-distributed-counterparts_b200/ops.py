@@ -156,6 +156,19 @@ def stem_stage(x4, R, S, pad):
     return out
 
 
+def stem_stage_nchw(x, R, S, pad):
+    """[N,C<=4,H,W] fp32 NCHW -> the row-pair window tensor of stem_stage, without the NHWC4 intermediate."""
+    _need_cuda(x)
+    if x.dtype != torch.float32:
+        x = x.float()
+    x = x.contiguous()
+    N, C, H, W = x.shape
+    Ho, Wo = (H + 2 * pad - R) // 2 + 1, (W + 2 * pad - S) // 2 + 1
+    out = torch.empty((N, Ho + (R + 1) // 2 - 1, Wo, 64), dtype=torch.bfloat16, device=x.device)
+    check(lib.b200_stem_stage_nchw(x.data_ptr(), out.data_ptr(), N, C, H, W, R, S, pad, _stream()), "stem_stage_nchw")
+    return out
+
+
 def stem_pack_weight(w):
     """OIHW fp32 stem filter -> [K][R'*64] bf16 in the staged column order."""
     K, Cw, R, S = w.shape

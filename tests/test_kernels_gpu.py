@@ -234,6 +234,18 @@ def test_stem_row_pair_staging(N, H, W):
     assert _rel(dw, wd.grad) < 5e-3
 
 
+@pytest.mark.parametrize("N,C,H,W", [(3, 3, 160, 160), (2, 3, 37, 45), (1, 1, 16, 20), (2, 4, 21, 18)])
+def test_stem_stage_from_nchw_matches_two_pass(N, C, H, W):
+    """b200_stem_stage_nchw (fp32 NCHW batch -> row-pair window tensor in one pass) is bit-identical to
+    b200_nchw_to_nhwc (4-channel bf16) followed by b200_stem_stage."""
+    from b200net import ops
+    x = _rand((N, C, H, W), torch.float32, 71)
+    two = ops.stem_stage(ops.to_nhwc(x, torch.bfloat16, 4), 7, 7, 3)
+    one = ops.stem_stage_nchw(x, 7, 7, 3)
+    assert one.shape == two.shape and torch.equal(one, two)
+
+
+
 @pytest.mark.parametrize("case", [c for c in CONV_CASES if c[2] % 64 == 0 and c[3] % 64 == 0])
 def test_conv_fprop_fused_bn_statistics(case):
     """The fprop epilogue also emits per-pixel-tile column sums / sums of squares of the bf16 output: they must add up
