@@ -176,6 +176,24 @@ __global__ void avgpool_bwd_kernel(const float* __restrict__ dy, T* __restrict__
   }
 }
 
+// eight channels per thread, 16-byte stores, 32-bit indices (the scalar kernel above: 41 us for the 26 MB gradient of the
+// N = 256 step)
+__global__ void __launch_bounds__(256) avgpool_bwd_bf16x8_kernel(const float* __restrict__ dy, uint4* __restrict__ dx, int N,
+                                                                 int HW, int C8) {
+  const int total = N * HW * C8;
+  const float inv = 1.f / (float)HW;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int c8 = i % C8, n = i / (HW * C8);
+    const float4 a = reinterpret_cast<const float4*>(dy)[(n * C8 + c8) * 2];
+    const float4 b = reinterpret_cast<const float4*>(dy)[(n * C8 + c8) * 2 + 1];
+    uint4 v;
+    __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&v);
+    h[0] = __floats2bfloat162_rn(a.x * inv, a.y * inv); h[1] = __floats2bfloat162_rn(a.z * inv, a.w * inv);
+    h[2] = __floats2bfloat162_rn(b.x * inv, b.y * inv); h[3] = __floats2bfloat162_rn(b.z * inv, b.w * inv);
+    dx[i] = v;
+  }
+}
+
 static inline int pgrid(long long total) {
   long long b = (total + 255) / 256;
   const long long cap = (long long)num_sms() * 8;
@@ -241,6 +259,11 @@ extern "C" int32_t b200_avgpool_bwd(const float* dy, void* dx, int32_t N, int32_
   if (!dy || !dx || N <= 0 || HW <= 0 || C <= 0) return fail(B200_INVALID_ARG, "avgpool_bwd: bad arguments");
   cudaStream_t st = as_stream(stream);
   const long long total = (long long)N * HW * C;
+  if (dtype == B200_BF16 && C % 8 == 0 && total < (1LL << 31) &&
+      ((reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(dx)) & 15) == 0) {
+    avgpool_bwd_bf16x8_kernel<<<pgrid(total / 8), 256, 0, st>>>(dy, (uint4*)dx, N, HW, C / 8);
+    return check_launch("avgpool_bwd");
+  }
   if (dtype == B200_F32) avgpool_bwd_kernel<float><<<pgrid(total), 256, 0, st>>>(dy, (float*)dx, N, HW, C);
   else if (dtype == B200_BF16) avgpool_bwd_kernel<__nv_bfloat16><<<pgrid(total), 256, 0, st>>>(dy, (__nv_bfloat16*)dx, N, HW, C);
   else return fail(B200_INVALID_ARG, "avgpool_bwd: bad dtype");
