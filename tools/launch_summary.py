@@ -1,5 +1,5 @@
 """Summarises an `ncu --metrics gpu__time_duration.sum --csv` launch list of bench.py: per-kernel count / time / share
-for ONE training step (the step boundaries are the nchw_to_nhwc launches).  usage: launch_summary.py file.csv [step]"""
+for ONE training step (the step boundaries are the launches of the kernel that reads the fp32 NCHW batch).  usage: launch_summary.py file.csv [step]"""
 import collections
 import csv
 import re
@@ -19,7 +19,10 @@ def load(path):
 def main():
     rows = load(sys.argv[1])
     which = int(sys.argv[2]) if len(sys.argv) > 2 else 3
-    starts = [i for i, r in enumerate(rows) if "nchw_to_nhwc" in r[0]]
+    # a step starts with the kernel that takes the fp32 NCHW batch in: the fused staging kernel (round 2) or nchw_to_nhwc
+    starts = [i for i, r in enumerate(rows) if "stem_stage_nchw" in r[0]]
+    if len(starts) < 2:
+        starts = [i for i, r in enumerate(rows) if "nchw_to_nhwc" in r[0]]
     step = rows[starts[which]:starts[which + 1]]
     agg = collections.defaultdict(lambda: [0, 0.0])
     for k, v, _, _ in step:
