@@ -106,12 +106,14 @@ class DistributedDataParallel(_nn.Module):
                         off += t.numel()
 
     def _flatten_buffers(self):
-        """Re-homes every fp32 buffer (BatchNorm running statistics) into ONE flat tensor, so that the per-step buffer
-        broadcast is a single collective on that tensor -- no pack / unpack kernels, no allocation, no Python walk
-        over 106 tensors -- issued on the communication stream right after the forward that updated the statistics
-        (it overlaps loss + backward; the next training forward only waits on its event).  The module's buffers stay
-        the same tensor objects (state_dict, load_state_dict and in-place updates are unaffected); if the user
-        re-allocates them (`module.to(...)`), the aliasing check in forward() falls back to the coalesced broadcast."""
+        """Re-homes every fp32 buffer (BatchNorm running statistics) into ONE flat tensor, so that the buffer broadcast
+        before every training forward (torch DDP's `broadcast_buffers=True`) is a single collective on that tensor --
+        no pack / unpack kernels, no allocation, no Python walk over 106 tensors.  The module's buffers stay the same
+        tensor objects (state_dict, load_state_dict and in-place updates are unaffected); if the user re-allocates
+        them (`module.to(...)`), the aliasing check in forward() falls back to the coalesced broadcast.
+        (Issuing the broadcast right AFTER the forward, on the communication stream, would hide its ~40 us entirely,
+        but then a buffer modified between two forwards -- load_state_dict on a resumed run -- would not be replaced
+        by rank 0's value, which is what torch does; tests/test_ddp_gpu.py checks exactly that.)"""
         self._buf_flat = None
         self._buf_event = None
         if not (self.on_cuda and self.broadcast_buffers and self.world_size > 1):
@@ -134,16 +136,6 @@ class DistributedDataParallel(_nn.Module):
 
     def _buffers_still_flat(self):
         return all(b.data_ptr() == p for b, p in zip(self._bufs, self._buf_ptrs))
-
-    def _broadcast_buffers_async(self):
-        """After a training forward: rank 0's statistics -> every rank, on the communication stream."""
-        ev = torch.cuda.Event()
-        ev.record(torch.cuda.current_stream())
-        self._comm_stream.wait_event(ev)
-        with torch.cuda.stream(self._comm_stream):
-            dist.broadcast(self._buf_flat, 0, group=self.process_group)
-            self._buf_event = torch.cuda.Event()
-            self._buf_event.record(self._comm_stream)
 
     def _sync_module_states(self):
         with torch.no_grad():
@@ -320,14 +312,9 @@ class DistributedDataParallel(_nn.Module):
 
     # ---------------------------------------------------------------- module protocol
     def forward(self, *inputs, **kwargs):
-        flat_bufs = False
         if self.broadcast_buffers and self.module.training and self.world_size > 1:
-            flat_bufs = self._buf_flat is not None and self._buffers_still_flat()
-            if flat_bufs:
-                # the broadcast that followed the previous training forward (construction synchronised the first one)
-                if self._buf_event is not None:
-                    torch.cuda.current_stream().wait_event(self._buf_event)
-                    self._buf_event = None
+            if self._buf_flat is not None and self._buffers_still_flat():
+                dist.broadcast(self._buf_flat, 0, group=self.process_group)      # rank 0's statistics -> every rank
             else:
                 bufs = [b for b in self.module.buffers() if b.dtype.is_floating_point]
                 if bufs:
@@ -337,10 +324,7 @@ class DistributedDataParallel(_nn.Module):
             F.set_grad_sink(self._sink)
         else:
             F.set_grad_sink(None)
-        out = self.module(*inputs, **kwargs)
-        if flat_bufs:
-            self._broadcast_buffers_async()
-        return out
+        return self.module(*inputs, **kwargs)
 
     class _NoSync(object):
         def __init__(self, ddp):
