@@ -115,7 +115,6 @@ class DistributedDataParallel(_nn.Module):
         but then a buffer modified between two forwards -- load_state_dict on a resumed run -- would not be replaced
         by rank 0's value, which is what torch does; tests/test_ddp_gpu.py checks exactly that.)"""
         self._buf_flat = None
-        self._buf_event = None
         if not (self.on_cuda and self.broadcast_buffers and self.world_size > 1):
             return
         bufs = [b for b in self.module.buffers() if b.dtype == torch.float32 and b.is_contiguous() and b.numel() > 0]
