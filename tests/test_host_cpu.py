@@ -117,3 +117,26 @@ def test_torch_save_roundtrip_bert_and_vgg():
         assert repr(m2) == repr(m)
         a, b = next(iter(m.parameters())), next(iter(m2.parameters()))
         assert torch.equal(a, b)
+
+
+def test_bench_per_layer_roofline_constant():
+    """bench.py's per-layer convolution roofline (sum over the 53 convolutions x {fprop, dgrad, wgrad} of
+    max(tensor time, HBM time)) counts 53 layers and 12.4 GFLOP per image, scales linearly with the batch, and equals
+    the pure tensor time when HBM is infinitely fast / the pure HBM time when the tensor pipe is."""
+    import importlib.util
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location("bench_for_test", os.path.join(root, "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    assert sum(c[-1] for c in bench.RESNET50_CONV_CLASSES) == 52          # + the stem = 53 convolutions
+    fwd = sum(2.0 * ((H + 2 * p - R) // s + 1) ** 2 * K * C * R * R * n for H, C, K, R, s, p, n in bench.RESNET50_CONV_CLASSES)
+    fwd += 2.0 * 80 * 80 * 64 * 147
+    assert abs(fwd / 1e9 - 4.1727 + 2 * (2048 * 512 + 512 * 10) / 1e9) < 0.02      # BASELINE.md: 4.173 GFLOP/img incl. head
+    a = bench.conv_per_layer_roofline_ms(256, 1402.4, 6550.1)
+    assert abs(bench.conv_per_layer_roofline_ms(512, 1402.4, 6550.1) / a - 2.0) < 0.02
+    tensor_only = bench.conv_per_layer_roofline_ms(256, 1402.4, 1e12)
+    stem = 2.0 * 256 * 80 * 80 * 64 * 147
+    flops = 3.0 * 256 * (fwd - 2.0 * 80 * 80 * 64 * 147) + 2.0 * stem             # no dgrad for the stem
+    assert abs(tensor_only - flops / 1402.4e12 * 1e3) / tensor_only < 1e-6
+    assert a >= tensor_only and a >= bench.conv_per_layer_roofline_ms(256, 1e9, 6550.1)
