@@ -167,7 +167,7 @@ static inline WgradPlan wgrad_plan(const b200_conv_desc* d, const ConvGeom& g) {
 // the leader issues one M = 256 MMA for both (conv_sm100_kernel<..., CG = 2>, validated by tools/umma2sm_probe.cu and
 // tests/test_kernels_gpu.py::test_cta_pair_kernels).  OPT-IN (B200_2SM=1): measured on BERT's Linears it is not
 // faster than the single-CTA kernel (fprop 31.0 -> 35.2 us, dgrad 34.6 -> 33.6 us at 8192 x 768 x 2304/3072) -- those
-// GEMMs already run at 1.0-1.15 PFLOP/s against a measured sustained cuBLAS peak of 1.38, so B-operand traffic per SM
+// GEMMs already run at 1.0-1.15 PFLOP/s against a measured sustained cuBLAS peak of 1.40, so B-operand traffic per SM
 // was not the limiter it looked like.  Not combined with the fused BatchNorm statistics (their per-CTA partial rows
 // assume the single-CTA tile walk).
 // Two-pixel-tile work items for 256-wide fprop / dgrad tiles; both variants are built, parity-tested
